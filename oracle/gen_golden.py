@@ -1,0 +1,215 @@
+"""TEST INFRASTRUCTURE ONLY -- generates tests/golden/*.npz from the reference.
+
+Runs the reference's own hot-path source (sort_impl, _ShufflePartitionOp,
+_GroupbyOp, ArrowBlockAccessor.*) from /root/reference under oracle/ref_shim.py
+on small seeded inputs and stores inputs + outputs.  Only runnable in the build
+container (the GPU box has no /root/reference); the produced fixtures are
+committed and are what the GPU-side tests read.
+
+    python -m oracle.gen_golden
+"""
+import os
+import random
+
+import numpy as np
+import pyarrow as pa
+
+from oracle import datasets_oracle as O
+from oracle import ref_shim
+
+OUT = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "tests", "golden")
+
+
+def _split(n, nblocks):
+    cuts = np.linspace(0, n, nblocks + 1).astype(int)
+    return list(zip(cuts[:-1], cuts[1:]))
+
+
+def gen_sort_int64():
+    n, nb = 20000, 4
+    rng = np.random.default_rng(0)
+    out = {}
+    for name, keys in (
+        ("unique", rng.integers(-(2**63), 2**63 - 1, n, dtype=np.int64)),
+        ("ties", rng.integers(-500, 500, n, dtype=np.int64)),
+    ):
+        tabs = [
+            pa.table({"value": np.arange(a, b, dtype=np.int64), "key": keys[a:b]})
+            for a, b in _split(n, nb)
+        ]
+        out[f"{name}_keys"] = keys
+        for desc in (False, True):
+            res = []
+            for push in (False, True):
+                random.seed(7)
+                blocks = ref_shim.ref_sort(tabs, "key", descending=desc, push_based=push)
+                assert len(blocks) == nb
+                cat = pa.concat_tables([b for b in blocks if b.num_rows])
+                res.append(cat["value"].to_numpy())
+                # a key value never spans two output blocks (sort.py:118-119)
+                seen = set()
+                for b in blocks:
+                    ks = set(b["key"].to_pylist()) if b.num_rows else set()
+                    assert not (ks & seen)
+                    seen |= ks
+            assert np.array_equal(res[0], res[1]), "plans disagree"
+            out[f"{name}_{'desc' if desc else 'asc'}_value_order"] = res[0]
+    out["block_cuts"] = np.array(_split(n, nb))
+    np.savez_compressed(os.path.join(OUT, "sort_int64.npz"), **out)
+
+
+def gen_sort_graysort():
+    n, nb = 8000, 4
+    out = {}
+    for name, entropy in (("uniform", 10), ("ties", 1)):
+        t = O.graysort_table(n, seed=11)
+        keys = O.fsb_to_numpy(t["key"]).copy()
+        if entropy < 10:
+            keys[:, : 10 - entropy] = 7  # only the last byte varies -> ~31 rows per key
+            keys[:, -1] &= 0x3F
+            t = pa.table({"key": O.fsb_from_numpy(keys), "payload": t["payload"]})
+        tabs = [t.slice(a, b - a) for a, b in _split(n, nb)]
+        out[f"{name}_keys"] = keys
+        for desc in (False, True):
+            random.seed(3)
+            blocks = ref_shim.ref_sort(tabs, "key", descending=desc)
+            cat = pa.concat_tables([b for b in blocks if b.num_rows])
+            rowid = O.fsb_to_numpy(cat["payload"])[:, :8].copy().view("<u8").ravel()
+            out[f"{name}_{'desc' if desc else 'asc'}_rowid_order"] = rowid
+    out["block_cuts"] = np.array(_split(n, nb))
+    np.savez_compressed(os.path.join(OUT, "sort_graysort.npz"), **out)
+
+
+def gen_partition():
+    ns = ref_shim.load()
+    rng = np.random.default_rng(5)
+    n = 5000
+    keys = rng.integers(0, 100, n, dtype=np.int64)
+    t = pa.table({"key": keys, "value": np.arange(n, dtype=np.int64)})
+    out = {"keys": keys}
+    asc_b = [10, 10, 37, 99, 150]
+    desc_b = [150, 99, 37, 10, 10]
+    for desc, bounds in ((False, asc_b), (True, desc_b)):
+        key = [("key", "descending" if desc else "ascending")]
+        parts = ns.BlockAccessor.for_block(t).sort_and_partition(bounds, key, desc)
+        tag = "desc" if desc else "asc"
+        out[f"{tag}_boundaries"] = np.array(bounds, dtype=np.int64)
+        out[f"{tag}_sizes"] = np.array([p.num_rows for p in parts])
+        out[f"{tag}_value_order"] = pa.concat_tables(parts)["value"].to_numpy()
+    # merge_sorted_blocks on mapper-ordered sorted blocks
+    blocks = [
+        ns.BlockAccessor.for_block(t.slice(a, b - a)).sort_and_partition(
+            [], [("key", "ascending")], False
+        )[0]
+        for a, b in _split(n, 3)
+    ]
+    merged, meta = ns.arrow_block.ArrowBlockAccessor.merge_sorted_blocks(
+        blocks, [("key", "ascending")], False
+    )
+    out["merge_value_order"] = merged["value"].to_numpy()
+    out["merge_cuts"] = np.array(_split(n, 3))
+    assert meta.num_rows == n
+    np.savez_compressed(os.path.join(OUT, "partition.npz"), **out)
+
+
+def gen_boundaries():
+    ns = ref_shim.load()
+    out = {}
+    rng = np.random.default_rng(9)
+    # the deterministic half: np.sort + nearest-rank quantiles (sort.py:110-115)
+    cases = []
+    for nsamp, r in ((80, 8), (10, 4), (7, 3), (40, 5), (1, 2), (2, 3), (33, 16), (100, 1)):
+        samples = rng.integers(-1000, 1000, nsamp, dtype=np.int64)
+        s = np.sort(samples)
+        import warnings
+
+        with warnings.catch_warnings():
+            warnings.simplefilter("ignore")
+            ret = [np.quantile(s, q, interpolation="nearest") for q in np.linspace(0, 1, r)][1:]
+        out[f"q_{nsamp}_{r}_samples"] = samples
+        out[f"q_{nsamp}_{r}_bounds"] = np.array(ret, dtype=np.int64)
+        cases.append((nsamp, r))
+    out["q_cases"] = np.array(cases)
+    # the sampled half, replayed with random.seed
+    n, nb = 4000, 4
+    keys = rng.integers(0, 10**6, n, dtype=np.int64)
+    tabs = [pa.table({"key": keys[a:b]}) for a, b in _split(n, nb)]
+    bl = ref_shim.make_block_list(ns, tabs)
+    random.seed(1234)
+    b = ns.sort.sample_boundaries(bl.get_blocks(), [("key", "ascending")], nb)
+    out["sampled_keys"] = keys
+    out["sampled_cuts"] = np.array(_split(n, nb))
+    out["sampled_bounds"] = np.array(b, dtype=np.int64)
+    # empty dataset -> [None]*(R-1)  (sort.py:100-103)
+    ebl = ref_shim.make_block_list(ns, [pa.table({"key": pa.array([], pa.int64())})] * 3)
+    eb = ns.sort.sample_boundaries(ebl.get_blocks(), [("key", "ascending")], 3)
+    assert eb == [None, None]
+    np.savez_compressed(os.path.join(OUT, "boundaries.npz"), **out)
+
+
+def gen_shuffle():
+    n, nb = 4000, 4
+    tabs = [pa.table({"value": np.arange(a, b, dtype=np.int64)}) for a, b in _split(n, nb)]
+    out = {"block_cuts": np.array(_split(n, nb))}
+    for seed in (42, 43):
+        blocks = ref_shim.ref_random_shuffle(tabs, seed)
+        again = ref_shim.ref_random_shuffle(tabs, seed)
+        assert all(a.equals(b) for a, b in zip(blocks, again))
+        out[f"seed{seed}_sizes"] = np.array([b.num_rows for b in blocks])
+        out[f"seed{seed}_values"] = pa.concat_tables(blocks)["value"].to_numpy()
+    # num_blocks != input blocks, ragged (ceil slicing: shuffle_and_partition.py:56-59)
+    tabs2 = [pa.table({"value": np.arange(a, b, dtype=np.int64)}) for a, b in ((0, 10), (10, 13), (13, 13), (13, 50))]
+    blocks = ref_shim.ref_random_shuffle(tabs2, 5, num_blocks=3)
+    out["ragged_cuts"] = np.array([(0, 10), (10, 13), (13, 13), (13, 50)])
+    out["ragged_sizes"] = np.array([b.num_rows if b.num_columns else 0 for b in blocks])
+    out["ragged_values"] = np.concatenate(
+        [b["value"].to_numpy() for b in blocks if b.num_columns and b.num_rows]
+    )
+    np.savez_compressed(os.path.join(OUT, "shuffle.npz"), **out)
+
+
+def gen_groupby():
+    ns = ref_shim.load()
+    A = ns.aggregate
+    n, nb, g = 6000, 4, 150
+    rng = np.random.default_rng(21)
+    k = rng.integers(0, g, n, dtype=np.int64)
+    vf = rng.random(n)
+    vi = rng.integers(-1000, 1000, n, dtype=np.int64)
+    tabs = [pa.table({"k": k[a:b], "vf": vf[a:b], "vi": vi[a:b]}) for a, b in _split(n, nb)]
+    out = {"k": k, "vf": vf, "vi": vi, "block_cuts": np.array(_split(n, nb))}
+    aggs = (A.Sum("vf"), A.Mean("vf"), A.Count(), A.Sum("vi"), A.Min("vi"), A.Max("vf"), A.Mean("vi"))
+    res = []
+    for push in (False, True):
+        random.seed(99)
+        blocks = ref_shim.ref_groupby(tabs, "k", aggs, push_based=push)
+        cat = pa.concat_tables([b for b in blocks if b.num_rows])
+        res.append(cat)
+    assert res[0].schema == res[1].schema
+    for name in res[0].column_names:
+        a, b = res[0][name].to_numpy(), res[1][name].to_numpy()
+        assert np.allclose(a, b, rtol=1e-12), name
+        out[f"out::{name}"] = a
+    out["out_names"] = np.array(res[0].column_names)
+    out["out_types"] = np.array([str(f.type) for f in res[0].schema])
+    # name-conflict munging (arrow_block.py:469-471; test_dataset.py:3043-3047)
+    random.seed(99)
+    blocks = ref_shim.ref_groupby(tabs, "k", (A.Sum("vi"), A.Sum("vi"), A.Count(), A.Count()))
+    out["conflict_names"] = np.array(pa.concat_tables(blocks).column_names)
+    np.savez_compressed(os.path.join(OUT, "groupby.npz"), **out)
+
+
+def main():
+    os.makedirs(OUT, exist_ok=True)
+    gen_sort_int64()
+    gen_sort_graysort()
+    gen_partition()
+    gen_boundaries()
+    gen_shuffle()
+    gen_groupby()
+    for f in sorted(os.listdir(OUT)):
+        print(f, os.path.getsize(os.path.join(OUT, f)))
+
+
+if __name__ == "__main__":
+    main()
