@@ -1,0 +1,377 @@
+#!/usr/bin/env python
+"""Headline benchmark: Dataset.sort of GraySort-format 100-byte records.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
+    python -m torch.distributed.run --nproc-per-node N ... bench.py --gpus N ...
+
+One step = one Dataset.sort(key) over this rank's batch of synthetic records
+({key: fixed_size_binary(10), payload: fixed_size_binary(90)}, BASELINE.json
+configs[1]: 100 M records = 10 GB per GPU).  Rank 0 prints ONE JSON line:
+
+  value     sort GB/s (input bytes / device time), inputs resident in HBM, whole job
+  e2e       the same through the public API from pinned HOST buffers: H2D copy of the
+            batch + sort + D2H copy of the sorted batch inside the timed region
+  roofline  the onesweep pass kernel: algorithmic bytes per launch / CUDA-event
+            duration of each launch, against MEASURED_PEAKS.json's hbm_gbs
+  cpu_baseline  the CPU restatement of the reference path (oracle/, kind "port") on a
+            bounded sample, all host cores
+
+--impl reference times that CPU path alone (the reference is Python over
+pyarrow/numpy; see oracle/cpu_baseline.py for why the port is what runs here).
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+ROW_BYTES = 100
+KEY_BYTES = 10
+PAYLOAD_BYTES = 90
+PASS_BYTES_PER_ROW = 2 * (KEY_BYTES + 4)  # read + write (key + idx)
+METRIC = "sort_throughput_100B_records"
+UNIT = "GB/s"
+
+
+def parse_args():
+    p = argparse.ArgumentParser()
+    p.add_argument("--gpus", type=int, default=1)
+    p.add_argument("--steps", type=int, default=5)
+    p.add_argument("--warmup", type=int, default=3)
+    p.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    p.add_argument("--rows-per-gpu", type=int, default=100_000_000)
+    p.add_argument("--cpu-rows", type=int, default=4_000_000,
+                   help="rows of the bounded CPU-baseline sample")
+    p.add_argument("--no-e2e", action="store_true")
+    p.add_argument("--no-cpu-baseline", action="store_true")
+    p.add_argument("--radix-config", type=int, default=-1, help="tuning: pass-kernel variant")
+    return p.parse_args()
+
+
+def measured_peak():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    try:
+        with open(path) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    except Exception:
+        return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled DURING the timed region."""
+
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,"
+         "clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index: int):
+        self.gpu, self.proc, self.lines = gpu_index, None, []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                 "-lms", "200", "-i", str(self.gpu)],
+                stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            threading.Thread(target=self._pump, daemon=True).start()
+        except Exception:
+            self.proc = None
+
+    def _pump(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.25)
+        self.proc.terminate()
+        sm, smax, reasons = [], None, set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ln in self.lines:
+            f = [x.strip() for x in ln.split(",")]
+            if len(f) < 9:
+                continue
+            try:
+                sm.append(float(f[1]))
+                smax = float(f[2])
+            except ValueError:
+                continue
+            for name, v in zip(names, f[5:9]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        sm.sort()
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": smax,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def cpu_baseline(rows: int, steps: int = 1, warmup: int = 0):
+    """(GB/s, descriptor) of the CPU port on a bounded sample, all host cores."""
+    from oracle import cpu_baseline as C
+
+    cores = C.host_cores()
+    blocks = max(cores, 2)
+    tabs = C.make_graysort_blocks(rows, blocks, seed=1)
+    for _ in range(warmup):
+        C.time_sort(tabs, cores)
+    secs = [C.time_sort(tabs, cores) for _ in range(max(steps, 1))]
+    best = min(secs)
+    gbs = rows * ROW_BYTES / best / 1e9
+    desc = {"value": gbs, "unit": UNIT, "cores": cores, "kind": "port",
+            "sample": f"{rows} GraySort records ({rows * ROW_BYTES / 1e9:.2f} GB) in {blocks} "
+                      f"blocks, best of {len(secs)}: {best:.2f} s; oracle/datasets_oracle.py "
+                      f"(pyarrow sort_indices/take + numpy searchsorted) over a {cores}-process pool"}
+    return gbs, desc, secs
+
+
+# ------------------------------------------------------------------------------ ours
+def make_records(n: int, seed: int):
+    """Synthetic GraySort batch in HBM: random 10-byte keys, payload = LE row id + filler."""
+    import collections
+
+    import pyarrow as pa
+    import torch
+
+    import ray_memory_management_b200 as ds
+
+    g = torch.Generator(device="cuda").manual_seed(seed)
+    keys = torch.randint(0, 256, (n * KEY_BYTES,), dtype=torch.uint8, device="cuda", generator=g)
+    payload = torch.zeros((n, PAYLOAD_BYTES), dtype=torch.uint8, device="cuda")
+    ids = torch.arange(n, dtype=torch.int64, device="cuda")
+    payload[:, :8] = ids.view(torch.uint8).view(n, 8)
+    del ids
+    cols = collections.OrderedDict(
+        key=ds.DeviceColumn(pa.binary(KEY_BYTES), keys),
+        payload=ds.DeviceColumn(pa.binary(PAYLOAD_BYTES), payload.view(-1)),
+    )
+    return ds.DeviceArrowBlock(cols, n)
+
+
+def check_sorted(block, n):
+    """Cheap on-device sanity check of one output (not timed): keys non-decreasing in
+    their first 8 bytes and row ids a permutation."""
+    import torch
+
+    k = block.columns["key"].data.view(n, KEY_BYTES)[:, :8].contiguous()
+    # big-endian bytes -> compare as int64 after byte swap; shift to keep the sign out of it
+    be = k.flip(1).contiguous().view(torch.int64).view(n)
+    hi = (be >> 1) & 0x7FFFFFFFFFFFFFFF
+    assert bool((hi[1:] >= hi[:-1]).all()), "output keys are not sorted"
+    ids = block.columns["payload"].data.view(n, PAYLOAD_BYTES)[:, :8].contiguous().view(torch.int64).view(n)
+    assert int(ids.sum().item()) == n * (n - 1) // 2, "row ids are not a permutation"
+
+
+def run_ours(args):
+    import torch
+    import torch.distributed as dist
+
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    if not torch.cuda.is_available():
+        raise RuntimeError("bench.py needs a CUDA device: there is no CPU fallback for the product path")
+    torch.cuda.set_device(local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+
+    import ray_memory_management_b200 as ds
+    from ray_memory_management_b200 import _lib
+
+    lib = _lib.lib
+    lib.ds_debug_launch_count.restype = __import__("ctypes").c_uint64
+    if args.radix_config >= 0:
+        lib.ds_debug_set_radix_config(args.radix_config)
+
+    n = args.rows_per_gpu
+    block = make_records(n, seed=1 + rank)
+    torch.cuda.synchronize()
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def one_step():
+        if world > 1:
+            from ray_memory_management_b200 import distributed
+
+            out = distributed.sort_block(block, "key", descending=False)
+        else:
+            bl = ds.BlockList.from_blocks([block])
+            res, _ = ds.sort_impl(bl, False, "key")
+            out = res.get_blocks()[0]
+        return out
+
+    for i in range(args.warmup):
+        out = one_step()
+        if i == 0 and world == 1:
+            torch.cuda.synchronize()
+            check_sorted(out, n)
+        del out
+
+    import ctypes
+
+    sampler = ClockSampler(local_rank)
+    barrier()
+    if rank == 0:
+        sampler.start()
+    launches0 = lib.ds_debug_launch_count()
+    lib.ds_debug_pass_timing(1)
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    ev0.record()
+    for _ in range(args.steps):
+        out = one_step()
+        del out
+    ev1.record()
+    barrier()
+    lib.ds_debug_pass_timing(0)
+    launches = int(lib.ds_debug_launch_count() - launches0)
+    clocks = sampler.stop() if rank == 0 else None
+    ms = ev0.elapsed_time(ev1)
+    tot_ms, cnt = ctypes.c_double(0), ctypes.c_int32(0)
+    lib.ds_debug_collect_pass_timing(ctypes.byref(tot_ms), ctypes.byref(cnt))
+    if world > 1:
+        t = torch.tensor([ms], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t.item())
+    ms_per_step = ms / args.steps
+    value = world * n * ROW_BYTES / (ms_per_step * 1e-3) / 1e9
+
+    pass_ms = tot_ms.value / max(cnt.value, 1)
+    peak, peak_src = measured_peak()
+    achieved = n_pass_rows(world, n) * PASS_BYTES_PER_ROW / (pass_ms * 1e-3) / 1e9 if cnt.value else None
+
+    # ---- e2e: pinned host buffers in, pinned host buffers out
+    e2e = None
+    if not args.no_e2e:
+        e2e = run_e2e(args, ds, block, n, world, rank, barrier)
+    del block
+
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+    line = {
+        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
+        "rows_per_s": world * n / (ms_per_step * 1e-3),
+        "config": {
+            "workload": f"GraySort-format Dataset.sort: {n} x 100-byte records per GPU "
+                        f"(10-byte key fixed_size_binary(10) + 90-byte payload), "
+                        f"{world * n * ROW_BYTES / 1e9:.1f} GB total, BASELINE.json configs[1] per GPU",
+            "rows_per_gpu": n, "blocks_per_gpu": 1,
+            "l2": "inputs (10 GB/GPU) far exceed the 126 MB L2; no flush needed",
+            "parallelism": f"range-partitioned x{world}" if world > 1 else "single GPU",
+        },
+        "clocks": clocks,
+        "gpu_launches": launches,
+        "roofline": {
+            "kernel": "onesweep_pass_kernel (one 8-bit LSD pass over key80+idx32)",
+            "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
+            "frac": (achieved / peak) if achieved else None, "traffic": None,
+            "peak_source": peak_src, "launches_timed": cnt.value, "avg_launch_ms": pass_ms,
+            "bytes_per_row_per_launch": PASS_BYTES_PER_ROW,
+        },
+        "e2e": e2e,
+    }
+    if not args.no_cpu_baseline and world == 1:
+        _, desc, _ = cpu_baseline(args.cpu_rows, steps=2)
+        line["cpu_baseline"] = desc
+    print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def n_pass_rows(world, n):
+    # rows one pass launch processes on rank 0; with W ranks the received partition is
+    # ~n rows for uniform keys (exact count is data dependent)
+    return n
+
+
+def run_e2e(args, ds, block, n, world, rank, barrier):
+    import pyarrow as pa
+    import torch
+    import torch.distributed as dist
+
+    schema = [("key", pa.binary(KEY_BYTES)), ("payload", pa.binary(PAYLOAD_BYTES))]
+    hk = torch.empty(n * KEY_BYTES, dtype=torch.uint8, pin_memory=True)
+    hp = torch.empty(n * PAYLOAD_BYTES, dtype=torch.uint8, pin_memory=True)
+    hk.copy_(block.columns["key"].data)
+    hp.copy_(block.columns["payload"].data)
+    ok = torch.empty(int(n * KEY_BYTES * (1.5 if world > 1 else 1)), dtype=torch.uint8, pin_memory=True)
+    op = torch.empty(int(n * PAYLOAD_BYTES * (1.5 if world > 1 else 1)), dtype=torch.uint8, pin_memory=True)
+    torch.cuda.synchronize()
+
+    def step():
+        blk = ds.DeviceArrowBlock.from_host_buffers(schema, [hk, hp], n)
+        if world > 1:
+            from ray_memory_management_b200 import distributed
+
+            out = distributed.sort_block(blk, "key", descending=False)
+        else:
+            out = ds.Dataset.from_blocks([blk]).sort("key").get_blocks()[0]
+        del blk
+        out.to_host_buffers([ok, op])
+        return out.num_rows
+
+    step()
+    barrier()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    ev0.record()
+    for _ in range(args.steps):
+        step()
+    ev1.record()
+    barrier()
+    ms = ev0.elapsed_time(ev1)
+    if world > 1:
+        t = torch.tensor([ms], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t.item())
+    per = ms / args.steps
+    # spot-check what landed in host memory
+    if world == 1:
+        a = ok[: 8 * KEY_BYTES].view(8, KEY_BYTES)
+        assert bytes(a[0].tolist()) <= bytes(a[7].tolist())
+    return {"value": world * n * ROW_BYTES / (per * 1e-3) / 1e9, "unit": UNIT,
+            "h2d_bytes_per_step": world * n * ROW_BYTES, "d2h_bytes_per_step": world * n * ROW_BYTES,
+            "ms_per_step": per}
+
+
+# ------------------------------------------------------------------------------ reference arm
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    if rank != 0:
+        return
+    rows = args.cpu_rows
+    gbs, desc, secs = cpu_baseline(rows, steps=args.steps, warmup=min(args.warmup, 1))
+    per = sum(secs) / len(secs)
+    gbs_mean = rows * ROW_BYTES / per / 1e9
+    desc = dict(desc, value=gbs_mean)
+    line = {
+        "impl": "reference", "metric": METRIC, "value": gbs_mean, "unit": UNIT, "n_gpus": world,
+        "steps": args.steps, "warmup": min(args.warmup, 1), "ms_per_step": per * 1e3,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8",
+        "data": "synthetic",
+        "config": {"workload": f"GraySort-format Dataset.sort on host cores: bounded sample of "
+                               f"{rows} x 100-byte records per step (same record format as the GPU arm)",
+                   "rows_per_step": rows},
+        "cpu_baseline": desc,
+        "e2e": {"value": gbs_mean, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }
+    print(json.dumps(line), flush=True)
+
+
+if __name__ == "__main__":
+    a = parse_args()
+    if a.impl == "reference":
+        run_reference(a)
+    else:
+        run_ours(a)

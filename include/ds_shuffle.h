@@ -1,0 +1,205 @@
+/*
+ * ds_shuffle.h -- C ABI of the B200 (sm_100a) Datasets shuffle/sort hot path.
+ *
+ * Drop-in boundary for the per-block compute of the reference's Exoshuffle path
+ * (Dataset.sort / random_shuffle / groupby().aggregate()).  In the reference this
+ * arithmetic is done by pyarrow / numpy calls made from
+ * python/ray/data/_internal/{arrow_block,sort,shuffle_and_partition}.py and
+ * python/ray/data/_internal/arrow_ops/transform_pyarrow.py; each entry point below
+ * cites the call site(s) it replaces (paths relative to python/ray/data/).
+ *
+ * Conventions
+ *   - plain pointers + sizes; every pointer is a DEVICE pointer unless it is
+ *     documented as host; no C++ or torch types cross this boundary.
+ *   - every call is asynchronous on `stream` (a cudaStream_t passed as void*),
+ *     except where "host sync" is stated.
+ *   - the library never allocates or frees device memory: temporaries come from
+ *     a caller-provided workspace.  Two-phase protocol (like CUB): call with
+ *     ws == NULL to get the required size in *ws_bytes, then call again.
+ *   - the caller owns every buffer; nothing is retained after the call's work on
+ *     `stream` completes.
+ *   - return value: DS_OK (0) or a negative ds_status; ds_last_error() gives a
+ *     thread-local message for the last failing call on this thread.
+ *   - row counts are limited to DS_MAX_ROWS per call (32-bit row indices and
+ *     30-bit look-back counters).
+ */
+#ifndef DS_SHUFFLE_H_
+#define DS_SHUFFLE_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef int32_t ds_status;
+#define DS_OK 0
+#define DS_ERR_INVALID_ARG (-1)
+#define DS_ERR_UNSUPPORTED (-2)
+#define DS_ERR_WORKSPACE (-3)
+#define DS_ERR_CUDA (-4)
+#define DS_ERR_TOO_LARGE (-5)
+
+#define DS_MAX_ROWS ((uint64_t)((1u << 30) - 1))
+#define DS_MAX_KEY_BYTES 10 /* fixed_size_binary sort keys: 1..10 bytes */
+#define DS_MAX_PARTITIONS 256
+
+/* ds_sort_indices_* option bits */
+#define DS_SORT_NO_PASS_SKIP 1 /* never read the digit histogram back: no host sync */
+
+/* aggregation ops for ds_segmented_reduce_* */
+#define DS_OP_SUM 0
+#define DS_OP_MIN 1
+#define DS_OP_MAX 2
+
+/* Library version (major*10000 + minor*100 + patch).  No reference counterpart. */
+int32_t ds_version(void);
+
+/* Thread-local message of the last failing call.  Replaces the Python exceptions
+ * the reference raises from these code paths (e.g. _internal/arrow_block.py:356-359). */
+const char* ds_last_error(void);
+
+/* ---------------------------------------------------------------- sort ---- */
+
+/* Stable argsort of an int64 / uint64 / float64 key column.
+ * Replaces pyarrow.compute.sort_indices(table, sort_keys=[(col, order)]) at
+ * _internal/arrow_ops/transform_pyarrow.py:15 and :74 (called from
+ * ArrowBlockAccessor.sort_and_partition, _internal/arrow_block.py:366-369, and
+ * merge_sorted_blocks, _internal/arrow_block.py:473-486).
+ *   col            n keys
+ *   descending     0: ascending; 1: Arrow's stable descending (equal keys keep
+ *                  their input order)
+ *   idx_out        n uint32 row indices: idx_out[j] = input row of output row j
+ *   sorted_out     optional (may be NULL): the key column in sorted order
+ *   options        DS_SORT_* bits.  Unless DS_SORT_NO_PASS_SKIP is set the call
+ *                  does ONE small host sync to skip radix passes whose digit is
+ *                  constant over the whole column.
+ * float64 order: -inf < ... < -0.0 == 0.0 ... < +inf < NaN (NaNs last in ascending
+ * and in descending order, like Arrow); -0.0 and 0.0 compare equal (stable). */
+ds_status ds_sort_indices_i64(const int64_t* col, uint64_t n, int32_t descending,
+                              uint32_t* idx_out, int64_t* sorted_out, int32_t options,
+                              void* ws, size_t* ws_bytes, void* stream);
+ds_status ds_sort_indices_u64(const uint64_t* col, uint64_t n, int32_t descending,
+                              uint32_t* idx_out, uint64_t* sorted_out, int32_t options,
+                              void* ws, size_t* ws_bytes, void* stream);
+ds_status ds_sort_indices_f64(const double* col, uint64_t n, int32_t descending,
+                              uint32_t* idx_out, double* sorted_out, int32_t options,
+                              void* ws, size_t* ws_bytes, void* stream);
+
+/* Stable argsort of a fixed_size_binary(width) key column (memcmp order), width in
+ * 1..DS_MAX_KEY_BYTES -- the 10-byte GraySort key.  Same call sites as above.
+ *   col          n*width bytes, rows packed (Arrow fixed_size_binary data buffer)
+ *   sorted_out   optional: n*width bytes, the key column in sorted order */
+ds_status ds_sort_indices_fsb(const uint8_t* col, uint32_t width, uint64_t n,
+                              int32_t descending, uint32_t* idx_out, uint8_t* sorted_out,
+                              int32_t options, void* ws, size_t* ws_bytes, void* stream);
+
+/* Row gather dst[j] = src[idx[j]] for rows of row_bytes bytes.
+ * Replaces Table.take / take_table at transform_pyarrow.py:16,46-67 and
+ * ArrowBlockAccessor.take (_internal/arrow_block.py:258-267); one call per column. */
+ds_status ds_gather_rows(const void* src, uint32_t row_bytes, const uint32_t* idx,
+                         uint64_t n, void* dst, void* stream);
+
+/* ----------------------------------------------------------- partition ---- */
+
+/* Cut positions of a SORTED key column at the given boundaries.
+ * Replaces np.searchsorted(table[col], boundaries) (ascending, side="left") and
+ * n - np.searchsorted(..., sorter=arange(n-1,-1,-1)) (descending) at
+ * _internal/arrow_block.py:380-386.
+ *   boundaries   nb keys in the same encoding as the column (ascending order for
+ *                ascending sorts, descending order for descending sorts)
+ *   bounds_out   nb uint64 row offsets (device) */
+ds_status ds_searchsorted_i64(const int64_t* sorted_col, uint64_t n, const int64_t* boundaries,
+                              uint32_t nb, int32_t descending, uint64_t* bounds_out, void* stream);
+ds_status ds_searchsorted_f64(const double* sorted_col, uint64_t n, const double* boundaries,
+                              uint32_t nb, int32_t descending, uint64_t* bounds_out, void* stream);
+ds_status ds_searchsorted_fsb(const uint8_t* sorted_col, uint32_t width, uint64_t n,
+                              const uint8_t* boundaries, uint32_t nb, int32_t descending,
+                              uint64_t* bounds_out, void* stream);
+
+/* Stable range partition of an UNSORTED key column: the map side of the exchange.
+ * Same partition rule as sort_and_partition (_internal/arrow_block.py:373-394):
+ * ascending  bucket(x) = #{i : boundaries[i] <= x};
+ * descending bucket(x) = #{i : boundaries[i] >  x}.
+ *   counts_out   nb+1 uint64 rows per bucket (device)
+ *   offsets_out  nb+1 uint64 exclusive prefix of counts_out (device)
+ *   perm_out     n uint32: rows grouped by bucket, input order kept inside a bucket
+ * Replaces the per-mapper slicing at _internal/arrow_block.py:387-393 when the plan
+ * partitions before sorting (multi-GPU plan). */
+ds_status ds_partition_hist_scatter_i64(const int64_t* col, uint64_t n, const int64_t* boundaries,
+                                        uint32_t nb, int32_t descending, uint64_t* counts_out,
+                                        uint64_t* offsets_out, uint32_t* perm_out, void* ws,
+                                        size_t* ws_bytes, void* stream);
+ds_status ds_partition_hist_scatter_fsb(const uint8_t* col, uint32_t width, uint64_t n,
+                                        const uint8_t* boundaries, uint32_t nb, int32_t descending,
+                                        uint64_t* counts_out, uint64_t* offsets_out,
+                                        uint32_t* perm_out, void* ws, size_t* ws_bytes,
+                                        void* stream);
+
+/* ------------------------------------------------------------- sampling ---- */
+
+/* k sample rows of a column, without replacement: sample j is taken from stratum
+ * [floor(j*n/k), floor((j+1)*n/k)) at a Philox4x32-10(seed, j) offset.
+ * Replaces random.sample(range(n), k) + take at _internal/arrow_block.py:269-272
+ * (reference sampling is unseeded; which rows are drawn is not part of its contract).
+ * Requires 1 <= k <= n.  out: k*row_bytes bytes. */
+ds_status ds_sample_rows(const void* col, uint32_t row_bytes, uint64_t n, uint32_t k,
+                         uint64_t seed, void* out, void* stream);
+
+/* -------------------------------------------------------- random_shuffle ---- */
+
+/* A seeded uniform permutation of range(n): Philox4x32-10(seed, subsequence, row)
+ * 64-bit keys, stable radix sort, row index as payload.
+ * Replaces np.random.RandomState(seed).permutation(n) at
+ * _internal/arrow_block.py:184-186 (and the reducer-side call,
+ * _internal/shuffle_and_partition.py:86-89).  NOT bit-equal to MT19937: the
+ * contract kept is "a permutation, deterministic per (seed, subsequence, n)". */
+ds_status ds_random_permutation(uint64_t seed, uint64_t subsequence, uint64_t n,
+                                uint32_t* perm_out, void* ws, size_t* ws_bytes, void* stream);
+
+/* --------------------------------------------------------------- groupby ---- */
+
+/* Run starts of a SORTED key column: seg_starts_out[s] = first row of the s-th run
+ * of equal keys, *nseg_out = number of runs.  Replaces the per-row group scan of
+ * ArrowBlockAccessor.combine (_internal/arrow_block.py:417-442) and the key-change
+ * test of aggregate_combined_blocks (_internal/arrow_block.py:520-547).
+ *   seg_starts_out  capacity n+1 uint32; entry nseg is set to n
+ *   nseg_out        one uint32 (device) */
+ds_status ds_segment_heads_i64(const int64_t* sorted_keys, uint64_t n, uint32_t* seg_starts_out,
+                               uint32_t* nseg_out, void* ws, size_t* ws_bytes, void* stream);
+
+/* Per-run reduction of a value column that is still in INPUT order: run s reduces
+ * vals[idx[i]] for i in [seg_starts[s], seg_starts[s+1]).  idx may be NULL (values
+ * already in sorted order).  Replaces pyarrow.compute.sum/min/max on a group slice
+ * (_internal/arrow_block.py:311-329 via aggregate.py:97-211) and the accumulator
+ * merges a1+a2 of aggregate_combined_blocks (aggregate.py:107,119,185-187).
+ *   seg_starts  nseg+1 entries as written by ds_segment_heads_i64
+ *   nseg        HOST value (the caller reads *nseg_out back to size `out`)
+ *   op          DS_OP_SUM / DS_OP_MIN / DS_OP_MAX
+ * Summation order inside a run is fixed by (n, seg_starts) alone: results are
+ * reproducible run to run (no floating-point atomics). */
+ds_status ds_segmented_reduce_f64(const double* vals, const uint32_t* idx,
+                                  const uint32_t* seg_starts, uint32_t nseg, uint64_t n,
+                                  int32_t op, double* out, void* ws, size_t* ws_bytes,
+                                  void* stream);
+ds_status ds_segmented_reduce_i64(const int64_t* vals, const uint32_t* idx,
+                                  const uint32_t* seg_starts, uint32_t nseg, uint64_t n,
+                                  int32_t op, int64_t* out, void* ws, size_t* ws_bytes,
+                                  void* stream);
+
+/* Row counts per run: out[s] = seg_starts[s+1] - seg_starts[s].
+ * Replaces Count.accumulate_block (aggregate.py:97-109). */
+ds_status ds_segment_counts(const uint32_t* seg_starts, uint32_t nseg, int64_t* out,
+                            void* stream);
+
+/* Mean finalize out[s] = sum[s] / count[s] (aggregate.py:209).  sum_is_i64 selects
+ * the accumulator type of `sum` (int64 sums of int64 columns stay integral until
+ * the true division, like Python's int / int). */
+ds_status ds_finalize_mean(const void* sum, int32_t sum_is_i64, const int64_t* count,
+                           uint64_t n, double* out, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* DS_SHUFFLE_H_ */

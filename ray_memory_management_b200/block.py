@@ -1,0 +1,730 @@
+"""Device-resident Arrow-layout block and its accessor.
+
+Mirrors, for one new block kind, the block surface the reference's shuffle ops call
+(python/ray/data/block.py:100,148-230,233-422 and the ArrowBlockAccessor methods in
+python/ray/data/_internal/arrow_block.py:178-186,226-232,258-272,353-394,396-587).
+
+A ``DeviceArrowBlock`` keeps every column as ONE contiguous uint8 torch tensor in HBM
+holding the Arrow data buffer of a fixed-width column (int64, float64,
+fixed_size_binary(w), any other fixed-width primitive as payload).  Slices are views
+(pointer arithmetic), never copies.  All arithmetic goes through the C ABI in
+``_lib`` (CUDA, sm_100a); torch is only the owner of device memory and streams.
+"""
+import collections
+import ctypes
+import os
+import random
+import time
+from dataclasses import dataclass
+from typing import Any, Dict, List, Optional, Sequence, Tuple, Union
+
+import numpy as np
+import pyarrow as pa
+import torch
+
+from . import _lib
+from .aggregate import AggregateFn
+
+# A sort key as the reference normalises it: [(column, "ascending"|"descending")]
+SortKeyT = Union[None, List[Tuple[str, str]]]
+
+
+# --------------------------------------------------------------------------- stats
+class BlockExecStats:
+    """python/ray/data/block.py:148-205."""
+
+    def __init__(self):
+        self.wall_time_s: Optional[float] = None
+        self.cpu_time_s: Optional[float] = None
+        self.node_id = f"cuda:{torch.cuda.current_device()}" if torch.cuda.is_available() else "host"
+        self.max_rss_bytes: int = 0
+
+    @staticmethod
+    def builder() -> "_BlockExecStatsBuilder":
+        return _BlockExecStatsBuilder()
+
+    def __repr__(self):
+        return repr(
+            {"wall_time_s": self.wall_time_s, "cpu_time_s": self.cpu_time_s, "node_id": self.node_id}
+        )
+
+
+class _BlockExecStatsBuilder:
+    def __init__(self):
+        self.start_time = time.perf_counter()
+        self.start_cpu = time.process_time()
+
+    def build(self) -> BlockExecStats:
+        stats = BlockExecStats()
+        stats.wall_time_s = time.perf_counter() - self.start_time
+        stats.cpu_time_s = time.process_time() - self.start_cpu
+        try:
+            import resource
+
+            stats.max_rss_bytes = int(resource.getrusage(resource.RUSAGE_SELF).ru_maxrss * 1e3)
+        except Exception:  # pragma: no cover
+            stats.max_rss_bytes = 0
+        return stats
+
+
+@dataclass
+class BlockMetadata:
+    """python/ray/data/block.py:208-230."""
+
+    num_rows: Optional[int]
+    size_bytes: Optional[int]
+    schema: Optional[Any]
+    input_files: Optional[List[str]]
+    exec_stats: Optional[BlockExecStats]
+
+    def __post_init__(self):
+        if self.input_files is None:
+            self.input_files = []
+
+
+# --------------------------------------------------------------------------- device helpers
+def _stream() -> int:
+    return torch.cuda.current_stream().cuda_stream
+
+
+def _empty_u8(nbytes: int) -> torch.Tensor:
+    return torch.empty(max(int(nbytes), 0), dtype=torch.uint8, device="cuda")
+
+
+def _workspace(nbytes: int) -> torch.Tensor:
+    # 256-byte alignment is what the library asks for; torch's allocator gives 512.
+    return _empty_u8(nbytes)
+
+
+def _row_bytes(t: pa.DataType) -> int:
+    if pa.types.is_fixed_size_binary(t):
+        return t.byte_width
+    if pa.types.is_boolean(t):
+        raise NotImplementedError("boolean (bit-packed) columns are not supported on device")
+    try:
+        bw = t.bit_width
+    except ValueError:
+        raise NotImplementedError(f"variable-width Arrow type {t} is not supported on device yet")
+    if bw % 8:
+        raise NotImplementedError(f"Arrow type {t} is not byte-aligned")
+    return bw // 8
+
+
+def _key_kind(t: pa.DataType) -> str:
+    if pa.types.is_int64(t):
+        return "i64"
+    if pa.types.is_float64(t):
+        return "f64"
+    if pa.types.is_fixed_size_binary(t) and 1 <= t.byte_width <= _lib.DS_MAX_KEY_BYTES:
+        return "fsb"
+    raise NotImplementedError(
+        f"sort/groupby key of Arrow type {t} is not supported on device "
+        f"(int64, float64, fixed_size_binary(1..{_lib.DS_MAX_KEY_BYTES}))"
+    )
+
+
+class DeviceColumn:
+    """One fixed-width Arrow column in HBM: ``data`` is a uint8 view of n*row_bytes bytes."""
+
+    __slots__ = ("type", "row_bytes", "data")
+
+    def __init__(self, arrow_type: pa.DataType, data: torch.Tensor):
+        self.type = arrow_type
+        self.row_bytes = _row_bytes(arrow_type)
+        assert data.dtype == torch.uint8 and data.dim() == 1, (data.dtype, data.shape)
+        assert data.numel() % self.row_bytes == 0
+        self.data = data
+
+    @property
+    def num_rows(self) -> int:
+        return self.data.numel() // self.row_bytes
+
+    @property
+    def ptr(self) -> int:
+        return self.data.data_ptr()
+
+    def slice(self, start: int, end: int) -> "DeviceColumn":
+        return DeviceColumn(self.type, self.data[start * self.row_bytes : end * self.row_bytes])
+
+    def typed(self) -> torch.Tensor:
+        """int64/float64 view of the buffer (plumbing for tests and finalisation)."""
+        if pa.types.is_int64(self.type):
+            return self.data.view(torch.int64)
+        if pa.types.is_float64(self.type):
+            return self.data.view(torch.float64)
+        return self.data.view(-1, self.row_bytes)
+
+
+class DeviceArrowBlock:
+    """An Arrow-layout table whose column buffers live in HBM."""
+
+    def __init__(self, columns: "collections.OrderedDict[str, DeviceColumn]", num_rows: int):
+        self.columns = columns
+        self._num_rows = int(num_rows)
+        for name, c in columns.items():
+            assert c.num_rows == self._num_rows, (name, c.num_rows, num_rows)
+
+    # -- construction --------------------------------------------------------------
+    @staticmethod
+    def empty() -> "DeviceArrowBlock":
+        return DeviceArrowBlock(collections.OrderedDict(), 0)
+
+    @staticmethod
+    def from_arrow(table: pa.Table) -> "DeviceArrowBlock":
+        """H2D import of a pyarrow.Table (python/ray/data/_internal/arrow_block.py:135-138
+        is where the reference materialises Arrow blocks)."""
+        if not torch.cuda.is_available():
+            raise RuntimeError("DeviceArrowBlock needs a CUDA device; there is no CPU fallback")
+        cols = collections.OrderedDict()
+        n = table.num_rows if table.num_columns > 0 else 0
+        for name in table.column_names:
+            ca = table[name]
+            if ca.null_count:
+                raise NotImplementedError(f"column {name!r} has nulls; validity bitmaps are not supported on device yet")
+            arr = ca.combine_chunks() if ca.num_chunks != 1 else ca.chunk(0)
+            if isinstance(arr, pa.ChunkedArray):
+                arr = arr.chunk(0) if arr.num_chunks else pa.array([], type=ca.type)
+            w = _row_bytes(arr.type)
+            buf = arr.buffers()[1]
+            if buf is None or n == 0:
+                host = np.zeros(0, dtype=np.uint8)
+            else:
+                host = np.frombuffer(buf, dtype=np.uint8)[arr.offset * w : (arr.offset + n) * w]
+            dev = torch.from_numpy(host.copy() if not host.flags.writeable else host).to("cuda", non_blocking=False)
+            cols[name] = DeviceColumn(arr.type, dev)
+        return DeviceArrowBlock(cols, n)
+
+    @staticmethod
+    def from_host_buffers(
+        schema: Sequence[Tuple[str, pa.DataType]], buffers: Sequence[torch.Tensor], num_rows: int
+    ) -> "DeviceArrowBlock":
+        """H2D import of raw (ideally pinned) uint8 host buffers, one per column; the
+        copies are asynchronous on the current stream."""
+        cols = collections.OrderedDict()
+        for (name, t), host in zip(schema, buffers):
+            assert host.dtype == torch.uint8
+            dev = torch.empty(host.numel(), dtype=torch.uint8, device="cuda")
+            dev.copy_(host, non_blocking=True)
+            cols[name] = DeviceColumn(t, dev)
+        return DeviceArrowBlock(cols, num_rows)
+
+    def to_host_buffers(self, out: Sequence[torch.Tensor]) -> None:
+        """D2H export into caller-provided (ideally pinned) uint8 buffers."""
+        for c, host in zip(self.columns.values(), out):
+            host[: c.data.numel()].copy_(c.data, non_blocking=True)
+
+    def to_arrow(self) -> pa.Table:
+        """D2H export (synchronises)."""
+        if not self.columns:
+            return pa.Table.from_pydict({})
+        arrays, fields = [], []
+        for name, c in self.columns.items():
+            host = c.data.cpu().numpy()
+            buf = pa.py_buffer(host.tobytes())
+            arrays.append(pa.Array.from_buffers(c.type, self._num_rows, [None, buf]))
+            fields.append(pa.field(name, c.type))
+        return pa.Table.from_arrays(arrays, schema=pa.schema(fields))
+
+    # -- shape ---------------------------------------------------------------------
+    @property
+    def num_rows(self) -> int:
+        return self._num_rows if self.columns else 0
+
+    @property
+    def num_columns(self) -> int:
+        return len(self.columns)
+
+    @property
+    def column_names(self) -> List[str]:
+        return list(self.columns)
+
+    @property
+    def nbytes(self) -> int:
+        return sum(c.data.numel() for c in self.columns.values())
+
+    @property
+    def schema(self) -> pa.Schema:
+        return pa.schema([pa.field(n, c.type) for n, c in self.columns.items()])
+
+    def slice(self, start: int, end: int) -> "DeviceArrowBlock":
+        start = max(0, min(start, self.num_rows))
+        end = max(start, min(end, self.num_rows))
+        cols = collections.OrderedDict((n, c.slice(start, end)) for n, c in self.columns.items())
+        return DeviceArrowBlock(cols, end - start)
+
+    def select(self, names: Sequence[str]) -> "DeviceArrowBlock":
+        return DeviceArrowBlock(
+            collections.OrderedDict((n, self.columns[n]) for n in names), self._num_rows
+        )
+
+    def column(self, name: str) -> DeviceColumn:
+        if name not in self.columns:
+            raise ValueError(
+                f"Cannot find column {name}, available columns: {self.column_names}"
+            )
+        return self.columns[name]
+
+    @staticmethod
+    def concat(blocks: Sequence["DeviceArrowBlock"]) -> "DeviceArrowBlock":
+        """Row-wise concatenation in the given order (pyarrow.concat_tables at
+        _internal/arrow_ops/transform_pyarrow.py:73)."""
+        blocks = [b for b in blocks if b.num_columns > 0]
+        if not blocks:
+            return DeviceArrowBlock.empty()
+        if len(blocks) == 1:
+            return blocks[0]
+        names = blocks[0].column_names
+        for b in blocks[1:]:
+            if b.column_names != names or any(
+                b.columns[n].type != blocks[0].columns[n].type for n in names
+            ):
+                raise ValueError("cannot concatenate device blocks with different schemas")
+        cols = collections.OrderedDict()
+        for n in names:
+            cols[n] = DeviceColumn(
+                blocks[0].columns[n].type, torch.cat([b.columns[n].data for b in blocks])
+            )
+        return DeviceArrowBlock(cols, sum(b.num_rows for b in blocks))
+
+
+Block = Union[DeviceArrowBlock, pa.Table]
+
+
+# --------------------------------------------------------------------------- kernels (thin wrappers)
+def _argsort(col: DeviceColumn, descending: bool, want_sorted: bool, options: int = 0):
+    """ds_sort_indices_* -> (idx int32 tensor holding uint32 values, sorted key column or None)."""
+    n = col.num_rows
+    kind = _key_kind(col.type)
+    idx = torch.empty(n, dtype=torch.int32, device="cuda")
+    out = _empty_u8(n * col.row_bytes) if want_sorted else None
+    optr = out.data_ptr() if out is not None else None
+    stream = _stream()
+    if kind == "fsb":
+        args = (col.ptr, col.row_bytes, n, int(descending), idx.data_ptr(), optr, options)
+    else:
+        args = (col.ptr, n, int(descending), idx.data_ptr(), optr, options)
+    ws = _lib.call_ws(f"ds_sort_indices_{kind}", _workspace, *args, stream=stream)
+    ws.record_stream(torch.cuda.current_stream())
+    return idx, (DeviceColumn(col.type, out) if want_sorted else None)
+
+
+def _gather(col: DeviceColumn, idx: torch.Tensor) -> DeviceColumn:
+    n = idx.numel()
+    out = _empty_u8(n * col.row_bytes)
+    _lib.call("ds_gather_rows", col.ptr, col.row_bytes, idx.data_ptr(), n, out.data_ptr(), _stream())
+    return DeviceColumn(col.type, out)
+
+
+def _take_block(block: DeviceArrowBlock, idx: torch.Tensor, ready: Optional[Dict[str, DeviceColumn]] = None) -> DeviceArrowBlock:
+    cols = collections.OrderedDict()
+    for name, c in block.columns.items():
+        cols[name] = ready[name] if ready and name in ready else _gather(c, idx)
+    return DeviceArrowBlock(cols, idx.numel())
+
+
+def _boundaries_to_device(boundaries: Sequence, col: DeviceColumn) -> torch.Tensor:
+    kind = _key_kind(col.type)
+    if kind == "i64":
+        host = np.asarray([int(b) for b in boundaries], dtype=np.int64).view(np.uint8)
+    elif kind == "f64":
+        host = np.asarray([float(b) for b in boundaries], dtype=np.float64).view(np.uint8)
+    else:
+        raw = b"".join(bytes(b) for b in boundaries)
+        if len(raw) != len(boundaries) * col.row_bytes:
+            raise ValueError("fixed_size_binary boundaries must have the key's width")
+        host = np.frombuffer(raw, dtype=np.uint8)
+    return torch.from_numpy(host.copy()).to("cuda")
+
+
+def _searchsorted(sorted_col: DeviceColumn, boundaries: Sequence, descending: bool) -> List[int]:
+    nb = len(boundaries)
+    kind = _key_kind(sorted_col.type)
+    b = _boundaries_to_device(boundaries, sorted_col)
+    out = torch.empty(nb, dtype=torch.int64, device="cuda")
+    if kind == "fsb":
+        _lib.call("ds_searchsorted_fsb", sorted_col.ptr, sorted_col.row_bytes, sorted_col.num_rows,
+                  b.data_ptr(), nb, int(descending), out.data_ptr(), _stream())
+    else:
+        _lib.call(f"ds_searchsorted_{kind}", sorted_col.ptr, sorted_col.num_rows, b.data_ptr(), nb,
+                  int(descending), out.data_ptr(), _stream())
+    return [int(x) for x in out.cpu().tolist()]
+
+
+def _range_partition(col: DeviceColumn, boundaries: Sequence, descending: bool):
+    """ds_partition_hist_scatter_* -> (perm tensor, counts list)."""
+    kind = _key_kind(col.type)
+    if kind == "f64":
+        raise NotImplementedError("range partition of float64 keys is not supported on device yet")
+    n, nb = col.num_rows, len(boundaries)
+    b = _boundaries_to_device(boundaries, col)
+    counts = torch.empty(nb + 1, dtype=torch.int64, device="cuda")
+    offsets = torch.empty(nb + 1, dtype=torch.int64, device="cuda")
+    perm = torch.empty(n, dtype=torch.int32, device="cuda")
+    if kind == "fsb":
+        args = (col.ptr, col.row_bytes, n, b.data_ptr(), nb, int(descending))
+    else:
+        args = (col.ptr, n, b.data_ptr(), nb, int(descending))
+    ws = _lib.call_ws(f"ds_partition_hist_scatter_{kind}", _workspace, *args, counts.data_ptr(),
+                      offsets.data_ptr(), perm.data_ptr(), stream=_stream())
+    ws.record_stream(torch.cuda.current_stream())
+    return perm, [int(x) for x in counts.cpu().tolist()]
+
+
+def _random_permutation(n: int, seed: int, subsequence: int = 0) -> torch.Tensor:
+    perm = torch.empty(n, dtype=torch.int32, device="cuda")
+    ws = _lib.call_ws("ds_random_permutation", _workspace, seed & (2**64 - 1), subsequence, n,
+                      perm.data_ptr(), stream=_stream())
+    ws.record_stream(torch.cuda.current_stream())
+    return perm
+
+
+def _segment_heads(sorted_keys: DeviceColumn):
+    n = sorted_keys.num_rows
+    starts = torch.empty(n + 1, dtype=torch.int32, device="cuda")
+    nseg = torch.empty(1, dtype=torch.int32, device="cuda")
+    ws = _lib.call_ws("ds_segment_heads_i64", _workspace, sorted_keys.ptr, n, starts.data_ptr(),
+                      nseg.data_ptr(), stream=_stream())
+    ws.record_stream(torch.cuda.current_stream())
+    return starts, int(nseg.item())
+
+
+_OPS = {"sum": _lib.DS_OP_SUM, "min": _lib.DS_OP_MIN, "max": _lib.DS_OP_MAX}
+
+
+def _segmented_reduce(vals: DeviceColumn, idx: Optional[torch.Tensor], starts: torch.Tensor,
+                      nseg: int, n: int, op: str) -> DeviceColumn:
+    if pa.types.is_float64(vals.type):
+        fn = "ds_segmented_reduce_f64"
+    elif pa.types.is_int64(vals.type):
+        fn = "ds_segmented_reduce_i64"
+    else:
+        raise NotImplementedError(f"aggregation over Arrow type {vals.type} is not supported on device (int64, float64)")
+    out = _empty_u8(nseg * 8)
+    ws = _lib.call_ws(fn, _workspace, vals.ptr, idx.data_ptr() if idx is not None else None,
+                      starts.data_ptr(), nseg, n, _OPS[op], out.data_ptr(), stream=_stream())
+    ws.record_stream(torch.cuda.current_stream())
+    return DeviceColumn(vals.type, out)
+
+
+def _segment_counts(starts: torch.Tensor, nseg: int) -> DeviceColumn:
+    out = _empty_u8(nseg * 8)
+    _lib.call("ds_segment_counts", starts.data_ptr(), nseg, out.data_ptr(), _stream())
+    return DeviceColumn(pa.int64(), out)
+
+
+def _finalize_mean(s: DeviceColumn, c: DeviceColumn) -> DeviceColumn:
+    n = c.num_rows
+    out = _empty_u8(n * 8)
+    _lib.call("ds_finalize_mean", s.ptr, int(pa.types.is_int64(s.type)), c.ptr, n, out.data_ptr(), _stream())
+    return DeviceColumn(pa.float64(), out)
+
+
+# --------------------------------------------------------------------------- accessor
+def _normalize_key(key) -> Tuple[str, bool]:
+    """[(col, order)] -> (col, descending); arrow_block.py:356-359 for the error."""
+    if isinstance(key, str):
+        return key, False
+    if key is None or callable(key):
+        raise NotImplementedError(f"Table sort key must be a column name, was: {key}")
+    if len(key) > 1:
+        raise NotImplementedError("sorting by multiple columns is not supported yet")
+    col, order = key[0]
+    return col, order == "descending"
+
+
+class PartialAggBlock(DeviceArrowBlock):
+    """A combined (partially aggregated) block: key column + SoA accumulator columns.
+
+    The reference stores each accumulator as an Arrow list column with a trailing
+    has_data flag (python/ray/data/_internal/null_aggregate.py:29-46); on device the
+    numeric parts are kept as plain columns named ``<agg>#sum`` / ``<agg>#count`` / ...
+    and the list wrapper is not materialised."""
+
+
+class DeviceArrowBlockAccessor:
+    """BlockAccessor for DeviceArrowBlock (python/ray/data/block.py:233-422)."""
+
+    def __init__(self, block: DeviceArrowBlock):
+        self._block = block
+
+    # -- plain accessors -------------------------------------------------------------
+    def num_rows(self) -> int:
+        return self._block.num_rows
+
+    def size_bytes(self) -> int:
+        return self._block.nbytes  # arrow_block.py:231-232 (table.nbytes)
+
+    def schema(self) -> pa.Schema:
+        return self._block.schema
+
+    def to_block(self) -> DeviceArrowBlock:
+        return self._block
+
+    def to_arrow(self) -> pa.Table:
+        return self._block.to_arrow()
+
+    def to_numpy(self, columns=None):
+        t = self._block.to_arrow()
+        if columns is None:
+            columns = t.column_names
+        single = not isinstance(columns, list)
+        cols = [columns] if single else columns
+        for c in cols:
+            if c not in t.column_names:
+                raise ValueError(f"Cannot find column {c}, available columns: {t.column_names}")
+        arrs = [t[c].combine_chunks().to_numpy(zero_copy_only=False) for c in cols]
+        return arrs[0] if len(arrs) == 1 else dict(zip(cols, arrs))
+
+    def get_metadata(self, input_files, exec_stats) -> BlockMetadata:
+        return BlockMetadata(
+            num_rows=self.num_rows(),
+            size_bytes=self.size_bytes(),
+            schema=self.schema(),
+            input_files=input_files,
+            exec_stats=exec_stats,
+        )
+
+    def slice(self, start: int, end: int, copy: bool = False) -> DeviceArrowBlock:
+        """arrow_block.py:178-182.  Device slices are views; ``copy=True`` clones."""
+        view = self._block.slice(start, end)
+        if copy:
+            cols = collections.OrderedDict(
+                (n, DeviceColumn(c.type, c.data.clone())) for n, c in view.columns.items()
+            )
+            view = DeviceArrowBlock(cols, view.num_rows)
+        return view
+
+    def take(self, indices) -> DeviceArrowBlock:
+        """arrow_block.py:258-267."""
+        if not isinstance(indices, torch.Tensor):
+            indices = torch.as_tensor(np.asarray(indices, dtype=np.int64).astype(np.int32))
+        idx = indices.to(device="cuda", dtype=torch.int32)
+        return _take_block(self._block, idx)
+
+    @staticmethod
+    def _empty_table() -> DeviceArrowBlock:
+        return DeviceArrowBlock.empty()
+
+    # -- sampling (table_block.py:186-196, arrow_block.py:269-272) ------------------
+    def sample(self, n_samples: int, key: SortKeyT) -> DeviceArrowBlock:
+        if key is None or callable(key):
+            raise NotImplementedError(f"Table sort key must be a column name, was: {key}")
+        if self.num_rows() == 0:
+            return self._empty_table()
+        k = min(n_samples, self.num_rows())
+        names = [key] if isinstance(key, str) else [kk[0] for kk in key]
+        seed = random.getrandbits(63)  # the reference draws from the global `random` too
+        cols = collections.OrderedDict()
+        for name in names:
+            c = self._block.column(name)
+            out = _empty_u8(k * c.row_bytes)
+            if k:
+                _lib.call("ds_sample_rows", c.ptr, c.row_bytes, c.num_rows, k, seed, out.data_ptr(), _stream())
+            cols[name] = DeviceColumn(c.type, out)
+        return DeviceArrowBlock(cols, k)
+
+    # -- sort (arrow_block.py:353-394) ------------------------------------------------
+    def _sorted(self, col: str, descending: bool) -> DeviceArrowBlock:
+        keycol = self._block.column(col)
+        idx, sorted_key = _argsort(keycol, descending, want_sorted=True)
+        return _take_block(self._block, idx, ready={col: sorted_key})
+
+    def sort_and_partition(self, boundaries: List, key: SortKeyT, descending: bool) -> List[DeviceArrowBlock]:
+        if not isinstance(key, str) and key is not None and not callable(key) and len(key) > 1:
+            raise NotImplementedError("sorting by multiple columns is not supported yet")
+        if self._block.num_rows == 0:
+            return [self._empty_table() for _ in range(len(boundaries) + 1)]
+        col, _ = _normalize_key(key)
+        table = self._sorted(col, descending)
+        if len(boundaries) == 0:
+            return [table]
+        bounds = _searchsorted(table.column(col), boundaries, descending)
+        parts, last = [], 0
+        for b in bounds:
+            parts.append(table.slice(last, b))
+            last = b
+        parts.append(table.slice(last, table.num_rows))
+        return parts
+
+    def partition_unsorted(self, boundaries: List, key: SortKeyT, descending: bool) -> List[DeviceArrowBlock]:
+        """Stable range partition WITHOUT sorting: same partition rule and same
+        in-partition input order as slicing the stably sorted block would give, up to
+        the order inside a partition (which the reducer's stable sort restores).  Used by
+        the device plan, which sorts once on the reduce side."""
+        nparts = len(boundaries) + 1
+        if self._block.num_rows == 0:
+            return [self._empty_table() for _ in range(nparts)]
+        if nparts == 1:
+            return [self._block]
+        col, _ = _normalize_key(key)
+        perm, counts = _range_partition(self._block.column(col), boundaries, descending)
+        table = _take_block(self._block, perm)
+        parts, last = [], 0
+        for c in counts:
+            parts.append(table.slice(last, last + c))
+            last += c
+        return parts
+
+    @staticmethod
+    def merge_sorted_blocks(blocks: List[Block], key: SortKeyT, _descending: bool):
+        """arrow_block.py:473-486: concat in mapper order + stable sort."""
+        stats = BlockExecStats.builder()
+        blocks = [BlockAccessor.for_block(b).to_block() for b in blocks]
+        blocks = [b for b in blocks if b.num_rows > 0]
+        if len(blocks) == 0:
+            ret = DeviceArrowBlock.empty()
+        else:
+            col, desc_from_key = _normalize_key(key)
+            ret = DeviceArrowBlockAccessor(DeviceArrowBlock.concat(blocks))._sorted(
+                col, desc_from_key if not isinstance(key, str) else _descending
+            )
+        return ret, DeviceArrowBlockAccessor(ret).get_metadata(None, exec_stats=stats.build())
+
+    # -- random_shuffle (arrow_block.py:184-186) ----------------------------------------
+    def random_shuffle(self, random_seed: Optional[int]) -> DeviceArrowBlock:
+        if random_seed is None:
+            random_seed = int.from_bytes(os.urandom(8), "little")
+        n = self.num_rows()
+        if n == 0:
+            return self._block
+        perm = _random_permutation(n, int(random_seed))
+        return _take_block(self._block, perm)
+
+    # -- groupby (arrow_block.py:396-467, 488-587) ----------------------------------------
+    def combine(self, key: Optional[str], aggs: Tuple[AggregateFn]) -> PartialAggBlock:
+        """Partial aggregation of a key-sorted block: one row per run of equal keys."""
+        if key is not None and not isinstance(key, str):
+            raise ValueError(
+                "key must be a string or None when aggregating on Arrow blocks, but "
+                f"got: {type(key)}."
+            )
+        blk = self._block
+        n = blk.num_rows
+        cols = collections.OrderedDict()
+        if n == 0:
+            return PartialAggBlock(cols, 0)
+        if key is None:
+            starts = torch.tensor([0, n], dtype=torch.int32, device="cuda")
+            nseg = 1
+        else:
+            keycol = blk.column(key)
+            if _key_kind(keycol.type) != "i64":
+                raise NotImplementedError("groupby keys must be int64 on device for now")
+            starts, nseg = _segment_heads(keycol)
+            cols[key] = _gather(keycol, starts[:nseg])
+        for name, agg in zip(resolve_agg_names(aggs), aggs):
+            for part, col in agg._device_accumulate(blk, starts, nseg, n).items():
+                cols[f"{name}#{part}"] = col
+        return PartialAggBlock(cols, nseg)
+
+    @staticmethod
+    def aggregate_combined_blocks(blocks: List[PartialAggBlock], key: Optional[str],
+                                  aggs: Tuple[AggregateFn], finalize: bool):
+        """Merge partials of one key range (arrow_block.py:488-587): concat in mapper
+        order, stable sort by key, merge accumulators of equal keys left to right."""
+        stats = BlockExecStats.builder()
+        blocks = [b for b in blocks if b.num_rows > 0]
+        names = resolve_agg_names(aggs)
+        if not blocks:
+            ret = DeviceArrowBlock.empty()
+            return ret, DeviceArrowBlockAccessor(ret).get_metadata(None, exec_stats=stats.build())
+        cat = DeviceArrowBlock.concat(blocks)
+        n = cat.num_rows
+        cols = collections.OrderedDict()
+        if key is None:
+            idx = None
+            starts = torch.tensor([0, n], dtype=torch.int32, device="cuda")
+            nseg = 1
+        else:
+            keycol = cat.columns[key]
+            if len(blocks) == 1:
+                idx, sorted_key = None, keycol  # a single combined block is already key-sorted
+            else:
+                idx, sorted_key = _argsort(keycol, False, want_sorted=True)
+            starts, nseg = _segment_heads(sorted_key)
+            cols[key] = _gather(sorted_key, starts[:nseg])
+        for name, agg in zip(names, aggs):
+            parts = {
+                p: _segmented_reduce(cat.columns[f"{name}#{p}"], idx, starts, nseg, n, op)
+                for p, op in agg._device_merge_ops().items()
+            }
+            if finalize:
+                cols[name] = agg._device_finalize(parts)
+            else:
+                for p, c in parts.items():
+                    cols[f"{name}#{p}"] = c
+        ret = (DeviceArrowBlock if finalize else PartialAggBlock)(cols, nseg)
+        return ret, DeviceArrowBlockAccessor(ret).get_metadata(None, exec_stats=stats.build())
+
+
+def resolve_agg_names(aggs) -> List[str]:
+    """arrow_block.py:456-463,469-471: duplicate names become name_2, name_3, ..."""
+    count = collections.defaultdict(int)
+    out = []
+    for agg in aggs:
+        name = agg.name
+        if count[name] > 0:
+            name = f"{name}_{count[name] + 1}"
+        count[agg.name] += 1
+        out.append(name)
+    return out
+
+
+class BlockAccessor:
+    """python/ray/data/block.py:370-394: dispatch on the block kind."""
+
+    @staticmethod
+    def for_block(block) -> DeviceArrowBlockAccessor:
+        if isinstance(block, DeviceArrowBlock):
+            return DeviceArrowBlockAccessor(block)
+        if isinstance(block, pa.Table):
+            # host Arrow tables enter the device path through an H2D import
+            return DeviceArrowBlockAccessor(DeviceArrowBlock.from_arrow(block))
+        raise TypeError(f"Not a device block type: {block!r} ({type(block)})")
+
+
+class BlockList:
+    """python/ray/data/_internal/block_list.py:10-60,172-220 -- the subset the plans use.
+    Holds device blocks directly (there is no object store between stages)."""
+
+    def __init__(self, blocks: List[Block], metadata: List[BlockMetadata], *, owned_by_consumer: bool = False):
+        assert len(blocks) == len(metadata), (blocks, metadata)
+        self._blocks = blocks
+        self._num_blocks = len(blocks)
+        self._metadata = metadata
+        self._owned_by_consumer = owned_by_consumer
+
+    def get_metadata(self, fetch_if_missing: bool = False) -> List[BlockMetadata]:
+        return self._metadata.copy()
+
+    def copy(self) -> "BlockList":
+        return BlockList(self._blocks, self._metadata, owned_by_consumer=self._owned_by_consumer)
+
+    def clear(self) -> None:
+        self._blocks = None
+
+    def is_cleared(self) -> bool:
+        return self._blocks is None
+
+    def _check_if_cleared(self) -> None:
+        if self.is_cleared():
+            raise ValueError(
+                "This Dataset's blocks have been moved, which means that you "
+                "can no longer use this Dataset."
+            )
+
+    def get_blocks(self) -> List[Block]:
+        self._check_if_cleared()
+        return list(self._blocks)
+
+    def initial_num_blocks(self) -> int:
+        return self._num_blocks
+
+    def executed_num_blocks(self) -> int:
+        return len(self.get_blocks())
+
+    @staticmethod
+    def from_blocks(blocks: Sequence[Block]) -> "BlockList":
+        blocks = [BlockAccessor.for_block(b).to_block() for b in blocks]
+        metas = [DeviceArrowBlockAccessor(b).get_metadata(None, None) for b in blocks]
+        return BlockList(blocks, metas, owned_by_consumer=False)

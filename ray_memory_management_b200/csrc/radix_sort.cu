@@ -1,0 +1,631 @@
+// LSD "onesweep" radix sort of (key, uint32 row index) pairs for sm_100a.
+//
+// Replaces pyarrow.compute.sort_indices at
+// python/ray/data/_internal/arrow_ops/transform_pyarrow.py:15,74 (reference).
+//
+// Data layout in HBM (all SoA, so every pass streams contiguous arrays):
+//   hi[n]  uint64  radix-order encoding of the first <=8 key bytes
+//   lo[n]  uint16  key bytes 8..9 of a fixed_size_binary(9|10) key (else absent)
+//   idx[n] uint32  row index payload (generated, not loaded, by the first pass)
+// Each array is double-buffered inside the caller's workspace.
+//
+// Kernels
+//   encode_hist_kernel   reads the Arrow key column once, writes hi/lo and the 256-bin
+//                        histograms of ALL digit positions (shared-memory atomics,
+//                        one global flush per block).
+//   scan_hist_kernel     exclusive scan per digit position -> global bin bases, and a
+//                        "constant digit" flag per position (such passes are skipped).
+//   onesweep_pass_kernel one 8-bit pass: warp-striped coalesced loads, per-warp digit
+//                        histograms ranked with match.any (stable), per-digit
+//                        decoupled look-back across tiles (tile ids handed out by an
+//                        atomic counter, so a tile only ever waits on tiles that are
+//                        already resident), shared-memory exchange, coalesced scatter.
+//                        Algorithmic bytes per key per pass: 2*(8[+2]+4) = 24 / 28.
+//   decode_kernel        sorted hi/lo -> sorted key column in its Arrow form.
+#include <utility>
+#include <vector>
+
+#include "ds_common.cuh"
+#include "ds_keys.cuh"
+
+namespace ds {
+
+constexpr int RADIX = 256;
+constexpr uint32_t LB_AGGREGATE = 1u << 30;
+constexpr uint32_t LB_INCLUSIVE = 2u << 30;
+constexpr uint32_t LB_VALUE = (1u << 30) - 1;
+constexpr int MAX_PASSES = 10;
+
+struct PassList {
+  int count;
+  int shift[MAX_PASSES];
+  int from_lo[MAX_PASSES];
+};
+
+// ---------------------------------------------------------------- encode + hist
+template <int KIND, bool HAS_LO>
+__global__ void __launch_bounds__(512) encode_hist_kernel(const void* __restrict__ col,
+                                                          uint32_t width, uint32_t n, bool desc,
+                                                          uint64_t* __restrict__ hi_out,
+                                                          uint16_t* __restrict__ lo_out, PassList pl,
+                                                          uint32_t* __restrict__ ghist,
+                                                          uint64_t seed, uint64_t subseq) {
+  __shared__ uint32_t sh[MAX_PASSES * RADIX];
+  for (int i = threadIdx.x; i < pl.count * RADIX; i += blockDim.x) sh[i] = 0;
+  __syncthreads();
+  const uint32_t stride = gridDim.x * blockDim.x;
+  for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+    uint64_t hi;
+    uint32_t lo;
+    if (KIND == KIND_PHILOX) {
+      hi = philox64(seed, subseq, i);
+      lo = 0;
+    } else {
+      load_key<KIND>(col, width, i, desc, hi, lo);
+    }
+    st_stream(hi_out + i, hi);
+    if (HAS_LO) st_stream(lo_out + i, static_cast<uint16_t>(lo));
+    const unsigned m = __activemask();
+    const int leader = __ffs(m) - 1;
+#pragma unroll
+    for (int p = 0; p < MAX_PASSES; ++p) {
+      if (p < pl.count) {
+        uint32_t d = (HAS_LO && pl.from_lo[p]) ? (lo >> pl.shift[p]) & 255u
+                                               : static_cast<uint32_t>(hi >> pl.shift[p]) & 255u;
+        int same;
+        __match_all_sync(m, d, &same);
+        if (same) {  // constant digit across the warp: one atomic instead of 32 colliding
+          if ((int)lane_id() == leader) atomicAdd(&sh[p * RADIX + d], __popc(m));
+        } else {
+          atomicAdd(&sh[p * RADIX + d], 1u);
+        }
+      }
+    }
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < pl.count * RADIX; i += blockDim.x) {
+    uint32_t c = sh[i];
+    if (c) atomicAdd(&ghist[i], c);
+  }
+}
+
+// One block of 256 threads per digit position.
+__global__ void scan_hist_kernel(const uint32_t* __restrict__ ghist, uint32_t n,
+                                 uint32_t* __restrict__ bin_base, uint32_t* __restrict__ skip) {
+  __shared__ uint32_t warp_tot[8];
+  const int p = blockIdx.x, d = threadIdx.x;
+  const uint32_t c = ghist[p * RADIX + d];
+  uint32_t v = c;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    uint32_t t = __shfl_up_sync(0xffffffffu, v, o);
+    if ((int)lane_id() >= o) v += t;
+  }
+  if (lane_id() == 31) warp_tot[d >> 5] = v;
+  __syncthreads();
+  uint32_t add = 0;
+  for (int w = 0; w < (d >> 5); ++w) add += warp_tot[w];
+  bin_base[p * RADIX + d] = v + add - c;
+  const int any = __syncthreads_or(c == n);
+  if (d == 0) skip[p] = any ? 1u : 0u;
+}
+
+__global__ void iota_kernel(uint32_t* out, uint32_t n) {
+  uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) out[i] = i;
+}
+
+// ---------------------------------------------------------------- onesweep pass
+template <bool HAS_LO, bool DIGIT_LO>
+__device__ __forceinline__ uint32_t digit_of(uint64_t hi, uint32_t lo, int shift) {
+  return DIGIT_LO && HAS_LO ? (lo >> shift) & 255u : static_cast<uint32_t>(hi >> shift) & 255u;
+}
+
+template <int THREADS, int ITEMS, bool HAS_LO>
+struct PassSmem {
+  static constexpr int TILE = THREADS * ITEMS;
+  static constexpr int WARPS = THREADS / 32;
+  static constexpr int ITEM_BYTES = 8 + (HAS_LO ? 2 : 0) + 4;
+  static constexpr int EXCH = TILE * ITEM_BYTES;
+  static constexpr int HIST = WARPS * RADIX * 4;
+  static constexpr int BYTES = (EXCH > HIST ? EXCH : HIST);
+};
+
+template <int THREADS, int ITEMS, int MIN_BLOCKS, bool HAS_LO, bool DIGIT_LO, bool GEN_IDX>
+__global__ void __launch_bounds__(THREADS, MIN_BLOCKS)
+    onesweep_pass_kernel(const uint64_t* __restrict__ hi_in, const uint16_t* __restrict__ lo_in,
+                         const uint32_t* __restrict__ idx_in, uint64_t* __restrict__ hi_out,
+                         uint16_t* __restrict__ lo_out, uint32_t* __restrict__ idx_out, uint32_t n,
+                         int shift, const uint32_t* __restrict__ bin_base,
+                         volatile uint32_t* lookback, uint32_t* tile_counter) {
+  static_assert(THREADS >= RADIX && THREADS % 32 == 0, "one thread per digit is required");
+  using S = PassSmem<THREADS, ITEMS, HAS_LO>;
+  constexpr int TILE = S::TILE;
+  constexpr int WARPS = S::WARPS;
+  extern __shared__ __align__(16) unsigned char smem[];
+  uint32_t* warp_hist = reinterpret_cast<uint32_t*>(smem);  // [WARPS][RADIX], then reused:
+  uint64_t* ex_hi = reinterpret_cast<uint64_t*>(smem);      // [TILE]
+  uint32_t* ex_idx = reinterpret_cast<uint32_t*>(smem + TILE * 8);
+  uint16_t* ex_lo = reinterpret_cast<uint16_t*>(smem + TILE * 12);
+  __shared__ uint32_t s_gofs[RADIX];
+  __shared__ uint32_t s_dstart[RADIX];
+  __shared__ uint32_t s_warp_tot[8];
+  __shared__ uint32_t s_tile;
+
+  const int tid = threadIdx.x;
+  const int warp = tid >> 5;
+  const uint32_t lane = tid & 31;
+  if (tid == 0) s_tile = atomicAdd(tile_counter, 1u);
+#pragma unroll
+  for (int i = tid; i < WARPS * RADIX; i += THREADS) warp_hist[i] = 0;
+  __syncthreads();
+  const uint32_t tile = s_tile;
+  const uint32_t tile_base = tile * TILE;
+  const uint32_t tile_valid = min(static_cast<uint32_t>(TILE), n - tile_base);
+  const bool full = tile_valid == TILE;
+
+  // ---- load (warp-striped: item i of lane l sits at warp_base + i*32 + l)
+  uint64_t hi[ITEMS];
+  uint32_t lo[ITEMS];
+  uint32_t idx[ITEMS];
+  uint32_t rank[ITEMS];
+  const uint32_t wofs = warp * 32 * ITEMS + lane;  // tile-local position of item 0
+#pragma unroll
+  for (int i = 0; i < ITEMS; ++i) {
+    const uint32_t lp = wofs + i * 32;
+    const uint32_t gp = tile_base + lp;
+    if (full || lp < tile_valid) {
+      hi[i] = ld_stream(hi_in + gp);
+      lo[i] = HAS_LO ? ld_stream(lo_in + gp) : 0;
+      idx[i] = GEN_IDX ? gp : ld_stream(idx_in + gp);
+    } else {
+      hi[i] = 0;
+      lo[i] = 0;
+      idx[i] = 0;
+    }
+  }
+
+  // ---- rank inside the warp (stable: items visited in position order, peers by lane)
+  uint32_t* wh = warp_hist + warp * RADIX;
+  const uint32_t lt_mask = lanemask_lt();
+#pragma unroll
+  for (int i = 0; i < ITEMS; ++i) {
+    const bool valid = full || (wofs + i * 32 < tile_valid);
+    const uint32_t d = valid ? digit_of<HAS_LO, DIGIT_LO>(hi[i], lo[i], shift) : 0xFFFFFFFFu;
+    const uint32_t peers = __match_any_sync(0xffffffffu, d);
+    const uint32_t lt = __popc(peers & lt_mask);
+    uint32_t prev = 0;
+    if (valid) prev = wh[d];
+    __syncwarp();
+    if (valid && lt == 0) wh[d] = prev + __popc(peers);
+    __syncwarp();
+    rank[i] = prev + lt;
+  }
+  __syncthreads();
+
+  // ---- per digit: scan over warps, scan over digits, look back over earlier tiles
+  if (tid < RADIX) {
+    uint32_t sum = 0;
+#pragma unroll
+    for (int w = 0; w < WARPS; ++w) {
+      const uint32_t c = warp_hist[w * RADIX + tid];
+      warp_hist[w * RADIX + tid] = sum;
+      sum += c;
+    }
+    // publish this tile's count as early as possible
+    volatile uint32_t* my = lookback + static_cast<size_t>(tile) * RADIX + tid;
+    if (tile == 0) {
+      *my = LB_INCLUSIVE | sum;
+    } else {
+      *my = LB_AGGREGATE | sum;
+    }
+    // block-wide exclusive scan of the 256 digit counts
+    uint32_t v = sum;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      uint32_t t = __shfl_up_sync(0xffffffffu, v, o);
+      if ((int)lane >= o) v += t;
+    }
+    if (lane == 31) s_warp_tot[warp] = v;
+    asm volatile("bar.sync 1, 256;");
+    uint32_t add = 0;
+#pragma unroll
+    for (int w = 0; w < 8; ++w)
+      if (w < warp) add += s_warp_tot[w];
+    const uint32_t dstart = v + add - sum;
+    s_dstart[tid] = dstart;
+    uint32_t excl = 0;
+    if (tile != 0) {
+      int t = static_cast<int>(tile) - 1;
+      while (true) {
+        uint32_t s = lookback[static_cast<size_t>(t) * RADIX + tid];
+        if ((s & ~LB_VALUE) == 0) continue;  // not published yet: that tile is resident, spin
+        excl += s & LB_VALUE;
+        if (s & LB_INCLUSIVE) break;
+        --t;
+      }
+      *my = LB_INCLUSIVE | (excl + sum);
+    }
+    s_gofs[tid] = bin_base[tid] + excl - dstart;
+  }
+  __syncthreads();
+
+  // ---- tile-local sorted position of every item
+#pragma unroll
+  for (int i = 0; i < ITEMS; ++i) {
+    const bool valid = full || (wofs + i * 32 < tile_valid);
+    if (valid) {
+      const uint32_t d = digit_of<HAS_LO, DIGIT_LO>(hi[i], lo[i], shift);
+      rank[i] += s_dstart[d] + wh[d];
+    }
+  }
+  __syncthreads();  // warp_hist is dead from here: the exchange buffers overlay it
+
+#pragma unroll
+  for (int i = 0; i < ITEMS; ++i) {
+    const bool valid = full || (wofs + i * 32 < tile_valid);
+    if (valid) {
+      ex_hi[rank[i]] = hi[i];
+      ex_idx[rank[i]] = idx[i];
+      if (HAS_LO) ex_lo[rank[i]] = static_cast<uint16_t>(lo[i]);
+    }
+  }
+  __syncthreads();
+
+  // ---- coalesced scatter: consecutive threads own consecutive sorted positions
+#pragma unroll
+  for (int i = 0; i < ITEMS; ++i) {
+    const uint32_t p = tid + i * THREADS;
+    if (full || p < tile_valid) {
+      const uint64_t h = ex_hi[p];
+      const uint32_t l = HAS_LO ? ex_lo[p] : 0;
+      const uint32_t x = ex_idx[p];
+      const uint32_t d = digit_of<HAS_LO, DIGIT_LO>(h, l, shift);
+      const uint32_t dst = s_gofs[d] + p;
+      hi_out[dst] = h;
+      if (HAS_LO) lo_out[dst] = static_cast<uint16_t>(l);
+      idx_out[dst] = x;
+    }
+  }
+}
+
+// ---------------------------------------------------------------- decode
+template <int KIND>
+__global__ void decode_kernel(const uint64_t* __restrict__ hi, const uint16_t* __restrict__ lo,
+                              uint32_t width, uint32_t n, bool desc, void* __restrict__ out) {
+  uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  uint64_t h = hi[i];
+  if (KIND == KIND_I64) {
+    static_cast<int64_t*>(out)[i] = dec_i64(h, desc);
+  } else if (KIND == KIND_U64) {
+    static_cast<uint64_t*>(out)[i] = desc ? ~h : h;
+  } else {
+    uint32_t l = width > 8 ? lo[i] : 0;
+    if (desc) {
+      h = ~h;
+      l = ~l;
+    }
+    uint8_t* p = static_cast<uint8_t*>(out) + static_cast<uint64_t>(i) * width;
+#pragma unroll
+    for (int b = 0; b < 8; ++b)
+      if (b < (int)width) p[b] = static_cast<uint8_t>(h >> (56 - 8 * b));
+    if (width == 9) p[8] = static_cast<uint8_t>(l);
+    if (width == 10) {
+      p[8] = static_cast<uint8_t>(l >> 8);
+      p[9] = static_cast<uint8_t>(l);
+    }
+  }
+}
+
+// ---------------------------------------------------------------- host driver
+// Optional per-launch timing of the pass kernel (bench.py's roofline figure): CUDA events
+// recorded on the launching stream around each launch; read back by
+// ds_debug_collect_pass_timing after the caller has synchronised.
+static bool g_timing = false;
+static std::vector<std::pair<cudaEvent_t, cudaEvent_t>> g_events;
+struct PassTimer {
+  cudaStream_t s;
+  cudaEvent_t a = nullptr, b = nullptr;
+  explicit PassTimer(cudaStream_t st) : s(st) {
+    if (!g_timing) return;
+    if (cudaEventCreate(&a) != cudaSuccess || cudaEventCreate(&b) != cudaSuccess) { a = b = nullptr; return; }
+    cudaEventRecord(a, s);
+  }
+  void stop() {
+    if (!a) return;
+    cudaEventRecord(b, s);
+    g_events.emplace_back(a, b);
+  }
+};
+
+struct PassConfig {
+  int threads, items;
+};
+static int g_cfg = 0;  // tuning knob (ds_debug_set_radix_config)
+
+template <int THREADS, int ITEMS, int MIN_BLOCKS, bool HAS_LO, bool DIGIT_LO, bool GEN_IDX>
+static cudaError_t launch_pass_t(const uint64_t* hi_in, const uint16_t* lo_in,
+                                 const uint32_t* idx_in, uint64_t* hi_out, uint16_t* lo_out,
+                                 uint32_t* idx_out, uint32_t n, int shift, const uint32_t* bin_base,
+                                 uint32_t* lookback, uint32_t* tile_counter, cudaStream_t s) {
+  using S = PassSmem<THREADS, ITEMS, HAS_LO>;
+  auto k = onesweep_pass_kernel<THREADS, ITEMS, MIN_BLOCKS, HAS_LO, DIGIT_LO, GEN_IDX>;
+  static unsigned long long attr_done = 0;  // per instantiation, one bit per device
+  int dev = 0;
+  cudaGetDevice(&dev);
+  if (!(attr_done >> (dev & 63) & 1ull)) {
+    cudaError_t e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, S::BYTES);
+    if (e != cudaSuccess) return e;
+    attr_done |= 1ull << (dev & 63);
+  }
+  const uint32_t tiles = (n + S::TILE - 1) / S::TILE;
+  PassTimer timer(s);
+  ds::note_launch(); k<<<tiles, THREADS, S::BYTES, s>>>(hi_in, lo_in, idx_in, hi_out, lo_out, idx_out, n, shift,
+                                     bin_base, lookback, tile_counter);
+  timer.stop();
+  return cudaGetLastError();
+}
+
+template <int THREADS, int ITEMS, int MIN_BLOCKS>
+static cudaError_t launch_pass_cfg(bool has_lo, bool digit_lo, bool gen_idx, const uint64_t* hi_in,
+                                   const uint16_t* lo_in, const uint32_t* idx_in, uint64_t* hi_out,
+                                   uint16_t* lo_out, uint32_t* idx_out, uint32_t n, int shift,
+                                   const uint32_t* bin_base, uint32_t* lookback,
+                                   uint32_t* tile_counter, cudaStream_t s) {
+#define DS_PASS(HL, DL, GI)                                                                      \
+  return launch_pass_t<THREADS, ITEMS, MIN_BLOCKS, HL, DL, GI>(hi_in, lo_in, idx_in, hi_out,     \
+                                                               lo_out, idx_out, n, shift,        \
+                                                               bin_base, lookback, tile_counter, s)
+  if (has_lo) {
+    if (digit_lo) {
+      if (gen_idx) DS_PASS(true, true, true);
+      DS_PASS(true, true, false);
+    }
+    if (gen_idx) DS_PASS(true, false, true);
+    DS_PASS(true, false, false);
+  }
+  if (gen_idx) DS_PASS(false, false, true);
+  DS_PASS(false, false, false);
+#undef DS_PASS
+}
+
+static int cfg_tile(int cfg) {
+  switch (cfg) {
+    case 1: return 512 * 8;
+    case 2: return 384 * 12;
+    case 3: return 256 * 12;
+    default: return 256 * 16;
+  }
+}
+
+static cudaError_t launch_pass(int cfg, bool has_lo, bool digit_lo, bool gen_idx,
+                               const uint64_t* hi_in, const uint16_t* lo_in, const uint32_t* idx_in,
+                               uint64_t* hi_out, uint16_t* lo_out, uint32_t* idx_out, uint32_t n,
+                               int shift, const uint32_t* bin_base, uint32_t* lookback,
+                               uint32_t* tile_counter, cudaStream_t s) {
+#define DS_ARGS                                                                                  \
+  has_lo, digit_lo, gen_idx, hi_in, lo_in, idx_in, hi_out, lo_out, idx_out, n, shift, bin_base,  \
+      lookback, tile_counter, s
+  switch (cfg) {
+    case 1: return launch_pass_cfg<512, 8, 2>(DS_ARGS);
+    case 2: return launch_pass_cfg<384, 12, 2>(DS_ARGS);
+    case 3: return launch_pass_cfg<256, 12, 3>(DS_ARGS);
+    default: return launch_pass_cfg<256, 16, 2>(DS_ARGS);
+  }
+#undef DS_ARGS
+}
+
+static PassList make_passes(int kind, uint32_t width) {
+  PassList pl{};
+  if (kind != KIND_FSB) {
+    pl.count = 8;
+    for (int p = 0; p < 8; ++p) {
+      pl.shift[p] = 8 * p;
+      pl.from_lo[p] = 0;
+    }
+    return pl;
+  }
+  int c = 0;
+  if (width > 8) {
+    for (uint32_t b = 0; b < width - 8; ++b) {
+      pl.shift[c] = 8 * b;
+      pl.from_lo[c] = 1;
+      ++c;
+    }
+  }
+  const int hi_bytes = width < 8 ? (int)width : 8;
+  for (int b = 0; b < hi_bytes; ++b) {
+    pl.shift[c] = 64 - 8 * hi_bytes + 8 * b;
+    pl.from_lo[c] = 0;
+    ++c;
+  }
+  pl.count = c;
+  return pl;
+}
+
+template <int KIND>
+static cudaError_t launch_encode(bool has_lo, const void* col, uint32_t width, uint32_t n, bool desc,
+                                 uint64_t* hi, uint16_t* lo, const PassList& pl, uint32_t* ghist,
+                                 cudaStream_t s, uint64_t seed = 0, uint64_t subseq = 0) {
+  const int threads = 512;
+  int blocks = sm_count() * 4;
+  const int need = (n + threads - 1) / threads;
+  if (blocks > need) blocks = need;
+  note_launch();
+  if (has_lo)
+    encode_hist_kernel<KIND, true><<<blocks, threads, 0, s>>>(col, width, n, desc, hi, lo, pl, ghist, seed, subseq);
+  else
+    encode_hist_kernel<KIND, false><<<blocks, threads, 0, s>>>(col, width, n, desc, hi, lo, pl, ghist, seed, subseq);
+  return cudaGetLastError();
+}
+
+ds_status gather_rows_impl(const void* src, uint32_t row_bytes, const uint32_t* idx, uint64_t n,
+                           void* dst, cudaStream_t s);  // gather.cu
+
+static ds_status sort_indices_impl(int kind, const void* col, uint32_t width, uint64_t n64,
+                                   int32_t descending, uint32_t* idx_out, void* sorted_out,
+                                   int32_t options, void* ws, size_t* ws_bytes, void* stream,
+                                   const char* fn, uint64_t seed = 0, uint64_t subseq = 0) {
+  if (n64 > DS_MAX_ROWS) {
+    set_error("%s: n=%llu exceeds DS_MAX_ROWS", fn, (unsigned long long)n64);
+    return DS_ERR_TOO_LARGE;
+  }
+  if (kind == KIND_FSB && (width < 1 || width > DS_MAX_KEY_BYTES)) {
+    set_error("%s: fixed_size_binary key width %u unsupported (1..%d)", fn, width,
+              DS_MAX_KEY_BYTES);
+    return DS_ERR_UNSUPPORTED;
+  }
+  const uint32_t n = static_cast<uint32_t>(n64);
+  const bool has_lo = kind == KIND_FSB && width > 8;
+  const PassList pl = make_passes(kind, width);
+  const int cfg = g_cfg;
+  const uint32_t tiles = (n + cfg_tile(cfg) - 1) / cfg_tile(cfg);
+
+  Workspace w(ws);
+  uint64_t* hi[2] = {w.take<uint64_t>(n), w.take<uint64_t>(n)};
+  uint16_t* lo[2] = {nullptr, nullptr};
+  if (has_lo) {
+    lo[0] = w.take<uint16_t>(n);
+    lo[1] = w.take<uint16_t>(n);
+  }
+  uint32_t* idx_alt = w.take<uint32_t>(n);
+  uint32_t* ctrl = w.take<uint32_t>(MAX_PASSES * RADIX * 2 + 2 * MAX_PASSES);
+  uint32_t* lookback = w.take<uint32_t>(static_cast<size_t>(tiles) * RADIX);
+  ds_status st;
+  if (ws_resolve(w, ws, ws_bytes, fn, &st)) return st;
+  if (n == 0) return DS_OK;
+  if ((col == nullptr && kind != KIND_PHILOX) || idx_out == nullptr) {
+    set_error("%s: col and idx_out must not be NULL", fn);
+    return DS_ERR_INVALID_ARG;
+  }
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  uint32_t* ghist = ctrl;
+  uint32_t* bin_base = ctrl + MAX_PASSES * RADIX;
+  uint32_t* skip = ctrl + 2 * MAX_PASSES * RADIX;
+  uint32_t* tile_counters = skip + MAX_PASSES;
+  const bool desc = descending != 0;
+
+  DS_CUDA(cudaMemsetAsync(ctrl, 0, sizeof(uint32_t) * (MAX_PASSES * RADIX * 2 + 2 * MAX_PASSES), s));
+  cudaError_t e;
+  switch (kind) {
+    case KIND_I64: e = launch_encode<KIND_I64>(has_lo, col, width, n, desc, hi[0], lo[0], pl, ghist, s); break;
+    case KIND_U64: e = launch_encode<KIND_U64>(has_lo, col, width, n, desc, hi[0], lo[0], pl, ghist, s); break;
+    case KIND_F64: e = launch_encode<KIND_F64>(has_lo, col, width, n, desc, hi[0], lo[0], pl, ghist, s); break;
+    case KIND_PHILOX: e = launch_encode<KIND_PHILOX>(false, nullptr, 8, n, false, hi[0], lo[0], pl, ghist, s, seed, subseq); break;
+    default: e = launch_encode<KIND_FSB>(has_lo, col, width, n, desc, hi[0], lo[0], pl, ghist, s); break;
+  }
+  DS_CUDA(e);
+  ds::note_launch(); scan_hist_kernel<<<pl.count, RADIX, 0, s>>>(ghist, n, bin_base, skip);
+  DS_LAUNCH_CHECK();
+
+  uint32_t skip_h[MAX_PASSES] = {0};
+  if (!(options & DS_SORT_NO_PASS_SKIP)) {
+    DS_CUDA(cudaMemcpyAsync(skip_h, skip, sizeof(uint32_t) * pl.count, cudaMemcpyDeviceToHost, s));
+    DS_CUDA(cudaStreamSynchronize(s));  // the one host sync: <= 40 bytes
+  }
+  int exec[MAX_PASSES], ne = 0;
+  for (int p = 0; p < pl.count; ++p)
+    if (!skip_h[p]) exec[ne++] = p;
+
+  int cur = 0;
+  if (ne == 0) {
+    ds::note_launch(); iota_kernel<<<(n + 255) / 256, 256, 0, s>>>(idx_out, n);
+    DS_LAUNCH_CHECK();
+  }
+  const uint32_t* idx_src = nullptr;
+  for (int j = 0; j < ne; ++j) {
+    const int p = exec[j];
+    uint32_t* idx_dst = ((ne - 1 - j) % 2 == 0) ? idx_out : idx_alt;
+    DS_CUDA(cudaMemsetAsync(lookback, 0, sizeof(uint32_t) * static_cast<size_t>(tiles) * RADIX, s));
+    DS_CUDA(launch_pass(cfg, has_lo, pl.from_lo[p] != 0, j == 0, hi[cur], lo[cur], idx_src,
+                        hi[cur ^ 1], lo[cur ^ 1], idx_dst, n, pl.shift[p], bin_base + p * RADIX,
+                        lookback, tile_counters + p, s));
+    idx_src = idx_dst;
+    cur ^= 1;
+  }
+  if (sorted_out != nullptr) {
+    const int threads = 256, blocks = (n + threads - 1) / threads;
+    switch (kind) {
+      case KIND_I64: ds::note_launch(); decode_kernel<KIND_I64><<<blocks, threads, 0, s>>>(hi[cur], lo[cur], width, n, desc, sorted_out); break;
+      case KIND_U64: ds::note_launch(); decode_kernel<KIND_U64><<<blocks, threads, 0, s>>>(hi[cur], lo[cur], width, n, desc, sorted_out); break;
+      case KIND_F64: return gather_rows_impl(col, 8, idx_out, n, sorted_out, s);
+      default: ds::note_launch(); decode_kernel<KIND_FSB><<<blocks, threads, 0, s>>>(hi[cur], lo[cur], width, n, desc, sorted_out); break;
+    }
+    DS_LAUNCH_CHECK();
+  }
+  return DS_OK;
+}
+
+}  // namespace ds
+
+extern "C" {
+
+ds_status ds_sort_indices_i64(const int64_t* col, uint64_t n, int32_t descending, uint32_t* idx_out,
+                              int64_t* sorted_out, int32_t options, void* ws, size_t* ws_bytes,
+                              void* stream) {
+  return ds::sort_indices_impl(ds::KIND_I64, col, 8, n, descending, idx_out, sorted_out, options, ws,
+                               ws_bytes, stream, __func__);
+}
+
+ds_status ds_sort_indices_u64(const uint64_t* col, uint64_t n, int32_t descending, uint32_t* idx_out,
+                              uint64_t* sorted_out, int32_t options, void* ws, size_t* ws_bytes,
+                              void* stream) {
+  return ds::sort_indices_impl(ds::KIND_U64, col, 8, n, descending, idx_out, sorted_out, options, ws,
+                               ws_bytes, stream, __func__);
+}
+
+ds_status ds_sort_indices_f64(const double* col, uint64_t n, int32_t descending, uint32_t* idx_out,
+                              double* sorted_out, int32_t options, void* ws, size_t* ws_bytes,
+                              void* stream) {
+  return ds::sort_indices_impl(ds::KIND_F64, col, 8, n, descending, idx_out, sorted_out, options, ws,
+                               ws_bytes, stream, __func__);
+}
+
+ds_status ds_sort_indices_fsb(const uint8_t* col, uint32_t width, uint64_t n, int32_t descending,
+                              uint32_t* idx_out, uint8_t* sorted_out, int32_t options, void* ws,
+                              size_t* ws_bytes, void* stream) {
+  return ds::sort_indices_impl(ds::KIND_FSB, col, width, n, descending, idx_out, sorted_out, options,
+                               ws, ws_bytes, stream, __func__);
+}
+
+ds_status ds_random_permutation(uint64_t seed, uint64_t subsequence, uint64_t n, uint32_t* perm_out,
+                                void* ws, size_t* ws_bytes, void* stream) {
+  // Philox keys are produced inside the encode kernel (nothing is read from HBM);
+  // colliding 64-bit keys are ordered by row index, which keeps the result a permutation.
+  return ds::sort_indices_impl(ds::KIND_PHILOX, nullptr, 8, n, 0, perm_out, nullptr,
+                               DS_SORT_NO_PASS_SKIP, ws, ws_bytes, stream, __func__, seed,
+                               subsequence);
+}
+
+// Measurement hooks used by bench.py; not part of the reference-facing surface.
+void ds_debug_pass_timing(int32_t enable) { ds::g_timing = enable != 0; }
+
+// Sums the recorded pass-kernel durations (ms) and clears the record.  The caller must
+// have synchronised the stream(s) first.
+int32_t ds_debug_collect_pass_timing(double* total_ms, int32_t* launches) {
+  double tot = 0;
+  int cnt = 0;
+  for (auto& ev : ds::g_events) {
+    float ms = 0;
+    if (cudaEventElapsedTime(&ms, ev.first, ev.second) == cudaSuccess) {
+      tot += ms;
+      ++cnt;
+    }
+    cudaEventDestroy(ev.first);
+    cudaEventDestroy(ev.second);
+  }
+  ds::g_events.clear();
+  if (total_ms) *total_ms = tot;
+  if (launches) *launches = cnt;
+  return 0;
+}
+
+// Tuning hook used by bench.py --sweep; not part of the reference-facing surface.
+int32_t ds_debug_set_radix_config(int32_t cfg) {
+  int old = ds::g_cfg;
+  if (cfg >= 0 && cfg <= 3) ds::g_cfg = cfg;
+  return old;
+}
+
+}  // extern "C"

@@ -1,0 +1,96 @@
+"""A minimal Dataset facade over a BlockList of device blocks.
+
+Only the three operations on the hot path are provided, with the reference's call
+shapes: Dataset.sort (python/ray/data/dataset.py:1714-1754), Dataset.random_shuffle
+(:750-783) and Dataset.groupby (:1321-1353), plus the few inspection helpers the
+reference's tests use (count, take, _block_num_rows, iter_rows, to_arrow).
+"""
+from typing import Any, Dict, List, Optional, Sequence
+
+import pyarrow as pa
+
+from .block import BlockAccessor, BlockList, DeviceArrowBlock
+from .grouped_dataset import GroupedDataset
+from .shuffle_and_partition import DeviceShufflePartitionOp
+from .sort import sort_impl
+
+
+class Dataset:
+    def __init__(self, blocks: BlockList, stats: Optional[Dict[str, Any]] = None):
+        self._blocks = blocks
+        self._stats = stats or {}
+
+    # -- construction ----------------------------------------------------------------
+    @staticmethod
+    def from_arrow(tables: Sequence[pa.Table]) -> "Dataset":
+        if isinstance(tables, pa.Table):
+            tables = [tables]
+        return Dataset(BlockList.from_blocks(list(tables)))
+
+    @staticmethod
+    def from_blocks(blocks: Sequence[DeviceArrowBlock]) -> "Dataset":
+        return Dataset(BlockList.from_blocks(list(blocks)))
+
+    # -- the hot path ------------------------------------------------------------------
+    def sort(self, key: Optional[str] = None, descending: bool = False) -> "Dataset":
+        if self._blocks.initial_num_blocks() == 0:
+            return self
+        if key is None or callable(key):
+            raise ValueError("Table datasets need a column name as sort key")
+        out, stage_info = sort_impl(self._blocks.copy(), False, key, descending)
+        return Dataset(out, {"sort": stage_info})
+
+    def random_shuffle(self, *, seed: Optional[int] = None, num_blocks: Optional[int] = None) -> "Dataset":
+        if self._blocks.initial_num_blocks() == 0:
+            return self
+        n = num_blocks or self._blocks.initial_num_blocks()
+        op = DeviceShufflePartitionOp(None, random_shuffle=True, random_seed=seed)
+        out, stage_info = op.execute(self._blocks.copy(), n, False)
+        return Dataset(out, {"random_shuffle": stage_info})
+
+    def groupby(self, key: Optional[str]) -> GroupedDataset:
+        if key is not None and not isinstance(key, str):
+            raise ValueError("Table datasets can only be grouped by a column name or None")
+        return GroupedDataset(self, key)
+
+    def aggregate(self, *aggs):
+        ret = self.groupby(None).aggregate(*aggs).take(1)
+        return ret[0] if ret else None
+
+    # -- inspection --------------------------------------------------------------------
+    def num_blocks(self) -> int:
+        return self._blocks.initial_num_blocks()
+
+    def _block_num_rows(self) -> List[int]:
+        return [BlockAccessor.for_block(b).num_rows() for b in self._blocks.get_blocks()]
+
+    def count(self) -> int:
+        return sum(self._block_num_rows())
+
+    def get_blocks(self) -> List[DeviceArrowBlock]:
+        return self._blocks.get_blocks()
+
+    def to_arrow(self) -> List[pa.Table]:
+        return [BlockAccessor.for_block(b).to_arrow() for b in self._blocks.get_blocks()]
+
+    def to_arrow_concat(self) -> pa.Table:
+        tabs = [t for t in self.to_arrow() if t.num_columns > 0]
+        return pa.concat_tables(tabs) if tabs else pa.Table.from_pydict({})
+
+    def iter_rows(self):
+        for t in self.to_arrow():
+            for row in t.to_pylist():
+                yield row
+
+    def take(self, limit: int = 20) -> List[dict]:
+        out = []
+        for row in self.iter_rows():
+            out.append(row)
+            if len(out) >= limit:
+                break
+        return out
+
+    def stats(self) -> Dict[str, Any]:
+        """{stage: {"map": [BlockMetadata...], "reduce": [...]}} -- the substage naming of
+        python/ray/data/_internal/stats.py:60-75 (<stage>_map, <stage>_reduce)."""
+        return self._stats

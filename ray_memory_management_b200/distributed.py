@@ -1,0 +1,284 @@
+"""Multi-GPU plans: one process per GPU, the M x N block exchange as an all-to-all-v.
+
+In the reference the exchange between map and reduce tasks is implicit: every reduce
+task lists M object refs and the object manager pulls the chunks
+(python/ray/data/_internal/shuffle.py:106-112, src/ray/object_manager/object_manager.cc:336-559).
+Here every rank holds the input blocks of its position in block order, the partitions a
+rank produces are contiguous slices of one device buffer per column, and the exchange is
+``torch.distributed.all_to_all_single`` with per-peer split sizes -- on the NCCL backend a
+grouped ncclSend/ncclRecv over NVLink -- after a tiny all-gather of the count matrix.
+Receivers get the chunks concatenated in source-rank order, which together with the
+stable partition and the stable sort makes the global result the stable sort of the
+concatenated input (ties keep (rank, row) order), bit-exact to Dataset.sort.
+
+The sort plan sends the key column first and starts the local radix sort of the received
+keys while the 9x larger payload column is still in flight on NCCL's stream.
+
+Only the host logic here (splitters from gathered samples, count matrix, split sizes) is
+backend independent and is what the gloo CPU tests exercise; the compute is CUDA only.
+"""
+import collections
+from typing import List, Optional, Sequence, Tuple
+
+import numpy as np
+import pyarrow as pa
+import torch
+import torch.distributed as dist
+
+SAMPLES_PER_RANK = 2048
+
+
+# ----------------------------------------------------------------------------- host logic
+def exchange_counts(counts: Sequence[int], group=None, device=None) -> np.ndarray:
+    """All-gather of each rank's per-destination row counts -> W x W matrix M with
+    M[src, dst] = rows src sends to dst."""
+    world = dist.get_world_size(group)
+    assert len(counts) == world
+    mine = torch.tensor(list(counts), dtype=torch.int64, device=device)
+    allc = torch.empty(world * world, dtype=torch.int64, device=device)
+    dist.all_gather_into_tensor(allc, mine, group=group)
+    return allc.cpu().numpy().reshape(world, world)
+
+
+def alltoallv_rows(send: torch.Tensor, row_bytes: int, matrix: np.ndarray, group=None,
+                   async_op: bool = False):
+    """Exchange rows of ``row_bytes`` bytes: ``send`` holds this rank's partitions back to
+    back (partition d goes to rank d).  Returns (recv uint8 tensor, work handle or None);
+    recv holds the chunks of ranks 0..W-1 back to back."""
+    rank = dist.get_rank(group)
+    send_rows = [int(x) for x in matrix[rank]]
+    recv_rows = [int(x) for x in matrix[:, rank]]
+    assert send.numel() == sum(send_rows) * row_bytes, (send.numel(), send_rows, row_bytes)
+    recv = torch.empty(sum(recv_rows) * row_bytes, dtype=torch.uint8, device=send.device)
+    work = dist.all_to_all_single(
+        recv, send,
+        output_split_sizes=[r * row_bytes for r in recv_rows],
+        input_split_sizes=[r * row_bytes for r in send_rows],
+        group=group, async_op=async_op,
+    )
+    return recv, work
+
+
+def gather_samples(local: np.ndarray, width: int, group=None, device=None) -> np.ndarray:
+    """All-gather of up to SAMPLES_PER_RANK sampled keys (rows of ``width`` bytes) per
+    rank; ranks may contribute fewer.  Returns the concatenation in rank order."""
+    world = dist.get_world_size(group)
+    k = local.shape[0]
+    buf = np.zeros((SAMPLES_PER_RANK + 1, width), dtype=np.uint8)
+    buf[:k] = local
+    buf[SAMPLES_PER_RANK, : min(width, 4)] = np.frombuffer(np.uint32(k).tobytes(), np.uint8)[: min(width, 4)]
+    cnt = torch.tensor([k], dtype=torch.int64, device=device)
+    cnts = torch.empty(world, dtype=torch.int64, device=device)
+    dist.all_gather_into_tensor(cnts, cnt, group=group)
+    mine = torch.from_numpy(buf[:SAMPLES_PER_RANK].reshape(-1).copy()).to(device)
+    allb = torch.empty(world * mine.numel(), dtype=torch.uint8, device=device)
+    dist.all_gather_into_tensor(allb, mine, group=group)
+    allb = allb.cpu().numpy().reshape(world, SAMPLES_PER_RANK, width)
+    return np.concatenate([allb[r, : int(c)] for r, c in enumerate(cnts.cpu().tolist())], axis=0)
+
+
+def splitters_from_samples(samples: np.ndarray, arrow_type: pa.DataType, world: int) -> list:
+    """Identical W-1 splitters on every rank: sorted samples, nearest-rank quantiles --
+    the reference's rule (python/ray/data/_internal/sort.py:104-115), fed with denser
+    samples (its 10 per block give badly skewed partitions; sample density is not part
+    of its contract)."""
+    from .sort import boundaries_from_samples
+
+    n, w = samples.shape
+    if n == 0:
+        return [None] * (world - 1)
+    buf = pa.py_buffer(np.ascontiguousarray(samples).tobytes())
+    arr = pa.Array.from_buffers(arrow_type, n, [None, buf])
+    return boundaries_from_samples(arr, world)
+
+
+# ----------------------------------------------------------------------------- plans
+def _dev():
+    return torch.device("cuda", torch.cuda.current_device())
+
+
+def _sample_local(block, col: str) -> np.ndarray:
+    from .block import DeviceArrowBlockAccessor
+
+    c = block.column(col) if block.num_rows else None
+    if c is None:
+        return np.zeros((0, 1), dtype=np.uint8)
+    k = min(SAMPLES_PER_RANK, block.num_rows)
+    s = DeviceArrowBlockAccessor(block).sample(k, col)
+    return s.columns[col].data.cpu().numpy().reshape(k, c.row_bytes)
+
+
+def _key_width(block, col, group) -> Tuple[int, pa.DataType]:
+    return block.column(col).row_bytes, block.column(col).type
+
+
+def sort_block(block, key: str, descending: bool = False, group=None):
+    """Dataset.sort across the ranks of ``group``: this rank's input block in, this rank's
+    slice of the globally sorted dataset out (rank order = key order)."""
+    from .block import (DeviceArrowBlock, DeviceArrowBlockAccessor, DeviceColumn, _argsort,
+                        _gather, _take_block)
+
+    world = dist.get_world_size(group)
+    rank = dist.get_rank(group)
+    dev = _dev()
+    width, ktype = _key_width(block, key, group)
+    local = _sample_local(block, key)
+    if local.shape[1] != width:
+        local = np.zeros((0, width), dtype=np.uint8)
+    samples = gather_samples(local, width, group, dev)
+    boundaries = splitters_from_samples(samples, ktype, world)
+    if boundaries and boundaries[0] is None:
+        return block  # globally empty
+    if descending:
+        boundaries.reverse()
+
+    acc = DeviceArrowBlockAccessor(block)
+    sort_key = [(key, "descending" if descending else "ascending")]
+    parts = acc.partition_unsorted(boundaries, sort_key, descending)
+    counts = [p.num_rows for p in parts]
+    matrix = exchange_counts(counts, group, dev)
+    names = block.column_names
+    send = _spanning(parts, names, dev)
+    n_recv = int(matrix[:, rank].sum())
+
+    # keys first; sort them while the payload columns are still being exchanged
+    recv_key, _ = alltoallv_rows(send[key], width, matrix, group)
+    pending = []
+    for name in names:
+        if name == key:
+            continue
+        rb = block.columns[name].row_bytes
+        r, work = alltoallv_rows(send[name], rb, matrix, group, async_op=True)
+        pending.append((name, r, work))
+    keycol = DeviceColumn(ktype, recv_key)
+    idx, sorted_key = _argsort(keycol, descending, want_sorted=True)
+    cols = collections.OrderedDict()
+    got = {}
+    for name, r, work in pending:
+        work.wait()
+        got[name] = _gather(DeviceColumn(block.columns[name].type, r), idx)
+    for name in names:
+        cols[name] = sorted_key if name == key else got[name]
+    return DeviceArrowBlock(cols, n_recv)
+
+
+def _spanning(parts, names, dev):
+    """One send buffer per column holding the partitions back to back."""
+    base = _contiguous_base(parts, names)
+    if base is not None:
+        return base
+    out = {}
+    for name in names:
+        cols = [p.columns[name].data for p in parts if p.num_rows]
+        out[name] = torch.cat(cols) if cols else torch.empty(0, dtype=torch.uint8, device=dev)
+    return out
+
+
+def _contiguous_base(parts, names):
+    """If the partitions are back-to-back views of one storage per column (what
+    partition_unsorted returns), return {name: the spanning tensor} without copying."""
+    live = [p for p in parts if p.num_rows]
+    if not live:
+        return None
+    out = {}
+    for name in names:
+        ts = [p.columns[name].data for p in live]
+        start = ts[0].data_ptr()
+        total = 0
+        for t in ts:
+            if t.data_ptr() != start + total or t.untyped_storage().data_ptr() != ts[0].untyped_storage().data_ptr():
+                return None
+            total += t.numel()
+        off = ts[0].storage_offset()
+        out[name] = torch.as_strided(ts[0], (total,), (1,), off)
+    return out
+
+
+def random_shuffle_block(block, seed: Optional[int], group=None):
+    """Dataset.random_shuffle across ranks, structured as the reference's op
+    (python/ray/data/_internal/shuffle_and_partition.py:29-97): permute locally with
+    seed+rank, cut into W slices of ceil(n/W) rows, rotate which slice goes where with a
+    RandomState(seed+rank) list shuffle, exchange, permute the received rows with seed."""
+    import math
+
+    from .block import DeviceArrowBlock, DeviceArrowBlockAccessor, DeviceColumn
+
+    world = dist.get_world_size(group)
+    rank = dist.get_rank(group)
+    dev = _dev()
+    seed_i = seed + rank if seed is not None else None
+    shuffled = DeviceArrowBlockAccessor(block).random_shuffle(seed_i) if block.num_rows else block
+    n = shuffled.num_rows
+    slice_sz = max(1, math.ceil(n / world))
+    slices = [(min(i * slice_sz, n), min((i + 1) * slice_sz, n)) for i in range(world)]
+    order = list(range(world))
+    np.random.RandomState(seed_i).shuffle(order)  # slice order[d] goes to rank d
+    counts = [slices[order[d]][1] - slices[order[d]][0] for d in range(world)]
+    matrix = exchange_counts(counts, group, dev)
+    cols = collections.OrderedDict()
+    for name, c in shuffled.columns.items():
+        rb = c.row_bytes
+        send = torch.cat([c.data[slices[order[d]][0] * rb: slices[order[d]][1] * rb] for d in range(world)])
+        recv, _ = alltoallv_rows(send, rb, matrix, group)
+        cols[name] = DeviceColumn(c.type, recv)
+    out = DeviceArrowBlock(cols, int(matrix[:, rank].sum()))
+    # every reducer permutes with the same seed in the reference (:86-89); the
+    # subsequence keeps the streams of different ranks apart without changing that contract
+    return DeviceArrowBlockAccessor(out).random_shuffle(seed) if out.num_rows else out
+
+
+def groupby_block(block, key: str, aggs, group=None):
+    """groupby(key).aggregate(*aggs) across ranks (python/ray/data/grouped_dataset.py:24-68):
+    local sort + combine, range-partition the partial rows, exchange, merge + finalize."""
+    from .block import DeviceArrowBlock, DeviceArrowBlockAccessor, DeviceColumn, PartialAggBlock, _searchsorted
+
+    world = dist.get_world_size(group)
+    rank = dist.get_rank(group)
+    dev = _dev()
+    width, ktype = _key_width(block, key, group)
+    samples = gather_samples(_sample_local(block, key), width, group, dev)
+    boundaries = splitters_from_samples(samples, ktype, world)
+    acc = DeviceArrowBlockAccessor(block)
+    if boundaries and boundaries[0] is None:
+        return DeviceArrowBlock.empty()
+    sorted_blk = acc.sort_and_partition([], [(key, "ascending")], False)[0] if block.num_rows else block
+    partial = DeviceArrowBlockAccessor(sorted_blk).combine(key, aggs)
+    if partial.num_rows:
+        bounds = _searchsorted(partial.columns[key], boundaries, False)
+    else:
+        bounds = [0] * (world - 1)
+    edges = [0] + bounds + [partial.num_rows]
+    counts = [edges[i + 1] - edges[i] for i in range(world)]
+    matrix = exchange_counts(counts, group, dev)
+    names = _partial_names(key, aggs, block)
+    cols = collections.OrderedDict()
+    for name, t in names:
+        c = partial.columns.get(name)
+        send = c.data if c is not None else torch.empty(0, dtype=torch.uint8, device=dev)
+        recv, _ = alltoallv_rows(send, 8, matrix, group)
+        cols[name] = DeviceColumn(t, recv)
+    n_recv = int(matrix[:, rank].sum())
+    # received chunks are key-sorted per source and concatenated in rank order: hand them
+    # to the merge as W blocks so that it sorts them stably by key
+    chunks, off = [], 0
+    for src in range(world):
+        r = int(matrix[src, rank])
+        if r:
+            chunks.append(PartialAggBlock(collections.OrderedDict(
+                (nm, cc.slice(off, off + r)) for nm, cc in cols.items()), r))
+        off += r
+    out, _ = DeviceArrowBlockAccessor.aggregate_combined_blocks(chunks, key, aggs, finalize=True)
+    return out
+
+
+def _partial_names(key, aggs, block) -> List[Tuple[str, pa.DataType]]:
+    """Column layout of a combined block (needed on ranks whose partial block is empty):
+    counts are int64, sum/min/max parts have the value column's type."""
+    from .block import resolve_agg_names
+
+    out = [(key, block.column(key).type)]
+    for name, agg in zip(resolve_agg_names(aggs), aggs):
+        for part in agg._device_merge_ops():
+            t = pa.int64() if part == "count" else block.column(agg._key_fn).type
+            out.append((f"{name}#{part}", t))
+    return out

@@ -1,0 +1,96 @@
+"""groupby().aggregate() on device blocks.
+
+Mirrors python/ray/data/grouped_dataset.py:24-68 (the op) and :118-154 (the driver
+lines of GroupedDataset.aggregate) of the reference: range partition by sampled
+boundaries, per-partition combine on the map side, merge + finalize on the reduce side.
+"""
+from typing import List, Optional, Tuple, Union
+
+from . import sort
+from .aggregate import AggregateFn, Count, Max, Mean, Min, Sum
+from .block import Block, BlockAccessor, BlockExecStats, BlockList, BlockMetadata
+from .context import DatasetContext
+from .shuffle import DeviceShufflePlan, ShuffleOp
+
+
+class _GroupbyOp(ShuffleOp):
+    @staticmethod
+    def map(idx: int, block: Block, output_num_blocks: int, boundaries: List,
+            key: Optional[str], aggs: Tuple[AggregateFn]) -> List[Union[BlockMetadata, Block]]:
+        """Partition the block and combine rows with the same key."""
+        stats = BlockExecStats.builder()
+        acc = BlockAccessor.for_block(block)
+        if key is None:
+            partitions = [acc.to_block()]
+        else:
+            partitions = acc.sort_and_partition(
+                boundaries, [(key, "ascending")] if isinstance(key, str) else key, descending=False
+            )
+        parts = [BlockAccessor.for_block(p).combine(key, aggs) for p in partitions]
+        meta = acc.get_metadata(input_files=None, exec_stats=stats.build())
+        return parts + [meta]
+
+    @staticmethod
+    def reduce(key: Optional[str], aggs: Tuple[AggregateFn], *mapper_outputs: List[Block],
+               partial_reduce: bool = False) -> (Block, BlockMetadata):
+        """Aggregate sorted and partially combined blocks."""
+        return BlockAccessor.for_block(mapper_outputs[0]).aggregate_combined_blocks(
+            list(mapper_outputs), key, aggs, finalize=not partial_reduce
+        )
+
+
+class DeviceGroupbyOp(_GroupbyOp, DeviceShufflePlan):
+    pass
+
+
+def aggregate_impl(blocks: BlockList, clear_input_blocks: bool, key: Optional[str],
+                   aggs: Tuple[AggregateFn]):
+    """do_agg of the reference (grouped_dataset.py:118-154)."""
+    stage_info = {}
+    if len(aggs) == 0:
+        raise ValueError("Aggregate requires at least one aggregation")
+    if blocks.initial_num_blocks() == 0:
+        return blocks, stage_info
+    num_mappers = blocks.initial_num_blocks()
+    num_reducers = num_mappers
+    if key is None:
+        num_reducers = 1
+        boundaries = []
+    else:
+        boundaries = sort.sample_boundaries(
+            blocks.get_blocks(), [(key, "ascending")] if isinstance(key, str) else key, num_reducers
+        )
+    DatasetContext.get_current()  # plan selection point (grouped_dataset.py:142-146)
+    op = DeviceGroupbyOp(map_args=[boundaries, key, aggs], reduce_args=[key, aggs])
+    return op.execute(blocks, num_reducers, clear_input_blocks)
+
+
+class GroupedDataset:
+    """python/ray/data/grouped_dataset.py:71-161."""
+
+    def __init__(self, dataset, key: Optional[str]):
+        self._dataset = dataset
+        self._key = key
+
+    def aggregate(self, *aggs: AggregateFn):
+        from .dataset import Dataset
+
+        for agg in aggs:
+            agg._validate(self._dataset)
+        out, stats = aggregate_impl(self._dataset._blocks.copy(), False, self._key, aggs)
+        return Dataset(out, {"aggregate": stats})
+
+    def count(self):
+        return self.aggregate(Count())
+
+    def sum(self, on: str):
+        return self.aggregate(Sum(on))
+
+    def min(self, on: str):
+        return self.aggregate(Min(on))
+
+    def max(self, on: str):
+        return self.aggregate(Max(on))
+
+    def mean(self, on: str):
+        return self.aggregate(Mean(on))

@@ -1,0 +1,120 @@
+"""Dataset.sort on device blocks: splitter sampling, the sort op, sort_impl.
+
+Mirrors python/ray/data/_internal/sort.py:41-158 of the reference.  Differences that
+do not change the observable result (the concatenated output is the
+global stable sort of the concatenated input):
+  * the map side only range-partitions (stable), the reduce side sorts once; the
+    reference sorts on both sides (sort.py:52-54 and :67-69).
+  * samples are drawn by a Philox-stratified kernel instead of random.sample.
+"""
+from typing import Any, Callable, List, Tuple, TypeVar, Union
+
+import numpy as np
+import pyarrow as pa
+
+from .block import (
+    Block,
+    BlockAccessor,
+    BlockExecStats,
+    BlockList,
+    BlockMetadata,
+    DeviceArrowBlock,
+    _key_kind,
+)
+from .context import DatasetContext
+from .shuffle import DeviceShufflePlan, ShuffleOp
+
+T = TypeVar("T")
+SortKeyT = Union[None, List[Tuple[str, str]], Callable[[T], Any]]
+
+
+class _SortOp(ShuffleOp):
+    @staticmethod
+    def map(idx: int, block: Block, output_num_blocks: int, boundaries: List[T], key: SortKeyT,
+            descending: bool) -> List[Union[BlockMetadata, Block]]:
+        stats = BlockExecStats.builder()
+        acc = BlockAccessor.for_block(block)
+        out = acc.partition_unsorted(boundaries, key, descending)
+        meta = acc.get_metadata(input_files=None, exec_stats=stats.build())
+        return out + [meta]
+
+    @staticmethod
+    def reduce(key: SortKeyT, descending: bool, *mapper_outputs: List[Block],
+               partial_reduce: bool = False) -> (Block, BlockMetadata):
+        return BlockAccessor.for_block(mapper_outputs[0]).merge_sorted_blocks(
+            mapper_outputs, key, descending
+        )
+
+
+class DeviceSortOp(_SortOp, DeviceShufflePlan):
+    pass
+
+
+def nearest_rank_positions(num_samples: int, num_reducers: int) -> List[int]:
+    """Positions np.quantile(sorted, q, interpolation="nearest") picks for
+    q in linspace(0, 1, R), first dropped (sort.py:110-115): round-half-even of
+    q * (n - 1)."""
+    qs = np.linspace(0, 1, num_reducers)
+    return [int(np.around((num_samples - 1) * q)) for q in qs][1:]
+
+
+def boundaries_from_samples(samples: pa.Array, num_reducers: int) -> list:
+    """Driver-side half of sample_boundaries (sort.py:104-115): sort the <= 10*R sampled
+    keys on the host and take nearest-rank quantiles."""
+    n = len(samples)
+    if n == 0:
+        return [None] * (num_reducers - 1)
+    t = samples.type
+    if pa.types.is_fixed_size_binary(t):
+        w = t.byte_width
+        raw = np.frombuffer(samples.buffers()[1], dtype=np.uint8)[samples.offset * w : (samples.offset + n) * w]
+        rows = raw.reshape(n, w)
+        order = np.lexsort(tuple(rows[:, j] for j in range(w - 1, -1, -1)))
+        srt = rows[order]
+        return [srt[i].tobytes() for i in nearest_rank_positions(n, num_reducers)]
+    srt = np.sort(samples.to_numpy(zero_copy_only=False))
+    return [srt[i] for i in nearest_rank_positions(n, num_reducers)]
+
+
+def sample_boundaries(blocks: List[Block], key: SortKeyT, num_reducers: int) -> List[T]:
+    """Return (num_reducers - 1) items in ascending order that split the key domain
+    into ranges of about equally many rows (sort.py:80-115)."""
+    if isinstance(key, list) and len(key) > 1:
+        raise ValueError("Multiple boundary sampling keys not supported.")
+    n_samples = int(num_reducers * 10 / len(blocks))
+    samples = [_sample_block(block, n_samples, key) for block in blocks]
+    samples = [s for s in samples if s.num_rows > 0]
+    if len(samples) == 0:
+        return [None] * (num_reducers - 1)
+    column = key[0][0] if isinstance(key, list) else key
+    host = pa.concat_tables([s.to_arrow() for s in samples])[column].combine_chunks()
+    return boundaries_from_samples(host, num_reducers)
+
+
+def sort_impl(blocks: BlockList, clear_input_blocks: bool, key: SortKeyT,
+              descending: bool = False) -> Tuple[BlockList, dict]:
+    """sort.py:120-154."""
+    stage_info = {}
+    blocks_list = blocks.get_blocks()
+    if len(blocks_list) == 0:
+        return BlockList([], []), stage_info
+
+    if isinstance(key, str):
+        key = [(key, "descending" if descending else "ascending")]
+    if isinstance(key, list):
+        descending = key[0][1] == "descending"
+
+    num_mappers = len(blocks_list)
+    num_reducers = num_mappers  # same number of output partitions (sort.py:134-136)
+    boundaries = sample_boundaries(blocks_list, key, num_reducers)
+    if descending:
+        boundaries.reverse()
+    del blocks_list
+
+    DatasetContext.get_current()  # plan selection point (sort.py:142-146): device plan only
+    sort_op = DeviceSortOp(map_args=[boundaries, key, descending], reduce_args=[key, descending])
+    return sort_op.execute(blocks, num_reducers, clear_input_blocks)
+
+
+def _sample_block(block: Block, n_samples: int, key: SortKeyT) -> DeviceArrowBlock:
+    return BlockAccessor.for_block(block).sample(n_samples, key)

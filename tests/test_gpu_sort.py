@@ -1,0 +1,278 @@
+"""GPU parity: Dataset.sort / sort_and_partition / merge_sorted_blocks through the C ABI,
+against the oracle (seeded inputs) and the golden vectors recorded from the reference."""
+import ctypes
+import random
+
+import numpy as np
+import pyarrow as pa
+import pyarrow.compute  # noqa: F401
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+torch = pytest.importorskip("torch")
+
+
+@pytest.fixture(scope="module")
+def ds():
+    if not torch.cuda.is_available():
+        pytest.skip("no CUDA device")
+    import ray_memory_management_b200 as m
+
+    return m
+
+
+from oracle import datasets_oracle as O  # noqa: E402
+
+
+def _tabs(cuts, **cols):
+    return [pa.table({k: v[a:b] for k, v in cols.items()}) for a, b in cuts]
+
+
+def _argsort_c(ds, col_np, kind, descending, width=0, options=0, want_sorted=True):
+    """Direct C-ABI call of ds_sort_indices_* on a numpy column."""
+    lib = ds._lib
+    n = len(col_np) if kind != "fsb" else col_np.shape[0]
+    dev = torch.from_numpy(np.ascontiguousarray(col_np).view(np.uint8).reshape(-1).copy()).cuda()
+    idx = torch.empty(n, dtype=torch.int32, device="cuda")
+    out = torch.empty(dev.numel(), dtype=torch.uint8, device="cuda")
+    stream = torch.cuda.current_stream().cuda_stream
+    optr = out.data_ptr() if want_sorted else None
+    if kind == "fsb":
+        args = (dev.data_ptr(), width, n, int(descending), idx.data_ptr(), optr, options)
+    else:
+        args = (dev.data_ptr(), n, int(descending), idx.data_ptr(), optr, options)
+    ws = lib.call_ws(f"ds_sort_indices_{kind}", lambda b: torch.empty(b, dtype=torch.uint8, device="cuda"),
+                     *args, stream=stream)
+    torch.cuda.synchronize()
+    del ws
+    return idx.cpu().numpy().view(np.uint32), out.cpu().numpy()
+
+
+@pytest.mark.parametrize("name", ["unique", "ties"])
+@pytest.mark.parametrize("desc", [False, True])
+def test_sort_int64_golden(ds, golden, name, desc):
+    g = golden("sort_int64")
+    keys = g[f"{name}_keys"]
+    tabs = _tabs(g["block_cuts"], value=np.arange(len(keys), dtype=np.int64), key=keys)
+    random.seed(0)
+    out = ds.Dataset.from_arrow(tabs).sort("key", descending=desc)
+    assert out.num_blocks() == len(tabs)
+    got = out.to_arrow_concat()
+    assert np.array_equal(got["value"].to_numpy(), g[f"{name}_{'desc' if desc else 'asc'}_value_order"])
+    assert got.schema == tabs[0].schema
+    # a key value never spans two output blocks (sort.py:118-119 of the reference)
+    seen = set()
+    for t in out.to_arrow():
+        ks = set(t["key"].to_pylist()) if t.num_rows else set()
+        assert not (ks & seen)
+        seen |= ks
+
+
+@pytest.mark.parametrize("name", ["uniform", "ties"])
+@pytest.mark.parametrize("desc", [False, True])
+def test_sort_graysort_golden(ds, golden, name, desc):
+    g = golden("sort_graysort")
+    keys = g[f"{name}_keys"]
+    base = O.graysort_table(len(keys), seed=11)
+    t = pa.table({"key": O.fsb_from_numpy(keys), "payload": base["payload"]})
+    tabs = [t.slice(a, b - a) for a, b in g["block_cuts"]]
+    got = ds.Dataset.from_arrow(tabs).sort("key", descending=desc).to_arrow_concat()
+    rowid = O.fsb_to_numpy(got["payload"])[:, :8].copy().view("<u8").ravel()
+    assert np.array_equal(rowid, g[f"{name}_{'desc' if desc else 'asc'}_rowid_order"])
+    assert got.equals(O.global_stable_sort(tabs, "key", desc))
+
+
+@pytest.mark.parametrize("desc", [False, True])
+def test_sort_and_partition_golden(ds, golden, desc):
+    g = golden("partition")
+    keys = g["keys"]
+    t = pa.table({"key": keys, "value": np.arange(len(keys), dtype=np.int64)})
+    tag = "desc" if desc else "asc"
+    key = [("key", "descending" if desc else "ascending")]
+    parts = ds.BlockAccessor.for_block(t).sort_and_partition(list(g[f"{tag}_boundaries"]), key, desc)
+    assert [p.num_rows for p in parts] == list(g[f"{tag}_sizes"])
+    cat = pa.concat_tables([p.to_arrow() for p in parts])
+    assert np.array_equal(cat["value"].to_numpy(), g[f"{tag}_value_order"])
+    # the unsorted stable partition used by the device plan obeys the same rule
+    parts_u = ds.BlockAccessor.for_block(t).partition_unsorted(list(g[f"{tag}_boundaries"]), key, desc)
+    assert [p.num_rows for p in parts_u] == list(g[f"{tag}_sizes"])
+    for pu, ps in zip(parts_u, parts):
+        if pu.num_rows:
+            v = pu.to_arrow()["value"].to_numpy()
+            assert np.all(np.diff(v) > 0)  # input order kept inside a partition
+            assert np.array_equal(np.sort(v), np.sort(ps.to_arrow()["value"].to_numpy()))
+
+
+def test_merge_sorted_blocks_golden(ds, golden):
+    g = golden("partition")
+    keys = g["keys"]
+    t = pa.table({"key": keys, "value": np.arange(len(keys), dtype=np.int64)})
+    key = [("key", "ascending")]
+    blocks = [
+        ds.BlockAccessor.for_block(t.slice(a, b - a)).sort_and_partition([], key, False)[0]
+        for a, b in g["merge_cuts"]
+    ]
+    merged, meta = ds.DeviceArrowBlockAccessor.merge_sorted_blocks(blocks, key, False)
+    assert np.array_equal(merged.to_arrow()["value"].to_numpy(), g["merge_value_order"])
+    assert meta.num_rows == len(keys) and meta.size_bytes == 16 * len(keys)
+
+
+def test_empty_block_contracts(ds):
+    # test_sort.py:110-127 of the reference
+    empty = ds.DeviceArrowBlock.empty()
+    acc = ds.BlockAccessor.for_block(empty)
+    assert acc.sample(10, "A").num_rows == 0
+    parts = acc.sort_and_partition([1, 5, 10], "A", descending=False)
+    assert len(parts) == 4 and all(p.num_rows == 0 for p in parts)
+    assert acc.merge_sorted_blocks([empty], "A", False)[0].num_rows == 0
+    # empty dataset: boundaries are [None]*(R-1) and the sort has no rows
+    e = pa.table({"value": pa.array([], pa.int64())})
+    assert ds.sample_boundaries([ds.DeviceArrowBlock.from_arrow(e)] * 3, [("value", "ascending")], 3) == [None, None]
+    out = ds.Dataset.from_arrow([e, e, e]).sort("value")
+    assert out.count() == 0
+    assert ds.Dataset.from_arrow([]).sort("value").count() == 0
+
+
+def test_sort_with_empty_and_ragged_blocks(ds):
+    rng = np.random.default_rng(3)
+    sizes = [0, 1, 4097, 0, 33, 70000]
+    tabs, base = [], 0
+    for s in sizes:
+        tabs.append(pa.table({"key": rng.integers(-50, 50, s, dtype=np.int64),
+                              "value": np.arange(base, base + s, dtype=np.int64)}))
+        base += s
+    for desc in (False, True):
+        got = ds.Dataset.from_arrow(tabs).sort("key", descending=desc).to_arrow_concat()
+        assert got.equals(O.global_stable_sort(tabs, "key", desc))
+
+
+def test_reference_test_sort_arrow(ds):
+    # test_sort.py:55-97 of the reference (int key; the string column is carried as
+    # fixed_size_binary(3) payload and also used as a memcmp key)
+    for num_items, parallelism in ((100, 1), (1000, 4)):
+        a = list(reversed(range(num_items)))
+        b = [f"{x:03}".encode() for x in range(num_items)]
+        shard = int(np.ceil(num_items / parallelism))
+        tabs = []
+        for off in range(0, num_items, shard):
+            tabs.append(pa.table({"a": pa.array(a[off:off + shard], pa.int64()),
+                                  "b": pa.array(b[off:off + shard], pa.binary(3))}))
+        d = ds.Dataset.from_arrow(tabs)
+
+        def rows(x):
+            return [(r["a"], r["b"]) for r in x.iter_rows()]
+
+        assert rows(d.sort(key="a")) == list(zip(reversed(a), reversed(b)))
+        assert len([n for n in d.sort(key="a")._block_num_rows() if n > 0]) == parallelism
+        assert rows(d.sort(key="b")) == list(zip(a, b))
+        assert rows(d.sort(key="a", descending=True)) == list(zip(a, b))
+
+
+def test_same_key_to_same_block(ds):
+    # test_sort.py:37-52 of the reference
+    tabs = [pa.table({"x": np.ones(1, dtype=np.int64)}) for _ in range(100)]
+    out = ds.Dataset.from_arrow(tabs).sort("x")
+    nr = out._block_num_rows()
+    assert len(nr) == 100 and sum(1 for x in nr if x > 0) == 1 and sum(nr) == 100
+
+
+@pytest.mark.parametrize("kind", ["i64", "u64", "f64"])
+@pytest.mark.parametrize("desc", [False, True])
+@pytest.mark.parametrize("n", [1, 31, 4096, 4097, 100_003])
+def test_argsort_c_abi_64bit(ds, kind, desc, n):
+    rng = np.random.default_rng(n)
+    if kind == "i64":
+        col = rng.integers(-(2**63), 2**63 - 1, n, dtype=np.int64)
+        col[::7] = col[0]
+    elif kind == "u64":
+        col = rng.integers(0, 2**64 - 1, n, dtype=np.uint64)
+        col[::5] = 2**63
+    else:
+        col = rng.standard_normal(n) * 1e3
+        col[::11] = 0.0
+        col[1::11] = -0.0
+        if n > 40:
+            col[3], col[17], col[29], col[5] = np.nan, np.inf, -np.inf, -np.nan
+    idx, srt = _argsort_c(ds, col, kind, desc)
+    order = "descending" if desc else "ascending"
+    want = pa.compute.sort_indices(pa.table({"k": col}), sort_keys=[("k", order)]).to_numpy()
+    assert np.array_equal(idx.astype(np.int64), want)
+    assert np.array_equal(srt.view(col.dtype), col[want], equal_nan=True)
+    # the no-host-sync variant gives the same answer
+    idx2, _ = _argsort_c(ds, col, kind, desc, options=ds._lib.DS_SORT_NO_PASS_SKIP, want_sorted=False)
+    assert np.array_equal(idx, idx2)
+
+
+@pytest.mark.parametrize("width", [1, 2, 3, 7, 8, 9, 10])
+@pytest.mark.parametrize("desc", [False, True])
+def test_argsort_c_abi_fsb(ds, width, desc):
+    n = 50_001
+    rng = np.random.default_rng(width)
+    col = rng.integers(0, 256, (n, width), dtype=np.uint8)
+    col[:, : max(0, width - 2)] &= 1  # plenty of ties in the leading bytes
+    idx, srt = _argsort_c(ds, col, "fsb", desc, width=width)
+    arr = O.fsb_from_numpy(col)
+    order = "descending" if desc else "ascending"
+    want = pa.compute.sort_indices(pa.table({"k": arr}), sort_keys=[("k", order)]).to_numpy()
+    assert np.array_equal(idx.astype(np.int64), want)
+    assert np.array_equal(srt.reshape(n, width), col[want])
+
+
+def test_pass_skipping_constant_bytes(ds):
+    # keys in [0, 2^20): five of the eight digit positions are constant and skipped
+    rng = np.random.default_rng(0)
+    col = rng.integers(0, 1 << 20, 300_000, dtype=np.int64)
+    idx, srt = _argsort_c(ds, col, "i64", False)
+    want = np.argsort(col, kind="stable")
+    assert np.array_equal(idx.astype(np.int64), want)
+    # all-equal column: every pass is skipped
+    col = np.full(10_000, -7, dtype=np.int64)
+    idx, srt = _argsort_c(ds, col, "i64", True)
+    assert np.array_equal(idx, np.arange(10_000, dtype=np.uint32))
+    assert np.array_equal(srt.view(np.int64), col)
+
+
+def test_errors(ds):
+    lib = ds._lib
+    need = ctypes.c_size_t(0)
+    st = lib.lib.ds_sort_indices_fsb(None, 11, 10, 0, None, None, 0, None, ctypes.byref(need), None)
+    assert st == lib.DS_ERR_UNSUPPORTED and b"width" in lib.lib.ds_last_error()
+    st = lib.lib.ds_sort_indices_i64(None, 1 << 31, 0, None, None, 0, None, ctypes.byref(need), None)
+    assert st == lib.DS_ERR_TOO_LARGE
+    t = pa.table({"a": np.arange(4, dtype=np.int64), "b": np.arange(4, dtype=np.int64)})
+    with pytest.raises(NotImplementedError):
+        ds.BlockAccessor.for_block(t).sort_and_partition([], [("a", "ascending"), ("b", "ascending")], False)
+    with pytest.raises(ValueError):
+        ds.sample_boundaries([ds.DeviceArrowBlock.from_arrow(t)], [("a", "ascending"), ("b", "ascending")], 2)
+    with pytest.raises(NotImplementedError):
+        ds.DeviceArrowBlock.from_arrow(pa.table({"a": pa.array([1, None], pa.int64())}))
+
+
+def test_large_graysort_properties(ds):
+    """4M records (400 MB): sortedness, permutation and stability checked on device
+    without the oracle's O(n log n) host sort of the payload."""
+    n = 4_000_000
+    g = torch.Generator(device="cuda").manual_seed(1)
+    keys = torch.randint(0, 256, (n, 10), dtype=torch.uint8, device="cuda", generator=g)
+    keys[:, :6] = 0  # 4 random bytes over 4M rows -> many ties
+    keys[:, 6] &= 0x0F
+    payload = torch.zeros((n, 90), dtype=torch.uint8, device="cuda")
+    payload[:, :8] = torch.arange(n, device="cuda", dtype=torch.int64).view(torch.uint8).view(n, 8)
+    import collections
+
+    blk = ds.DeviceArrowBlock(collections.OrderedDict(
+        key=ds.DeviceColumn(pa.binary(10), keys.reshape(-1)),
+        payload=ds.DeviceColumn(pa.binary(90), payload.reshape(-1))), n)
+    out = ds.Dataset.from_blocks([blk]).sort("key").get_blocks()[0]
+    k = out.columns["key"].data.view(n, 10).to(torch.int64)
+    composite = torch.zeros(n, dtype=torch.int64, device="cuda")
+    for j in range(6, 10):
+        composite = composite * 256 + k[:, j]
+    rowid = out.columns["payload"].data.view(n, 90)[:, :8].contiguous().view(torch.int64).view(n)
+    assert bool((composite[1:] >= composite[:-1]).all())
+    tie = composite[1:] == composite[:-1]
+    assert bool((rowid[1:][tie] > rowid[:-1][tie]).all())  # stable
+    assert bool((torch.sort(rowid).values == torch.arange(n, device="cuda")).all())
+    # key bytes travelled with their rows
+    assert bool((keys[rowid] == out.columns["key"].data.view(n, 10)).all())
