@@ -169,6 +169,32 @@ ds_status ds_random_permutation(uint64_t seed, uint64_t subsequence, uint64_t n,
 ds_status ds_segment_heads_i64(const int64_t* sorted_keys, uint64_t n, uint32_t* seg_starts_out,
                                uint32_t* nseg_out, void* ws, size_t* ws_bytes, void* stream);
 
+/* Same result as ds_segment_heads_i64, for callers that cannot hand over a workspace
+ * because they cannot allocate device memory at the point of the call: a reduce task
+ * running inside a host runtime whose HBM is fully owned by its own pool, a binding
+ * (ctypes / cgo / JNI) that has the input and output buffers but no allocator handle,
+ * or a worker that has planned its HBM to the last block and must not see an
+ * unplanned cudaMalloc fail or stall the device.  This entry point has no counterpart
+ * in the reference.
+ *   - scratch (one counter per 2048 keys) is a fixed array inside the library image,
+ *     so n is limited to DS_SEGMENT_HEADS_STATIC_MAX_ROWS; larger n is rejected with
+ *     DS_ERR_TOO_LARGE.  Each GPU that loads the library holds the array (~256 KiB)
+ *     until the process exits.
+ *   - the call makes no cudaMalloc / cudaFree and calls no allocating routine.
+ *   - the first call on a device looks up the array's device address (a one-time
+ *     set-up step with that device current); make that first call before any stream
+ *     capture begins.
+ *   - all calls on a device share the one array and find it as the previous call
+ *     left it; nothing in it needs clearing (every counter is rewritten before it is
+ *     read).  Two calls whose kernels overlap on the GPU (different streams, no
+ *     ordering between them) race on it: serialise them.
+ *   seg_starts_out  capacity n+1 uint32; entry nseg is set to n
+ *   nseg_out        one uint32 (device) */
+#define DS_SEGMENT_HEADS_STATIC_MAX_ROWS (1u << 27)
+ds_status ds_segment_heads_i64_static(const int64_t* sorted_keys, uint64_t n,
+                                      uint32_t* seg_starts_out, uint32_t* nseg_out,
+                                      void* stream);
+
 /* Per-run reduction of a value column that is still in INPUT order: run s reduces
  * vals[idx[i]] for i in [seg_starts[s], seg_starts[s+1]).  idx may be NULL (values
  * already in sorted order).  Replaces pyarrow.compute.sum/min/max on a group slice

@@ -345,3 +345,76 @@ ds_status ds_finalize_mean(const void* sum, int32_t sum_is_i64, const int64_t* c
 }
 
 }  // extern "C"
+
+// ------------------------------------------------------------------ no-allocation variant
+// ds_segment_heads_i64_static: the same three kernels as ds_segment_heads_i64, but the
+// per-tile head counts live in a fixed array that is part of the loaded module instead
+// of a caller-provided workspace.  Every GPU that loads this library carries the array
+// (DS_SEGMENT_HEADS_STATIC_MAX_ROWS / 2048 + 1 counters, about 256 KiB) until the
+// process exits.
+namespace ds {
+
+constexpr uint32_t HEADS_STATIC_TILES = DS_SEGMENT_HEADS_STATIC_MAX_ROWS / SEG_TILE;
+static __device__ __align__(256) uint32_t g_heads_scratch[HEADS_STATIC_TILES + 1];
+
+// In host code `g_heads_scratch` is only a handle for the runtime, not an address a
+// kernel can use, so the device address is looked up once per device (with that
+// device current) and cached.
+static ds_status heads_scratch_address(uint32_t** out, const char* fn) {
+  static uint32_t* cached[64] = {nullptr};
+  int dev = 0;
+  DS_CUDA(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= 64) {
+    set_error("%s: device ordinal %d out of range", fn, dev);
+    return DS_ERR_UNSUPPORTED;
+  }
+  if (cached[dev] == nullptr) {
+    void* p = nullptr;
+    cudaError_t e = cudaGetSymbolAddress(&p, g_heads_scratch);
+    if (e != cudaSuccess || p == nullptr) {
+      set_error("%s: cudaGetSymbolAddress failed: %s", fn, cudaGetErrorString(e));
+      return DS_ERR_CUDA;
+    }
+    cached[dev] = static_cast<uint32_t*>(p);
+  }
+  *out = cached[dev];
+  return DS_OK;
+}
+
+}  // namespace ds
+
+extern "C" ds_status ds_segment_heads_i64_static(const int64_t* sorted_keys, uint64_t n64,
+                                                 uint32_t* seg_starts_out, uint32_t* nseg_out,
+                                                 void* stream) {
+  using namespace ds;
+  if (n64 > DS_SEGMENT_HEADS_STATIC_MAX_ROWS) {
+    set_error("%s: n=%llu exceeds DS_SEGMENT_HEADS_STATIC_MAX_ROWS=%u; use "
+              "ds_segment_heads_i64 with a caller workspace for larger columns",
+              __func__, (unsigned long long)n64, (unsigned)DS_SEGMENT_HEADS_STATIC_MAX_ROWS);
+    return DS_ERR_TOO_LARGE;
+  }
+  if (!seg_starts_out || !nseg_out || (n64 > 0 && !sorted_keys)) {
+    set_error("%s: NULL pointer", __func__);
+    return DS_ERR_INVALID_ARG;
+  }
+  uint32_t* tile_counts = nullptr;
+  ds_status st = heads_scratch_address(&tile_counts, __func__);
+  if (st != DS_OK) return st;
+  const uint32_t n = static_cast<uint32_t>(n64);
+  const uint32_t tiles = (n + SEG_TILE - 1) / SEG_TILE;
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  // Nothing in the array has to start at zero: head_count_kernel overwrites entries
+  // [0, tiles) before tile_scan_kernel and head_write_kernel read them, and entries
+  // beyond `tiles` (left over from an earlier, larger call) are never read.
+  if (n > 0) {
+    ds::note_launch(); head_count_kernel<<<tiles, SEG_THREADS, 0, s>>>(sorted_keys, n, tile_counts);
+    DS_LAUNCH_CHECK();
+  }
+  ds::note_launch(); tile_scan_kernel<<<1, 1024, 0, s>>>(tile_counts, tiles, nseg_out, seg_starts_out, n);
+  DS_LAUNCH_CHECK();
+  if (n > 0) {
+    ds::note_launch(); head_write_kernel<<<tiles, SEG_THREADS, 0, s>>>(sorted_keys, n, tile_counts, seg_starts_out);
+    DS_LAUNCH_CHECK();
+  }
+  return DS_OK;
+}
