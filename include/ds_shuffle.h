@@ -97,9 +97,12 @@ ds_status ds_sort_indices_fsb(const uint8_t* col, uint32_t width, uint64_t n,
 
 /* Row gather dst[j] = src[idx[j]] for rows of row_bytes bytes.
  * Replaces Table.take / take_table at transform_pyarrow.py:16,46-67 and
- * ArrowBlockAccessor.take (_internal/arrow_block.py:258-267); one call per column. */
-ds_status ds_gather_rows(const void* src, uint32_t row_bytes, const uint32_t* idx,
-                         uint64_t n, void* dst, void* stream);
+ * ArrowBlockAccessor.take (_internal/arrow_block.py:258-267); one call per column.
+ *   src_rows   rows in the source column (the kernels read whole aligned 16-byte
+ *              vectors and need the end of the buffer to stay inside it)
+ *   idx        n uint32 source row numbers, each < src_rows (not checked) */
+ds_status ds_gather_rows(const void* src, uint32_t row_bytes, uint64_t src_rows,
+                         const uint32_t* idx, uint64_t n, void* dst, void* stream);
 
 /* ----------------------------------------------------------- partition ---- */
 

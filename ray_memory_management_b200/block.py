@@ -311,7 +311,7 @@ def _argsort(col: DeviceColumn, descending: bool, want_sorted: bool, options: in
 def _gather(col: DeviceColumn, idx: torch.Tensor) -> DeviceColumn:
     n = idx.numel()
     out = _empty_u8(n * col.row_bytes)
-    _lib.call("ds_gather_rows", col.ptr, col.row_bytes, idx.data_ptr(), n, out.data_ptr(), _stream())
+    _lib.call("ds_gather_rows", col.ptr, col.row_bytes, col.num_rows, idx.data_ptr(), n, out.data_ptr(), _stream())
     return DeviceColumn(col.type, out)
 
 

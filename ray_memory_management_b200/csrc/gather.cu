@@ -12,6 +12,8 @@
 
 namespace ds {
 
+static int g_gather_mode = 0;
+
 template <typename G>
 __global__ void __launch_bounds__(256) gather_single_kernel(const G* __restrict__ src,
                                                             const uint32_t* __restrict__ idx,
@@ -43,6 +45,113 @@ __global__ void __launch_bounds__(GATHER_THREADS)
   }
 }
 
+
+// ---- staged gather for rows that are not a multiple of 16 bytes (e.g. 90-byte payloads)
+// Phase 1 pulls every source row in as ALIGNED 16-byte vectors (the aligned span that
+// covers the row: at most ceil((W+15)/16)+... chunks) into a shared-memory slot; phase 2
+// re-reads the slots at their byte misalignment (two aligned 32-bit words + byte_perm per
+// output word) and writes the block's contiguous output span as aligned 16-byte vectors.
+// Global traffic is therefore all 128-bit; only shared memory sees the odd alignment.
+constexpr int STAGE_THREADS = 256;
+
+__device__ __forceinline__ uint32_t smem_word_unaligned(const uint8_t* base, uint32_t byte_off) {
+  const uint32_t* w = reinterpret_cast<const uint32_t*>(base + (byte_off & ~3u));
+  return __byte_perm(w[0], w[1], 0x3210u + 0x1111u * (byte_off & 3u));
+}
+
+__global__ void __launch_bounds__(STAGE_THREADS)
+    gather_staged_kernel(const uint8_t* __restrict__ src, uint32_t W, uint64_t src_bytes,
+                         const uint32_t* __restrict__ idx, uint32_t n, uint8_t* __restrict__ dst,
+                         uint32_t rows_per_block, uint32_t chunks, uint32_t magic_w,
+                         uint32_t magic_c) {
+  extern __shared__ __align__(16) uint8_t sm[];
+  const uint32_t slot = chunks * 16 + 16;  // +16: the word pair read in phase 2 may overhang
+  uint64_t* s_a0 = reinterpret_cast<uint64_t*>(sm);                       // [R] aligned source address
+  uint32_t* s_shift = reinterpret_cast<uint32_t*>(sm + rows_per_block * 8);  // [R] misalignment
+  uint8_t* data = sm + rows_per_block * 12;                                // [R][slot], 16-aligned
+  const uint32_t row0 = blockIdx.x * rows_per_block;
+  const uint32_t rows = min(rows_per_block, n - row0);
+  const uintptr_t base = reinterpret_cast<uintptr_t>(src);
+  const uintptr_t safe_lo = (base + 15) & ~uintptr_t(15);
+  const uintptr_t safe_hi = (base + src_bytes) & ~uintptr_t(15);
+
+  for (uint32_t r = threadIdx.x; r < rows; r += STAGE_THREADS) {
+    const uintptr_t a = base + static_cast<uint64_t>(ld_stream(idx + row0 + r)) * W;
+    s_a0[r] = a & ~uintptr_t(15);
+    s_shift[r] = static_cast<uint32_t>(a & 15);
+  }
+  __syncthreads();
+
+  const uint32_t items = rows * chunks;
+  for (uint32_t e = threadIdx.x; e < items; e += STAGE_THREADS) {
+    const uint32_t r = __umulhi(e, magic_c);
+    const uint32_t c = e - r * chunks;
+    if (c * 16 >= s_shift[r] + W) continue;  // chunk lies wholly after the row
+    const uintptr_t a = s_a0[r] + c * 16;
+    uint4 v;
+    if (a >= safe_lo && a + 16 <= safe_hi) {
+      v = __ldg(reinterpret_cast<const uint4*>(a));
+    } else {  // first / last partial vector of the source buffer: guarded byte loads
+      uint8_t t[16];
+#pragma unroll
+      for (int b = 0; b < 16; ++b)
+        t[b] = (a + b >= base && a + b < base + src_bytes) ? *reinterpret_cast<const uint8_t*>(a + b) : 0;
+      v = *reinterpret_cast<uint4*>(t);
+    }
+    *reinterpret_cast<uint4*>(data + r * slot + c * 16) = v;
+  }
+  __syncthreads();
+
+  const uint32_t nbytes = rows * W;
+  uint8_t* out = dst + static_cast<uint64_t>(row0) * W;  // 16-aligned (rows_per_block % 16 == 0)
+  const uint32_t nvec = nbytes >> 4;
+  for (uint32_t q = threadIdx.x; q < nvec; q += STAGE_THREADS) {
+    uint32_t w[4];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      const uint32_t o = q * 16 + k * 4;
+      const uint32_t r = __umulhi(o, magic_w);
+      const uint32_t off = o - r * W;
+      if (off + 4 <= W) {
+        w[k] = smem_word_unaligned(data + r * slot, s_shift[r] + off);
+      } else {  // word straddles two rows
+        uint32_t acc = 0;
+#pragma unroll
+        for (int b = 0; b < 4; ++b) {
+          const uint32_t ob = off + b;
+          const uint32_t rr = ob >= W ? r + 1 : r;
+          const uint32_t oo = ob >= W ? ob - W : ob;
+          acc |= static_cast<uint32_t>(data[rr * slot + s_shift[rr] + oo]) << (8 * b);
+        }
+        w[k] = acc;
+      }
+    }
+    st_stream(reinterpret_cast<uint4*>(out) + q, make_uint4(w[0], w[1], w[2], w[3]));
+  }
+  for (uint32_t o = (nvec << 4) + threadIdx.x; o < nbytes; o += STAGE_THREADS) {
+    const uint32_t r = __umulhi(o, magic_w);
+    const uint32_t off = o - r * W;
+    out[o] = data[r * slot + s_shift[r] + off];
+  }
+}
+
+static cudaError_t launch_gather_staged(const void* src, uint32_t W, uint64_t src_rows,
+                                        const uint32_t* idx, uint32_t n, void* dst, cudaStream_t s) {
+  const uint32_t chunks = (W + 15 + 15) / 16;        // worst-case aligned span of a W-byte row
+  const uint32_t slot = chunks * 16 + 16;
+  uint32_t rows = 128;                               // multiple of 16 -> aligned output spans
+  while (rows > 16 && rows * (slot + 12) > 40 * 1024) rows >>= 1;
+  const uint32_t smem = rows * (slot + 12);
+  const uint32_t magic_w = static_cast<uint32_t>((0x100000000ull + W - 1) / W);
+  const uint32_t magic_c = static_cast<uint32_t>((0x100000000ull + chunks - 1) / chunks);
+  const uint32_t blocks = (n + rows - 1) / rows;
+  ds::note_launch();
+  gather_staged_kernel<<<blocks, STAGE_THREADS, smem, s>>>(
+      static_cast<const uint8_t*>(src), W, src_rows * W, idx, n, static_cast<uint8_t*>(dst), rows,
+      chunks, magic_w, magic_c);
+  return cudaGetLastError();
+}
+
 template <typename G>
 static cudaError_t launch_gather(const void* src, const uint32_t* idx, void* dst, uint32_t n,
                                  uint32_t row_bytes, cudaStream_t s) {
@@ -62,8 +171,8 @@ static cudaError_t launch_gather(const void* src, const uint32_t* idx, void* dst
   return cudaGetLastError();
 }
 
-ds_status gather_rows_impl(const void* src, uint32_t row_bytes, const uint32_t* idx, uint64_t n64,
-                           void* dst, cudaStream_t s) {
+ds_status gather_rows_impl(const void* src, uint32_t row_bytes, uint64_t src_rows,
+                           const uint32_t* idx, uint64_t n64, void* dst, cudaStream_t s) {
   if (n64 == 0) return DS_OK;
   if (n64 > 0xFFFFFFFFull) {
     set_error("ds_gather_rows: n=%llu exceeds 2^32-1", (unsigned long long)n64);
@@ -80,7 +189,11 @@ ds_status gather_rows_impl(const void* src, uint32_t row_bytes, const uint32_t* 
   const uint32_t n = static_cast<uint32_t>(n64);
   const uintptr_t bits = reinterpret_cast<uintptr_t>(src) | reinterpret_cast<uintptr_t>(dst) | row_bytes;
   cudaError_t e;
-  if ((bits & 15) == 0) e = launch_gather<uint4>(src, idx, dst, n, row_bytes, s);
+  // rows that are not 16-byte multiples: aligned-vector staging through shared memory
+  if ((row_bytes & 15) != 0 && row_bytes >= 16 && row_bytes <= 2048 && src_rows > 0 &&
+      (reinterpret_cast<uintptr_t>(dst) & 15) == 0 && g_gather_mode != 1)
+    e = launch_gather_staged(src, row_bytes, src_rows, idx, n, dst, s);
+  else if ((bits & 15) == 0) e = launch_gather<uint4>(src, idx, dst, n, row_bytes, s);
   else if ((bits & 7) == 0) e = launch_gather<uint2>(src, idx, dst, n, row_bytes, s);
   else if ((bits & 3) == 0) e = launch_gather<uint32_t>(src, idx, dst, n, row_bytes, s);
   else if ((bits & 1) == 0) e = launch_gather<uint16_t>(src, idx, dst, n, row_bytes, s);
@@ -94,7 +207,14 @@ ds_status gather_rows_impl(const void* src, uint32_t row_bytes, const uint32_t* 
 
 }  // namespace ds
 
-extern "C" ds_status ds_gather_rows(const void* src, uint32_t row_bytes, const uint32_t* idx,
-                                    uint64_t n, void* dst, void* stream) {
-  return ds::gather_rows_impl(src, row_bytes, idx, n, dst, static_cast<cudaStream_t>(stream));
+extern "C" ds_status ds_gather_rows(const void* src, uint32_t row_bytes, uint64_t src_rows,
+                                    const uint32_t* idx, uint64_t n, void* dst, void* stream) {
+  return ds::gather_rows_impl(src, row_bytes, src_rows, idx, n, dst, static_cast<cudaStream_t>(stream));
+}
+
+// Tuning hook: 0 = automatic, 1 = never use the staged kernel.
+extern "C" int32_t ds_debug_set_gather_mode(int32_t mode) {
+  int old = ds::g_gather_mode;
+  ds::g_gather_mode = mode;
+  return old;
 }

@@ -289,6 +289,10 @@ __global__ void __launch_bounds__(THREADS, MIN_BLOCKS)
   }
 }
 
+}  // namespace ds
+#include "onesweep_v2.cuh"
+namespace ds {
+
 // ---------------------------------------------------------------- decode
 template <int KIND>
 __global__ void decode_kernel(const uint64_t* __restrict__ hi, const uint16_t* __restrict__ lo,
@@ -318,6 +322,40 @@ __global__ void decode_kernel(const uint64_t* __restrict__ hi, const uint16_t* _
   }
 }
 
+// fixed_size_binary decode with coalesced 16-byte stores: 256 rows are laid out in shared
+// memory exactly as they appear in the output buffer, then copied out as uint4.
+__global__ void __launch_bounds__(256)
+    decode_fsb_staged_kernel(const uint64_t* __restrict__ hi, const uint16_t* __restrict__ lo,
+                             uint32_t width, uint32_t n, bool desc, uint8_t* __restrict__ out) {
+  __shared__ __align__(16) uint8_t buf[256 * DS_MAX_KEY_BYTES];
+  const uint32_t row0 = blockIdx.x * 256u;
+  const uint32_t i = row0 + threadIdx.x;
+  if (i < n) {
+    uint64_t h = ld_stream(hi + i);
+    uint32_t l = width > 8 ? ld_stream(lo + i) : 0;
+    if (desc) {
+      h = ~h;
+      l = ~l;
+    }
+    uint8_t* p = buf + threadIdx.x * width;
+#pragma unroll
+    for (int b = 0; b < 8; ++b)
+      if (b < (int)width) p[b] = static_cast<uint8_t>(h >> (56 - 8 * b));
+    if (width == 9) p[8] = static_cast<uint8_t>(l);
+    if (width == 10) {
+      p[8] = static_cast<uint8_t>(l >> 8);
+      p[9] = static_cast<uint8_t>(l);
+    }
+  }
+  __syncthreads();
+  const uint32_t nbytes = min(256u, n - row0) * width;
+  uint8_t* dst = out + static_cast<uint64_t>(row0) * width;  // 16-byte aligned: 256*width % 16 == 0
+  const uint32_t vec = nbytes >> 4;
+  for (uint32_t v = threadIdx.x; v < vec; v += 256)
+    st_stream(reinterpret_cast<uint4*>(dst) + v, reinterpret_cast<const uint4*>(buf)[v]);
+  for (uint32_t o = (vec << 4) + threadIdx.x; o < nbytes; o += 256) dst[o] = buf[o];
+}
+
 // ---------------------------------------------------------------- host driver
 // Optional per-launch timing of the pass kernel (bench.py's roofline figure): CUDA events
 // recorded on the launching stream around each launch; read back by
@@ -344,37 +382,65 @@ struct PassConfig {
 };
 static int g_cfg = 0;  // tuning knob (ds_debug_set_radix_config)
 
-template <int THREADS, int ITEMS, int MIN_BLOCKS, bool HAS_LO, bool DIGIT_LO, bool GEN_IDX>
+template <typename K>
+static cudaError_t set_smem_attr(K k, int bytes, unsigned long long* done_mask) {
+  int dev = 0;
+  cudaGetDevice(&dev);
+  if (!(*done_mask >> (dev & 63) & 1ull)) {
+    cudaError_t e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+    if (e != cudaSuccess) return e;
+    *done_mask |= 1ull << (dev & 63);
+  }
+  return cudaSuccess;
+}
+
+template <int VARIANT, int THREADS, int ITEMS, int MIN_BLOCKS, bool HAS_LO, bool DIGIT_LO, bool GEN_IDX>
 static cudaError_t launch_pass_t(const uint64_t* hi_in, const uint16_t* lo_in,
                                  const uint32_t* idx_in, uint64_t* hi_out, uint16_t* lo_out,
                                  uint32_t* idx_out, uint32_t n, int shift, const uint32_t* bin_base,
                                  uint32_t* lookback, uint32_t* tile_counter, cudaStream_t s) {
   using S = PassSmem<THREADS, ITEMS, HAS_LO>;
-  auto k = onesweep_pass_kernel<THREADS, ITEMS, MIN_BLOCKS, HAS_LO, DIGIT_LO, GEN_IDX>;
-  static unsigned long long attr_done = 0;  // per instantiation, one bit per device
-  int dev = 0;
-  cudaGetDevice(&dev);
-  if (!(attr_done >> (dev & 63) & 1ull)) {
-    cudaError_t e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, S::BYTES);
-    if (e != cudaSuccess) return e;
-    attr_done |= 1ull << (dev & 63);
-  }
+  static unsigned long long done_a = 0, done_b = 0;  // per instantiation, one bit per device
   const uint32_t tiles = (n + S::TILE - 1) / S::TILE;
+  cudaError_t e;
   PassTimer timer(s);
-  ds::note_launch(); k<<<tiles, THREADS, S::BYTES, s>>>(hi_in, lo_in, idx_in, hi_out, lo_out, idx_out, n, shift,
-                                     bin_base, lookback, tile_counter);
+  if (VARIANT == 1) {
+    auto k = onesweep_pass_kernel<THREADS, ITEMS, MIN_BLOCKS, HAS_LO, DIGIT_LO, GEN_IDX>;
+    if ((e = set_smem_attr(k, S::BYTES, &done_a)) != cudaSuccess) return e;
+    ds::note_launch();
+    k<<<tiles, THREADS, S::BYTES, s>>>(hi_in, lo_in, idx_in, hi_out, lo_out, idx_out, n, shift,
+                                       bin_base, lookback, tile_counter);
+  } else {
+    // full tiles first, then (stream-ordered) the ragged last tile as tile id `full_tiles`
+    constexpr bool M = VARIANT == 3;
+    auto kf = onesweep_pass_kernel_v2<THREADS, ITEMS, MIN_BLOCKS, HAS_LO, DIGIT_LO, GEN_IDX, true, M>;
+    auto kt = onesweep_pass_kernel_v2<THREADS, ITEMS, MIN_BLOCKS, HAS_LO, DIGIT_LO, GEN_IDX, false, M>;
+    if ((e = set_smem_attr(kf, S::BYTES, &done_a)) != cudaSuccess) return e;
+    if ((e = set_smem_attr(kt, S::BYTES, &done_b)) != cudaSuccess) return e;
+    const uint32_t full_tiles = n / S::TILE;
+    if (full_tiles) {
+      ds::note_launch();
+      kf<<<full_tiles, THREADS, S::BYTES, s>>>(hi_in, lo_in, idx_in, hi_out, lo_out, idx_out, n,
+                                               shift, bin_base, lookback, tile_counter);
+    }
+    if (tiles > full_tiles) {
+      ds::note_launch();
+      kt<<<1, THREADS, S::BYTES, s>>>(hi_in, lo_in, idx_in, hi_out, lo_out, idx_out, n, shift,
+                                      bin_base, lookback, tile_counter);
+    }
+  }
   timer.stop();
   return cudaGetLastError();
 }
 
-template <int THREADS, int ITEMS, int MIN_BLOCKS>
+template <int VARIANT, int THREADS, int ITEMS, int MIN_BLOCKS>
 static cudaError_t launch_pass_cfg(bool has_lo, bool digit_lo, bool gen_idx, const uint64_t* hi_in,
                                    const uint16_t* lo_in, const uint32_t* idx_in, uint64_t* hi_out,
                                    uint16_t* lo_out, uint32_t* idx_out, uint32_t n, int shift,
                                    const uint32_t* bin_base, uint32_t* lookback,
                                    uint32_t* tile_counter, cudaStream_t s) {
 #define DS_PASS(HL, DL, GI)                                                                      \
-  return launch_pass_t<THREADS, ITEMS, MIN_BLOCKS, HL, DL, GI>(hi_in, lo_in, idx_in, hi_out,     \
+  return launch_pass_t<VARIANT, THREADS, ITEMS, MIN_BLOCKS, HL, DL, GI>(hi_in, lo_in, idx_in, hi_out,     \
                                                                lo_out, idx_out, n, shift,        \
                                                                bin_base, lookback, tile_counter, s)
   if (has_lo) {
@@ -390,11 +456,13 @@ static cudaError_t launch_pass_cfg(bool has_lo, bool digit_lo, bool gen_idx, con
 #undef DS_PASS
 }
 
+constexpr int NUM_CFGS = 13;
 static int cfg_tile(int cfg) {
   switch (cfg) {
-    case 1: return 512 * 8;
-    case 2: return 384 * 12;
-    case 3: return 256 * 12;
+    case 1: case 4: case 9: return 512 * 8;
+    case 2: case 6: case 11: return 384 * 12;
+    case 3: case 7: case 12: return 256 * 12;
+    case 8: return 256 * 8;
     default: return 256 * 16;
   }
 }
@@ -408,10 +476,19 @@ static cudaError_t launch_pass(int cfg, bool has_lo, bool digit_lo, bool gen_idx
   has_lo, digit_lo, gen_idx, hi_in, lo_in, idx_in, hi_out, lo_out, idx_out, n, shift, bin_base,  \
       lookback, tile_counter, s
   switch (cfg) {
-    case 1: return launch_pass_cfg<512, 8, 2>(DS_ARGS);
-    case 2: return launch_pass_cfg<384, 12, 2>(DS_ARGS);
-    case 3: return launch_pass_cfg<256, 12, 3>(DS_ARGS);
-    default: return launch_pass_cfg<256, 16, 2>(DS_ARGS);
+    case 1: return launch_pass_cfg<1, 512, 8, 2>(DS_ARGS);
+    case 2: return launch_pass_cfg<1, 384, 12, 2>(DS_ARGS);
+    case 3: return launch_pass_cfg<1, 256, 12, 3>(DS_ARGS);
+    case 4: return launch_pass_cfg<2, 512, 8, 2>(DS_ARGS);
+    case 5: return launch_pass_cfg<2, 256, 16, 2>(DS_ARGS);
+    case 6: return launch_pass_cfg<2, 384, 12, 2>(DS_ARGS);
+    case 7: return launch_pass_cfg<2, 256, 12, 3>(DS_ARGS);
+    case 8: return launch_pass_cfg<2, 256, 8, 4>(DS_ARGS);
+    case 9: return launch_pass_cfg<3, 512, 8, 2>(DS_ARGS);
+    case 10: return launch_pass_cfg<3, 256, 16, 2>(DS_ARGS);
+    case 11: return launch_pass_cfg<3, 384, 12, 2>(DS_ARGS);
+    case 12: return launch_pass_cfg<3, 256, 12, 3>(DS_ARGS);
+    default: return launch_pass_cfg<1, 256, 16, 2>(DS_ARGS);
   }
 #undef DS_ARGS
 }
@@ -460,8 +537,8 @@ static cudaError_t launch_encode(bool has_lo, const void* col, uint32_t width, u
   return cudaGetLastError();
 }
 
-ds_status gather_rows_impl(const void* src, uint32_t row_bytes, const uint32_t* idx, uint64_t n,
-                           void* dst, cudaStream_t s);  // gather.cu
+ds_status gather_rows_impl(const void* src, uint32_t row_bytes, uint64_t src_rows,
+                           const uint32_t* idx, uint64_t n, void* dst, cudaStream_t s);  // gather.cu
 
 static ds_status sort_indices_impl(int kind, const void* col, uint32_t width, uint64_t n64,
                                    int32_t descending, uint32_t* idx_out, void* sorted_out,
@@ -549,8 +626,15 @@ static ds_status sort_indices_impl(int kind, const void* col, uint32_t width, ui
     switch (kind) {
       case KIND_I64: ds::note_launch(); decode_kernel<KIND_I64><<<blocks, threads, 0, s>>>(hi[cur], lo[cur], width, n, desc, sorted_out); break;
       case KIND_U64: ds::note_launch(); decode_kernel<KIND_U64><<<blocks, threads, 0, s>>>(hi[cur], lo[cur], width, n, desc, sorted_out); break;
-      case KIND_F64: return gather_rows_impl(col, 8, idx_out, n, sorted_out, s);
-      default: ds::note_launch(); decode_kernel<KIND_FSB><<<blocks, threads, 0, s>>>(hi[cur], lo[cur], width, n, desc, sorted_out); break;
+      case KIND_F64: return gather_rows_impl(col, 8, n, idx_out, n, sorted_out, s);
+      default:
+        ds::note_launch();
+        if ((reinterpret_cast<uintptr_t>(sorted_out) & 15) == 0)
+          decode_fsb_staged_kernel<<<blocks, 256, 0, s>>>(hi[cur], lo[cur], width, n, desc,
+                                                          static_cast<uint8_t*>(sorted_out));
+        else
+          decode_kernel<KIND_FSB><<<blocks, threads, 0, s>>>(hi[cur], lo[cur], width, n, desc, sorted_out);
+        break;
     }
     DS_LAUNCH_CHECK();
   }
@@ -624,7 +708,7 @@ int32_t ds_debug_collect_pass_timing(double* total_ms, int32_t* launches) {
 // Tuning hook used by bench.py --sweep; not part of the reference-facing surface.
 int32_t ds_debug_set_radix_config(int32_t cfg) {
   int old = ds::g_cfg;
-  if (cfg >= 0 && cfg <= 3) ds::g_cfg = cfg;
+  if (cfg >= 0 && cfg < ds::NUM_CFGS) ds::g_cfg = cfg;
   return old;
 }
 

@@ -276,3 +276,69 @@ def test_large_graysort_properties(ds):
     assert bool((torch.sort(rowid).values == torch.arange(n, device="cuda")).all())
     # key bytes travelled with their rows
     assert bool((keys[rowid] == out.columns["key"].data.view(n, 10)).all())
+
+
+@pytest.mark.parametrize("cfg", list(range(13)))
+def test_every_pass_kernel_variant(ds, cfg):
+    """all tile shapes / both generations of the pass kernel give the same bit-exact order."""
+    lib = ds._lib.lib
+    old = lib.ds_debug_set_radix_config(cfg)
+    try:
+        n = 70_001
+        rng = np.random.default_rng(cfg)
+        col = rng.integers(0, 256, (n, 10), dtype=np.uint8)
+        col[:, :7] &= 1
+        for desc in (False, True):
+            idx, srt = _argsort_c(ds, col, "fsb", desc, width=10)
+            order = "descending" if desc else "ascending"
+            want = pa.compute.sort_indices(pa.table({"k": O.fsb_from_numpy(col)}), sort_keys=[("k", order)]).to_numpy()
+            assert np.array_equal(idx.astype(np.int64), want)
+            assert np.array_equal(srt.reshape(n, 10), col[want])
+        k64 = rng.integers(-1000, 1000, n, dtype=np.int64)
+        idx, _ = _argsort_c(ds, k64, "i64", False, want_sorted=False)
+        assert np.array_equal(idx.astype(np.int64), np.argsort(k64, kind="stable"))
+        # unaligned sorted_out pointer takes the byte-store decode path
+    finally:
+        lib.ds_debug_set_radix_config(old)
+
+
+@pytest.mark.parametrize("width", [1, 2, 3, 8, 10, 16, 17, 24, 33, 90, 100, 250])
+@pytest.mark.parametrize("start_row", [0, 1, 3])
+def test_gather_rows_c_abi(ds, width, start_row):
+    """every granule path of ds_gather_rows (incl. the staged kernel for rows that are not a
+    multiple of 16 bytes), with the source column starting at odd byte offsets."""
+    lib = ds._lib
+    rng = np.random.default_rng(width * 7 + start_row)
+    n_src, n_out = 10_007, 12_345
+    full = rng.integers(0, 256, (n_src + start_row, width), dtype=np.uint8)
+    dev = torch.from_numpy(full.reshape(-1).copy()).cuda()
+    src = dev[start_row * width:]
+    idx = rng.integers(0, n_src, n_out, dtype=np.int64)
+    idx[:3] = [n_src - 1, 0, n_src - 1]  # first / last source rows: guarded edge vectors
+    idx_dev = torch.from_numpy(idx.astype(np.int32)).cuda()
+    out = torch.zeros(n_out * width + 16, dtype=torch.uint8, device="cuda")
+    lib.call("ds_gather_rows", src.data_ptr(), width, n_src, idx_dev.data_ptr(), n_out,
+             out.data_ptr(), torch.cuda.current_stream().cuda_stream)
+    torch.cuda.synchronize()
+    got = out.cpu().numpy()
+    assert np.array_equal(got[: n_out * width].reshape(n_out, width), full[start_row:][idx])
+    assert not got[n_out * width:].any()  # nothing written past the output
+
+
+def test_gather_staged_equals_plain(ds):
+    lib = ds._lib
+    rng = np.random.default_rng(0)
+    n = 300_001
+    src = torch.from_numpy(rng.integers(0, 256, n * 90, dtype=np.uint8)).cuda()
+    idx = torch.from_numpy(rng.permutation(n).astype(np.int32)).cuda()
+    outs = []
+    for mode in (0, 1):
+        old = lib.lib.ds_debug_set_gather_mode(mode)
+        out = torch.empty(n * 90, dtype=torch.uint8, device="cuda")
+        lib.call("ds_gather_rows", src.data_ptr(), 90, n, idx.data_ptr(), n, out.data_ptr(),
+                 torch.cuda.current_stream().cuda_stream)
+        torch.cuda.synchronize()
+        lib.lib.ds_debug_set_gather_mode(old)
+        outs.append(out)
+    assert bool((outs[0] == outs[1]).all())
+    assert bool((outs[0].view(n, 90) == src.view(n, 90)[idx.long()]).all())
