@@ -51,6 +51,8 @@ def parse_args():
     p.add_argument("--no-e2e", action="store_true")
     p.add_argument("--no-cpu-baseline", action="store_true")
     p.add_argument("--radix-config", type=int, default=-1, help="tuning: pass-kernel variant")
+    p.add_argument("--gather-mode", type=int, default=-1, help="tuning: see csrc/gather.cu g_gather_mode")
+    p.add_argument("--l2-fetch", type=int, default=-1, help="tuning: cudaLimitMaxL2FetchGranularity")
     return p.parse_args()
 
 
@@ -187,6 +189,10 @@ def run_ours(args):
     lib.ds_debug_launch_count.restype = __import__("ctypes").c_uint64
     if args.radix_config >= 0:
         lib.ds_debug_set_radix_config(args.radix_config)
+    if args.gather_mode >= 0:
+        lib.ds_debug_set_gather_mode(args.gather_mode)
+    if args.l2_fetch > 0:
+        print("l2 fetch granularity was", lib.ds_debug_set_l2_fetch_granularity(args.l2_fetch), file=sys.stderr)
 
     n = args.rows_per_gpu
     block = make_records(n, seed=1 + rank)

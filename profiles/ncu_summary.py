@@ -6,7 +6,9 @@ import collections, csv, subprocess, sys
 
 rep = sys.argv[1]
 chunk = int(sys.argv[2]) if len(sys.argv) > 2 else 50
-raw = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
+skip = sys.argv[3] if len(sys.argv) > 3 else "0"   # which launch of the report
+sel = ["--launch-skip", skip, "--launch-count", "1"]
+raw = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"] + sel, capture_output=True, text=True).stdout
 rows = list(csv.reader(raw.splitlines()))
 hdr, units = rows[0], rows[1]
 keys = ["gpu__time_duration.sum", "dram__bytes_read.sum", "dram__bytes_write.sum",
@@ -28,7 +30,7 @@ for r in rows[2:3]:
             print(f"  {k} = {d[k]} {units[hdr.index(k)]}")
     st = [(float(d[h]), h.split("stalled_")[1].split("_per")[0]) for h in hdr if "average_warps_issue_stalled" in h and d[h]]
     print("  stalls/issue:", ", ".join(f"{n}={v:.2f}" for v, n in sorted(st, reverse=True)[:8]))
-src = subprocess.run(["ncu", "-i", rep, "--page", "source", "--csv"], capture_output=True, text=True).stdout
+src = subprocess.run(["ncu", "-i", rep, "--page", "source", "--csv"] + sel, capture_output=True, text=True).stdout
 rows = [r for r in csv.reader(src.splitlines()) if len(r) > 5 and r[0].startswith("0x")]
 # first kernel only: addresses restart when the listing repeats
 first = []

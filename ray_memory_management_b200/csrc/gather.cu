@@ -12,20 +12,52 @@
 
 namespace ds {
 
-static int g_gather_mode = 0;
+static int g_gather_mode = 0;  // 0 auto, 1 plain, 2 plain + L2::64B, 3 staged, 4 staged + L2::64B
 
-template <typename G>
+// Read-only loads that ask L2 to fetch only 64 bytes around a miss: random rows gain
+// nothing from the default 128-byte fetch, it only multiplies DRAM traffic.
+__device__ __forceinline__ uint16_t ld_nc_64B(const uint16_t* p) {
+  uint16_t v;
+  asm volatile("ld.global.nc.L2::64B.u16 %0, [%1];" : "=h"(v) : "l"(p));
+  return v;
+}
+__device__ __forceinline__ uint8_t ld_nc_64B(const uint8_t* p) {
+  uint32_t v;
+  asm volatile("ld.global.nc.L2::64B.u8 %0, [%1];" : "=r"(v) : "l"(p));
+  return static_cast<uint8_t>(v);
+}
+__device__ __forceinline__ uint32_t ld_nc_64B(const uint32_t* p) {
+  uint32_t v;
+  asm volatile("ld.global.nc.L2::64B.u32 %0, [%1];" : "=r"(v) : "l"(p));
+  return v;
+}
+__device__ __forceinline__ uint2 ld_nc_64B(const uint2* p) {
+  uint2 v;
+  asm volatile("ld.global.nc.L2::64B.v2.u32 {%0, %1}, [%2];" : "=r"(v.x), "=r"(v.y) : "l"(p));
+  return v;
+}
+__device__ __forceinline__ uint4 ld_nc_64B(const uint4* p) {
+  uint4 v;
+  asm volatile("ld.global.nc.L2::64B.v4.u32 {%0, %1, %2, %3}, [%4];"
+               : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p));
+  return v;
+}
+
+template <typename G, bool HINT>
 __global__ void __launch_bounds__(256) gather_single_kernel(const G* __restrict__ src,
                                                             const uint32_t* __restrict__ idx,
                                                             G* __restrict__ dst, uint32_t n) {
   const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i < n) st_stream(dst + i, __ldg(src + ld_stream(idx + i)));
+  if (i < n) {
+    const G* p = src + ld_stream(idx + i);
+    st_stream(dst + i, HINT ? ld_nc_64B(p) : __ldg(p));
+  }
 }
 
 constexpr int GATHER_THREADS = 256;
 constexpr int GATHER_MAX_ROWS = 1024;
 
-template <typename G>
+template <typename G, bool HINT>
 __global__ void __launch_bounds__(GATHER_THREADS)
     gather_rows_kernel(const G* __restrict__ src, const uint32_t* __restrict__ idx,
                        G* __restrict__ dst, uint32_t n, uint32_t gpr, uint32_t rows_per_block,
@@ -41,7 +73,8 @@ __global__ void __launch_bounds__(GATHER_THREADS)
   for (uint32_t e = threadIdx.x; e < total; e += GATHER_THREADS) {
     const uint32_t r = __umulhi(e, magic);  // e / gpr, exact for e*gpr < 2^32
     const uint32_t c = e - r * gpr;
-    st_stream(out + e, __ldg(src + static_cast<uint64_t>(s_idx[r]) * gpr + c));
+    const G* p = src + static_cast<uint64_t>(s_idx[r]) * gpr + c;
+    st_stream(out + e, HINT ? ld_nc_64B(p) : __ldg(p));
   }
 }
 
@@ -63,7 +96,7 @@ __global__ void __launch_bounds__(STAGE_THREADS)
     gather_staged_kernel(const uint8_t* __restrict__ src, uint32_t W, uint64_t src_bytes,
                          const uint32_t* __restrict__ idx, uint32_t n, uint8_t* __restrict__ dst,
                          uint32_t rows_per_block, uint32_t chunks, uint32_t magic_w,
-                         uint32_t magic_c) {
+                         uint32_t magic_c, bool hint) {
   extern __shared__ __align__(16) uint8_t sm[];
   const uint32_t slot = chunks * 16 + 16;  // +16: the word pair read in phase 2 may overhang
   uint64_t* s_a0 = reinterpret_cast<uint64_t*>(sm);                       // [R] aligned source address
@@ -90,7 +123,7 @@ __global__ void __launch_bounds__(STAGE_THREADS)
     const uintptr_t a = s_a0[r] + c * 16;
     uint4 v;
     if (a >= safe_lo && a + 16 <= safe_hi) {
-      v = __ldg(reinterpret_cast<const uint4*>(a));
+      v = hint ? ld_nc_64B(reinterpret_cast<const uint4*>(a)) : __ldg(reinterpret_cast<const uint4*>(a));
     } else {  // first / last partial vector of the source buffer: guarded byte loads
       uint8_t t[16];
 #pragma unroll
@@ -148,7 +181,7 @@ static cudaError_t launch_gather_staged(const void* src, uint32_t W, uint64_t sr
   ds::note_launch();
   gather_staged_kernel<<<blocks, STAGE_THREADS, smem, s>>>(
       static_cast<const uint8_t*>(src), W, src_rows * W, idx, n, static_cast<uint8_t*>(dst), rows,
-      chunks, magic_w, magic_c);
+      chunks, magic_w, magic_c, g_gather_mode == 4);
   return cudaGetLastError();
 }
 
@@ -157,8 +190,13 @@ static cudaError_t launch_gather(const void* src, const uint32_t* idx, void* dst
                                  uint32_t row_bytes, cudaStream_t s) {
   const uint32_t gpr = row_bytes / sizeof(G);
   if (gpr == 1) {
-    ds::note_launch(); gather_single_kernel<G><<<(n + 255) / 256, 256, 0, s>>>(static_cast<const G*>(src), idx,
-                                                           static_cast<G*>(dst), n);
+    ds::note_launch();
+    if (g_gather_mode == 1)
+      gather_single_kernel<G, false><<<(n + 255) / 256, 256, 0, s>>>(static_cast<const G*>(src), idx,
+                                                                     static_cast<G*>(dst), n);
+    else
+      gather_single_kernel<G, true><<<(n + 255) / 256, 256, 0, s>>>(static_cast<const G*>(src), idx,
+                                                                    static_cast<G*>(dst), n);
     return cudaGetLastError();
   }
   uint32_t rows = 8192 / gpr;
@@ -166,8 +204,13 @@ static cudaError_t launch_gather(const void* src, const uint32_t* idx, void* dst
   if (rows > GATHER_MAX_ROWS) rows = GATHER_MAX_ROWS;
   const uint32_t magic = static_cast<uint32_t>((0x100000000ull + gpr - 1) / gpr);
   const uint32_t blocks = (n + rows - 1) / rows;
-  ds::note_launch(); gather_rows_kernel<G><<<blocks, GATHER_THREADS, 0, s>>>(static_cast<const G*>(src), idx,
-                                                         static_cast<G*>(dst), n, gpr, rows, magic);
+  ds::note_launch();
+  if (g_gather_mode == 1)
+    gather_rows_kernel<G, false><<<blocks, GATHER_THREADS, 0, s>>>(
+        static_cast<const G*>(src), idx, static_cast<G*>(dst), n, gpr, rows, magic);
+  else
+    gather_rows_kernel<G, true><<<blocks, GATHER_THREADS, 0, s>>>(
+        static_cast<const G*>(src), idx, static_cast<G*>(dst), n, gpr, rows, magic);
   return cudaGetLastError();
 }
 
@@ -191,7 +234,7 @@ ds_status gather_rows_impl(const void* src, uint32_t row_bytes, uint64_t src_row
   cudaError_t e;
   // rows that are not 16-byte multiples: aligned-vector staging through shared memory
   if ((row_bytes & 15) != 0 && row_bytes >= 16 && row_bytes <= 2048 && src_rows > 0 &&
-      (reinterpret_cast<uintptr_t>(dst) & 15) == 0 && g_gather_mode != 1)
+      (reinterpret_cast<uintptr_t>(dst) & 15) == 0 && g_gather_mode >= 3)
     e = launch_gather_staged(src, row_bytes, src_rows, idx, n, dst, s);
   else if ((bits & 15) == 0) e = launch_gather<uint4>(src, idx, dst, n, row_bytes, s);
   else if ((bits & 7) == 0) e = launch_gather<uint2>(src, idx, dst, n, row_bytes, s);
@@ -212,9 +255,17 @@ extern "C" ds_status ds_gather_rows(const void* src, uint32_t row_bytes, uint64_
   return ds::gather_rows_impl(src, row_bytes, src_rows, idx, n, dst, static_cast<cudaStream_t>(stream));
 }
 
-// Tuning hook: 0 = automatic, 1 = never use the staged kernel.
+// Tuning hook, see g_gather_mode.
 extern "C" int32_t ds_debug_set_gather_mode(int32_t mode) {
   int old = ds::g_gather_mode;
   ds::g_gather_mode = mode;
   return old;
+}
+
+// Tuning hook: cudaLimitMaxL2FetchGranularity of the current device (32 / 64 / 128).
+extern "C" int32_t ds_debug_set_l2_fetch_granularity(int32_t bytes) {
+  size_t old = 0;
+  cudaDeviceGetLimit(&old, cudaLimitMaxL2FetchGranularity);
+  if (bytes > 0) cudaDeviceSetLimit(cudaLimitMaxL2FetchGranularity, static_cast<size_t>(bytes));
+  return static_cast<int32_t>(old);
 }

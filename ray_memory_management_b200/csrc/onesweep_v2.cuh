@@ -102,17 +102,15 @@ __global__ void __launch_bounds__(THREADS, MIN_BLOCKS)
   }
   __syncthreads();
 
-  // ---- B. per digit: exclusive scan over warps, publish the tile aggregate at once
+  // ---- B. per digit: tile count -> publish the aggregate at once; scan over digits; then
+  // turn each warp's count into its running offset INCLUDING the digit's tile start, so
+  // that ranking needs no second table lookup.
   volatile uint32_t* my = lookback + static_cast<size_t>(tile) * RADIX + tid;
   uint32_t my_sum = 0;
   if (tid < RADIX) {
     uint32_t sum = 0;
 #pragma unroll
-    for (int w = 0; w < WARPS; ++w) {
-      const uint32_t c = warp_hist[w * RADIX + tid];
-      warp_hist[w * RADIX + tid] = sum;  // becomes this warp's running offset
-      sum += c;
-    }
+    for (int w = 0; w < WARPS; ++w) sum += warp_hist[w * RADIX + tid];
     st_relaxed_gpu(my, (tile == 0 ? LB_INCLUSIVE : LB_AGGREGATE) | sum);
     my_sum = sum;
     uint32_t v = sum;
@@ -127,7 +125,14 @@ __global__ void __launch_bounds__(THREADS, MIN_BLOCKS)
 #pragma unroll
     for (int w = 0; w < 8; ++w)
       if (w < warp) add += s_warp_tot[w];
-    s_dstart[tid] = v + add - sum;
+    uint32_t run = v + add - sum;  // first tile-local position of this digit
+    s_dstart[tid] = run;
+#pragma unroll
+    for (int w = 0; w < WARPS; ++w) {
+      const uint32_t c = warp_hist[w * RADIX + tid];
+      warp_hist[w * RADIX + tid] = run;
+      run += c;
+    }
   }
   __syncthreads();
 
@@ -148,7 +153,7 @@ __global__ void __launch_bounds__(THREADS, MIN_BLOCKS)
     uint32_t base = 0;
     if (valid && lt == 0) base = atomicAdd(&wh[d], __popc(peers));
     base = __shfl_sync(0xffffffffu, base, __ffs(peers) - 1);
-    pos[i] = s_dstart[d] + base + lt;
+    pos[i] = base + lt;
   }
   __syncthreads();  // warp_hist is dead from here: the exchange buffers overlay it
 

@@ -380,7 +380,7 @@ struct PassTimer {
 struct PassConfig {
   int threads, items;
 };
-static int g_cfg = 0;  // tuning knob (ds_debug_set_radix_config)
+static int g_cfg = 6;  // tuning knob (ds_debug_set_radix_config); 6 = v2 <384 x 12>, best measured
 
 template <typename K>
 static cudaError_t set_smem_attr(K k, int bytes, unsigned long long* done_mask) {
@@ -456,13 +456,17 @@ static cudaError_t launch_pass_cfg(bool has_lo, bool digit_lo, bool gen_idx, con
 #undef DS_PASS
 }
 
-constexpr int NUM_CFGS = 13;
+constexpr int NUM_CFGS = 17;
 static int cfg_tile(int cfg) {
   switch (cfg) {
     case 1: case 4: case 9: return 512 * 8;
     case 2: case 6: case 11: return 384 * 12;
     case 3: case 7: case 12: return 256 * 12;
     case 8: return 256 * 8;
+    case 13: return 256 * 10;
+    case 14: return 384 * 8;
+    case 15: return 512 * 10;
+    case 16: return 640 * 8;
     default: return 256 * 16;
   }
 }
@@ -488,6 +492,10 @@ static cudaError_t launch_pass(int cfg, bool has_lo, bool digit_lo, bool gen_idx
     case 10: return launch_pass_cfg<3, 256, 16, 2>(DS_ARGS);
     case 11: return launch_pass_cfg<3, 384, 12, 2>(DS_ARGS);
     case 12: return launch_pass_cfg<3, 256, 12, 3>(DS_ARGS);
+    case 13: return launch_pass_cfg<2, 256, 10, 3>(DS_ARGS);
+    case 14: return launch_pass_cfg<2, 384, 8, 2>(DS_ARGS);
+    case 15: return launch_pass_cfg<2, 512, 10, 1>(DS_ARGS);
+    case 16: return launch_pass_cfg<2, 640, 8, 1>(DS_ARGS);
     default: return launch_pass_cfg<1, 256, 16, 2>(DS_ARGS);
   }
 #undef DS_ARGS

@@ -278,7 +278,7 @@ def test_large_graysort_properties(ds):
     assert bool((keys[rowid] == out.columns["key"].data.view(n, 10)).all())
 
 
-@pytest.mark.parametrize("cfg", list(range(13)))
+@pytest.mark.parametrize("cfg", list(range(17)))
 def test_every_pass_kernel_variant(ds, cfg):
     """all tile shapes / both generations of the pass kernel give the same bit-exact order."""
     lib = ds._lib.lib
@@ -304,7 +304,8 @@ def test_every_pass_kernel_variant(ds, cfg):
 
 @pytest.mark.parametrize("width", [1, 2, 3, 8, 10, 16, 17, 24, 33, 90, 100, 250])
 @pytest.mark.parametrize("start_row", [0, 1, 3])
-def test_gather_rows_c_abi(ds, width, start_row):
+@pytest.mark.parametrize("mode", [0, 3])
+def test_gather_rows_c_abi(ds, width, start_row, mode):
     """every granule path of ds_gather_rows (incl. the staged kernel for rows that are not a
     multiple of 16 bytes), with the source column starting at odd byte offsets."""
     lib = ds._lib
@@ -317,9 +318,13 @@ def test_gather_rows_c_abi(ds, width, start_row):
     idx[:3] = [n_src - 1, 0, n_src - 1]  # first / last source rows: guarded edge vectors
     idx_dev = torch.from_numpy(idx.astype(np.int32)).cuda()
     out = torch.zeros(n_out * width + 16, dtype=torch.uint8, device="cuda")
-    lib.call("ds_gather_rows", src.data_ptr(), width, n_src, idx_dev.data_ptr(), n_out,
-             out.data_ptr(), torch.cuda.current_stream().cuda_stream)
-    torch.cuda.synchronize()
+    old = lib.lib.ds_debug_set_gather_mode(mode)
+    try:
+        lib.call("ds_gather_rows", src.data_ptr(), width, n_src, idx_dev.data_ptr(), n_out,
+                 out.data_ptr(), torch.cuda.current_stream().cuda_stream)
+        torch.cuda.synchronize()
+    finally:
+        lib.lib.ds_debug_set_gather_mode(old)
     got = out.cpu().numpy()
     assert np.array_equal(got[: n_out * width].reshape(n_out, width), full[start_row:][idx])
     assert not got[n_out * width:].any()  # nothing written past the output
@@ -332,7 +337,7 @@ def test_gather_staged_equals_plain(ds):
     src = torch.from_numpy(rng.integers(0, 256, n * 90, dtype=np.uint8)).cuda()
     idx = torch.from_numpy(rng.permutation(n).astype(np.int32)).cuda()
     outs = []
-    for mode in (0, 1):
+    for mode in (1, 2, 3, 4):
         old = lib.lib.ds_debug_set_gather_mode(mode)
         out = torch.empty(n * 90, dtype=torch.uint8, device="cuda")
         lib.call("ds_gather_rows", src.data_ptr(), 90, n, idx.data_ptr(), n, out.data_ptr(),
@@ -340,5 +345,6 @@ def test_gather_staged_equals_plain(ds):
         torch.cuda.synchronize()
         lib.lib.ds_debug_set_gather_mode(old)
         outs.append(out)
-    assert bool((outs[0] == outs[1]).all())
+    for o in outs[1:]:
+        assert bool((outs[0] == o).all())
     assert bool((outs[0].view(n, 90) == src.view(n, 90)[idx.long()]).all())
