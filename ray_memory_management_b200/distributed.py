@@ -78,18 +78,22 @@ def gather_samples(local: np.ndarray, width: int, group=None, device=None) -> np
 
 
 def splitters_from_samples(samples: np.ndarray, arrow_type: pa.DataType, world: int) -> list:
-    """Identical W-1 splitters on every rank: sorted samples, nearest-rank quantiles --
-    the reference's rule (python/ray/data/_internal/sort.py:104-115), fed with denser
-    samples (its 10 per block give badly skewed partitions; sample density is not part
-    of its contract)."""
-    from .sort import boundaries_from_samples
+    """Identical W-1 splitters on every rank: the i/W quantiles (i = 1..W-1) of the sorted
+    gathered samples.
+
+    The reference takes the quantiles i/(R-1), i = 1..R-1, of 10 samples per block
+    (python/ray/data/_internal/sort.py:110-115), whose last splitter is the largest sample,
+    so its last partition is almost empty and the others are uneven ("splitter
+    quality").  Output block sizes are not part of its contract -- only the concatenation
+    is -- so the multi-GPU plan uses evenly spaced quantiles of 2048 samples per rank."""
+    from .sort import sort_samples
 
     n, w = samples.shape
     if n == 0:
         return [None] * (world - 1)
     buf = pa.py_buffer(np.ascontiguousarray(samples).tobytes())
-    arr = pa.Array.from_buffers(arrow_type, n, [None, buf])
-    return boundaries_from_samples(arr, world)
+    srt = sort_samples(pa.Array.from_buffers(arrow_type, n, [None, buf]))
+    return [srt[min(n - 1, (i * n) // world)] for i in range(1, world)]
 
 
 # ----------------------------------------------------------------------------- plans

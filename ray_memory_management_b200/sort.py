@@ -58,21 +58,27 @@ def nearest_rank_positions(num_samples: int, num_reducers: int) -> List[int]:
     return [int(np.around((num_samples - 1) * q)) for q in qs][1:]
 
 
-def boundaries_from_samples(samples: pa.Array, num_reducers: int) -> list:
-    """Driver-side half of sample_boundaries (sort.py:104-115): sort the <= 10*R sampled
-    keys on the host and take nearest-rank quantiles."""
+def sort_samples(samples: pa.Array) -> list:
+    """Host sort of the few sampled keys (np.sort at sort.py:110); fixed_size_binary keys
+    are ordered bytewise (memcmp), as Arrow orders them."""
     n = len(samples)
-    if n == 0:
-        return [None] * (num_reducers - 1)
     t = samples.type
     if pa.types.is_fixed_size_binary(t):
         w = t.byte_width
         raw = np.frombuffer(samples.buffers()[1], dtype=np.uint8)[samples.offset * w : (samples.offset + n) * w]
         rows = raw.reshape(n, w)
         order = np.lexsort(tuple(rows[:, j] for j in range(w - 1, -1, -1)))
-        srt = rows[order]
-        return [srt[i].tobytes() for i in nearest_rank_positions(n, num_reducers)]
-    srt = np.sort(samples.to_numpy(zero_copy_only=False))
+        return [r.tobytes() for r in rows[order]]
+    return list(np.sort(samples.to_numpy(zero_copy_only=False)))
+
+
+def boundaries_from_samples(samples: pa.Array, num_reducers: int) -> list:
+    """Driver-side half of sample_boundaries (sort.py:104-115): sort the <= 10*R sampled
+    keys on the host and take nearest-rank quantiles."""
+    n = len(samples)
+    if n == 0:
+        return [None] * (num_reducers - 1)
+    srt = sort_samples(samples)
     return [srt[i] for i in nearest_rank_positions(n, num_reducers)]
 
 

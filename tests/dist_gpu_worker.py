@@ -1,0 +1,99 @@
+"""Worker for tests/test_gpu_distributed.py: run under torchrun, one rank per GPU.
+Checks the multi-GPU sort / random_shuffle / groupby plans against the oracle."""
+import os
+import sys
+
+import numpy as np
+import pyarrow as pa
+import torch
+import torch.distributed as dist
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+
+from oracle import datasets_oracle as O  # noqa: E402
+
+
+def gather_tables(t: pa.Table, rank, world):
+    """all ranks' tables on every rank (pickled through all_gather_object)."""
+    sink = pa.BufferOutputStream()
+    with pa.ipc.new_stream(sink, t.schema) as w:
+        w.write_table(t)
+    out = [None] * world
+    dist.all_gather_object(out, sink.getvalue().to_pybytes())
+    return [pa.ipc.open_stream(b).read_all() for b in out]
+
+
+def main():
+    rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
+    torch.cuda.set_device(int(os.environ["LOCAL_RANK"]))
+    dist.init_process_group("nccl", device_id=torch.device("cuda", int(os.environ["LOCAL_RANK"])))
+    import ray_memory_management_b200 as ds
+    from ray_memory_management_b200 import distributed as D
+
+    # ---- sort, GraySort records with heavy ties, ragged per-rank sizes
+    n = 200_000 + 1000 * rank
+    t = O.graysort_table(n, seed=100 + rank)
+    keys = O.fsb_to_numpy(t["key"]).copy()
+    keys[:, :7] = 3
+    keys[:, 7] &= 0x0F
+    payload = O.fsb_to_numpy(t["payload"]).copy()
+    payload[:, 8] = rank  # make rows of different ranks distinguishable
+    t = pa.table({"key": O.fsb_from_numpy(keys), "payload": O.fsb_from_numpy(payload)})
+    inputs = gather_tables(t, rank, world)
+    for desc in (False, True):
+        out = D.sort_block(ds.DeviceArrowBlock.from_arrow(t), "key", descending=desc)
+        outs = gather_tables(out.to_arrow(), rank, world)
+        got = pa.concat_tables([o for o in outs if o.num_rows])
+        want = O.global_stable_sort(inputs, "key", desc)
+        assert got.equals(want), f"distributed sort mismatch desc={desc}"
+        sizes = [o.num_rows for o in outs]
+        assert max(sizes) < 1.3 * sum(sizes) / world, f"unbalanced partitions {sizes}"
+
+    # ---- int64 sort
+    rng = np.random.default_rng(rank)
+    ti = pa.table({"k": rng.integers(-10**6, 10**6, 150_000, dtype=np.int64),
+                   "v": np.arange(150_000, dtype=np.int64) + rank * 10**7})
+    inputs = gather_tables(ti, rank, world)
+    out = D.sort_block(ds.DeviceArrowBlock.from_arrow(ti), "k")
+    got = pa.concat_tables(gather_tables(out.to_arrow(), rank, world))
+    assert got.equals(O.global_stable_sort(inputs, "k", False)), "int64 distributed sort mismatch"
+
+    # ---- random_shuffle: permutation + determinism
+    a = D.random_shuffle_block(ds.DeviceArrowBlock.from_arrow(ti), 42)
+    b = D.random_shuffle_block(ds.DeviceArrowBlock.from_arrow(ti), 42)
+    c = D.random_shuffle_block(ds.DeviceArrowBlock.from_arrow(ti), 43)
+    ga = pa.concat_tables(gather_tables(a.to_arrow(), rank, world))
+    gb = pa.concat_tables(gather_tables(b.to_arrow(), rank, world))
+    gc = pa.concat_tables(gather_tables(c.to_arrow(), rank, world))
+    assert ga.equals(gb) and not ga.equals(gc)
+    allv = np.sort(pa.concat_tables(inputs)["v"].to_numpy())
+    assert np.array_equal(np.sort(ga["v"].to_numpy()), allv)
+    # rows really moved between ranks
+    mine = a.to_arrow()["v"].to_numpy() // 10**7
+    assert len(np.unique(mine)) == world
+
+    # ---- groupby
+    tg = pa.table({"k": rng.integers(0, 5000, 120_000, dtype=np.int64), "v": rng.random(120_000),
+                   "w": rng.integers(-100, 100, 120_000, dtype=np.int64)})
+    inputs = gather_tables(tg, rank, world)
+    aggs = (ds.Sum("v"), ds.Mean("v"), ds.Count(), ds.Sum("w"), ds.Max("w"))
+    out = D.groupby_block(ds.DeviceArrowBlock.from_arrow(tg), "k", aggs)
+    got = pa.concat_tables([o for o in gather_tables(out.to_arrow(), rank, world) if o.num_rows])
+    want = O.groupby_global(inputs, "k", (("sum", "v"), ("mean", "v"), ("count", None), ("sum", "w"), ("max", "w")))
+    assert got.column_names == want.column_names
+    for name in want.column_names:
+        x, y = got[name].to_numpy(), want[name].to_numpy()
+        if y.dtype.kind == "f":
+            assert np.allclose(x, y, rtol=1e-6, atol=0), name
+        else:
+            assert np.array_equal(x, y), name
+    torch.cuda.synchronize()
+    dist.barrier()
+    if rank == 0:
+        print("DIST_GPU_OK", world)
+    dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()
