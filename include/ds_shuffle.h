@@ -46,7 +46,9 @@ typedef int32_t ds_status;
 #define DS_MAX_PARTITIONS 256
 
 /* ds_sort_indices_* option bits */
-#define DS_SORT_NO_PASS_SKIP 1 /* never read the digit histogram back: no host sync */
+#define DS_SORT_NO_PASS_SKIP 1 /* never read the digit histogram back: no host sync at all
+                                  (implies DS_SORT_NO_PREFIX_REPAIR) */
+#define DS_SORT_NO_PREFIX_REPAIR 2 /* always run every (non-constant) digit pass */
 
 /* aggregation ops for ds_segmented_reduce_* */
 #define DS_OP_SUM 0
@@ -74,7 +76,12 @@ const char* ds_last_error(void);
  *   sorted_out     optional (may be NULL): the key column in sorted order
  *   options        DS_SORT_* bits.  Unless DS_SORT_NO_PASS_SKIP is set the call
  *                  does ONE small host sync to skip radix passes whose digit is
- *                  constant over the whole column.
+ *                  constant over the whole column.  Unless DS_SORT_NO_PREFIX_REPAIR is
+ *                  set it may also sort by the most significant digits only when the
+ *                  histograms show that they separate almost all rows, then order the
+ *                  remaining short runs of equal prefixes by the full key (verified on
+ *                  device; a second 4-byte host sync; falls back to all passes if a run
+ *                  is long).  The result is identical in every mode.
  * float64 order: -inf < ... < -0.0 == 0.0 ... < +inf < NaN (NaNs last in ascending
  * and in descending order, like Arrow); -0.0 and 0.0 compare equal (stable). */
 ds_status ds_sort_indices_i64(const int64_t* col, uint64_t n, int32_t descending,

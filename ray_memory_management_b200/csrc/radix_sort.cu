@@ -91,8 +91,10 @@ __global__ void __launch_bounds__(512) encode_hist_kernel(const void* __restrict
 
 // One block of 256 threads per digit position.
 __global__ void scan_hist_kernel(const uint32_t* __restrict__ ghist, uint32_t n,
-                                 uint32_t* __restrict__ bin_base, uint32_t* __restrict__ skip) {
+                                 uint32_t* __restrict__ bin_base, uint32_t* __restrict__ skip,
+                                 float* __restrict__ coll) {
   __shared__ uint32_t warp_tot[8];
+  __shared__ float warp_sq[8];
   const int p = blockIdx.x, d = threadIdx.x;
   const uint32_t c = ghist[p * RADIX + d];
   uint32_t v = c;
@@ -108,6 +110,71 @@ __global__ void scan_hist_kernel(const uint32_t* __restrict__ ghist, uint32_t n,
   bin_base[p * RADIX + d] = v + add - c;
   const int any = __syncthreads_or(c == n);
   if (d == 0) skip[p] = any ? 1u : 0u;
+  // probability that two random rows share this digit: sum_b (c_b / n)^2
+  float f = static_cast<float>(c) / static_cast<float>(n);
+  f *= f;
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) f += __shfl_xor_sync(0xffffffffu, f, o);
+  if (lane_id() == 0) warp_sq[d >> 5] = f;
+  __syncthreads();
+  if (d == 0) {
+    float t = 0;
+    for (int w = 0; w < 8; ++w) t += warp_sq[w];
+    coll[p] = t;
+  }
+}
+
+// ---------------------------------------------------------------- prefix sort + run repair
+// After sorting (stably) by the key bits >= prefix_shift only, rows whose prefixes are equal
+// form runs in input order.  One thread per run head sorts its run by the full key with a
+// stable insertion sort.  Runs longer than REPAIR_MAX_RUN raise *too_long (the caller then
+// falls back to the full LSD sort).
+constexpr int REPAIR_MAX_RUN = 16;
+
+template <bool HAS_LO>
+__global__ void __launch_bounds__(256)
+    repair_runs_kernel(uint64_t* __restrict__ hi, uint16_t* __restrict__ lo, uint32_t* __restrict__ idx,
+                       uint32_t n, int prefix_shift, uint32_t* __restrict__ too_long) {
+  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const uint64_t pfx = hi[i] >> prefix_shift;
+  if (i > 0 && (hi[i - 1] >> prefix_shift) == pfx) return;        // not a run head
+  if (i + 1 >= n || (hi[i + 1] >> prefix_shift) != pfx) return;   // singleton run
+  uint32_t len = 2;
+  while (i + len < n && len <= REPAIR_MAX_RUN && (hi[i + len] >> prefix_shift) == pfx) ++len;
+  if (len > REPAIR_MAX_RUN) {
+    atomicOr(too_long, 1u);
+    return;
+  }
+  uint64_t h[REPAIR_MAX_RUN];
+  uint32_t l[REPAIR_MAX_RUN], x[REPAIR_MAX_RUN];
+  for (uint32_t k = 0; k < len; ++k) {
+    h[k] = hi[i + k];
+    l[k] = HAS_LO ? lo[i + k] : 0;
+    x[k] = idx[i + k];
+  }
+  bool moved = false;
+  for (uint32_t a = 1; a < len; ++a) {  // stable: only strictly smaller keys move left
+    const uint64_t kh = h[a];
+    const uint32_t kl = l[a], kx = x[a];
+    uint32_t b = a;
+    while (b > 0 && (h[b - 1] > kh || (h[b - 1] == kh && l[b - 1] > kl))) {
+      h[b] = h[b - 1];
+      l[b] = l[b - 1];
+      x[b] = x[b - 1];
+      --b;
+      moved = true;
+    }
+    h[b] = kh;
+    l[b] = kl;
+    x[b] = kx;
+  }
+  if (!moved) return;
+  for (uint32_t k = 0; k < len; ++k) {
+    hi[i + k] = h[k];
+    if (HAS_LO) lo[i + k] = static_cast<uint16_t>(l[k]);
+    idx[i + k] = x[k];
+  }
 }
 
 __global__ void iota_kernel(uint32_t* out, uint32_t n) {
@@ -551,7 +618,12 @@ ds_status gather_rows_impl(const void* src, uint32_t row_bytes, uint64_t src_row
 static ds_status sort_indices_impl(int kind, const void* col, uint32_t width, uint64_t n64,
                                    int32_t descending, uint32_t* idx_out, void* sorted_out,
                                    int32_t options, void* ws, size_t* ws_bytes, void* stream,
-                                   const char* fn, uint64_t seed = 0, uint64_t subseq = 0) {
+                                   const char* fn, uint64_t seed, uint64_t subseq);
+
+static ds_status sort_indices_impl(int kind, const void* col, uint32_t width, uint64_t n64,
+                                   int32_t descending, uint32_t* idx_out, void* sorted_out,
+                                   int32_t options, void* ws, size_t* ws_bytes, void* stream,
+                                   const char* fn, uint64_t seed, uint64_t subseq) {
   if (n64 > DS_MAX_ROWS) {
     set_error("%s: n=%llu exceeds DS_MAX_ROWS", fn, (unsigned long long)n64);
     return DS_ERR_TOO_LARGE;
@@ -575,7 +647,7 @@ static ds_status sort_indices_impl(int kind, const void* col, uint32_t width, ui
     lo[1] = w.take<uint16_t>(n);
   }
   uint32_t* idx_alt = w.take<uint32_t>(n);
-  uint32_t* ctrl = w.take<uint32_t>(MAX_PASSES * RADIX * 2 + 2 * MAX_PASSES);
+  uint32_t* ctrl = w.take<uint32_t>(MAX_PASSES * RADIX * 2 + 4 * MAX_PASSES);
   uint32_t* lookback = w.take<uint32_t>(static_cast<size_t>(tiles) * RADIX);
   ds_status st;
   if (ws_resolve(w, ws, ws_bytes, fn, &st)) return st;
@@ -589,9 +661,11 @@ static ds_status sort_indices_impl(int kind, const void* col, uint32_t width, ui
   uint32_t* bin_base = ctrl + MAX_PASSES * RADIX;
   uint32_t* skip = ctrl + 2 * MAX_PASSES * RADIX;
   uint32_t* tile_counters = skip + MAX_PASSES;
+  float* coll = reinterpret_cast<float*>(tile_counters + MAX_PASSES);  // directly after skip..: read back together
+  uint32_t* too_long = tile_counters + 2 * MAX_PASSES;
   const bool desc = descending != 0;
 
-  DS_CUDA(cudaMemsetAsync(ctrl, 0, sizeof(uint32_t) * (MAX_PASSES * RADIX * 2 + 2 * MAX_PASSES), s));
+  DS_CUDA(cudaMemsetAsync(ctrl, 0, sizeof(uint32_t) * (MAX_PASSES * RADIX * 2 + 4 * MAX_PASSES), s));
   cudaError_t e;
   switch (kind) {
     case KIND_I64: e = launch_encode<KIND_I64>(has_lo, col, width, n, desc, hi[0], lo[0], pl, ghist, s); break;
@@ -601,17 +675,42 @@ static ds_status sort_indices_impl(int kind, const void* col, uint32_t width, ui
     default: e = launch_encode<KIND_FSB>(has_lo, col, width, n, desc, hi[0], lo[0], pl, ghist, s); break;
   }
   DS_CUDA(e);
-  ds::note_launch(); scan_hist_kernel<<<pl.count, RADIX, 0, s>>>(ghist, n, bin_base, skip);
+  ds::note_launch(); scan_hist_kernel<<<pl.count, RADIX, 0, s>>>(ghist, n, bin_base, skip, coll);
   DS_LAUNCH_CHECK();
 
   uint32_t skip_h[MAX_PASSES] = {0};
+  float coll_h[MAX_PASSES] = {0};
   if (!(options & DS_SORT_NO_PASS_SKIP)) {
-    DS_CUDA(cudaMemcpyAsync(skip_h, skip, sizeof(uint32_t) * pl.count, cudaMemcpyDeviceToHost, s));
-    DS_CUDA(cudaStreamSynchronize(s));  // the one host sync: <= 40 bytes
+    uint32_t back[3 * MAX_PASSES];  // skip | tile_counters (unused here) | coll
+    DS_CUDA(cudaMemcpyAsync(back, skip, sizeof(back), cudaMemcpyDeviceToHost, s));
+    DS_CUDA(cudaStreamSynchronize(s));  // host sync #1: 120 bytes
+    memcpy(skip_h, back, sizeof(skip_h));
+    memcpy(coll_h, back + 2 * MAX_PASSES, sizeof(coll_h));
   }
   int exec[MAX_PASSES], ne = 0;
   for (int p = 0; p < pl.count; ++p)
     if (!skip_h[p]) exec[ne++] = p;
+
+  // Prefix sort + run repair: if the digit histograms say that the top m digits alone
+  // already separate almost all rows (expected colliding pairs <= 2% of n, digits taken as
+  // independent), run only those m passes and let repair_runs_kernel order the few short
+  // runs of equal prefixes by the full key.  The estimate is only a heuristic: the repair
+  // kernel VERIFIES every run, and a run it cannot handle sends us back to the full sort.
+  int prefix_shift = -1;
+  if (!(options & (DS_SORT_NO_PASS_SKIP | DS_SORT_NO_PREFIX_REPAIR)) && n >= (1u << 16) && ne >= 3) {
+    double pairs = 0.5 * static_cast<double>(n) * static_cast<double>(n);
+    for (int m = 1; m <= ne - 2; ++m) {
+      const int p = exec[ne - m];
+      if (pl.from_lo[p]) break;  // the prefix must lie inside `hi`
+      pairs *= static_cast<double>(coll_h[p]);
+      if (pairs <= 0.02 * static_cast<double>(n)) {
+        prefix_shift = pl.shift[p];
+        for (int k = 0; k < m; ++k) exec[k] = exec[ne - m + k];
+        ne = m;
+        break;
+      }
+    }
+  }
 
   int cur = 0;
   if (ne == 0) {
@@ -628,6 +727,20 @@ static ds_status sort_indices_impl(int kind, const void* col, uint32_t width, ui
                         lookback, tile_counters + p, s));
     idx_src = idx_dst;
     cur ^= 1;
+  }
+  if (prefix_shift >= 0) {
+    ds::note_launch();
+    if (has_lo)
+      repair_runs_kernel<true><<<(n + 255) / 256, 256, 0, s>>>(hi[cur], lo[cur], idx_out, n, prefix_shift, too_long);
+    else
+      repair_runs_kernel<false><<<(n + 255) / 256, 256, 0, s>>>(hi[cur], lo[cur], idx_out, n, prefix_shift, too_long);
+    DS_LAUNCH_CHECK();
+    uint32_t flag = 0;
+    DS_CUDA(cudaMemcpyAsync(&flag, too_long, sizeof(flag), cudaMemcpyDeviceToHost, s));
+    DS_CUDA(cudaStreamSynchronize(s));  // host sync #2 (prefix mode only): 4 bytes
+    if (flag)  // a long run of equal prefixes: the estimate was wrong, sort all digits
+      return sort_indices_impl(kind, col, width, n64, descending, idx_out, sorted_out,
+                               options | DS_SORT_NO_PREFIX_REPAIR, ws, ws_bytes, stream, fn, seed, subseq);
   }
   if (sorted_out != nullptr) {
     const int threads = 256, blocks = (n + threads - 1) / threads;
@@ -657,37 +770,36 @@ ds_status ds_sort_indices_i64(const int64_t* col, uint64_t n, int32_t descending
                               int64_t* sorted_out, int32_t options, void* ws, size_t* ws_bytes,
                               void* stream) {
   return ds::sort_indices_impl(ds::KIND_I64, col, 8, n, descending, idx_out, sorted_out, options, ws,
-                               ws_bytes, stream, __func__);
+                               ws_bytes, stream, __func__, 0, 0);
 }
 
 ds_status ds_sort_indices_u64(const uint64_t* col, uint64_t n, int32_t descending, uint32_t* idx_out,
                               uint64_t* sorted_out, int32_t options, void* ws, size_t* ws_bytes,
                               void* stream) {
   return ds::sort_indices_impl(ds::KIND_U64, col, 8, n, descending, idx_out, sorted_out, options, ws,
-                               ws_bytes, stream, __func__);
+                               ws_bytes, stream, __func__, 0, 0);
 }
 
 ds_status ds_sort_indices_f64(const double* col, uint64_t n, int32_t descending, uint32_t* idx_out,
                               double* sorted_out, int32_t options, void* ws, size_t* ws_bytes,
                               void* stream) {
   return ds::sort_indices_impl(ds::KIND_F64, col, 8, n, descending, idx_out, sorted_out, options, ws,
-                               ws_bytes, stream, __func__);
+                               ws_bytes, stream, __func__, 0, 0);
 }
 
 ds_status ds_sort_indices_fsb(const uint8_t* col, uint32_t width, uint64_t n, int32_t descending,
                               uint32_t* idx_out, uint8_t* sorted_out, int32_t options, void* ws,
                               size_t* ws_bytes, void* stream) {
   return ds::sort_indices_impl(ds::KIND_FSB, col, width, n, descending, idx_out, sorted_out, options,
-                               ws, ws_bytes, stream, __func__);
+                               ws, ws_bytes, stream, __func__, 0, 0);
 }
 
 ds_status ds_random_permutation(uint64_t seed, uint64_t subsequence, uint64_t n, uint32_t* perm_out,
                                 void* ws, size_t* ws_bytes, void* stream) {
   // Philox keys are produced inside the encode kernel (nothing is read from HBM);
   // colliding 64-bit keys are ordered by row index, which keeps the result a permutation.
-  return ds::sort_indices_impl(ds::KIND_PHILOX, nullptr, 8, n, 0, perm_out, nullptr,
-                               DS_SORT_NO_PASS_SKIP, ws, ws_bytes, stream, __func__, seed,
-                               subsequence);
+  return ds::sort_indices_impl(ds::KIND_PHILOX, nullptr, 8, n, 0, perm_out, nullptr, 0, ws,
+                               ws_bytes, stream, __func__, seed, subsequence);
 }
 
 // Measurement hooks used by bench.py; not part of the reference-facing surface.

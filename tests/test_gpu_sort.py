@@ -348,3 +348,42 @@ def test_gather_staged_equals_plain(ds):
     for o in outs[1:]:
         assert bool((outs[0] == o).all())
     assert bool((outs[0].view(n, 90) == src.view(n, 90)[idx.long()]).all())
+
+
+def _arrow_order(col, kind, desc, width=0):
+    order = "descending" if desc else "ascending"
+    arr = O.fsb_from_numpy(col) if kind == "fsb" else pa.array(col)
+    return pa.compute.sort_indices(pa.table({"k": arr}), sort_keys=[("k", order)]).to_numpy()
+
+
+@pytest.mark.parametrize("desc", [False, True])
+def test_prefix_repair_mode_matches_full_sort(ds, desc):
+    """uniform keys take the prefix-sort + run-repair path; the result must equal both the
+    all-passes mode and Arrow, including planted short runs, duplicates (stability) and a
+    planted run that is too long for the repair kernel (verified fallback)."""
+    L = ds._lib
+    n = 400_000
+    rng = np.random.default_rng(12)
+    col = rng.integers(0, 256, (n, 10), dtype=np.uint8)
+    # short runs sharing 6 leading bytes, in random low-byte order, with exact duplicates
+    for s in range(0, 3000, 10):
+        rows = rng.choice(n, 7, replace=False)
+        col[rows, :6] = col[rows[0], :6]
+        col[rows[3]] = col[rows[1]]
+    want = _arrow_order(col, "fsb", desc)
+    a, sa = _argsort_c(ds, col, "fsb", desc, width=10)
+    b, sb = _argsort_c(ds, col, "fsb", desc, width=10, options=L.DS_SORT_NO_PREFIX_REPAIR)
+    assert np.array_equal(a.astype(np.int64), want) and np.array_equal(b, a)
+    assert np.array_equal(sa, sb) and np.array_equal(sa.reshape(n, 10), col[want])
+    # one run of 500 rows with equal 8-byte prefix: estimate still says "prefix mode"
+    rows = rng.choice(n, 500, replace=False)
+    col[rows, :8] = 77
+    want = _arrow_order(col, "fsb", desc)
+    a, sa = _argsort_c(ds, col, "fsb", desc, width=10)
+    assert np.array_equal(a.astype(np.int64), want)
+    assert np.array_equal(sa.reshape(n, 10), col[want])
+    # 64-bit keys take the same path
+    k = rng.integers(-(2**63), 2**63 - 1, n, dtype=np.int64)
+    k[::1000] = k[0]
+    a, _ = _argsort_c(ds, k, "i64", desc, want_sorted=False)
+    assert np.array_equal(a.astype(np.int64), _arrow_order(k, "i64", desc))
