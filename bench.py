@@ -253,6 +253,13 @@ def run_ours(args):
     peak, peak_src = measured_peak()
     achieved = n_pass_rows(world, n) * PASS_BYTES_PER_ROW / (pass_ms * 1e-3) / 1e9 if cnt.value else None
 
+    if world > 1 and os.environ.get("DS_DIST_TIMING") == "1":
+        from ray_memory_management_b200 import distributed as _D
+
+        one_step()  # collective: every rank takes part, rank 0 reports
+        if rank == 0:
+            print("dist phases (ms):", [(k, round(v, 2)) for k, v in _D.LAST_TIMING], file=sys.stderr)
+
     # ---- e2e: pinned host buffers in, pinned host buffers out
     e2e = None
     if not args.no_e2e:

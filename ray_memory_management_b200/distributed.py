@@ -27,6 +27,30 @@ import torch.distributed as dist
 
 SAMPLES_PER_RANK = 2048
 
+# Optional phase timing (DS_DIST_TIMING=1): CUDA events on the current stream; the list of
+# (phase, ms) of the last call is left in LAST_TIMING.  Measurement aid only.
+import os as _os
+
+_TIMING = _os.environ.get("DS_DIST_TIMING", "0") == "1"
+LAST_TIMING: list = []
+
+
+class _Phases:
+    def __init__(self):
+        self.ev = []
+
+    def mark(self, name):
+        if _TIMING:
+            e = torch.cuda.Event(enable_timing=True)
+            e.record()
+            self.ev.append((name, e))
+
+    def finish(self):
+        if _TIMING and self.ev:
+            torch.cuda.synchronize()
+            LAST_TIMING[:] = [(self.ev[i + 1][0], self.ev[i][1].elapsed_time(self.ev[i + 1][1]))
+                              for i in range(len(self.ev) - 1)]
+
 
 # ----------------------------------------------------------------------------- host logic
 def exchange_counts(counts: Sequence[int], group=None, device=None) -> np.ndarray:
@@ -96,6 +120,80 @@ def splitters_from_samples(samples: np.ndarray, arrow_type: pa.DataType, world: 
     return [srt[min(n - 1, (i * n) // world)] for i in range(1, world)]
 
 
+# ----------------------------------------------------------------------------- peer-memory exchange
+# The all-to-all-v without NCCL: every rank owns one symmetric (peer-mapped) receive buffer;
+# a sender copies each of its partitions straight into the destination GPU's buffer at the
+# offset its source rank owns there (copy engines over NVLink / NVSwitch, no SMs, no staging
+# on the receiver), so the receiver finds the chunks already concatenated in source-rank
+# order.  Device-side barriers on the buffer's signal pad order the phases.  Measured on
+# 2 x B200 this moves the 9 GB payload exchange from 28 ms (NCCL send/recv sharing SMs with
+# the radix sort) to copy-engine speed while the key sort runs.
+_EXCHANGE = _os.environ.get("DS_EXCHANGE", "p2p")  # "p2p" | "nccl"
+_peer_cache: dict = {}
+
+
+class _PeerBuffer:
+    def __init__(self, nbytes: int, group):
+        import torch.distributed._symmetric_memory as symm_mem
+
+        self.nbytes = nbytes
+        pg = group if group is not None else dist.group.WORLD
+        enable = getattr(symm_mem, "enable_symm_mem_for_group", None)
+        if enable is not None:  # needed by older torch, a deprecated no-op in newer ones
+            import warnings
+
+            with warnings.catch_warnings():
+                warnings.simplefilter("ignore")
+                try:
+                    enable(pg.group_name)
+                except Exception:
+                    pass
+        self.buf = symm_mem.empty(nbytes, dtype=torch.uint8, device=_dev())
+        self.hdl = symm_mem.rendezvous(self.buf, pg)
+        self.side = torch.cuda.Stream()
+
+
+def _peer_buffer(nbytes: int, group) -> "_PeerBuffer":
+    """Grow-only cache; collective (every rank calls with the same nbytes)."""
+    key = id(group) if group is not None else 0
+    pb = _peer_cache.get(key)
+    if pb is None or pb.nbytes < nbytes:
+        _peer_cache.pop(key, None)
+        pb = _PeerBuffer(int(nbytes * 1.25) + 4096, group)
+        _peer_cache[key] = pb
+    return pb
+
+
+def _align(x: int, a: int = 256) -> int:
+    return (x + a - 1) // a * a
+
+
+class _PeerLayout:
+    """Where each column's received rows live inside the symmetric buffer."""
+
+    def __init__(self, names, row_bytes, matrix: np.ndarray):
+        self.cap_rows = int(matrix.sum(axis=0).max())
+        self.off, total = {}, 0
+        for nme in names:
+            self.off[nme] = total
+            total += _align(self.cap_rows * row_bytes[nme])
+        self.total = max(total, 256)
+
+
+def _p2p_send_column(pb, layout, name, rb, send: torch.Tensor, matrix: np.ndarray, rank: int):
+    """Copy this rank's partitions of one column into every destination's buffer."""
+    world = matrix.shape[0]
+    offs = np.concatenate([[0], np.cumsum(matrix[rank])])
+    for step in range(world):
+        d = (rank + step) % world  # start with self, then rotate: every link gets used at once
+        rows = int(matrix[rank, d])
+        if rows == 0:
+            continue
+        before = int(matrix[:rank, d].sum())  # rows lower ranks place in d's buffer
+        dst = pb.hdl.get_buffer(d, (rows * rb,), torch.uint8, layout.off[name] + before * rb)
+        dst.copy_(send[int(offs[d]) * rb: int(offs[d + 1]) * rb], non_blocking=True)
+
+
 # ----------------------------------------------------------------------------- plans
 def _dev():
     return torch.device("cuda", torch.cuda.current_device())
@@ -125,6 +223,8 @@ def sort_block(block, key: str, descending: bool = False, group=None):
     world = dist.get_world_size(group)
     rank = dist.get_rank(group)
     dev = _dev()
+    ph = _Phases()
+    ph.mark("start")
     width, ktype = _key_width(block, key, group)
     local = _sample_local(block, key)
     if local.shape[1] != width:
@@ -138,29 +238,72 @@ def sort_block(block, key: str, descending: bool = False, group=None):
 
     acc = DeviceArrowBlockAccessor(block)
     sort_key = [(key, "descending" if descending else "ascending")]
+    ph.mark("sample+splitters")
     parts = acc.partition_unsorted(boundaries, sort_key, descending)
     counts = [p.num_rows for p in parts]
+    ph.mark("partition")
     matrix = exchange_counts(counts, group, dev)
     names = block.column_names
     send = _spanning(parts, names, dev)
     n_recv = int(matrix[:, rank].sum())
 
-    # keys first; sort them while the payload columns are still being exchanged
-    recv_key, _ = alltoallv_rows(send[key], width, matrix, group)
-    pending = []
-    for name in names:
-        if name == key:
-            continue
-        rb = block.columns[name].row_bytes
-        r, work = alltoallv_rows(send[name], rb, matrix, group, async_op=True)
-        pending.append((name, r, work))
-    keycol = DeviceColumn(ktype, recv_key)
-    idx, sorted_key = _argsort(keycol, descending, want_sorted=True)
+    use_p2p = _EXCHANGE == "p2p" and world > 1 and dist.get_backend(group) == "nccl"
+    if use_p2p:
+        try:
+            rbs = {nm: block.columns[nm].row_bytes for nm in names}
+            layout = _PeerLayout(names, rbs, matrix)
+            pb = _peer_buffer(layout.total, group)
+        except Exception as e:  # symmetric memory unavailable on this system: NCCL path
+            import warnings
+
+            warnings.warn(f"peer-memory exchange unavailable ({e!r}); using NCCL all_to_all")
+            use_p2p = False
+    ph.mark("counts")
     cols = collections.OrderedDict()
     got = {}
-    for name, r, work in pending:
-        work.wait()
-        got[name] = _gather(DeviceColumn(block.columns[name].type, r), idx)
+    if use_p2p:
+        main = torch.cuda.current_stream()
+        pb.hdl.barrier(channel=0)  # every rank is done with the buffer's previous contents
+        _p2p_send_column(pb, layout, key, width, send[key], matrix, rank)
+        pb.side.wait_stream(main)
+        with torch.cuda.stream(pb.side):  # payload copies run beside the key sort
+            for name in names:
+                if name != key:
+                    _p2p_send_column(pb, layout, name, rbs[name], send[name], matrix, rank)
+                    send[name].record_stream(pb.side)
+        pb.hdl.barrier(channel=1)  # all keys have landed everywhere
+        ph.mark("p2p keys")
+        keycol = DeviceColumn(ktype, pb.buf[layout.off[key]: layout.off[key] + n_recv * width])
+        idx, sorted_key = _argsort(keycol, descending, want_sorted=True)
+        ph.mark("key sort")
+        main.wait_stream(pb.side)
+        pb.hdl.barrier(channel=2)  # all payload rows have landed everywhere
+        ph.mark("wait payload")
+        for name in names:
+            if name != key:
+                view = pb.buf[layout.off[name]: layout.off[name] + n_recv * rbs[name]]
+                got[name] = _gather(DeviceColumn(block.columns[name].type, view), idx)
+        ph.mark("gather payload")
+    else:
+        # keys first; sort them while the payload columns are still being exchanged
+        recv_key, _ = alltoallv_rows(send[key], width, matrix, group)
+        ph.mark("a2a keys")
+        pending = []
+        for name in names:
+            if name == key:
+                continue
+            rb = block.columns[name].row_bytes
+            r, work = alltoallv_rows(send[name], rb, matrix, group, async_op=True)
+            pending.append((name, r, work))
+        keycol = DeviceColumn(ktype, recv_key)
+        idx, sorted_key = _argsort(keycol, descending, want_sorted=True)
+        ph.mark("key sort")
+        for name, r, work in pending:
+            work.wait()
+            ph.mark("wait " + name)
+            got[name] = _gather(DeviceColumn(block.columns[name].type, r), idx)
+            ph.mark("gather " + name)
+    ph.finish()
     for name in names:
         cols[name] = sorted_key if name == key else got[name]
     return DeviceArrowBlock(cols, n_recv)
