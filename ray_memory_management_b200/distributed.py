@@ -151,6 +151,7 @@ class _PeerBuffer:
         self.buf = symm_mem.empty(nbytes, dtype=torch.uint8, device=_dev())
         self.hdl = symm_mem.rendezvous(self.buf, pg)
         self.side = torch.cuda.Stream()
+        self.lanes = [torch.cuda.Stream() for _ in range(self.hdl.world_size)]  # one per destination
 
 
 def _peer_buffer(nbytes: int, group) -> "_PeerBuffer":
@@ -180,18 +181,30 @@ class _PeerLayout:
         self.total = max(total, 256)
 
 
-def _p2p_send_column(pb, layout, name, rb, send: torch.Tensor, matrix: np.ndarray, rank: int):
-    """Copy this rank's partitions of one column into every destination's buffer."""
+def _p2p_send_column(pb, layout, name, rb, send: torch.Tensor, matrix: np.ndarray, rank: int,
+                     after: "torch.cuda.Stream"):
+    """Copy this rank's partitions of one column into every destination's buffer, one CUDA
+    stream per destination so that the copy engines drive all NVLink directions at once.
+    The copies start after the work already queued on ``after``."""
     world = matrix.shape[0]
     offs = np.concatenate([[0], np.cumsum(matrix[rank])])
     for step in range(world):
-        d = (rank + step) % world  # start with self, then rotate: every link gets used at once
+        d = (rank + step) % world
         rows = int(matrix[rank, d])
         if rows == 0:
             continue
         before = int(matrix[:rank, d].sum())  # rows lower ranks place in d's buffer
         dst = pb.hdl.get_buffer(d, (rows * rb,), torch.uint8, layout.off[name] + before * rb)
-        dst.copy_(send[int(offs[d]) * rb: int(offs[d + 1]) * rb], non_blocking=True)
+        lane = pb.lanes[d]
+        lane.wait_stream(after)
+        with torch.cuda.stream(lane):
+            dst.copy_(send[int(offs[d]) * rb: int(offs[d + 1]) * rb], non_blocking=True)
+        send.record_stream(lane)
+
+
+def _join_lanes(pb, stream):
+    for lane in pb.lanes:
+        stream.wait_stream(lane)
 
 
 # ----------------------------------------------------------------------------- plans
@@ -264,19 +277,17 @@ def sort_block(block, key: str, descending: bool = False, group=None):
     if use_p2p:
         main = torch.cuda.current_stream()
         pb.hdl.barrier(channel=0)  # every rank is done with the buffer's previous contents
-        _p2p_send_column(pb, layout, key, width, send[key], matrix, rank)
-        pb.side.wait_stream(main)
-        with torch.cuda.stream(pb.side):  # payload copies run beside the key sort
-            for name in names:
-                if name != key:
-                    _p2p_send_column(pb, layout, name, rbs[name], send[name], matrix, rank)
-                    send[name].record_stream(pb.side)
+        _p2p_send_column(pb, layout, key, width, send[key], matrix, rank, main)
+        _join_lanes(pb, main)
         pb.hdl.barrier(channel=1)  # all keys have landed everywhere
+        for name in names:  # payload copies run beside the key sort
+            if name != key:
+                _p2p_send_column(pb, layout, name, rbs[name], send[name], matrix, rank, main)
         ph.mark("p2p keys")
         keycol = DeviceColumn(ktype, pb.buf[layout.off[key]: layout.off[key] + n_recv * width])
         idx, sorted_key = _argsort(keycol, descending, want_sorted=True)
         ph.mark("key sort")
-        main.wait_stream(pb.side)
+        _join_lanes(pb, main)
         pb.hdl.barrier(channel=2)  # all payload rows have landed everywhere
         ph.mark("wait payload")
         for name in names:
