@@ -49,6 +49,8 @@ def parse_args():
     p.add_argument("--cpu-rows", type=int, default=4_000_000,
                    help="rows of the bounded CPU-baseline sample")
     p.add_argument("--no-e2e", action="store_true")
+    p.add_argument("--e2e-inflight", type=int, default=2,
+                   help="single-GPU e2e: steps in flight (2 = H2D of step k+1 overlaps D2H of step k)")
     p.add_argument("--no-cpu-baseline", action="store_true")
     p.add_argument("--radix-config", type=int, default=-1, help="tuning: pass-kernel variant")
     p.add_argument("--gather-mode", type=int, default=-1, help="tuning: see csrc/gather.cu g_gather_mode")
@@ -249,6 +251,14 @@ def run_ours(args):
     ms_per_step = ms / args.steps
     value = world * n * ROW_BYTES / (ms_per_step * 1e-3) / 1e9
 
+    traffic = None
+    try:
+        with open(os.path.join(ROOT, "profiles", "r01_pass_kernel_traffic.json")) as f:
+            tj = json.load(f)
+        # ncu-measured DRAM bytes per row of one pass launch, scaled to this launch's rows
+        traffic = tj["traffic_bytes_per_row"] * n_pass_rows(world, n)
+    except Exception:
+        pass
     pass_ms = tot_ms.value / max(cnt.value, 1)
     peak, peak_src = measured_peak()
     achieved = n_pass_rows(world, n) * PASS_BYTES_PER_ROW / (pass_ms * 1e-3) / 1e9 if cnt.value else None
@@ -288,7 +298,9 @@ def run_ours(args):
         "roofline": {
             "kernel": "onesweep_pass_kernel (one 8-bit LSD pass over key80+idx32)",
             "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
-            "frac": (achieved / peak) if achieved else None, "traffic": None,
+            "frac": (achieved / peak) if achieved else None, "traffic": traffic,
+            "traffic_source": "ncu dram__bytes_read.sum+dram__bytes_write.sum per launch, "
+                              "profiles/r01_pass_kernel_traffic.json",
             "peak_source": peak_src, "launches_timed": cnt.value, "avg_launch_ms": pass_ms,
             "bytes_per_row_per_launch": PASS_BYTES_PER_ROW,
         },
@@ -334,12 +346,36 @@ def run_e2e(args, ds, block, n, world, rank, barrier):
         out.to_host_buffers([ok, op])
         return out.num_rows
 
-    step()
+    # Single GPU: two steps in flight on two streams, each with its own pinned output
+    # buffers, so step k's D2H overlaps step k+1's H2D (PCIe is full duplex).  Every step
+    # still copies its whole input in and its whole result out inside the timed region.
+    inflight = 2 if (world == 1 and args.e2e_inflight >= 2) else 1
+    outs = [(ok, op)]
+    streams = [torch.cuda.current_stream()]
+    if inflight == 2:
+        outs.append((torch.empty_like(ok, pin_memory=True), torch.empty_like(op, pin_memory=True)))
+        streams = [torch.cuda.Stream(), torch.cuda.Stream()]
+
+    def step_on(i):
+        nonlocal ok, op
+        ok, op = outs[i % inflight]
+        if inflight == 1:
+            return step()
+        with torch.cuda.stream(streams[i % inflight]):
+            return step()
+
+    for i in range(inflight):
+        step_on(i)
     barrier()
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    cur = torch.cuda.current_stream()
     ev0.record()
-    for _ in range(args.steps):
-        step()
+    for st in streams:
+        st.wait_stream(cur)
+    for i in range(args.steps):
+        step_on(i)
+    for st in streams:
+        cur.wait_stream(st)
     ev1.record()
     barrier()
     ms = ev0.elapsed_time(ev1)
@@ -354,7 +390,7 @@ def run_e2e(args, ds, block, n, world, rank, barrier):
         assert bytes(a[0].tolist()) <= bytes(a[7].tolist())
     return {"value": world * n * ROW_BYTES / (per * 1e-3) / 1e9, "unit": UNIT,
             "h2d_bytes_per_step": world * n * ROW_BYTES, "d2h_bytes_per_step": world * n * ROW_BYTES,
-            "ms_per_step": per}
+            "ms_per_step": per, "steps_in_flight": inflight}
 
 
 # ------------------------------------------------------------------------------ reference arm

@@ -358,6 +358,7 @@ __global__ void __launch_bounds__(THREADS, MIN_BLOCKS)
 
 }  // namespace ds
 #include "onesweep_v2.cuh"
+#include "onesweep_v3.cuh"
 namespace ds {
 
 // ---------------------------------------------------------------- decode
@@ -447,7 +448,7 @@ struct PassTimer {
 struct PassConfig {
   int threads, items;
 };
-static int g_cfg = 6;  // tuning knob (ds_debug_set_radix_config); 6 = v2 <384 x 12>, best measured
+static int g_cfg = 18;  // tuning knob (ds_debug_set_radix_config); 18 = v3 table match <384 x 12>, best measured
 
 template <typename K>
 static cudaError_t set_smem_attr(K k, int bytes, unsigned long long* done_mask) {
@@ -477,6 +478,25 @@ static cudaError_t launch_pass_t(const uint64_t* hi_in, const uint16_t* lo_in,
     ds::note_launch();
     k<<<tiles, THREADS, S::BYTES, s>>>(hi_in, lo_in, idx_in, hi_out, lo_out, idx_out, n, shift,
                                        bin_base, lookback, tile_counter);
+  } else if (VARIANT >= 4) {
+    constexpr bool TABLE = VARIANT == 4 || VARIANT == 5;
+    constexpr bool PACKED = VARIANT == 4 || VARIANT == 6;
+    using S3 = PassSmemV3<THREADS, ITEMS, PACKED, HAS_LO>;
+    auto kf = onesweep_pass_kernel_v3<THREADS, ITEMS, MIN_BLOCKS, HAS_LO, DIGIT_LO, GEN_IDX, true, TABLE, PACKED>;
+    auto kt = onesweep_pass_kernel_v3<THREADS, ITEMS, MIN_BLOCKS, HAS_LO, DIGIT_LO, GEN_IDX, false, TABLE, PACKED>;
+    if ((e = set_smem_attr(kf, S3::BYTES, &done_a)) != cudaSuccess) return e;
+    if ((e = set_smem_attr(kt, S3::BYTES, &done_b)) != cudaSuccess) return e;
+    const uint32_t full_tiles = n / S::TILE;
+    if (full_tiles) {
+      ds::note_launch();
+      kf<<<full_tiles, THREADS, S3::BYTES, s>>>(hi_in, lo_in, idx_in, hi_out, lo_out, idx_out, n,
+                                                shift, bin_base, lookback, tile_counter);
+    }
+    if (tiles > full_tiles) {
+      ds::note_launch();
+      kt<<<1, THREADS, S3::BYTES, s>>>(hi_in, lo_in, idx_in, hi_out, lo_out, idx_out, n, shift,
+                                       bin_base, lookback, tile_counter);
+    }
   } else {
     // full tiles first, then (stream-ordered) the ragged last tile as tile id `full_tiles`
     constexpr bool M = VARIANT == 3;
@@ -523,17 +543,29 @@ static cudaError_t launch_pass_cfg(bool has_lo, bool digit_lo, bool gen_idx, con
 #undef DS_PASS
 }
 
-constexpr int NUM_CFGS = 17;
+// (variant, threads, items, min blocks per SM); variant 1 = first kernel, 2 = v2 ballots,
+// 3 = v2 match.any, 4 = v3 table+packed, 5 = v3 table, 6 = v3 packed
+#define DS_PASS_CONFIGS(X) \
+  X(0, 1, 256, 16, 2) X(4, 2, 512, 8, 2) X(6, 2, 384, 12, 2) X(7, 2, 256, 12, 3) \
+  X(11, 3, 384, 12, 2) X(17, 4, 384, 12, 2) X(18, 5, 384, 12, 2) X(19, 6, 384, 12, 2) \
+  X(20, 4, 512, 8, 2) X(21, 5, 256, 12, 3) X(25, 5, 512, 8, 2)
+constexpr int NUM_CFGS = 26;  // ids are sparse: unknown ids are rejected
+
+static bool cfg_known(int cfg) {
+  switch (cfg) {
+#define X(id, v, t, i, m) case id:
+    DS_PASS_CONFIGS(X)
+#undef X
+    return true;
+    default: return false;
+  }
+}
+
 static int cfg_tile(int cfg) {
   switch (cfg) {
-    case 1: case 4: case 9: return 512 * 8;
-    case 2: case 6: case 11: return 384 * 12;
-    case 3: case 7: case 12: return 256 * 12;
-    case 8: return 256 * 8;
-    case 13: return 256 * 10;
-    case 14: return 384 * 8;
-    case 15: return 512 * 10;
-    case 16: return 640 * 8;
+#define X(id, v, t, i, m) case id: return t * i;
+    DS_PASS_CONFIGS(X)
+#undef X
     default: return 256 * 16;
   }
 }
@@ -543,29 +575,16 @@ static cudaError_t launch_pass(int cfg, bool has_lo, bool digit_lo, bool gen_idx
                                uint64_t* hi_out, uint16_t* lo_out, uint32_t* idx_out, uint32_t n,
                                int shift, const uint32_t* bin_base, uint32_t* lookback,
                                uint32_t* tile_counter, cudaStream_t s) {
-#define DS_ARGS                                                                                  \
-  has_lo, digit_lo, gen_idx, hi_in, lo_in, idx_in, hi_out, lo_out, idx_out, n, shift, bin_base,  \
-      lookback, tile_counter, s
   switch (cfg) {
-    case 1: return launch_pass_cfg<1, 512, 8, 2>(DS_ARGS);
-    case 2: return launch_pass_cfg<1, 384, 12, 2>(DS_ARGS);
-    case 3: return launch_pass_cfg<1, 256, 12, 3>(DS_ARGS);
-    case 4: return launch_pass_cfg<2, 512, 8, 2>(DS_ARGS);
-    case 5: return launch_pass_cfg<2, 256, 16, 2>(DS_ARGS);
-    case 6: return launch_pass_cfg<2, 384, 12, 2>(DS_ARGS);
-    case 7: return launch_pass_cfg<2, 256, 12, 3>(DS_ARGS);
-    case 8: return launch_pass_cfg<2, 256, 8, 4>(DS_ARGS);
-    case 9: return launch_pass_cfg<3, 512, 8, 2>(DS_ARGS);
-    case 10: return launch_pass_cfg<3, 256, 16, 2>(DS_ARGS);
-    case 11: return launch_pass_cfg<3, 384, 12, 2>(DS_ARGS);
-    case 12: return launch_pass_cfg<3, 256, 12, 3>(DS_ARGS);
-    case 13: return launch_pass_cfg<2, 256, 10, 3>(DS_ARGS);
-    case 14: return launch_pass_cfg<2, 384, 8, 2>(DS_ARGS);
-    case 15: return launch_pass_cfg<2, 512, 10, 1>(DS_ARGS);
-    case 16: return launch_pass_cfg<2, 640, 8, 1>(DS_ARGS);
-    default: return launch_pass_cfg<1, 256, 16, 2>(DS_ARGS);
+#define X(id, v, t, i, m)                                                                        \
+  case id:                                                                                       \
+    return launch_pass_cfg<v, t, i, m>(has_lo, digit_lo, gen_idx, hi_in, lo_in, idx_in, hi_out,  \
+                                       lo_out, idx_out, n, shift, bin_base, lookback,            \
+                                       tile_counter, s);
+    DS_PASS_CONFIGS(X)
+#undef X
+    default: return cudaErrorInvalidValue;
   }
-#undef DS_ARGS
 }
 
 static PassList make_passes(int kind, uint32_t width) {
@@ -828,7 +847,7 @@ int32_t ds_debug_collect_pass_timing(double* total_ms, int32_t* launches) {
 // Tuning hook used by bench.py --sweep; not part of the reference-facing surface.
 int32_t ds_debug_set_radix_config(int32_t cfg) {
   int old = ds::g_cfg;
-  if (cfg >= 0 && cfg < ds::NUM_CFGS) ds::g_cfg = cfg;
+  if (cfg >= 0 && cfg < ds::NUM_CFGS && ds::cfg_known(cfg)) ds::g_cfg = cfg;
   return old;
 }
 
