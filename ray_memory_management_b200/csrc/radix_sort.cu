@@ -89,6 +89,36 @@ __global__ void __launch_bounds__(512) encode_hist_kernel(const void* __restrict
   }
 }
 
+// Digit histograms of every `stride`-th key only: a cheap estimate of how well the leading
+// digits separate the rows (the plan choice in sort_indices_impl), nothing is written back.
+template <int KIND>
+__global__ void __launch_bounds__(256) sample_hist_kernel(const void* __restrict__ col, uint32_t width,
+                                                          uint32_t n, bool desc, uint32_t stride,
+                                                          PassList pl, uint32_t* __restrict__ ghist) {
+  __shared__ uint32_t sh[MAX_PASSES * RADIX];
+  for (int i = threadIdx.x; i < pl.count * RADIX; i += blockDim.x) sh[i] = 0;
+  __syncthreads();
+  const uint32_t ns = (n + stride - 1) / stride;
+  for (uint32_t j = blockIdx.x * blockDim.x + threadIdx.x; j < ns; j += gridDim.x * blockDim.x) {
+    uint64_t hi;
+    uint32_t lo;
+    load_key<KIND>(col, width, static_cast<uint64_t>(j) * stride, desc, hi, lo);
+#pragma unroll
+    for (int p = 0; p < MAX_PASSES; ++p) {
+      if (p < pl.count) {
+        const uint32_t d = pl.from_lo[p] ? (lo >> pl.shift[p]) & 255u
+                                         : static_cast<uint32_t>(hi >> pl.shift[p]) & 255u;
+        atomicAdd(&sh[p * RADIX + d], 1u);
+      }
+    }
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < pl.count * RADIX; i += blockDim.x) {
+    const uint32_t c = sh[i];
+    if (c) atomicAdd(&ghist[i], c);
+  }
+}
+
 // One block of 256 threads per digit position.
 __global__ void scan_hist_kernel(const uint32_t* __restrict__ ghist, uint32_t n,
                                  uint32_t* __restrict__ bin_base, uint32_t* __restrict__ skip,
@@ -684,52 +714,77 @@ static ds_status sort_indices_impl(int kind, const void* col, uint32_t width, ui
   uint32_t* too_long = tile_counters + 2 * MAX_PASSES;
   const bool desc = descending != 0;
 
-  DS_CUDA(cudaMemsetAsync(ctrl, 0, sizeof(uint32_t) * (MAX_PASSES * RADIX * 2 + 4 * MAX_PASSES), s));
+  const size_t ctrl_bytes = sizeof(uint32_t) * (MAX_PASSES * RADIX * 2 + 4 * MAX_PASSES);
+  DS_CUDA(cudaMemsetAsync(ctrl, 0, ctrl_bytes, s));
   cudaError_t e;
-  switch (kind) {
-    case KIND_I64: e = launch_encode<KIND_I64>(has_lo, col, width, n, desc, hi[0], lo[0], pl, ghist, s); break;
-    case KIND_U64: e = launch_encode<KIND_U64>(has_lo, col, width, n, desc, hi[0], lo[0], pl, ghist, s); break;
-    case KIND_F64: e = launch_encode<KIND_F64>(has_lo, col, width, n, desc, hi[0], lo[0], pl, ghist, s); break;
-    case KIND_PHILOX: e = launch_encode<KIND_PHILOX>(false, nullptr, 8, n, false, hi[0], lo[0], pl, ghist, s, seed, subseq); break;
-    default: e = launch_encode<KIND_FSB>(has_lo, col, width, n, desc, hi[0], lo[0], pl, ghist, s); break;
-  }
-  DS_CUDA(e);
-  ds::note_launch(); scan_hist_kernel<<<pl.count, RADIX, 0, s>>>(ghist, n, bin_base, skip, coll);
-  DS_LAUNCH_CHECK();
 
-  uint32_t skip_h[MAX_PASSES] = {0};
-  float coll_h[MAX_PASSES] = {0};
-  if (!(options & DS_SORT_NO_PASS_SKIP)) {
-    uint32_t back[3 * MAX_PASSES];  // skip | tile_counters (unused here) | coll
-    DS_CUDA(cudaMemcpyAsync(back, skip, sizeof(back), cudaMemcpyDeviceToHost, s));
-    DS_CUDA(cudaStreamSynchronize(s));  // host sync #1: 120 bytes
-    memcpy(skip_h, back, sizeof(skip_h));
-    memcpy(coll_h, back + 2 * MAX_PASSES, sizeof(coll_h));
-  }
-  int exec[MAX_PASSES], ne = 0;
-  for (int p = 0; p < pl.count; ++p)
-    if (!skip_h[p]) exec[ne++] = p;
-
-  // Prefix sort + run repair: if the digit histograms say that the top m digits alone
-  // already separate almost all rows (expected colliding pairs <= 2% of n, digits taken as
-  // independent), run only those m passes and let repair_runs_kernel order the few short
-  // runs of equal prefixes by the full key.  The estimate is only a heuristic: the repair
-  // kernel VERIFIES every run, and a run it cannot handle sends us back to the full sort.
+  // ---- plan.  Prefix sort + run repair: if the leading m digits alone already separate
+  // almost all rows (expected colliding pairs <= 2% of n, digits taken as independent), run
+  // only those m passes and let repair_runs_kernel order the few short runs of equal
+  // prefixes by the full key.  The decision uses digit histograms of a ~1M-key sample (or
+  // the known uniformity of Philox keys); it is only a heuristic: the repair kernel VERIFIES
+  // every run, and a run it cannot handle sends the call back to the all-passes plan.
+  PassList run = pl;  // the digit positions that get exact histograms (and passes)
   int prefix_shift = -1;
-  if (!(options & (DS_SORT_NO_PASS_SKIP | DS_SORT_NO_PREFIX_REPAIR)) && n >= (1u << 16) && ne >= 3) {
+  if (!(options & (DS_SORT_NO_PASS_SKIP | DS_SORT_NO_PREFIX_REPAIR)) && n >= (1u << 16) &&
+      pl.count >= 3) {
+    float coll_h[MAX_PASSES];
+    if (kind == KIND_PHILOX) {
+      for (int p = 0; p < pl.count; ++p) coll_h[p] = 1.0f / 256.0f;
+    } else {
+      const uint32_t stride = n > (1u << 20) ? n >> 20 : 1;
+      const uint32_t ns = (n + stride - 1) / stride;
+      const int blocks = static_cast<int>((ns + 255) / 256 < 1184u ? (ns + 255) / 256 : 1184u);
+      ds::note_launch();
+      switch (kind) {
+        case KIND_I64: sample_hist_kernel<KIND_I64><<<blocks, 256, 0, s>>>(col, width, n, desc, stride, pl, ghist); break;
+        case KIND_U64: sample_hist_kernel<KIND_U64><<<blocks, 256, 0, s>>>(col, width, n, desc, stride, pl, ghist); break;
+        case KIND_F64: sample_hist_kernel<KIND_F64><<<blocks, 256, 0, s>>>(col, width, n, desc, stride, pl, ghist); break;
+        default: sample_hist_kernel<KIND_FSB><<<blocks, 256, 0, s>>>(col, width, n, desc, stride, pl, ghist); break;
+      }
+      DS_LAUNCH_CHECK();
+      ds::note_launch(); scan_hist_kernel<<<pl.count, RADIX, 0, s>>>(ghist, ns, bin_base, skip, coll);
+      DS_LAUNCH_CHECK();
+      DS_CUDA(cudaMemcpyAsync(coll_h, coll, sizeof(coll_h), cudaMemcpyDeviceToHost, s));
+      DS_CUDA(cudaMemsetAsync(ctrl, 0, ctrl_bytes, s));
+      DS_CUDA(cudaStreamSynchronize(s));  // host sync: 40 bytes
+    }
     double pairs = 0.5 * static_cast<double>(n) * static_cast<double>(n);
-    for (int m = 1; m <= ne - 2; ++m) {
-      const int p = exec[ne - m];
+    for (int m = 1; m <= pl.count - 2; ++m) {
+      const int p = pl.count - m;
       if (pl.from_lo[p]) break;  // the prefix must lie inside `hi`
       pairs *= static_cast<double>(coll_h[p]);
       if (pairs <= 0.02 * static_cast<double>(n)) {
         prefix_shift = pl.shift[p];
-        for (int k = 0; k < m; ++k) exec[k] = exec[ne - m + k];
-        ne = m;
+        run.count = m;
+        for (int k = 0; k < m; ++k) {
+          run.shift[k] = pl.shift[p + k];
+          run.from_lo[k] = pl.from_lo[p + k];
+        }
         break;
       }
     }
   }
+
+  switch (kind) {
+    case KIND_I64: e = launch_encode<KIND_I64>(has_lo, col, width, n, desc, hi[0], lo[0], run, ghist, s); break;
+    case KIND_U64: e = launch_encode<KIND_U64>(has_lo, col, width, n, desc, hi[0], lo[0], run, ghist, s); break;
+    case KIND_F64: e = launch_encode<KIND_F64>(has_lo, col, width, n, desc, hi[0], lo[0], run, ghist, s); break;
+    case KIND_PHILOX: e = launch_encode<KIND_PHILOX>(false, nullptr, 8, n, false, hi[0], lo[0], run, ghist, s, seed, subseq); break;
+    default: e = launch_encode<KIND_FSB>(has_lo, col, width, n, desc, hi[0], lo[0], run, ghist, s); break;
+  }
+  DS_CUDA(e);
+  ds::note_launch(); scan_hist_kernel<<<run.count, RADIX, 0, s>>>(ghist, n, bin_base, skip, coll);
+  DS_LAUNCH_CHECK();
+
+  uint32_t skip_h[MAX_PASSES] = {0};
+  if (prefix_shift < 0 && !(options & DS_SORT_NO_PASS_SKIP)) {
+    DS_CUDA(cudaMemcpyAsync(skip_h, skip, sizeof(skip_h), cudaMemcpyDeviceToHost, s));
+    DS_CUDA(cudaStreamSynchronize(s));  // host sync: 40 bytes (constant digits are skipped)
+  }
+  int exec[MAX_PASSES], ne = 0;
+  for (int p = 0; p < run.count; ++p)
+    if (!skip_h[p]) exec[ne++] = p;
 
   int cur = 0;
   if (ne == 0) {
@@ -741,8 +796,8 @@ static ds_status sort_indices_impl(int kind, const void* col, uint32_t width, ui
     const int p = exec[j];
     uint32_t* idx_dst = ((ne - 1 - j) % 2 == 0) ? idx_out : idx_alt;
     DS_CUDA(cudaMemsetAsync(lookback, 0, sizeof(uint32_t) * static_cast<size_t>(tiles) * RADIX, s));
-    DS_CUDA(launch_pass(cfg, has_lo, pl.from_lo[p] != 0, j == 0, hi[cur], lo[cur], idx_src,
-                        hi[cur ^ 1], lo[cur ^ 1], idx_dst, n, pl.shift[p], bin_base + p * RADIX,
+    DS_CUDA(launch_pass(cfg, has_lo, run.from_lo[p] != 0, j == 0, hi[cur], lo[cur], idx_src,
+                        hi[cur ^ 1], lo[cur ^ 1], idx_dst, n, run.shift[p], bin_base + p * RADIX,
                         lookback, tile_counters + p, s));
     idx_src = idx_dst;
     cur ^= 1;
