@@ -12,7 +12,7 @@
 
 namespace ds {
 
-static int g_gather_mode = 0;  // 0 auto, 1 plain, 2 plain + L2::64B, 3 staged, 4 staged + L2::64B
+static int g_gather_mode = 0;  // 0 auto, 1 plain, 2 plain + L2::64B, 3 staged, 4 staged + L2::64B, 5 direct (no smem idx)
 
 // Read-only loads that ask L2 to fetch only 64 bytes around a miss: random rows gain
 // nothing from the default 128-byte fetch, it only multiplies DRAM traffic.
@@ -57,6 +57,44 @@ __global__ void __launch_bounds__(256) gather_single_kernel(const G* __restrict_
 constexpr int GATHER_THREADS = 256;
 constexpr int GATHER_MAX_ROWS = 1024;
 
+// Same work without the shared-memory index stage: every element reads its row number
+// through L1 (consecutive lanes share it), so a block never waits at a barrier.
+template <typename G, bool HINT>
+__global__ void __launch_bounds__(GATHER_THREADS)
+    gather_rows_direct_kernel(const G* __restrict__ src, const uint32_t* __restrict__ idx,
+                              G* __restrict__ dst, uint32_t n, uint32_t gpr, uint32_t rows_per_block,
+                              uint32_t magic) {
+  const uint32_t row0 = blockIdx.x * rows_per_block;
+  const uint32_t rows = min(rows_per_block, n - row0);
+  const uint32_t total = rows * gpr;
+  const uint32_t* ib = idx + row0;
+  G* out = dst + static_cast<uint64_t>(row0) * gpr;
+  constexpr int UNROLL = 16;
+  uint32_t e = threadIdx.x;
+  for (; e + (UNROLL - 1) * GATHER_THREADS < total; e += UNROLL * GATHER_THREADS) {
+    uint32_t rr[UNROLL], ii[UNROLL];
+#pragma unroll
+    for (int k = 0; k < UNROLL; ++k) {
+      rr[k] = __umulhi(e + k * GATHER_THREADS, magic);
+      ii[k] = __ldg(ib + rr[k]);
+    }
+    G v[UNROLL];
+#pragma unroll
+    for (int k = 0; k < UNROLL; ++k) {
+      const uint32_t ee = e + k * GATHER_THREADS;
+      const G* p = src + static_cast<uint64_t>(ii[k]) * gpr + (ee - rr[k] * gpr);
+      v[k] = HINT ? ld_nc_64B(p) : __ldg(p);
+    }
+#pragma unroll
+    for (int k = 0; k < UNROLL; ++k) st_stream(out + e + k * GATHER_THREADS, v[k]);
+  }
+  for (; e < total; e += GATHER_THREADS) {
+    const uint32_t r = __umulhi(e, magic);
+    const G* p = src + static_cast<uint64_t>(__ldg(ib + r)) * gpr + (e - r * gpr);
+    st_stream(out + e, HINT ? ld_nc_64B(p) : __ldg(p));
+  }
+}
+
 template <typename G, bool HINT>
 __global__ void __launch_bounds__(GATHER_THREADS)
     gather_rows_kernel(const G* __restrict__ src, const uint32_t* __restrict__ idx,
@@ -69,15 +107,28 @@ __global__ void __launch_bounds__(GATHER_THREADS)
   __syncthreads();
   const uint32_t total = rows * gpr;
   G* out = dst + static_cast<uint64_t>(row0) * gpr;
-#pragma unroll 4
-  for (uint32_t e = threadIdx.x; e < total; e += GATHER_THREADS) {
-    const uint32_t r = __umulhi(e, magic);  // e / gpr, exact for e*gpr < 2^32
-    const uint32_t c = e - r * gpr;
-    const G* p = src + static_cast<uint64_t>(s_idx[r]) * gpr + c;
+  // The loop is latency bound (2..16 useful bytes per load): keep UNROLL independent loads
+  // in flight per thread before the first store.
+  constexpr int UNROLL = 16;
+  uint32_t e = threadIdx.x;
+  for (; e + (UNROLL - 1) * GATHER_THREADS < total; e += UNROLL * GATHER_THREADS) {
+    G v[UNROLL];
+#pragma unroll
+    for (int k = 0; k < UNROLL; ++k) {
+      const uint32_t ee = e + k * GATHER_THREADS;
+      const uint32_t r = __umulhi(ee, magic);  // ee / gpr, exact for ee*gpr < 2^32
+      const G* p = src + static_cast<uint64_t>(s_idx[r]) * gpr + (ee - r * gpr);
+      v[k] = HINT ? ld_nc_64B(p) : __ldg(p);
+    }
+#pragma unroll
+    for (int k = 0; k < UNROLL; ++k) st_stream(out + e + k * GATHER_THREADS, v[k]);
+  }
+  for (; e < total; e += GATHER_THREADS) {
+    const uint32_t r = __umulhi(e, magic);
+    const G* p = src + static_cast<uint64_t>(s_idx[r]) * gpr + (e - r * gpr);
     st_stream(out + e, HINT ? ld_nc_64B(p) : __ldg(p));
   }
 }
-
 
 // ---- staged gather for rows that are not a multiple of 16 bytes (e.g. 90-byte payloads)
 // Phase 1 pulls every source row in as ALIGNED 16-byte vectors (the aligned span that
@@ -116,6 +167,7 @@ __global__ void __launch_bounds__(STAGE_THREADS)
   __syncthreads();
 
   const uint32_t items = rows * chunks;
+#pragma unroll 4
   for (uint32_t e = threadIdx.x; e < items; e += STAGE_THREADS) {
     const uint32_t r = __umulhi(e, magic_c);
     const uint32_t c = e - r * chunks;
@@ -207,6 +259,9 @@ static cudaError_t launch_gather(const void* src, const uint32_t* idx, void* dst
   ds::note_launch();
   if (g_gather_mode == 1)
     gather_rows_kernel<G, false><<<blocks, GATHER_THREADS, 0, s>>>(
+        static_cast<const G*>(src), idx, static_cast<G*>(dst), n, gpr, rows, magic);
+  else if (g_gather_mode == 5)
+    gather_rows_direct_kernel<G, true><<<blocks, GATHER_THREADS, 0, s>>>(
         static_cast<const G*>(src), idx, static_cast<G*>(dst), n, gpr, rows, magic);
   else
     gather_rows_kernel<G, true><<<blocks, GATHER_THREADS, 0, s>>>(
