@@ -216,7 +216,9 @@ def run_ours(args):
             out = res.get_blocks()[0]
         return out
 
-    for i in range(args.warmup):
+    # the first exchanges on a fresh box also set up NCCL and the symmetric buffers
+    warmup = args.warmup if world == 1 else max(args.warmup, 5)
+    for i in range(warmup):
         out = one_step()
         if i == 0 and world == 1:
             torch.cuda.synchronize()
@@ -282,7 +284,7 @@ def run_ours(args):
         return
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
-        "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True,
+        "warmup": warmup, "ms_per_step": ms_per_step, "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
         "rows_per_s": world * n / (ms_per_step * 1e-3),
         "config": {

@@ -127,8 +127,12 @@ def splitters_from_samples(samples: np.ndarray, arrow_type: pa.DataType, world: 
 # on the receiver), so the receiver finds the chunks already concatenated in source-rank
 # order.  Device-side barriers on the buffer's signal pad order the phases.  Measured on
 # 2 x B200 this moves the 9 GB payload exchange from 28 ms (NCCL send/recv sharing SMs with
-# the radix sort) to copy-engine speed while the key sort runs.
+# the radix sort) to copy-engine speed while the key sort runs.  (A variant that also cut
+# the partition into 4 row ranges and pipelined gather / copy per range was measured slower
+# on 2 and on 8 GPUs -- the ranges' gathers compete with the key sort for HBM -- and was
+# dropped; see profiles/r01_multi_gpu.md.)
 _EXCHANGE = _os.environ.get("DS_EXCHANGE", "p2p")  # "p2p" | "nccl"
+_LANES = _os.environ.get("DS_P2P_LANES", "1") == "1"  # one copy stream per destination
 _peer_cache: dict = {}
 
 
@@ -195,7 +199,7 @@ def _p2p_send_column(pb, layout, name, rb, send: torch.Tensor, matrix: np.ndarra
             continue
         before = int(matrix[:rank, d].sum())  # rows lower ranks place in d's buffer
         dst = pb.hdl.get_buffer(d, (rows * rb,), torch.uint8, layout.off[name] + before * rb)
-        lane = pb.lanes[d]
+        lane = pb.lanes[d] if _LANES else pb.lanes[0]
         lane.wait_stream(after)
         with torch.cuda.stream(lane):
             dst.copy_(send[int(offs[d]) * rb: int(offs[d + 1]) * rb], non_blocking=True)
@@ -205,6 +209,32 @@ def _p2p_send_column(pb, layout, name, rb, send: torch.Tensor, matrix: np.ndarra
 def _join_lanes(pb, stream):
     for lane in pb.lanes:
         stream.wait_stream(lane)
+
+
+def _p2p_exchange_all(names, rbs, send, matrix, group):
+    """Exchange every column through peer memory; returns {name: view of this rank's
+    receive buffer} (valid until the next exchange on this group), or None when peer memory
+    cannot be used (the caller then takes the NCCL path)."""
+    world = matrix.shape[0]
+    if not (_EXCHANGE == "p2p" and world > 1 and dist.get_backend(group) == "nccl"):
+        return None
+    try:
+        layout = _PeerLayout(names, rbs, matrix)
+        pb = _peer_buffer(layout.total, group)
+    except Exception as e:  # pragma: no cover - depends on the system
+        import warnings
+
+        warnings.warn(f"peer-memory exchange unavailable ({e!r}); using NCCL all_to_all")
+        return None
+    rank = dist.get_rank(group)
+    main = torch.cuda.current_stream()
+    pb.hdl.barrier(channel=0)
+    for name in names:
+        _p2p_send_column(pb, layout, name, rbs[name], send[name], matrix, rank, main)
+    _join_lanes(pb, main)
+    pb.hdl.barrier(channel=1)
+    n_recv = int(matrix[:, rank].sum())
+    return {nm: pb.buf[layout.off[nm]: layout.off[nm] + n_recv * rbs[nm]] for nm in names}
 
 
 # ----------------------------------------------------------------------------- plans
@@ -374,11 +404,19 @@ def random_shuffle_block(block, seed: Optional[int], group=None):
     counts = [slices[order[d]][1] - slices[order[d]][0] for d in range(world)]
     matrix = exchange_counts(counts, group, dev)
     cols = collections.OrderedDict()
+    names = list(shuffled.columns)
+    rbs = {nm: shuffled.columns[nm].row_bytes for nm in names}
+    send = {}
     for name, c in shuffled.columns.items():
         rb = c.row_bytes
-        send = torch.cat([c.data[slices[order[d]][0] * rb: slices[order[d]][1] * rb] for d in range(world)])
-        recv, _ = alltoallv_rows(send, rb, matrix, group)
-        cols[name] = DeviceColumn(c.type, recv)
+        send[name] = torch.cat([c.data[slices[order[d]][0] * rb: slices[order[d]][1] * rb] for d in range(world)])
+    got = _p2p_exchange_all(names, rbs, send, matrix, group)
+    for name, c in shuffled.columns.items():
+        if got is not None:
+            cols[name] = DeviceColumn(c.type, got[name])
+        else:
+            recv, _ = alltoallv_rows(send[name], c.row_bytes, matrix, group)
+            cols[name] = DeviceColumn(c.type, recv)
     out = DeviceArrowBlock(cols, int(matrix[:, rank].sum()))
     # every reducer permutes with the same seed in the reference (:86-89); the
     # subsequence keeps the streams of different ranks apart without changing that contract
