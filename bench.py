@@ -242,7 +242,6 @@ def run_ours(args):
     barrier()
     lib.ds_debug_pass_timing(0)
     launches = int(lib.ds_debug_launch_count() - launches0)
-    clocks = sampler.stop() if rank == 0 else None
     ms = ev0.elapsed_time(ev1)
     tot_ms, cnt = ctypes.c_double(0), ctypes.c_int32(0)
     lib.ds_debug_collect_pass_timing(ctypes.byref(tot_ms), ctypes.byref(cnt))
@@ -277,6 +276,8 @@ def run_ours(args):
     if not args.no_e2e:
         e2e = run_e2e(args, ds, block, n, world, rank, barrier)
     del block
+    # sampled from the start of the timed region to the end of the e2e region
+    clocks = sampler.stop() if rank == 0 else None
 
     if rank != 0:
         if world > 1:
