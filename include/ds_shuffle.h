@@ -54,6 +54,7 @@ typedef int32_t ds_status;
 #define DS_OP_SUM 0
 #define DS_OP_MIN 1
 #define DS_OP_MAX 2
+#define DS_OP_ABSMAX 3 /* max of |x| (aggregate.py:289-305) */
 
 /* Library version (major*10000 + minor*100 + patch).  No reference counterpart. */
 int32_t ds_version(void);
@@ -210,24 +211,44 @@ ds_status ds_segment_heads_i64_static(const int64_t* sorted_keys, uint64_t n,
  * already in sorted order).  Replaces pyarrow.compute.sum/min/max on a group slice
  * (_internal/arrow_block.py:311-329 via aggregate.py:97-211) and the accumulator
  * merges a1+a2 of aggregate_combined_blocks (aggregate.py:107,119,185-187).
+ *   valid       optional (may be NULL): one byte per INPUT row, 0 = null.  Null rows
+ *               contribute the op's identity, i.e. they are skipped
+ *               (skip_nulls=True at _internal/arrow_block.py:309); use
+ *               ds_segmented_count_valid to learn how many rows of a run were non-null
  *   seg_starts  nseg+1 entries as written by ds_segment_heads_i64
  *   nseg        HOST value (the caller reads *nseg_out back to size `out`)
- *   op          DS_OP_SUM / DS_OP_MIN / DS_OP_MAX
+ *   op          DS_OP_SUM / DS_OP_MIN / DS_OP_MAX / DS_OP_ABSMAX
  * Summation order inside a run is fixed by (n, seg_starts) alone: results are
  * reproducible run to run (no floating-point atomics). */
-ds_status ds_segmented_reduce_f64(const double* vals, const uint32_t* idx,
+ds_status ds_segmented_reduce_f64(const double* vals, const uint8_t* valid, const uint32_t* idx,
                                   const uint32_t* seg_starts, uint32_t nseg, uint64_t n,
                                   int32_t op, double* out, void* ws, size_t* ws_bytes,
                                   void* stream);
-ds_status ds_segmented_reduce_i64(const int64_t* vals, const uint32_t* idx,
+ds_status ds_segmented_reduce_i64(const int64_t* vals, const uint8_t* valid, const uint32_t* idx,
                                   const uint32_t* seg_starts, uint32_t nseg, uint64_t n,
                                   int32_t op, int64_t* out, void* ws, size_t* ws_bytes,
                                   void* stream);
+
+/* Non-null rows per run: out[s] = #{i in run s : valid[idx[i]] != 0} (all rows if valid is
+ * NULL).  Replaces ArrowBlockAccessor.count (_internal/arrow_block.py:274-288, used by
+ * Mean at aggregate.py:191) and the has_data bookkeeping of
+ * _internal/null_aggregate.py:191-225. */
+ds_status ds_segmented_count_valid(const uint8_t* valid, const uint32_t* idx,
+                                   const uint32_t* seg_starts, uint32_t nseg, uint64_t n,
+                                   int64_t* out, void* ws, size_t* ws_bytes, void* stream);
 
 /* Row counts per run: out[s] = seg_starts[s+1] - seg_starts[s].
  * Replaces Count.accumulate_block (aggregate.py:97-109). */
 ds_status ds_segment_counts(const uint32_t* seg_starts, uint32_t nseg, int64_t* out,
                             void* stream);
+
+/* Validity of a finalized aggregate per group (null policy of
+ * _internal/null_aggregate.py:12-26, _null_wrap_finalize :228-251): with ignore_nulls the
+ * result is a value unless every row of the group was null; without, only if none was.
+ *   nvalid / nrows   non-null rows and all rows per group (int64)
+ *   out              one byte per group, 1 = value, 0 = null */
+ds_status ds_finalize_validity(const int64_t* nvalid, const int64_t* nrows, uint64_t n,
+                               int32_t ignore_nulls, uint8_t* out, void* stream);
 
 /* Mean finalize out[s] = sum[s] / count[s] (aggregate.py:209).  sum_is_i64 selects
  * the accumulator type of `sum` (int64 sums of int64 columns stay integral until

@@ -199,8 +199,52 @@ def gen_groupby():
     np.savez_compressed(os.path.join(OUT, "groupby.npz"), **out)
 
 
+def gen_nulls():
+    """Null policy (null_aggregate.py) and nulls-last sort, recorded from the reference."""
+    ns = ref_shim.load()
+    A = ns.aggregate
+    n, nb, g = 3000, 3, 40
+    rng = np.random.default_rng(33)
+    k = rng.integers(0, g, n, dtype=np.int64)
+    vf = rng.random(n)
+    vi = rng.integers(-50, 50, n, dtype=np.int64)
+    mf = rng.random(n) < 0.15          # nulls sprinkled in
+    mi = rng.random(n) < 0.15
+    mf[k == 3] = True                  # group 3: all null in vf
+    mi[k == 5] = False                 # group 5: no nulls in vi
+    tabs = [
+        pa.table({"k": k[a:b], "vf": pa.array(vf[a:b], mask=mf[a:b]), "vi": pa.array(vi[a:b], mask=mi[a:b])})
+        for a, b in _split(n, nb)
+    ]
+    out = {"k": k, "vf": vf, "vi": vi, "mf": mf, "mi": mi, "block_cuts": np.array(_split(n, nb))}
+    for ignore in (True, False):
+        aggs = (A.Sum("vf", ignore), A.Mean("vf", ignore), A.Min("vi", ignore), A.Max("vi", ignore),
+                A.Sum("vi", ignore), A.Mean("vi", ignore), A.Count(), A.AbsMax("vi", ignore))
+        random.seed(5)
+        blocks = ref_shim.ref_groupby(tabs, "k", aggs)
+        cat = pa.concat_tables([b for b in blocks if b.num_rows], promote=True)
+        tag = "ign" if ignore else "strict"
+        out[f"{tag}_names"] = np.array(cat.column_names)
+        for name in cat.column_names:
+            col = cat[name].combine_chunks()
+            valid = np.array([v is not None for v in col.to_pylist()])
+            vals = np.array([0 if v is None else v for v in col.to_pylist()], dtype=np.float64)
+            out[f"{tag}::{name}::valid"] = valid
+            out[f"{tag}::{name}::values"] = vals
+    # sort with null keys: nulls last in both directions, input order among them
+    ks = pa.array(vi, mask=mi)
+    st = [pa.table({"key": ks[a:b], "row": np.arange(a, b, dtype=np.int64)}) for a, b in _split(n, nb)]
+    for desc in (False, True):
+        random.seed(6)
+        blocks = ref_shim.ref_sort(st, "key", descending=desc)
+        cat = pa.concat_tables([b for b in blocks if b.num_rows])
+        out[f"sort_{'desc' if desc else 'asc'}_row_order"] = cat["row"].to_numpy()
+    np.savez_compressed(os.path.join(OUT, "nulls.npz"), **out)
+
+
 def main():
     os.makedirs(OUT, exist_ok=True)
+    gen_nulls()
     gen_sort_int64()
     gen_sort_graysort()
     gen_partition()

@@ -20,7 +20,7 @@ DS_MAX_KEY_BYTES = 10
 DS_MAX_PARTITIONS = 256
 DS_SORT_NO_PASS_SKIP = 1
 DS_SORT_NO_PREFIX_REPAIR = 2
-DS_OP_SUM, DS_OP_MIN, DS_OP_MAX = 0, 1, 2
+DS_OP_SUM, DS_OP_MIN, DS_OP_MAX, DS_OP_ABSMAX = 0, 1, 2, 3
 DS_SEGMENT_HEADS_STATIC_MAX_ROWS = 1 << 27
 
 
@@ -59,10 +59,12 @@ _PROTOS = {
     "ds_random_permutation": [c_uint64, c_uint64, c_uint64, _P, _P, _SZP, _P],
     "ds_segment_heads_i64": [_P, c_uint64, _P, _P, _P, _SZP, _P],
     "ds_segment_heads_i64_static": [_P, c_uint64, _P, _P, _P],
-    "ds_segmented_reduce_f64": [_P, _P, _P, c_uint32, c_uint64, c_int32, _P, _P, _SZP, _P],
-    "ds_segmented_reduce_i64": [_P, _P, _P, c_uint32, c_uint64, c_int32, _P, _P, _SZP, _P],
+    "ds_segmented_reduce_f64": [_P, _P, _P, _P, c_uint32, c_uint64, c_int32, _P, _P, _SZP, _P],
+    "ds_segmented_reduce_i64": [_P, _P, _P, _P, c_uint32, c_uint64, c_int32, _P, _P, _SZP, _P],
+    "ds_segmented_count_valid": [_P, _P, _P, c_uint32, c_uint64, _P, _P, _SZP, _P],
     "ds_segment_counts": [_P, c_uint32, _P, _P],
     "ds_finalize_mean": [_P, c_int32, _P, c_uint64, _P, _P],
+    "ds_finalize_validity": [_P, _P, c_uint64, c_int32, _P, _P],
 }
 EXPORTED = ["ds_version", "ds_last_error"] + sorted(_PROTOS)
 

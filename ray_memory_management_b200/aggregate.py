@@ -10,8 +10,11 @@ with the three phases expressed as device operations:
                       (aggregate_combined_blocks, arrow_block.py:549-565)
   finalize         -> identity, or sum / count for Mean (aggregate.py:209)
 
-Null handling (python/ray/data/_internal/null_aggregate.py) is not implemented yet:
-device blocks reject columns with nulls at import, so ``ignore_nulls`` has no effect.
+Null handling follows python/ray/data/_internal/null_aggregate.py:12-26: with
+``ignore_nulls=True`` nulls are skipped and an all-null group gives null; with
+``ignore_nulls=False`` any null in the group gives null.  On device the ``has_data`` flag of
+the reference's wrapped accumulators becomes two int64 parts per aggregate, ``nvalid`` and
+``nrows``, which merge by addition like the values do.
 """
 from typing import Dict, Optional
 
@@ -70,17 +73,40 @@ class Count(AggregateFn):
         return parts["count"]
 
 
+def _null_parts(block, on, starts, nseg, n):
+    """{"nvalid", "nrows"}: non-null rows and all rows per run -- the SoA form of the
+    reference's has_data bookkeeping (null_aggregate.py:29-65,191-225).  Without a validity
+    mask both are the run lengths (one kernel, one shared column)."""
+    from .block import _segment_counts, _segmented_count_valid
+
+    nrows = _segment_counts(starts, nseg)
+    col = block.column(on)
+    nvalid = nrows if col.valid is None else _segmented_count_valid(col, None, starts, nseg, n)
+    return {"nvalid": nvalid, "nrows": nrows}
+
+
+def _with_validity(value, parts, ignore_nulls):
+    """Attach the group validity of the null policy (null_aggregate.py:12-26,228-251)."""
+    from .block import DeviceColumn, _finalize_validity
+
+    if parts["nvalid"] is parts["nrows"]:
+        return value  # no nulls anywhere: every group has a value
+    return DeviceColumn(value.type, value.data, _finalize_validity(parts["nvalid"], parts["nrows"], ignore_nulls))
+
+
 class _Reduce(_AggregateOnKeyBase):
     def _device_accumulate(self, block, starts, nseg, n):
         from .block import _segmented_reduce
 
-        return {self._kind: _segmented_reduce(block.column(self._key_fn), None, starts, nseg, n, self._kind)}
+        parts = {self._kind: _segmented_reduce(block.column(self._key_fn), None, starts, nseg, n, self._kind)}
+        parts.update(_null_parts(block, self._key_fn, starts, nseg, n))
+        return parts
 
     def _device_merge_ops(self):
-        return {self._kind: self._kind}
+        return {self._kind: "max" if self._kind == "absmax" else self._kind, "nvalid": "sum", "nrows": "sum"}
 
     def _device_finalize(self, parts):
-        return parts[self._kind]
+        return _with_validity(parts[self._kind], parts, self._ignore_nulls)
 
 
 class Sum(_Reduce):
@@ -104,24 +130,31 @@ class Max(_Reduce):
         super().__init__(on, ignore_nulls, "max")
 
 
+class AbsMax(_Reduce):
+    """aggregate.py:289-305 -- max of |x|."""
+
+    def __init__(self, on: Optional[str] = None, ignore_nulls: bool = True):
+        super().__init__(on, ignore_nulls, "absmax")
+        self.name = f"abs_max({str(on)})"
+
+
 class Mean(_AggregateOnKeyBase):
-    """aggregate.py:178-211 -- accumulator [sum, count], finalize sum / count."""
+    """aggregate.py:178-211 -- accumulator [sum, count of non-null rows], finalize sum / count."""
 
     def __init__(self, on: Optional[str] = None, ignore_nulls: bool = True):
         super().__init__(on, ignore_nulls, "mean")
 
     def _device_accumulate(self, block, starts, nseg, n):
-        from .block import _segment_counts, _segmented_reduce
+        from .block import _segmented_reduce
 
-        return {
-            "sum": _segmented_reduce(block.column(self._key_fn), None, starts, nseg, n, "sum"),
-            "count": _segment_counts(starts, nseg),
-        }
+        parts = {"sum": _segmented_reduce(block.column(self._key_fn), None, starts, nseg, n, "sum")}
+        parts.update(_null_parts(block, self._key_fn, starts, nseg, n))
+        return parts
 
     def _device_merge_ops(self):
-        return {"sum": "sum", "count": "sum"}
+        return {"sum": "sum", "nvalid": "sum", "nrows": "sum"}
 
     def _device_finalize(self, parts):
         from .block import _finalize_mean
 
-        return _finalize_mean(parts["sum"], parts["count"])
+        return _with_validity(_finalize_mean(parts["sum"], parts["nvalid"]), parts, self._ignore_nulls)

@@ -124,16 +124,27 @@ def _key_kind(t: pa.DataType) -> str:
 
 
 class DeviceColumn:
-    """One fixed-width Arrow column in HBM: ``data`` is a uint8 view of n*row_bytes bytes."""
+    """One fixed-width Arrow column in HBM: ``data`` is a uint8 view of n*row_bytes bytes.
 
-    __slots__ = ("type", "row_bytes", "data")
+    ``valid`` (optional) is the column's validity as one byte per row (1 = value, 0 = null);
+    it is unpacked from / packed into the Arrow validity bitmap at the H2D / D2H boundary so
+    that it can be sliced and gathered like any 1-byte column.  ``None`` means "no nulls"."""
 
-    def __init__(self, arrow_type: pa.DataType, data: torch.Tensor):
+    __slots__ = ("type", "row_bytes", "data", "valid")
+
+    def __init__(self, arrow_type: pa.DataType, data: torch.Tensor, valid: Optional[torch.Tensor] = None):
         self.type = arrow_type
         self.row_bytes = _row_bytes(arrow_type)
         assert data.dtype == torch.uint8 and data.dim() == 1, (data.dtype, data.shape)
         assert data.numel() % self.row_bytes == 0
         self.data = data
+        if valid is not None:
+            assert valid.dtype == torch.uint8 and valid.numel() == data.numel() // self.row_bytes
+        self.valid = valid
+
+    @property
+    def valid_ptr(self) -> Optional[int]:
+        return self.valid.data_ptr() if self.valid is not None else None
 
     @property
     def num_rows(self) -> int:
@@ -144,7 +155,11 @@ class DeviceColumn:
         return self.data.data_ptr()
 
     def slice(self, start: int, end: int) -> "DeviceColumn":
-        return DeviceColumn(self.type, self.data[start * self.row_bytes : end * self.row_bytes])
+        return DeviceColumn(
+            self.type,
+            self.data[start * self.row_bytes : end * self.row_bytes],
+            self.valid[start:end] if self.valid is not None else None,
+        )
 
     def typed(self) -> torch.Tensor:
         """int64/float64 view of the buffer (plumbing for tests and finalisation)."""
@@ -179,8 +194,9 @@ class DeviceArrowBlock:
         n = table.num_rows if table.num_columns > 0 else 0
         for name in table.column_names:
             ca = table[name]
-            if ca.null_count:
-                raise NotImplementedError(f"column {name!r} has nulls; validity bitmaps are not supported on device yet")
+            if pa.types.is_null(ca.type):
+                # an all-null column as Arrow infers it from [None, ...]: kept as float64 nulls
+                ca = pa.chunked_array([pa.array([None] * n, pa.float64())])
             arr = ca.combine_chunks() if ca.num_chunks != 1 else ca.chunk(0)
             if isinstance(arr, pa.ChunkedArray):
                 arr = arr.chunk(0) if arr.num_chunks else pa.array([], type=ca.type)
@@ -191,7 +207,12 @@ class DeviceArrowBlock:
             else:
                 host = np.frombuffer(buf, dtype=np.uint8)[arr.offset * w : (arr.offset + n) * w]
             dev = torch.from_numpy(host.copy() if not host.flags.writeable else host).to("cuda", non_blocking=False)
-            cols[name] = DeviceColumn(arr.type, dev)
+            valid = None
+            if arr.null_count and n:
+                bits = np.frombuffer(arr.buffers()[0], dtype=np.uint8)
+                mask = np.unpackbits(bits, bitorder="little")[arr.offset : arr.offset + n]
+                valid = torch.from_numpy(np.ascontiguousarray(mask)).to("cuda")
+            cols[name] = DeviceColumn(arr.type, dev, valid)
         return DeviceArrowBlock(cols, n)
 
     @staticmethod
@@ -221,7 +242,13 @@ class DeviceArrowBlock:
         for name, c in self.columns.items():
             host = c.data.cpu().numpy()
             buf = pa.py_buffer(host.tobytes())
-            arrays.append(pa.Array.from_buffers(c.type, self._num_rows, [None, buf]))
+            vbuf, nulls = None, 0
+            if c.valid is not None:
+                mask = c.valid.cpu().numpy()
+                nulls = int(self._num_rows - np.count_nonzero(mask))
+                if nulls:
+                    vbuf = pa.py_buffer(np.packbits(mask != 0, bitorder="little").tobytes())
+            arrays.append(pa.Array.from_buffers(c.type, self._num_rows, [vbuf, buf], null_count=nulls))
             fields.append(pa.field(name, c.type))
         return pa.Table.from_arrays(arrays, schema=pa.schema(fields))
 
@@ -240,7 +267,11 @@ class DeviceArrowBlock:
 
     @property
     def nbytes(self) -> int:
-        return sum(c.data.numel() for c in self.columns.values())
+        # like pyarrow.Table.nbytes: data buffers plus validity bitmaps where present
+        return sum(
+            c.data.numel() + ((self._num_rows + 7) // 8 if c.valid is not None else 0)
+            for c in self.columns.values()
+        )
 
     @property
     def schema(self) -> pa.Schema:
@@ -281,8 +312,15 @@ class DeviceArrowBlock:
                 raise ValueError("cannot concatenate device blocks with different schemas")
         cols = collections.OrderedDict()
         for n in names:
+            valid = None
+            if any(b.columns[n].valid is not None for b in blocks):
+                valid = torch.cat([
+                    b.columns[n].valid if b.columns[n].valid is not None
+                    else torch.ones(b.num_rows, dtype=torch.uint8, device="cuda")
+                    for b in blocks
+                ])
             cols[n] = DeviceColumn(
-                blocks[0].columns[n].type, torch.cat([b.columns[n].data for b in blocks])
+                blocks[0].columns[n].type, torch.cat([b.columns[n].data for b in blocks]), valid
             )
         return DeviceArrowBlock(cols, sum(b.num_rows for b in blocks))
 
@@ -308,11 +346,52 @@ def _argsort(col: DeviceColumn, descending: bool, want_sorted: bool, options: in
     return idx, (DeviceColumn(col.type, out) if want_sorted else None)
 
 
-def _gather(col: DeviceColumn, idx: torch.Tensor) -> DeviceColumn:
+def _gather_raw(src: torch.Tensor, row_bytes: int, src_rows: int, idx: torch.Tensor) -> torch.Tensor:
     n = idx.numel()
-    out = _empty_u8(n * col.row_bytes)
-    _lib.call("ds_gather_rows", col.ptr, col.row_bytes, col.num_rows, idx.data_ptr(), n, out.data_ptr(), _stream())
-    return DeviceColumn(col.type, out)
+    out = _empty_u8(n * row_bytes)
+    _lib.call("ds_gather_rows", src.data_ptr(), row_bytes, src_rows, idx.data_ptr(), n, out.data_ptr(), _stream())
+    return out
+
+
+def _gather(col: DeviceColumn, idx: torch.Tensor) -> DeviceColumn:
+    out = _gather_raw(col.data, col.row_bytes, col.num_rows, idx)
+    valid = _gather_raw(col.valid, 1, col.num_rows, idx) if col.valid is not None else None
+    return DeviceColumn(col.type, out, valid)
+
+
+def _split_nulls(col: DeviceColumn) -> Tuple[torch.Tensor, int]:
+    """Row ids with the non-null rows first and the null rows last, input order kept in
+    both groups (a stable two-way partition on the validity byte), and the non-null count."""
+    vcol = DeviceColumn(pa.binary(1), col.valid)
+    perm, counts = _range_partition(vcol, [b"\x01"], True)  # descending: valid(1) -> bucket 0
+    return perm, counts[0]
+
+
+def _argsort_nulls_last(col: DeviceColumn, descending: bool):
+    """Arrow's sort_indices order: by key, nulls at the end in input order (both directions).
+    Returns (idx, sorted key column, number of non-null rows)."""
+    n = col.num_rows
+    if col.valid is None:
+        idx, sk = _argsort(col, descending, want_sorted=True)
+        return idx, sk, n
+    perm0, nv = _split_nulls(col)
+    if nv == n:
+        idx, sk = _argsort(DeviceColumn(col.type, col.data), descending, want_sorted=True)
+        return idx, sk, n
+    rb = col.row_bytes
+    head = DeviceColumn(col.type, _gather_raw(col.data, rb, n, perm0[:nv]))
+    idx = torch.empty(n, dtype=torch.int32, device="cuda")
+    if nv:
+        idx2, sk = _argsort(head, descending, want_sorted=True)
+        idx[:nv] = _gather_raw(perm0.view(torch.uint8), 4, n, idx2).view(torch.int32)
+        skd = sk.data
+    else:
+        skd = _empty_u8(0)
+    idx[nv:] = perm0[nv:]
+    tail = _gather_raw(col.data, rb, n, perm0[nv:])
+    valid = torch.zeros(n, dtype=torch.uint8, device="cuda")
+    valid[:nv] = 1
+    return idx, DeviceColumn(col.type, torch.cat([skd, tail]), valid), nv
 
 
 def _take_block(block: DeviceArrowBlock, idx: torch.Tensor, ready: Optional[Dict[str, DeviceColumn]] = None) -> DeviceArrowBlock:
@@ -388,7 +467,7 @@ def _segment_heads(sorted_keys: DeviceColumn):
     return starts, int(nseg.item())
 
 
-_OPS = {"sum": _lib.DS_OP_SUM, "min": _lib.DS_OP_MIN, "max": _lib.DS_OP_MAX}
+_OPS = {"sum": _lib.DS_OP_SUM, "min": _lib.DS_OP_MIN, "max": _lib.DS_OP_MAX, "absmax": _lib.DS_OP_ABSMAX}
 
 
 def _segmented_reduce(vals: DeviceColumn, idx: Optional[torch.Tensor], starts: torch.Tensor,
@@ -400,10 +479,27 @@ def _segmented_reduce(vals: DeviceColumn, idx: Optional[torch.Tensor], starts: t
     else:
         raise NotImplementedError(f"aggregation over Arrow type {vals.type} is not supported on device (int64, float64)")
     out = _empty_u8(nseg * 8)
-    ws = _lib.call_ws(fn, _workspace, vals.ptr, idx.data_ptr() if idx is not None else None,
+    ws = _lib.call_ws(fn, _workspace, vals.ptr, vals.valid_ptr, idx.data_ptr() if idx is not None else None,
                       starts.data_ptr(), nseg, n, _OPS[op], out.data_ptr(), stream=_stream())
     ws.record_stream(torch.cuda.current_stream())
     return DeviceColumn(vals.type, out)
+
+
+def _segmented_count_valid(vals: DeviceColumn, idx: Optional[torch.Tensor], starts: torch.Tensor,
+                           nseg: int, n: int) -> DeviceColumn:
+    out = _empty_u8(nseg * 8)
+    ws = _lib.call_ws("ds_segmented_count_valid", _workspace, vals.valid_ptr,
+                      idx.data_ptr() if idx is not None else None, starts.data_ptr(), nseg, n,
+                      out.data_ptr(), stream=_stream())
+    ws.record_stream(torch.cuda.current_stream())
+    return DeviceColumn(pa.int64(), out)
+
+
+def _finalize_validity(nvalid: DeviceColumn, nrows: DeviceColumn, ignore_nulls: bool) -> torch.Tensor:
+    n = nvalid.num_rows
+    out = _empty_u8(n)
+    _lib.call("ds_finalize_validity", nvalid.ptr, nrows.ptr, n, int(ignore_nulls), out.data_ptr(), _stream())
+    return out
 
 
 def _segment_counts(starts: torch.Tensor, nseg: int) -> DeviceColumn:
@@ -518,16 +614,21 @@ class DeviceArrowBlockAccessor:
         for name in names:
             c = self._block.column(name)
             out = _empty_u8(k * c.row_bytes)
+            valid = None
             if k:
                 _lib.call("ds_sample_rows", c.ptr, c.row_bytes, c.num_rows, k, seed, out.data_ptr(), _stream())
-            cols[name] = DeviceColumn(c.type, out)
+                if c.valid is not None:  # same seed -> same rows
+                    valid = _empty_u8(k)
+                    _lib.call("ds_sample_rows", c.valid_ptr, 1, c.num_rows, k, seed, valid.data_ptr(), _stream())
+            cols[name] = DeviceColumn(c.type, out, valid)
         return DeviceArrowBlock(cols, k)
 
     # -- sort (arrow_block.py:353-394) ------------------------------------------------
-    def _sorted(self, col: str, descending: bool) -> DeviceArrowBlock:
+    def _sorted(self, col: str, descending: bool, with_valid_count: bool = False):
         keycol = self._block.column(col)
-        idx, sorted_key = _argsort(keycol, descending, want_sorted=True)
-        return _take_block(self._block, idx, ready={col: sorted_key})
+        idx, sorted_key, nv = _argsort_nulls_last(keycol, descending)
+        out = _take_block(self._block, idx, ready={col: sorted_key})
+        return (out, nv) if with_valid_count else out
 
     def sort_and_partition(self, boundaries: List, key: SortKeyT, descending: bool) -> List[DeviceArrowBlock]:
         if not isinstance(key, str) and key is not None and not callable(key) and len(key) > 1:
@@ -535,10 +636,11 @@ class DeviceArrowBlockAccessor:
         if self._block.num_rows == 0:
             return [self._empty_table() for _ in range(len(boundaries) + 1)]
         col, _ = _normalize_key(key)
-        table = self._sorted(col, descending)
+        table, nv = self._sorted(col, descending, with_valid_count=True)
         if len(boundaries) == 0:
             return [table]
-        bounds = _searchsorted(table.column(col), boundaries, descending)
+        # null keys sit behind the last cut: they fall into the last partition
+        bounds = _searchsorted(table.column(col).slice(0, nv), boundaries, descending)
         parts, last = [], 0
         for b in bounds:
             parts.append(table.slice(last, b))
@@ -557,7 +659,18 @@ class DeviceArrowBlockAccessor:
         if nparts == 1:
             return [self._block]
         col, _ = _normalize_key(key)
-        perm, counts = _range_partition(self._block.column(col), boundaries, descending)
+        keycol = self._block.column(col)
+        if keycol.valid is None:
+            perm, counts = _range_partition(keycol, boundaries, descending)
+        else:  # null keys go, in input order, to the end of the last partition
+            n = keycol.num_rows
+            perm0, nv = _split_nulls(keycol)
+            head = DeviceColumn(keycol.type, _gather_raw(keycol.data, keycol.row_bytes, n, perm0[:nv]))
+            permv, counts = _range_partition(head, boundaries, descending)
+            perm = torch.empty(n, dtype=torch.int32, device="cuda")
+            perm[:nv] = _gather_raw(perm0.view(torch.uint8), 4, n, permv).view(torch.int32)
+            perm[nv:] = perm0[nv:]
+            counts[-1] += n - nv
         table = _take_block(self._block, perm)
         parts, last = [], 0
         for c in counts:
@@ -610,6 +723,8 @@ class DeviceArrowBlockAccessor:
             keycol = blk.column(key)
             if _key_kind(keycol.type) != "i64":
                 raise NotImplementedError("groupby keys must be int64 on device for now")
+            if keycol.valid is not None and not bool(keycol.valid.all()):
+                raise NotImplementedError("null groupby keys are not supported on device yet")
             starts, nseg = _segment_heads(keycol)
             cols[key] = _gather(keycol, starts[:nseg])
         for name, agg in zip(resolve_agg_names(aggs), aggs):

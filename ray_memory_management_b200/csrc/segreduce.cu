@@ -107,7 +107,7 @@ __global__ void __launch_bounds__(SEG_THREADS)
 // ------------------------------------------------------------------ reduce
 template <typename T, int OP>
 __device__ __forceinline__ T red_identity() {
-  if constexpr (OP == DS_OP_SUM) {
+  if constexpr (OP == DS_OP_SUM || OP == 100 /* OP_COUNT_VALID */ || OP == DS_OP_ABSMAX) {
     return T(0);
   } else if constexpr (std::is_floating_point<T>::value) {
     return OP == DS_OP_MIN ? __longlong_as_double(0x7FF0000000000000ll)
@@ -118,7 +118,7 @@ __device__ __forceinline__ T red_identity() {
 }
 template <typename T, int OP>
 __device__ __forceinline__ T red_op(T a, T b) {
-  if (OP == DS_OP_SUM) return a + b;
+  if (OP == DS_OP_SUM || OP == 100 /* OP_COUNT_VALID */) return a + b;
   if (OP == DS_OP_MIN) return b < a ? b : a;
   return b > a ? b : a;
 }
@@ -126,6 +126,22 @@ template <typename T>
 __device__ __forceinline__ T shfl_xor_t(T v, int o) {
   long long x = __shfl_xor_sync(0xffffffffu, *reinterpret_cast<long long*>(&v), o);
   return *reinterpret_cast<T*>(&x);
+}
+
+constexpr int OP_COUNT_VALID = 100;  // internal: sum of (valid[j] != 0)
+
+// Element j of the reduction: the value, or the op's identity where the row is null.
+template <typename T, int OP>
+__device__ __forceinline__ T seg_elem(const T* __restrict__ vals, const uint8_t* __restrict__ valid,
+                                      uint32_t j) {
+  if constexpr (OP == OP_COUNT_VALID) {
+    return static_cast<T>(valid ? (valid[j] != 0) : 1);
+  } else {
+    if (valid && valid[j] == 0) return red_identity<T, OP>();
+    const T v = vals[j];
+    if constexpr (OP == DS_OP_ABSMAX) return v < T(0) ? -v : v;
+    return v;
+  }
 }
 
 // last position p in [0, count) with starts[p] <= x   (starts[0] == 0 <= x always)
@@ -142,7 +158,8 @@ __device__ __forceinline__ uint32_t last_le(const uint32_t* __restrict__ starts,
 
 template <typename T, int OP>
 __global__ void __launch_bounds__(SEG_THREADS)
-    segreduce_tile_kernel(const T* __restrict__ vals, const uint32_t* __restrict__ idx,
+    segreduce_tile_kernel(const T* __restrict__ vals, const uint8_t* __restrict__ valid,
+                          const uint32_t* __restrict__ idx,
                           const uint32_t* __restrict__ seg_starts, uint32_t nseg, uint32_t n,
                           T* __restrict__ out, T* __restrict__ p_first, T* __restrict__ p_last,
                           uint32_t* __restrict__ t_first, uint32_t* __restrict__ t_last) {
@@ -169,7 +186,7 @@ __global__ void __launch_bounds__(SEG_THREADS)
       const uint32_t a0 = seg_starts[s], b0 = seg_starts[s + 1];
       const uint32_t a = max(a0, t0), b = min(b0, t1);
       T acc = red_identity<T, OP>();
-      for (uint32_t i = a; i < b; ++i) acc = red_op<T, OP>(acc, vals[idx ? idx[i] : i]);
+      for (uint32_t i = a; i < b; ++i) acc = red_op<T, OP>(acc, seg_elem<T, OP>(vals, valid, idx ? idx[i] : i));
       if (a0 >= t0 && b0 <= t1) out[s] = acc;
       else if (s == f) p_first[tile] = acc;
       else p_last[tile] = acc;
@@ -179,7 +196,7 @@ __global__ void __launch_bounds__(SEG_THREADS)
       const uint32_t a0 = seg_starts[s], b0 = seg_starts[s + 1];
       const uint32_t a = max(a0, t0), b = min(b0, t1);
       T acc = red_identity<T, OP>();
-      for (uint32_t i = a + lane; i < b; i += 32) acc = red_op<T, OP>(acc, vals[idx ? idx[i] : i]);
+      for (uint32_t i = a + lane; i < b; i += 32) acc = red_op<T, OP>(acc, seg_elem<T, OP>(vals, valid, idx ? idx[i] : i));
 #pragma unroll
       for (int o = 16; o > 0; o >>= 1) acc = red_op<T, OP>(acc, shfl_xor_t(acc, o));
       if (lane == 0) {
@@ -215,9 +232,9 @@ __global__ void segreduce_fixup_kernel(const uint32_t* __restrict__ seg_starts, 
 }
 
 template <typename T>
-static ds_status segreduce_impl(const T* vals, const uint32_t* idx, const uint32_t* seg_starts,
-                                uint32_t nseg, uint64_t n64, int32_t op, T* out, void* ws,
-                                size_t* ws_bytes, void* stream, const char* fn) {
+static ds_status segreduce_impl(const T* vals, const uint8_t* valid, const uint32_t* idx,
+                                const uint32_t* seg_starts, uint32_t nseg, uint64_t n64, int32_t op,
+                                T* out, void* ws, size_t* ws_bytes, void* stream, const char* fn) {
   if (n64 > DS_MAX_ROWS) {
     set_error("%s: n exceeds DS_MAX_ROWS", fn);
     return DS_ERR_TOO_LARGE;
@@ -232,23 +249,25 @@ static ds_status segreduce_impl(const T* vals, const uint32_t* idx, const uint32
   ds_status st;
   if (ws_resolve(w, ws, ws_bytes, fn, &st)) return st;
   if (n == 0 || nseg == 0) return DS_OK;
-  if (!vals || !seg_starts || !out) {
+  if ((!vals && op != OP_COUNT_VALID) || !seg_starts || !out) {
     set_error("%s: NULL pointer", fn);
     return DS_ERR_INVALID_ARG;
   }
-  if (op < DS_OP_SUM || op > DS_OP_MAX) {
+  if (!((op >= DS_OP_SUM && op <= DS_OP_ABSMAX) || op == OP_COUNT_VALID)) {
     set_error("%s: unknown op %d", fn, op);
     return DS_ERR_INVALID_ARG;
   }
   cudaStream_t s = static_cast<cudaStream_t>(stream);
 #define DS_SEG(OP)                                                                               \
-  ds::note_launch(); segreduce_tile_kernel<T, OP><<<tiles, SEG_THREADS, 0, s>>>(vals, idx, seg_starts, nseg, n, out, \
+  ds::note_launch(); segreduce_tile_kernel<T, OP><<<tiles, SEG_THREADS, 0, s>>>(vals, valid, idx, seg_starts, nseg, n, out, \
                                                              p_first, p_last, t_first, t_last);  \
   ds::note_launch(); segreduce_fixup_kernel<T, OP><<<(tiles + 127) / 128, 128, 0, s>>>(                             \
       seg_starts, n, tiles, p_first, p_last, t_first, t_last, out)
   if (op == DS_OP_SUM) { DS_SEG(DS_OP_SUM); }
   else if (op == DS_OP_MIN) { DS_SEG(DS_OP_MIN); }
-  else { DS_SEG(DS_OP_MAX); }
+  else if (op == DS_OP_MAX) { DS_SEG(DS_OP_MAX); }
+  else if (op == DS_OP_ABSMAX) { DS_SEG(DS_OP_ABSMAX); }
+  else { DS_SEG(OP_COUNT_VALID); }
 #undef DS_SEG
   DS_LAUNCH_CHECK();
   return DS_OK;
@@ -258,6 +277,15 @@ __global__ void segment_counts_kernel(const uint32_t* __restrict__ seg_starts, u
                                       int64_t* __restrict__ out) {
   const uint32_t s = blockIdx.x * blockDim.x + threadIdx.x;
   if (s < nseg) out[s] = static_cast<int64_t>(seg_starts[s + 1] - seg_starts[s]);
+}
+
+// Null policy of python/ray/data/_internal/null_aggregate.py:12-26 per group:
+// ignore_nulls: a value unless every row was null; otherwise: a value only if no row was.
+__global__ void finalize_validity_kernel(const int64_t* __restrict__ nvalid,
+                                         const int64_t* __restrict__ nrows, uint32_t n,
+                                         bool ignore_nulls, uint8_t* __restrict__ out) {
+  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) out[i] = ignore_nulls ? (nvalid[i] > 0) : (nvalid[i] == nrows[i] && nrows[i] > 0);
 }
 
 __global__ void finalize_mean_kernel(const void* __restrict__ sum, bool sum_is_i64,
@@ -305,18 +333,27 @@ ds_status ds_segment_heads_i64(const int64_t* sorted_keys, uint64_t n64, uint32_
   return DS_OK;
 }
 
-ds_status ds_segmented_reduce_f64(const double* vals, const uint32_t* idx, const uint32_t* seg_starts,
-                                  uint32_t nseg, uint64_t n, int32_t op, double* out, void* ws,
-                                  size_t* ws_bytes, void* stream) {
-  return ds::segreduce_impl<double>(vals, idx, seg_starts, nseg, n, op, out, ws, ws_bytes, stream,
-                                    __func__);
+ds_status ds_segmented_reduce_f64(const double* vals, const uint8_t* valid, const uint32_t* idx,
+                                  const uint32_t* seg_starts, uint32_t nseg, uint64_t n, int32_t op,
+                                  double* out, void* ws, size_t* ws_bytes, void* stream) {
+  if (op == ds::OP_COUNT_VALID) op = -1;
+  return ds::segreduce_impl<double>(vals, valid, idx, seg_starts, nseg, n, op, out, ws, ws_bytes,
+                                    stream, __func__);
 }
 
-ds_status ds_segmented_reduce_i64(const int64_t* vals, const uint32_t* idx, const uint32_t* seg_starts,
-                                  uint32_t nseg, uint64_t n, int32_t op, int64_t* out, void* ws,
-                                  size_t* ws_bytes, void* stream) {
-  return ds::segreduce_impl<int64_t>(vals, idx, seg_starts, nseg, n, op, out, ws, ws_bytes, stream,
-                                     __func__);
+ds_status ds_segmented_reduce_i64(const int64_t* vals, const uint8_t* valid, const uint32_t* idx,
+                                  const uint32_t* seg_starts, uint32_t nseg, uint64_t n, int32_t op,
+                                  int64_t* out, void* ws, size_t* ws_bytes, void* stream) {
+  if (op == ds::OP_COUNT_VALID) op = -1;
+  return ds::segreduce_impl<int64_t>(vals, valid, idx, seg_starts, nseg, n, op, out, ws, ws_bytes,
+                                     stream, __func__);
+}
+
+ds_status ds_segmented_count_valid(const uint8_t* valid, const uint32_t* idx,
+                                   const uint32_t* seg_starts, uint32_t nseg, uint64_t n,
+                                   int64_t* out, void* ws, size_t* ws_bytes, void* stream) {
+  return ds::segreduce_impl<int64_t>(nullptr, valid, idx, seg_starts, nseg, n, ds::OP_COUNT_VALID,
+                                     out, ws, ws_bytes, stream, __func__);
 }
 
 ds_status ds_segment_counts(const uint32_t* seg_starts, uint32_t nseg, int64_t* out, void* stream) {
@@ -327,6 +364,20 @@ ds_status ds_segment_counts(const uint32_t* seg_starts, uint32_t nseg, int64_t* 
   }
   ds::note_launch(); ds::segment_counts_kernel<<<(nseg + 255) / 256, 256, 0, static_cast<cudaStream_t>(stream)>>>(
       seg_starts, nseg, out);
+  DS_LAUNCH_CHECK();
+  return DS_OK;
+}
+
+ds_status ds_finalize_validity(const int64_t* nvalid, const int64_t* nrows, uint64_t n,
+                               int32_t ignore_nulls, uint8_t* out, void* stream) {
+  if (n == 0) return DS_OK;
+  if (!nvalid || !nrows || !out || n > 0xFFFFFFFFull) {
+    ds::set_error("%s: bad argument", __func__);
+    return DS_ERR_INVALID_ARG;
+  }
+  ds::note_launch();
+  ds::finalize_validity_kernel<<<(uint32_t)((n + 255) / 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      nvalid, nrows, static_cast<uint32_t>(n), ignore_nulls != 0, out);
   DS_LAUNCH_CHECK();
   return DS_OK;
 }

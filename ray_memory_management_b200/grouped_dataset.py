@@ -7,7 +7,7 @@ boundaries, per-partition combine on the map side, merge + finalize on the reduc
 from typing import List, Optional, Tuple, Union
 
 from . import sort
-from .aggregate import AggregateFn, Count, Max, Mean, Min, Sum
+from .aggregate import AbsMax, AggregateFn, Count, Max, Mean, Min, Sum
 from .block import Block, BlockAccessor, BlockExecStats, BlockList, BlockMetadata
 from .context import DatasetContext
 from .shuffle import DeviceShufflePlan, ShuffleOp
@@ -83,14 +83,14 @@ class GroupedDataset:
     def count(self):
         return self.aggregate(Count())
 
-    def sum(self, on: str):
-        return self.aggregate(Sum(on))
+    def sum(self, on: str, ignore_nulls: bool = True):
+        return self.aggregate(Sum(on, ignore_nulls))
 
-    def min(self, on: str):
-        return self.aggregate(Min(on))
+    def min(self, on: str, ignore_nulls: bool = True):
+        return self.aggregate(Min(on, ignore_nulls))
 
-    def max(self, on: str):
-        return self.aggregate(Max(on))
+    def max(self, on: str, ignore_nulls: bool = True):
+        return self.aggregate(Max(on, ignore_nulls))
 
-    def mean(self, on: str):
-        return self.aggregate(Mean(on))
+    def mean(self, on: str, ignore_nulls: bool = True):
+        return self.aggregate(Mean(on, ignore_nulls))

@@ -93,7 +93,9 @@ def sample_boundaries(blocks: List[Block], key: SortKeyT, num_reducers: int) -> 
     if len(samples) == 0:
         return [None] * (num_reducers - 1)
     column = key[0][0] if isinstance(key, list) else key
-    host = pa.concat_tables([s.to_arrow() for s in samples])[column].combine_chunks()
+    host = pa.concat_tables([s.to_arrow() for s in samples])[column].combine_chunks().drop_null()
+    if isinstance(host, pa.ChunkedArray):
+        host = host.combine_chunks()
     return boundaries_from_samples(host, num_reducers)
 
 

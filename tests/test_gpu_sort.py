@@ -234,6 +234,7 @@ def test_pass_skipping_constant_bytes(ds):
 
 
 def test_errors(ds):
+    # (nulls are supported since the validity masks were added: see tests/test_gpu_nulls.py)
     lib = ds._lib
     need = ctypes.c_size_t(0)
     st = lib.lib.ds_sort_indices_fsb(None, 11, 10, 0, None, None, 0, None, ctypes.byref(need), None)
@@ -245,8 +246,6 @@ def test_errors(ds):
         ds.BlockAccessor.for_block(t).sort_and_partition([], [("a", "ascending"), ("b", "ascending")], False)
     with pytest.raises(ValueError):
         ds.sample_boundaries([ds.DeviceArrowBlock.from_arrow(t)], [("a", "ascending"), ("b", "ascending")], 2)
-    with pytest.raises(NotImplementedError):
-        ds.DeviceArrowBlock.from_arrow(pa.table({"a": pa.array([1, None], pa.int64())}))
 
 
 def test_large_graysort_properties(ds):
