@@ -250,24 +250,69 @@ def _sample_local(block, col: str) -> np.ndarray:
         return np.zeros((0, 1), dtype=np.uint8)
     k = min(SAMPLES_PER_RANK, block.num_rows)
     s = DeviceArrowBlockAccessor(block).sample(k, col)
-    return s.columns[col].data.cpu().numpy().reshape(k, c.row_bytes)
+    rows = s.columns[col].data.cpu().numpy().reshape(k, c.row_bytes)
+    if s.columns[col].valid is not None:  # null keys take no part in the splitters
+        rows = rows[s.columns[col].valid.cpu().numpy() != 0]
+    return rows
 
 
 def _key_width(block, col, group) -> Tuple[int, pa.DataType]:
     return block.column(col).row_bytes, block.column(col).type
 
 
+_VALID = "\x00valid"  # wire-name suffix of a column's validity bytes
+
+
+def _agree_on_validity(block, group, dev):
+    """Every rank must exchange the same set of buffers: a column carries validity on the
+    wire if it has a mask on ANY rank (ranks without one send all-ones)."""
+    from .block import DeviceArrowBlock, DeviceColumn
+
+    flags = torch.tensor([int(c.valid is not None) for c in block.columns.values()],
+                         dtype=torch.int32, device=dev)
+    if flags.numel():
+        dist.all_reduce(flags, op=dist.ReduceOp.MAX, group=group)
+    need = [bool(x) for x in flags.cpu().tolist()]
+    if not any(need):
+        return block, set()
+    cols = collections.OrderedDict()
+    for (name, c), nd in zip(block.columns.items(), need):
+        if nd and c.valid is None:
+            c = DeviceColumn(c.type, c.data, torch.ones(c.num_rows, dtype=torch.uint8, device=dev))
+        cols[name] = c
+    return DeviceArrowBlock(cols, block.num_rows), {n for n, nd in zip(block.columns, need) if nd}
+
+
+def _wire_columns(parts, names, with_valid, key, dev):
+    """[(wire name, row bytes, send buffer)] with the key column(s) first."""
+    data = _spanning(parts, names, dev)
+    wires = []
+    order = [key] + [n for n in names if n != key] if key is not None else list(names)
+    live = [p for p in parts if p.num_rows]
+    for name in order:
+        rb = live[0].columns[name].row_bytes if live else 1
+        wires.append((name, rb, data[name]))
+        if name in with_valid:
+            vs = [p.columns[name].valid for p in live]
+            v = torch.cat(vs) if len(vs) != 1 else vs[0]
+            if not vs:
+                v = torch.empty(0, dtype=torch.uint8, device=dev)
+            wires.append((name + _VALID, 1, v.contiguous()))
+    return wires
+
+
 def sort_block(block, key: str, descending: bool = False, group=None):
     """Dataset.sort across the ranks of ``group``: this rank's input block in, this rank's
     slice of the globally sorted dataset out (rank order = key order)."""
-    from .block import (DeviceArrowBlock, DeviceArrowBlockAccessor, DeviceColumn, _argsort,
-                        _gather, _take_block)
+    from .block import (DeviceArrowBlock, DeviceArrowBlockAccessor, DeviceColumn,
+                        _argsort_nulls_last, _gather)
 
     world = dist.get_world_size(group)
     rank = dist.get_rank(group)
     dev = _dev()
     ph = _Phases()
     ph.mark("start")
+    block, with_valid = _agree_on_validity(block, group, dev)
     width, ktype = _key_width(block, key, group)
     local = _sample_local(block, key)
     if local.shape[1] != width:
@@ -275,7 +320,7 @@ def sort_block(block, key: str, descending: bool = False, group=None):
     samples = gather_samples(local, width, group, dev)
     boundaries = splitters_from_samples(samples, ktype, world)
     if boundaries and boundaries[0] is None:
-        return block  # globally empty
+        return block  # no non-null key anywhere: nothing to order
     if descending:
         boundaries.reverse()
 
@@ -287,14 +332,16 @@ def sort_block(block, key: str, descending: bool = False, group=None):
     ph.mark("partition")
     matrix = exchange_counts(counts, group, dev)
     names = block.column_names
-    send = _spanning(parts, names, dev)
+    types = {nm: block.columns[nm].type for nm in names}
+    wires = _wire_columns(parts, names, with_valid, key, dev)
+    nkey = 2 if key in with_valid else 1          # wires that make up the key column
     n_recv = int(matrix[:, rank].sum())
+    rbs = {w: rb for w, rb, _ in wires}
 
     use_p2p = _EXCHANGE == "p2p" and world > 1 and dist.get_backend(group) == "nccl"
     if use_p2p:
         try:
-            rbs = {nm: block.columns[nm].row_bytes for nm in names}
-            layout = _PeerLayout(names, rbs, matrix)
+            layout = _PeerLayout([w for w, _, _ in wires], rbs, matrix)
             pb = _peer_buffer(layout.total, group)
         except Exception as e:  # symmetric memory unavailable on this system: NCCL path
             import warnings
@@ -302,51 +349,49 @@ def sort_block(block, key: str, descending: bool = False, group=None):
             warnings.warn(f"peer-memory exchange unavailable ({e!r}); using NCCL all_to_all")
             use_p2p = False
     ph.mark("counts")
-    cols = collections.OrderedDict()
-    got = {}
+    recv = {}
+
+    def column(name):
+        v = recv.get(name + _VALID)
+        return DeviceColumn(types[name], recv[name], v)
+
     if use_p2p:
         main = torch.cuda.current_stream()
         pb.hdl.barrier(channel=0)  # every rank is done with the buffer's previous contents
-        _p2p_send_column(pb, layout, key, width, send[key], matrix, rank, main)
+        for w, rb, buf in wires[:nkey]:
+            _p2p_send_column(pb, layout, w, rb, buf, matrix, rank, main)
         _join_lanes(pb, main)
         pb.hdl.barrier(channel=1)  # all keys have landed everywhere
-        for name in names:  # payload copies run beside the key sort
-            if name != key:
-                _p2p_send_column(pb, layout, name, rbs[name], send[name], matrix, rank, main)
+        for w, rb, buf in wires[nkey:]:  # payload copies run beside the key sort
+            _p2p_send_column(pb, layout, w, rb, buf, matrix, rank, main)
         ph.mark("p2p keys")
-        keycol = DeviceColumn(ktype, pb.buf[layout.off[key]: layout.off[key] + n_recv * width])
-        idx, sorted_key = _argsort(keycol, descending, want_sorted=True)
+        for w, rb, _ in wires:
+            recv[w] = pb.buf[layout.off[w]: layout.off[w] + n_recv * rb]
+        idx, sorted_key, _ = _argsort_nulls_last(column(key), descending)
         ph.mark("key sort")
         _join_lanes(pb, main)
         pb.hdl.barrier(channel=2)  # all payload rows have landed everywhere
         ph.mark("wait payload")
-        for name in names:
-            if name != key:
-                view = pb.buf[layout.off[name]: layout.off[name] + n_recv * rbs[name]]
-                got[name] = _gather(DeviceColumn(block.columns[name].type, view), idx)
-        ph.mark("gather payload")
     else:
         # keys first; sort them while the payload columns are still being exchanged
-        recv_key, _ = alltoallv_rows(send[key], width, matrix, group)
+        for w, rb, buf in wires[:nkey]:
+            recv[w], _ = alltoallv_rows(buf, rb, matrix, group)
         ph.mark("a2a keys")
         pending = []
-        for name in names:
-            if name == key:
-                continue
-            rb = block.columns[name].row_bytes
-            r, work = alltoallv_rows(send[name], rb, matrix, group, async_op=True)
-            pending.append((name, r, work))
-        keycol = DeviceColumn(ktype, recv_key)
-        idx, sorted_key = _argsort(keycol, descending, want_sorted=True)
+        for w, rb, buf in wires[nkey:]:
+            r, work = alltoallv_rows(buf, rb, matrix, group, async_op=True)
+            recv[w] = r
+            pending.append(work)
+        idx, sorted_key, _ = _argsort_nulls_last(column(key), descending)
         ph.mark("key sort")
-        for name, r, work in pending:
+        for work in pending:
             work.wait()
-            ph.mark("wait " + name)
-            got[name] = _gather(DeviceColumn(block.columns[name].type, r), idx)
-            ph.mark("gather " + name)
-    ph.finish()
+        ph.mark("wait payload")
+    cols = collections.OrderedDict()
     for name in names:
-        cols[name] = sorted_key if name == key else got[name]
+        cols[name] = sorted_key if name == key else _gather(column(name), idx)
+    ph.mark("gather payload")
+    ph.finish()
     return DeviceArrowBlock(cols, n_recv)
 
 
@@ -395,6 +440,7 @@ def random_shuffle_block(block, seed: Optional[int], group=None):
     rank = dist.get_rank(group)
     dev = _dev()
     seed_i = seed + rank if seed is not None else None
+    block, with_valid = _agree_on_validity(block, group, dev)
     shuffled = DeviceArrowBlockAccessor(block).random_shuffle(seed_i) if block.num_rows else block
     n = shuffled.num_rows
     slice_sz = max(1, math.ceil(n / world))
@@ -404,19 +450,19 @@ def random_shuffle_block(block, seed: Optional[int], group=None):
     counts = [slices[order[d]][1] - slices[order[d]][0] for d in range(world)]
     matrix = exchange_counts(counts, group, dev)
     cols = collections.OrderedDict()
-    names = list(shuffled.columns)
-    rbs = {nm: shuffled.columns[nm].row_bytes for nm in names}
-    send = {}
+    wires = []
     for name, c in shuffled.columns.items():
         rb = c.row_bytes
-        send[name] = torch.cat([c.data[slices[order[d]][0] * rb: slices[order[d]][1] * rb] for d in range(world)])
-    got = _p2p_exchange_all(names, rbs, send, matrix, group)
+        wires.append((name, rb, torch.cat([c.data[slices[order[d]][0] * rb: slices[order[d]][1] * rb] for d in range(world)])))
+        if name in with_valid:
+            wires.append((name + _VALID, 1, torch.cat([c.valid[slices[order[d]][0]: slices[order[d]][1]] for d in range(world)])))
+    rbs = {w: rb for w, rb, _ in wires}
+    got = _p2p_exchange_all([w for w, _, _ in wires], rbs, {w: b for w, _, b in wires}, matrix, group)
+    recv = {}
+    for w, rb, buf in wires:
+        recv[w] = got[w] if got is not None else alltoallv_rows(buf, rb, matrix, group)[0]
     for name, c in shuffled.columns.items():
-        if got is not None:
-            cols[name] = DeviceColumn(c.type, got[name])
-        else:
-            recv, _ = alltoallv_rows(send[name], c.row_bytes, matrix, group)
-            cols[name] = DeviceColumn(c.type, recv)
+        cols[name] = DeviceColumn(c.type, recv[name], recv.get(name + _VALID))
     out = DeviceArrowBlock(cols, int(matrix[:, rank].sum()))
     # every reducer permutes with the same seed in the reference (:86-89); the
     # subsequence keeps the streams of different ranks apart without changing that contract

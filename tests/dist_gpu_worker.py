@@ -59,6 +59,18 @@ def main():
     got = pa.concat_tables(gather_tables(out.to_arrow(), rank, world))
     assert got.equals(O.global_stable_sort(inputs, "k", False)), "int64 distributed sort mismatch"
 
+    # ---- sort with null keys and null payload values on some ranks only
+    kn = rng.integers(-1000, 1000, 50_000, dtype=np.int64)
+    tn = pa.table({"k": pa.array(kn, mask=(rng.random(50_000) < 0.1) if rank % 2 == 0 else None),
+                   "v": pa.array(rng.random(50_000), mask=(rng.random(50_000) < 0.2) if rank == 0 else None),
+                   "r": np.arange(50_000, dtype=np.int64) + rank * 10**6})
+    inputs_n = gather_tables(tn, rank, world)
+    for desc in (False, True):
+        out = D.sort_block(ds.DeviceArrowBlock.from_arrow(tn), "k", descending=desc)
+        got = pa.concat_tables(gather_tables(out.to_arrow(), rank, world))
+        want = O.global_stable_sort(inputs_n, "k", desc)
+        assert got.equals(want), f"distributed sort with nulls mismatch desc={desc}"
+
     # ---- random_shuffle: permutation + determinism
     a = D.random_shuffle_block(ds.DeviceArrowBlock.from_arrow(ti), 42)
     b = D.random_shuffle_block(ds.DeviceArrowBlock.from_arrow(ti), 42)
