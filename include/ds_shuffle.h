@@ -112,6 +112,21 @@ ds_status ds_sort_indices_fsb(const uint8_t* col, uint32_t width, uint64_t n,
 ds_status ds_gather_rows(const void* src, uint32_t row_bytes, uint64_t src_rows,
                          const uint32_t* idx, uint64_t n, void* dst, void* stream);
 
+/* Partition scatter: copy the rows of a column, visited in partitioned order, to where
+ * each partition is consumed.  Row j (in the order of `perm`, as written by
+ * ds_partition_hist_scatter_*) belongs to partition d with part_offsets[d] <= j <
+ * part_offsets[d+1] and is stored at dst_bases[d] + (j - part_offsets[d]) * row_bytes.
+ * dst_bases[d] may be peer-mapped memory of another GPU (NVLink) or local memory, so one
+ * launch performs the map-side slicing AND the transfer of the all-to-all exchange.
+ * Replaces the M x N map-output objects and their pull by the reducers
+ * (_internal/shuffle.py:81-112; src/ray/object_manager/object_manager.cc:336-559).
+ *   part_offsets   HOST array of nparts+1 row offsets, part_offsets[nparts] == n
+ *   dst_bases      HOST array of nparts device pointers (nparts <= 16) */
+ds_status ds_scatter_rows_to_parts(const void* src, uint32_t row_bytes, uint64_t src_rows,
+                                   const uint32_t* perm, uint64_t n, uint32_t nparts,
+                                   const uint64_t* part_offsets, void* const* dst_bases,
+                                   void* stream);
+
 /* ----------------------------------------------------------- partition ---- */
 
 /* Cut positions of a SORTED key column at the given boundaries.

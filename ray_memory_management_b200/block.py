@@ -648,6 +648,24 @@ class DeviceArrowBlockAccessor:
         parts.append(table.slice(last, table.num_rows))
         return parts
 
+    def partition_perm(self, boundaries: List, key: SortKeyT, descending: bool):
+        """(perm, counts) of the stable range partition: ``perm`` lists the row ids grouped
+        by partition with input order kept inside each; null keys go, in input order, to the
+        end of the last partition."""
+        col, _ = _normalize_key(key)
+        keycol = self._block.column(col)
+        if keycol.valid is None:
+            return _range_partition(keycol, boundaries, descending)
+        n = keycol.num_rows
+        perm0, nv = _split_nulls(keycol)
+        head = DeviceColumn(keycol.type, _gather_raw(keycol.data, keycol.row_bytes, n, perm0[:nv]))
+        permv, counts = _range_partition(head, boundaries, descending)
+        perm = torch.empty(n, dtype=torch.int32, device="cuda")
+        perm[:nv] = _gather_raw(perm0.view(torch.uint8), 4, n, permv).view(torch.int32)
+        perm[nv:] = perm0[nv:]
+        counts[-1] += n - nv
+        return perm, counts
+
     def partition_unsorted(self, boundaries: List, key: SortKeyT, descending: bool) -> List[DeviceArrowBlock]:
         """Stable range partition WITHOUT sorting: same partition rule and same
         in-partition input order as slicing the stably sorted block would give, up to
@@ -658,19 +676,7 @@ class DeviceArrowBlockAccessor:
             return [self._empty_table() for _ in range(nparts)]
         if nparts == 1:
             return [self._block]
-        col, _ = _normalize_key(key)
-        keycol = self._block.column(col)
-        if keycol.valid is None:
-            perm, counts = _range_partition(keycol, boundaries, descending)
-        else:  # null keys go, in input order, to the end of the last partition
-            n = keycol.num_rows
-            perm0, nv = _split_nulls(keycol)
-            head = DeviceColumn(keycol.type, _gather_raw(keycol.data, keycol.row_bytes, n, perm0[:nv]))
-            permv, counts = _range_partition(head, boundaries, descending)
-            perm = torch.empty(n, dtype=torch.int32, device="cuda")
-            perm[:nv] = _gather_raw(perm0.view(torch.uint8), 4, n, permv).view(torch.int32)
-            perm[nv:] = perm0[nv:]
-            counts[-1] += n - nv
+        perm, counts = self.partition_perm(boundaries, key, descending)
         table = _take_block(self._block, perm)
         parts, last = [], 0
         for c in counts:

@@ -269,6 +269,185 @@ static cudaError_t launch_gather(const void* src, const uint32_t* idx, void* dst
   return cudaGetLastError();
 }
 
+// ---- partition scatter to peers: the map-side output of the exchange written where it
+// is consumed.  Rows are visited in partitioned order (perm, as produced by
+// ds_partition_hist_scatter_*); row j of partition d is stored at
+// dst_bases[d] + (j - part_offsets[d]) * row_bytes, where dst_bases[d] may point into
+// another GPU's memory (peer-mapped over NVLink) or into this GPU's own receive buffer.
+constexpr int MAX_PEER_PARTS = 16;
+struct PeerParts {
+  uint32_t count;
+  uint32_t offsets[MAX_PEER_PARTS + 1];
+  unsigned char* bases[MAX_PEER_PARTS];
+};
+
+template <typename G>
+__global__ void __launch_bounds__(GATHER_THREADS)
+    scatter_rows_to_parts_kernel(const G* __restrict__ src, const uint32_t* __restrict__ perm,
+                                 uint32_t n, uint32_t gpr, uint32_t rows_per_block, uint32_t magic,
+                                 PeerParts parts) {
+  __shared__ uint32_t s_idx[GATHER_MAX_ROWS];
+  const uint32_t row0 = blockIdx.x * rows_per_block;
+  const uint32_t rows = min(rows_per_block, n - row0);
+  for (uint32_t r = threadIdx.x; r < rows; r += GATHER_THREADS) s_idx[r] = ld_stream(perm + row0 + r);
+  __syncthreads();
+  const uint32_t total = rows * gpr;
+  constexpr int UNROLL = 8;
+  uint32_t e = threadIdx.x;
+  auto dst_of = [&](uint32_t ee, uint32_t r) -> G* {
+    const uint32_t j = row0 + r;
+    uint32_t d = 0;
+#pragma unroll
+    for (int k = 1; k < MAX_PEER_PARTS; ++k)
+      if (k < (int)parts.count && j >= parts.offsets[k]) d = k;
+    return reinterpret_cast<G*>(parts.bases[d]) + static_cast<uint64_t>(j - parts.offsets[d]) * gpr +
+           (ee - r * gpr);
+  };
+  for (; e + (UNROLL - 1) * GATHER_THREADS < total; e += UNROLL * GATHER_THREADS) {
+    G v[UNROLL];
+    uint32_t rr[UNROLL];
+#pragma unroll
+    for (int k = 0; k < UNROLL; ++k) {
+      const uint32_t ee = e + k * GATHER_THREADS;
+      rr[k] = gpr == 1 ? ee : __umulhi(ee, magic);
+      v[k] = __ldg(src + static_cast<uint64_t>(s_idx[rr[k]]) * gpr + (ee - rr[k] * gpr));
+    }
+#pragma unroll
+    for (int k = 0; k < UNROLL; ++k) *dst_of(e + k * GATHER_THREADS, rr[k]) = v[k];
+  }
+  for (; e < total; e += GATHER_THREADS) {
+    const uint32_t r = gpr == 1 ? e : __umulhi(e, magic);
+    *dst_of(e, r) = __ldg(src + static_cast<uint64_t>(s_idx[r]) * gpr + (e - r * gpr));
+  }
+}
+
+// Staged variant for rows that are not a multiple of 16 bytes: every block serves rows of ONE
+// partition, pulls them in as aligned 16-byte vectors (as gather_staged_kernel does) and
+// writes its contiguous destination span with 16-byte stores -- full-size NVLink writes when
+// the destination is a peer -- whatever the span's byte alignment (head and tail bytes are
+// stored one by one).
+struct PeerBlocks {
+  uint32_t first_block[MAX_PEER_PARTS + 1];  // prefix sum of blocks per partition
+};
+
+__global__ void __launch_bounds__(STAGE_THREADS)
+    scatter_staged_kernel(const uint8_t* __restrict__ src, uint32_t W, uint64_t src_bytes,
+                          const uint32_t* __restrict__ perm, uint32_t rows_per_block, uint32_t chunks,
+                          uint32_t magic_w, uint32_t magic_c, PeerParts parts, PeerBlocks pblk) {
+  extern __shared__ __align__(16) uint8_t sm[];
+  const uint32_t slot = chunks * 16 + 16;
+  uint64_t* s_a0 = reinterpret_cast<uint64_t*>(sm);
+  uint32_t* s_shift = reinterpret_cast<uint32_t*>(sm + rows_per_block * 8);
+  uint8_t* data = sm + rows_per_block * 12;
+  uint32_t d = 0;
+#pragma unroll
+  for (int k = 1; k < MAX_PEER_PARTS; ++k)
+    if (k < (int)parts.count && blockIdx.x >= pblk.first_block[k]) d = k;
+  const uint32_t local0 = (blockIdx.x - pblk.first_block[d]) * rows_per_block;  // row inside the partition
+  const uint32_t part_rows = parts.offsets[d + 1] - parts.offsets[d];
+  const uint32_t rows = min(rows_per_block, part_rows - local0);
+  const uint32_t row0 = parts.offsets[d] + local0;  // position in partitioned order
+  const uintptr_t base = reinterpret_cast<uintptr_t>(src);
+  const uintptr_t safe_lo = (base + 15) & ~uintptr_t(15);
+  const uintptr_t safe_hi = (base + src_bytes) & ~uintptr_t(15);
+
+  for (uint32_t r = threadIdx.x; r < rows; r += STAGE_THREADS) {
+    const uintptr_t a = base + static_cast<uint64_t>(ld_stream(perm + row0 + r)) * W;
+    s_a0[r] = a & ~uintptr_t(15);
+    s_shift[r] = static_cast<uint32_t>(a & 15);
+  }
+  __syncthreads();
+  const uint32_t items = rows * chunks;
+#pragma unroll 4
+  for (uint32_t e = threadIdx.x; e < items; e += STAGE_THREADS) {
+    const uint32_t r = __umulhi(e, magic_c);
+    const uint32_t c = e - r * chunks;
+    if (c * 16 >= s_shift[r] + W) continue;
+    const uintptr_t a = s_a0[r] + c * 16;
+    uint4 v;
+    if (a >= safe_lo && a + 16 <= safe_hi) {
+      v = __ldg(reinterpret_cast<const uint4*>(a));
+    } else {
+      uint8_t t[16];
+#pragma unroll
+      for (int b = 0; b < 16; ++b)
+        t[b] = (a + b >= base && a + b < base + src_bytes) ? *reinterpret_cast<const uint8_t*>(a + b) : 0;
+      v = *reinterpret_cast<uint4*>(t);
+    }
+    *reinterpret_cast<uint4*>(data + r * slot + c * 16) = v;
+  }
+  __syncthreads();
+
+  const uint32_t nbytes = rows * W;
+  uint8_t* out = parts.bases[d] + static_cast<uint64_t>(local0) * W;
+  auto byte_at = [&](uint32_t o) -> uint8_t {
+    const uint32_t r = __umulhi(o, magic_w);
+    return data[r * slot + s_shift[r] + (o - r * W)];
+  };
+  const uint32_t lead = min(nbytes, static_cast<uint32_t>((16 - (reinterpret_cast<uintptr_t>(out) & 15)) & 15));
+  for (uint32_t o = threadIdx.x; o < lead; o += STAGE_THREADS) out[o] = byte_at(o);
+  const uint32_t nvec = (nbytes - lead) >> 4;
+  uint4* vout = reinterpret_cast<uint4*>(out + lead);
+  for (uint32_t q = threadIdx.x; q < nvec; q += STAGE_THREADS) {
+    uint32_t w[4];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      const uint32_t o = lead + q * 16 + k * 4;
+      const uint32_t r = __umulhi(o, magic_w);
+      const uint32_t off = o - r * W;
+      if (off + 4 <= W) {
+        w[k] = smem_word_unaligned(data + r * slot, s_shift[r] + off);
+      } else {
+        uint32_t acc = 0;
+#pragma unroll
+        for (int b = 0; b < 4; ++b) acc |= static_cast<uint32_t>(byte_at(o + b)) << (8 * b);
+        w[k] = acc;
+      }
+    }
+    vout[q] = make_uint4(w[0], w[1], w[2], w[3]);
+  }
+  for (uint32_t o = lead + (nvec << 4) + threadIdx.x; o < nbytes; o += STAGE_THREADS) out[o] = byte_at(o);
+}
+
+static cudaError_t launch_scatter_staged(const void* src, uint32_t W, uint64_t src_rows,
+                                         const uint32_t* perm, const PeerParts& parts, cudaStream_t s) {
+  const uint32_t chunks = (W + 15 + 15) / 16;
+  const uint32_t slot = chunks * 16 + 16;
+  uint32_t rows = 128;
+  while (rows > 16 && rows * (slot + 12) > 40 * 1024) rows >>= 1;
+  const uint32_t smem = rows * (slot + 12);
+  PeerBlocks pblk{};
+  uint32_t blocks = 0;
+  for (uint32_t d = 0; d < parts.count; ++d) {
+    pblk.first_block[d] = blocks;
+    blocks += (parts.offsets[d + 1] - parts.offsets[d] + rows - 1) / rows;
+  }
+  pblk.first_block[parts.count] = blocks;
+  if (blocks == 0) return cudaSuccess;
+  const uint32_t magic_w = static_cast<uint32_t>((0x100000000ull + W - 1) / W);
+  const uint32_t magic_c = static_cast<uint32_t>((0x100000000ull + chunks - 1) / chunks);
+  ds::note_launch();
+  scatter_staged_kernel<<<blocks, STAGE_THREADS, smem, s>>>(static_cast<const uint8_t*>(src), W,
+                                                           src_rows * W, perm, rows, chunks, magic_w,
+                                                           magic_c, parts, pblk);
+  return cudaGetLastError();
+}
+
+template <typename G>
+static cudaError_t launch_scatter_parts(const void* src, const uint32_t* perm, uint32_t n,
+                                        uint32_t row_bytes, const PeerParts& parts, cudaStream_t s) {
+  const uint32_t gpr = row_bytes / sizeof(G);
+  uint32_t rows = 8192 / gpr;
+  if (rows < 1) rows = 1;
+  if (rows > GATHER_MAX_ROWS) rows = GATHER_MAX_ROWS;
+  const uint32_t magic = gpr == 1 ? 0u : static_cast<uint32_t>((0x100000000ull + gpr - 1) / gpr);
+  const uint32_t blocks = (n + rows - 1) / rows;
+  ds::note_launch();
+  scatter_rows_to_parts_kernel<G><<<blocks, GATHER_THREADS, 0, s>>>(static_cast<const G*>(src), perm, n,
+                                                                    gpr, rows, magic, parts);
+  return cudaGetLastError();
+}
+
 ds_status gather_rows_impl(const void* src, uint32_t row_bytes, uint64_t src_rows,
                            const uint32_t* idx, uint64_t n64, void* dst, cudaStream_t s) {
   if (n64 == 0) return DS_OK;
@@ -308,6 +487,54 @@ ds_status gather_rows_impl(const void* src, uint32_t row_bytes, uint64_t src_row
 extern "C" ds_status ds_gather_rows(const void* src, uint32_t row_bytes, uint64_t src_rows,
                                     const uint32_t* idx, uint64_t n, void* dst, void* stream) {
   return ds::gather_rows_impl(src, row_bytes, src_rows, idx, n, dst, static_cast<cudaStream_t>(stream));
+}
+
+extern "C" ds_status ds_scatter_rows_to_parts(const void* src, uint32_t row_bytes, uint64_t src_rows,
+                                              const uint32_t* perm, uint64_t n, uint32_t nparts,
+                                              const uint64_t* part_offsets, void* const* dst_bases,
+                                              void* stream) {
+  using namespace ds;
+  if (n == 0) return DS_OK;
+  if (n > DS_MAX_ROWS || row_bytes == 0 || row_bytes > 65536) {
+    set_error("%s: n or row_bytes out of range", __func__);
+    return DS_ERR_TOO_LARGE;
+  }
+  if (nparts == 0 || nparts > MAX_PEER_PARTS) {
+    set_error("%s: %u partitions unsupported (1..%d)", __func__, nparts, MAX_PEER_PARTS);
+    return DS_ERR_UNSUPPORTED;
+  }
+  if (!src || !perm || !part_offsets || !dst_bases) {
+    set_error("%s: NULL pointer", __func__);
+    return DS_ERR_INVALID_ARG;
+  }
+  PeerParts parts{};
+  parts.count = nparts;
+  uintptr_t bits = reinterpret_cast<uintptr_t>(src) | row_bytes;
+  for (uint32_t d = 0; d < nparts; ++d) {
+    parts.offsets[d] = static_cast<uint32_t>(part_offsets[d]);
+    parts.bases[d] = static_cast<unsigned char*>(dst_bases[d]);
+    if (part_offsets[d + 1] > part_offsets[d]) bits |= reinterpret_cast<uintptr_t>(dst_bases[d]);
+  }
+  parts.offsets[nparts] = static_cast<uint32_t>(part_offsets[nparts]);
+  if (part_offsets[nparts] != n) {
+    set_error("%s: part_offsets[nparts] must equal n", __func__);
+    return DS_ERR_INVALID_ARG;
+  }
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  const uint32_t n32 = static_cast<uint32_t>(n);
+  cudaError_t e;
+  if ((row_bytes & 15) != 0 && row_bytes >= 16 && row_bytes <= 2048 && src_rows > 0 && g_gather_mode != 1)
+    e = launch_scatter_staged(src, row_bytes, src_rows, perm, parts, s);
+  else if ((bits & 15) == 0) e = launch_scatter_parts<uint4>(src, perm, n32, row_bytes, parts, s);
+  else if ((bits & 7) == 0) e = launch_scatter_parts<uint2>(src, perm, n32, row_bytes, parts, s);
+  else if ((bits & 3) == 0) e = launch_scatter_parts<uint32_t>(src, perm, n32, row_bytes, parts, s);
+  else if ((bits & 1) == 0) e = launch_scatter_parts<uint16_t>(src, perm, n32, row_bytes, parts, s);
+  else e = launch_scatter_parts<uint8_t>(src, perm, n32, row_bytes, parts, s);
+  if (e != cudaSuccess) {
+    set_error("%s: launch failed: %s", __func__, cudaGetErrorString(e));
+    return DS_ERR_CUDA;
+  }
+  return DS_OK;
 }
 
 // Tuning hook, see g_gather_mode.

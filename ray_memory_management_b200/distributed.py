@@ -131,7 +131,7 @@ def splitters_from_samples(samples: np.ndarray, arrow_type: pa.DataType, world: 
 # the partition into 4 row ranges and pipelined gather / copy per range was measured slower
 # on 2 and on 8 GPUs -- the ranges' gathers compete with the key sort for HBM -- and was
 # dropped; see profiles/r01_multi_gpu.md.)
-_EXCHANGE = _os.environ.get("DS_EXCHANGE", "p2p")  # "p2p" | "nccl"
+_EXCHANGE = _os.environ.get("DS_EXCHANGE", "p2p")  # "fused" | "p2p" (copy engines) | "nccl"
 _LANES = _os.environ.get("DS_P2P_LANES", "1") == "1"  # one copy stream per destination
 _peer_cache: dict = {}
 
@@ -216,7 +216,7 @@ def _p2p_exchange_all(names, rbs, send, matrix, group):
     receive buffer} (valid until the next exchange on this group), or None when peer memory
     cannot be used (the caller then takes the NCCL path)."""
     world = matrix.shape[0]
-    if not (_EXCHANGE == "p2p" and world > 1 and dist.get_backend(group) == "nccl"):
+    if not (_EXCHANGE in ("p2p", "fused") and world > 1 and dist.get_backend(group) == "nccl"):
         return None
     try:
         layout = _PeerLayout(names, rbs, matrix)
@@ -301,6 +301,92 @@ def _wire_columns(parts, names, with_valid, key, dev):
     return wires
 
 
+def _sort_block_fused(block, key, descending, boundaries, with_valid, group, ph):
+    """Peer-memory sort plan whose map side is ONE kernel per column that slices the block by
+    destination and stores every row straight into the destination GPU's receive buffer
+    (ds_scatter_rows_to_parts over peer-mapped pointers): no send buffer, no copy pass.
+    Keys go first; the payload scatter runs on a second stream beside the key sort.
+    Returns None when peer memory is unavailable."""
+    import ctypes
+
+    from . import _lib
+    from .block import DeviceArrowBlock, DeviceArrowBlockAccessor, DeviceColumn, _argsort_nulls_last, _gather
+
+    world = dist.get_world_size(group)
+    rank = dist.get_rank(group)
+    dev = _dev()
+    n = block.num_rows
+    names = block.column_names
+    types = {nm: block.columns[nm].type for nm in names}
+    sort_key = [(key, "descending" if descending else "ascending")]
+    if n:
+        perm, counts = DeviceArrowBlockAccessor(block).partition_perm(boundaries, sort_key, descending)
+    else:
+        perm, counts = None, [0] * world
+    ph.mark("partition perm")
+    matrix = exchange_counts(counts, group, dev)
+    # wire columns: (wire name, row bytes, source tensor), key column(s) first
+    wires = []
+    for name in [key] + [nm for nm in names if nm != key]:
+        c = block.columns[name]
+        wires.append((name, c.row_bytes, c.data))
+        if name in with_valid:
+            wires.append((name + _VALID, 1, c.valid))
+    nkey = 2 if key in with_valid else 1
+    rbs = {w: rb for w, rb, _ in wires}
+    try:
+        layout = _PeerLayout([w for w, _, _ in wires], rbs, matrix)
+        pb = _peer_buffer(layout.total, group)
+    except Exception as e:  # pragma: no cover - depends on the system
+        import warnings
+
+        warnings.warn(f"peer-memory exchange unavailable ({e!r}); using NCCL all_to_all")
+        return None
+    n_recv = int(matrix[:, rank].sum())
+    offs = np.concatenate([[0], np.cumsum(counts)]).astype(np.uint64)
+    offs_c = (ctypes.c_uint64 * (world + 1))(*[int(x) for x in offs])
+    ptrs = [int(p) for p in pb.hdl.buffer_ptrs]
+    before = [int(matrix[:rank, d].sum()) for d in range(world)]
+    ph.mark("counts")
+
+    def scatter(w, rb, src):
+        if n == 0:
+            return
+        bases = (ctypes.c_void_p * world)(*[ptrs[d] + layout.off[w] + before[d] * rb for d in range(world)])
+        _lib.call("ds_scatter_rows_to_parts", src.data_ptr(), rb, n, perm.data_ptr(), n, world, offs_c,
+                  bases, torch.cuda.current_stream().cuda_stream)
+
+    main = torch.cuda.current_stream()
+    pb.hdl.barrier(channel=0)  # every rank is done with the buffer's previous contents
+    for w, rb, src in wires[:nkey]:
+        scatter(w, rb, src)
+    pb.hdl.barrier(channel=1)  # all keys have landed everywhere
+    ph.mark("scatter keys")
+    pb.side.wait_stream(main)
+    with torch.cuda.stream(pb.side):  # payload rows travel beside the key sort
+        for w, rb, src in wires[nkey:]:
+            scatter(w, rb, src)
+            src.record_stream(pb.side)
+        if perm is not None:
+            perm.record_stream(pb.side)
+    recv = {w: pb.buf[layout.off[w]: layout.off[w] + n_recv * rb] for w, rb, _ in wires}
+
+    def column(name):
+        return DeviceColumn(types[name], recv[name], recv.get(name + _VALID))
+
+    idx, sorted_key, _ = _argsort_nulls_last(column(key), descending)
+    ph.mark("key sort")
+    main.wait_stream(pb.side)
+    pb.hdl.barrier(channel=2)  # all payload rows have landed everywhere
+    ph.mark("wait payload")
+    cols = collections.OrderedDict()
+    for name in names:
+        cols[name] = sorted_key if name == key else _gather(column(name), idx)
+    ph.mark("gather payload")
+    ph.finish()
+    return DeviceArrowBlock(cols, n_recv)
+
+
 def sort_block(block, key: str, descending: bool = False, group=None):
     """Dataset.sort across the ranks of ``group``: this rank's input block in, this rank's
     slice of the globally sorted dataset out (rank order = key order)."""
@@ -327,6 +413,10 @@ def sort_block(block, key: str, descending: bool = False, group=None):
     acc = DeviceArrowBlockAccessor(block)
     sort_key = [(key, "descending" if descending else "ascending")]
     ph.mark("sample+splitters")
+    if _EXCHANGE == "fused" and 1 < world <= 16 and dist.get_backend(group) == "nccl":
+        out = _sort_block_fused(block, key, descending, boundaries, with_valid, group, ph)
+        if out is not None:
+            return out
     parts = acc.partition_unsorted(boundaries, sort_key, descending)
     counts = [p.num_rows for p in parts]
     ph.mark("partition")
@@ -338,7 +428,7 @@ def sort_block(block, key: str, descending: bool = False, group=None):
     n_recv = int(matrix[:, rank].sum())
     rbs = {w: rb for w, rb, _ in wires}
 
-    use_p2p = _EXCHANGE == "p2p" and world > 1 and dist.get_backend(group) == "nccl"
+    use_p2p = _EXCHANGE in ("p2p", "fused") and world > 1 and dist.get_backend(group) == "nccl"
     if use_p2p:
         try:
             layout = _PeerLayout([w for w, _, _ in wires], rbs, matrix)

@@ -386,3 +386,33 @@ def test_prefix_repair_mode_matches_full_sort(ds, desc):
     k[::1000] = k[0]
     a, _ = _argsort_c(ds, k, "i64", desc, want_sorted=False)
     assert np.array_equal(a.astype(np.int64), _arrow_order(k, "i64", desc))
+
+
+@pytest.mark.parametrize("width", [1, 8, 10, 90, 100])
+def test_scatter_rows_to_parts_c_abi(ds, width):
+    """the fused map-side slicing kernel against numpy (local destinations; over NVLink it is
+    exercised by tests/test_gpu_distributed.py with DS_EXCHANGE=fused)."""
+    import ctypes
+
+    lib = ds._lib
+    rng = np.random.default_rng(width)
+    n, nparts = 50_003, 5
+    src = rng.integers(0, 256, (n, width), dtype=np.uint8)
+    bucket = rng.integers(0, nparts, n)
+    bucket[bucket == 3] = 2  # an empty partition
+    perm = np.argsort(bucket, kind="stable").astype(np.int32)
+    counts = np.bincount(bucket, minlength=nparts)
+    offs = np.concatenate([[0], np.cumsum(counts)])
+    dsrc = torch.from_numpy(src.reshape(-1).copy()).cuda()
+    dperm = torch.from_numpy(perm).cuda()
+    outs = [torch.zeros(int(c) * width + 32, dtype=torch.uint8, device="cuda") for c in counts]
+    bases = (ctypes.c_void_p * nparts)(*[o.data_ptr() + 16 for o in outs])
+    offs_c = (ctypes.c_uint64 * (nparts + 1))(*[int(x) for x in offs])
+    lib.call("ds_scatter_rows_to_parts", dsrc.data_ptr(), width, n, dperm.data_ptr(), n, nparts, offs_c,
+             bases, torch.cuda.current_stream().cuda_stream)
+    torch.cuda.synchronize()
+    for d in range(nparts):
+        got = outs[d].cpu().numpy()
+        want = src[perm[offs[d]:offs[d + 1]]].reshape(-1)
+        assert np.array_equal(got[16:16 + len(want)], want)
+        assert not got[:16].any() and not got[16 + len(want):].any()
