@@ -257,6 +257,30 @@ ds_status ds_segmented_count_valid(const uint8_t* valid, const uint32_t* idx,
 ds_status ds_segment_counts(const uint32_t* seg_starts, uint32_t nseg, int64_t* out,
                             void* stream);
 
+/* Per-run sum of addend[j] + weights[j] * (vals[j] - means[s])^2 over the non-null rows of
+ * run s (weights and addend optional).  With neither it is the block-level half of Std,
+ * BlockAccessor.sum_of_squared_diffs_from_mean (_internal/arrow_block.py:331-351, used at
+ * aggregate.py:262); with weights = counts and addend = M2 over partial rows (vals = partial
+ * means) it is the merge of Std accumulators (aggregate.py:236-249), evaluated against the
+ * merged mean instead of pairwise. */
+ds_status ds_segmented_sumsqdiff_f64(const double* vals, const uint8_t* valid, const int64_t* weights,
+                                     const double* addend, const uint32_t* idx,
+                                     const uint32_t* seg_starts, uint32_t nseg, uint64_t n,
+                                     const double* means, double* out, void* ws, size_t* ws_bytes,
+                                     void* stream);
+ds_status ds_segmented_sumsqdiff_i64(const int64_t* vals, const uint8_t* valid, const uint32_t* idx,
+                                     const uint32_t* seg_starts, uint32_t nseg, uint64_t n,
+                                     const double* means, double* out, void* ws, size_t* ws_bytes,
+                                     void* stream);
+
+/* out[i] = a[i] * w[i]: partial mean x partial count = partial sum (aggregate.py:246). */
+ds_status ds_scale_f64_by_i64(const double* a, const int64_t* w, uint64_t n, double* out,
+                              void* stream);
+
+/* Std finalize (aggregate.py:270-276): 0.0 if count < 2 else sqrt(m2 / (count - ddof)). */
+ds_status ds_finalize_std(const double* m2, const int64_t* count, uint64_t n, int32_t ddof,
+                          double* out, void* stream);
+
 /* Validity of a finalized aggregate per group (null policy of
  * _internal/null_aggregate.py:12-26, _null_wrap_finalize :228-251): with ignore_nulls the
  * result is a value unless every row of the group was null; without, only if none was.

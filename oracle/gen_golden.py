@@ -219,7 +219,8 @@ def gen_nulls():
     out = {"k": k, "vf": vf, "vi": vi, "mf": mf, "mi": mi, "block_cuts": np.array(_split(n, nb))}
     for ignore in (True, False):
         aggs = (A.Sum("vf", ignore), A.Mean("vf", ignore), A.Min("vi", ignore), A.Max("vi", ignore),
-                A.Sum("vi", ignore), A.Mean("vi", ignore), A.Count(), A.AbsMax("vi", ignore))
+                A.Sum("vi", ignore), A.Mean("vi", ignore), A.Count(), A.AbsMax("vi", ignore),
+                A.Std("vf", ignore_nulls=ignore), A.Std("vi", ddof=0, ignore_nulls=ignore))
         random.seed(5)
         blocks = ref_shim.ref_groupby(tabs, "k", aggs)
         cat = pa.concat_tables([b for b in blocks if b.num_rows], promote=True)

@@ -4,7 +4,7 @@ Host-side mirror of the reference's operator/block interface; all per-block comp
 runs in the sm_100a CUDA library behind include/ds_shuffle.h (no CPU fallback).
 """
 from . import _lib  # noqa: F401  (raises if the CUDA library has not been built)
-from .aggregate import AbsMax, AggregateFn, Count, Max, Mean, Min, Sum
+from .aggregate import AbsMax, AggregateFn, Count, Max, Mean, Min, Std, Sum
 from .block import (
     BlockAccessor,
     BlockExecStats,
@@ -22,7 +22,7 @@ from .shuffle_and_partition import DeviceShufflePartitionOp
 from .sort import DeviceSortOp, sample_boundaries, sort_impl
 
 __all__ = [
-    "AbsMax", "AggregateFn", "Count", "Max", "Mean", "Min", "Sum", "BlockAccessor", "BlockExecStats",
+    "AbsMax", "AggregateFn", "Count", "Max", "Mean", "Min", "Std", "Sum", "BlockAccessor", "BlockExecStats",
     "BlockList", "BlockMetadata", "DeviceArrowBlock", "DeviceArrowBlockAccessor", "DeviceColumn",
     "DatasetContext", "Dataset", "DeviceGroupbyOp", "GroupedDataset", "aggregate_impl",
     "DeviceShufflePlan", "ShuffleOp", "DeviceShufflePartitionOp", "DeviceSortOp",

@@ -65,6 +65,10 @@ _PROTOS = {
     "ds_segmented_count_valid": [_P, _P, _P, c_uint32, c_uint64, _P, _P, _SZP, _P],
     "ds_segment_counts": [_P, c_uint32, _P, _P],
     "ds_finalize_mean": [_P, c_int32, _P, c_uint64, _P, _P],
+    "ds_segmented_sumsqdiff_f64": [_P, _P, _P, _P, _P, _P, c_uint32, c_uint64, _P, _P, _P, _SZP, _P],
+    "ds_segmented_sumsqdiff_i64": [_P, _P, _P, _P, c_uint32, c_uint64, _P, _P, _P, _SZP, _P],
+    "ds_scale_f64_by_i64": [_P, _P, c_uint64, _P, _P],
+    "ds_finalize_std": [_P, _P, c_uint64, c_int32, _P, _P],
     "ds_finalize_validity": [_P, _P, c_uint64, c_int32, _P, _P],
 }
 EXPORTED = ["ds_version", "ds_last_error"] + sorted(_PROTOS)

@@ -158,3 +158,48 @@ class Mean(_AggregateOnKeyBase):
         from .block import _finalize_mean
 
         return _with_validity(_finalize_mean(parts["sum"], parts["nvalid"]), parts, self._ignore_nulls)
+
+
+class Std(_AggregateOnKeyBase):
+    """aggregate.py:214-286 -- accumulator [M2, mean, count].
+
+    Per block: count, sum -> mean, then M2 = sum (x - mean)^2 in a second segmented pass
+    (sum_of_squared_diffs_from_mean, arrow_block.py:331-351).  Merging k partials of a key
+    evaluates the parallel-variance formula (aggregate.py:236-249) against the merged mean
+    in one pass, M2 = sum_i M2_i + n_i (mean_i - mean)^2, which equals the chain of pairwise
+    merges up to rounding."""
+
+    def __init__(self, on: Optional[str] = None, ddof: int = 1, ignore_nulls: bool = True):
+        super().__init__(on, ignore_nulls, "std")
+        self._ddof = ddof
+
+    def _device_accumulate(self, block, starts, nseg, n):
+        from .block import _finalize_mean, _segmented_reduce, _segmented_sumsqdiff
+
+        col = block.column(self._key_fn)
+        parts = _null_parts(block, self._key_fn, starts, nseg, n)
+        total = _segmented_reduce(col, None, starts, nseg, n, "sum")
+        mean = _finalize_mean(total, parts["nvalid"])
+        parts["mean"] = mean
+        parts["m2"] = _segmented_sumsqdiff(col, None, starts, nseg, n, mean)
+        return parts
+
+    def _device_merge_ops(self):
+        # layout of the partial block only (the merge itself is _device_merge)
+        return {"nvalid": "sum", "nrows": "sum", "mean": "sum", "m2": "sum"}
+
+    def _device_merge(self, part, idx, starts, nseg, n):
+        from .block import _finalize_mean, _scale, _segmented_reduce, _segmented_sumsqdiff
+
+        nvalid = _segmented_reduce(part("nvalid"), idx, starts, nseg, n, "sum")
+        nrows = _segmented_reduce(part("nrows"), idx, starts, nseg, n, "sum")
+        total = _segmented_reduce(_scale(part("mean"), part("nvalid")), idx, starts, nseg, n, "sum")
+        mean = _finalize_mean(total, nvalid)
+        m2 = _segmented_sumsqdiff(part("mean"), idx, starts, nseg, n, mean,
+                                  weights=part("nvalid"), addend=part("m2"))
+        return {"nvalid": nvalid, "nrows": nrows, "mean": mean, "m2": m2}
+
+    def _device_finalize(self, parts):
+        from .block import _finalize_std
+
+        return _with_validity(_finalize_std(parts["m2"], parts["nvalid"], self._ddof), parts, self._ignore_nulls)

@@ -495,6 +495,40 @@ def _segmented_count_valid(vals: DeviceColumn, idx: Optional[torch.Tensor], star
     return DeviceColumn(pa.int64(), out)
 
 
+def _segmented_sumsqdiff(vals: DeviceColumn, idx: Optional[torch.Tensor], starts: torch.Tensor, nseg: int,
+                         n: int, means: DeviceColumn, weights: Optional[DeviceColumn] = None,
+                         addend: Optional[DeviceColumn] = None) -> DeviceColumn:
+    out = _empty_u8(nseg * 8)
+    ip = idx.data_ptr() if idx is not None else None
+    if pa.types.is_float64(vals.type):
+        args = (vals.ptr, vals.valid_ptr, weights.ptr if weights is not None else None,
+                addend.ptr if addend is not None else None, ip, starts.data_ptr(), nseg, n, means.ptr,
+                out.data_ptr())
+        fn = "ds_segmented_sumsqdiff_f64"
+    elif pa.types.is_int64(vals.type) and weights is None and addend is None:
+        args = (vals.ptr, vals.valid_ptr, ip, starts.data_ptr(), nseg, n, means.ptr, out.data_ptr())
+        fn = "ds_segmented_sumsqdiff_i64"
+    else:
+        raise NotImplementedError(f"std over Arrow type {vals.type} is not supported on device (int64, float64)")
+    ws = _lib.call_ws(fn, _workspace, *args, stream=_stream())
+    ws.record_stream(torch.cuda.current_stream())
+    return DeviceColumn(pa.float64(), out)
+
+
+def _scale(a: DeviceColumn, w: DeviceColumn) -> DeviceColumn:
+    n = a.num_rows
+    out = _empty_u8(n * 8)
+    _lib.call("ds_scale_f64_by_i64", a.ptr, w.ptr, n, out.data_ptr(), _stream())
+    return DeviceColumn(pa.float64(), out)
+
+
+def _finalize_std(m2: DeviceColumn, count: DeviceColumn, ddof: int) -> DeviceColumn:
+    n = count.num_rows
+    out = _empty_u8(n * 8)
+    _lib.call("ds_finalize_std", m2.ptr, count.ptr, n, int(ddof), out.data_ptr(), _stream())
+    return DeviceColumn(pa.float64(), out)
+
+
 def _finalize_validity(nvalid: DeviceColumn, nrows: DeviceColumn, ignore_nulls: bool) -> torch.Tensor:
     n = nvalid.num_rows
     out = _empty_u8(n)
@@ -765,10 +799,13 @@ class DeviceArrowBlockAccessor:
             starts, nseg = _segment_heads(sorted_key)
             cols[key] = _gather(sorted_key, starts[:nseg])
         for name, agg in zip(names, aggs):
-            parts = {
-                p: _segmented_reduce(cat.columns[f"{name}#{p}"], idx, starts, nseg, n, op)
-                for p, op in agg._device_merge_ops().items()
-            }
+            if hasattr(agg, "_device_merge"):  # merges that are not plain per-part reductions
+                parts = agg._device_merge(lambda p: cat.columns[f"{name}#{p}"], idx, starts, nseg, n)
+            else:
+                parts = {
+                    p: _segmented_reduce(cat.columns[f"{name}#{p}"], idx, starts, nseg, n, op)
+                    for p, op in agg._device_merge_ops().items()
+                }
             if finalize:
                 cols[name] = agg._device_finalize(parts)
             else:

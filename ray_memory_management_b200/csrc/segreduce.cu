@@ -107,7 +107,7 @@ __global__ void __launch_bounds__(SEG_THREADS)
 // ------------------------------------------------------------------ reduce
 template <typename T, int OP>
 __device__ __forceinline__ T red_identity() {
-  if constexpr (OP == DS_OP_SUM || OP == 100 /* OP_COUNT_VALID */ || OP == DS_OP_ABSMAX) {
+  if constexpr (OP == DS_OP_SUM || OP == 100 || OP == 101 /* internal sums */ || OP == DS_OP_ABSMAX) {
     return T(0);
   } else if constexpr (std::is_floating_point<T>::value) {
     return OP == DS_OP_MIN ? __longlong_as_double(0x7FF0000000000000ll)
@@ -118,7 +118,7 @@ __device__ __forceinline__ T red_identity() {
 }
 template <typename T, int OP>
 __device__ __forceinline__ T red_op(T a, T b) {
-  if (OP == DS_OP_SUM || OP == 100 /* OP_COUNT_VALID */) return a + b;
+  if (OP == DS_OP_SUM || OP == 100 || OP == 101 /* internal sums */) return a + b;
   if (OP == DS_OP_MIN) return b < a ? b : a;
   return b > a ? b : a;
 }
@@ -129,12 +129,24 @@ __device__ __forceinline__ T shfl_xor_t(T v, int o) {
 }
 
 constexpr int OP_COUNT_VALID = 100;  // internal: sum of (valid[j] != 0)
+constexpr int OP_SUMSQDIFF = 101;    // internal: sum of addend[j] + w[j] * (x[j] - mean[s])^2
+
+struct SqDiffArgs {
+  const double* means;     // one per run
+  const int64_t* weights;  // optional, one per element
+  const double* addend;    // optional, one per element
+};
 
 // Element j of the reduction: the value, or the op's identity where the row is null.
-template <typename T, int OP>
-__device__ __forceinline__ T seg_elem(const T* __restrict__ vals, const uint8_t* __restrict__ valid,
-                                      uint32_t j) {
-  if constexpr (OP == OP_COUNT_VALID) {
+template <typename TIn, typename T, int OP>
+__device__ __forceinline__ T seg_elem(const TIn* __restrict__ vals, const uint8_t* __restrict__ valid,
+                                      uint32_t j, uint32_t s, const SqDiffArgs& sq) {
+  if constexpr (OP == OP_SUMSQDIFF) {
+    if (valid && valid[j] == 0) return T(0);
+    const double d = static_cast<double>(vals[j]) - sq.means[s];
+    const double w = sq.weights ? static_cast<double>(sq.weights[j]) : 1.0;
+    return (sq.addend ? sq.addend[j] : 0.0) + w * d * d;
+  } else if constexpr (OP == OP_COUNT_VALID) {
     return static_cast<T>(valid ? (valid[j] != 0) : 1);
   } else {
     if (valid && valid[j] == 0) return red_identity<T, OP>();
@@ -156,13 +168,14 @@ __device__ __forceinline__ uint32_t last_le(const uint32_t* __restrict__ starts,
   return lo;
 }
 
-template <typename T, int OP>
+template <typename TIn, typename T, int OP>
 __global__ void __launch_bounds__(SEG_THREADS)
-    segreduce_tile_kernel(const T* __restrict__ vals, const uint8_t* __restrict__ valid,
+    segreduce_tile_kernel(const TIn* __restrict__ vals, const uint8_t* __restrict__ valid,
                           const uint32_t* __restrict__ idx,
                           const uint32_t* __restrict__ seg_starts, uint32_t nseg, uint32_t n,
                           T* __restrict__ out, T* __restrict__ p_first, T* __restrict__ p_last,
-                          uint32_t* __restrict__ t_first, uint32_t* __restrict__ t_last) {
+                          uint32_t* __restrict__ t_first, uint32_t* __restrict__ t_last,
+                          SqDiffArgs sq) {
   __shared__ uint32_t s_f, s_l;
   const uint32_t tile = blockIdx.x;
   const uint32_t t0 = tile * SEG_TILE;
@@ -186,7 +199,7 @@ __global__ void __launch_bounds__(SEG_THREADS)
       const uint32_t a0 = seg_starts[s], b0 = seg_starts[s + 1];
       const uint32_t a = max(a0, t0), b = min(b0, t1);
       T acc = red_identity<T, OP>();
-      for (uint32_t i = a; i < b; ++i) acc = red_op<T, OP>(acc, seg_elem<T, OP>(vals, valid, idx ? idx[i] : i));
+      for (uint32_t i = a; i < b; ++i) acc = red_op<T, OP>(acc, seg_elem<TIn, T, OP>(vals, valid, idx ? idx[i] : i, s, sq));
       if (a0 >= t0 && b0 <= t1) out[s] = acc;
       else if (s == f) p_first[tile] = acc;
       else p_last[tile] = acc;
@@ -196,7 +209,7 @@ __global__ void __launch_bounds__(SEG_THREADS)
       const uint32_t a0 = seg_starts[s], b0 = seg_starts[s + 1];
       const uint32_t a = max(a0, t0), b = min(b0, t1);
       T acc = red_identity<T, OP>();
-      for (uint32_t i = a + lane; i < b; i += 32) acc = red_op<T, OP>(acc, seg_elem<T, OP>(vals, valid, idx ? idx[i] : i));
+      for (uint32_t i = a + lane; i < b; i += 32) acc = red_op<T, OP>(acc, seg_elem<TIn, T, OP>(vals, valid, idx ? idx[i] : i, s, sq));
 #pragma unroll
       for (int o = 16; o > 0; o >>= 1) acc = red_op<T, OP>(acc, shfl_xor_t(acc, o));
       if (lane == 0) {
@@ -231,10 +244,11 @@ __global__ void segreduce_fixup_kernel(const uint32_t* __restrict__ seg_starts, 
   out[s] = acc;
 }
 
-template <typename T>
-static ds_status segreduce_impl(const T* vals, const uint8_t* valid, const uint32_t* idx,
+template <typename TIn, typename T>
+static ds_status segreduce_impl(const TIn* vals, const uint8_t* valid, const uint32_t* idx,
                                 const uint32_t* seg_starts, uint32_t nseg, uint64_t n64, int32_t op,
-                                T* out, void* ws, size_t* ws_bytes, void* stream, const char* fn) {
+                                T* out, void* ws, size_t* ws_bytes, void* stream, const char* fn,
+                                SqDiffArgs sq = SqDiffArgs{nullptr, nullptr, nullptr}) {
   if (n64 > DS_MAX_ROWS) {
     set_error("%s: n exceeds DS_MAX_ROWS", fn);
     return DS_ERR_TOO_LARGE;
@@ -253,21 +267,26 @@ static ds_status segreduce_impl(const T* vals, const uint8_t* valid, const uint3
     set_error("%s: NULL pointer", fn);
     return DS_ERR_INVALID_ARG;
   }
-  if (!((op >= DS_OP_SUM && op <= DS_OP_ABSMAX) || op == OP_COUNT_VALID)) {
+  if (!((op >= DS_OP_SUM && op <= DS_OP_ABSMAX) || op == OP_COUNT_VALID || op == OP_SUMSQDIFF)) {
     set_error("%s: unknown op %d", fn, op);
     return DS_ERR_INVALID_ARG;
   }
   cudaStream_t s = static_cast<cudaStream_t>(stream);
 #define DS_SEG(OP)                                                                               \
-  ds::note_launch(); segreduce_tile_kernel<T, OP><<<tiles, SEG_THREADS, 0, s>>>(vals, valid, idx, seg_starts, nseg, n, out, \
-                                                             p_first, p_last, t_first, t_last);  \
+  ds::note_launch(); segreduce_tile_kernel<TIn, T, OP><<<tiles, SEG_THREADS, 0, s>>>(vals, valid, idx, seg_starts, nseg, n, out, \
+                                                             p_first, p_last, t_first, t_last, sq);  \
   ds::note_launch(); segreduce_fixup_kernel<T, OP><<<(tiles + 127) / 128, 128, 0, s>>>(                             \
       seg_starts, n, tiles, p_first, p_last, t_first, t_last, out)
-  if (op == DS_OP_SUM) { DS_SEG(DS_OP_SUM); }
-  else if (op == DS_OP_MIN) { DS_SEG(DS_OP_MIN); }
-  else if (op == DS_OP_MAX) { DS_SEG(DS_OP_MAX); }
-  else if (op == DS_OP_ABSMAX) { DS_SEG(DS_OP_ABSMAX); }
-  else { DS_SEG(OP_COUNT_VALID); }
+  if constexpr (std::is_same<TIn, T>::value) {
+    if (op == DS_OP_SUM) { DS_SEG(DS_OP_SUM); }
+    else if (op == DS_OP_MIN) { DS_SEG(DS_OP_MIN); }
+    else if (op == DS_OP_MAX) { DS_SEG(DS_OP_MAX); }
+    else if (op == DS_OP_ABSMAX) { DS_SEG(DS_OP_ABSMAX); }
+    else if (op == OP_SUMSQDIFF) { DS_SEG(OP_SUMSQDIFF); }
+    else { DS_SEG(OP_COUNT_VALID); }
+  } else {
+    DS_SEG(OP_SUMSQDIFF);  // int64 values, double accumulator
+  }
 #undef DS_SEG
   DS_LAUNCH_CHECK();
   return DS_OK;
@@ -277,6 +296,19 @@ __global__ void segment_counts_kernel(const uint32_t* __restrict__ seg_starts, u
                                       int64_t* __restrict__ out) {
   const uint32_t s = blockIdx.x * blockDim.x + threadIdx.x;
   if (s < nseg) out[s] = static_cast<int64_t>(seg_starts[s + 1] - seg_starts[s]);
+}
+
+__global__ void scale_kernel(const double* __restrict__ a, const int64_t* __restrict__ w, uint32_t n,
+                             double* __restrict__ out) {
+  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) out[i] = a[i] * static_cast<double>(w[i]);
+}
+
+// aggregate.py:270-276: 0.0 for fewer than two values, else sqrt(M2 / (count - ddof))
+__global__ void finalize_std_kernel(const double* __restrict__ m2, const int64_t* __restrict__ count,
+                                    uint32_t n, int ddof, double* __restrict__ out) {
+  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) out[i] = count[i] < 2 ? 0.0 : sqrt(m2[i] / static_cast<double>(count[i] - ddof));
 }
 
 // Null policy of python/ray/data/_internal/null_aggregate.py:12-26 per group:
@@ -295,7 +327,7 @@ __global__ void finalize_mean_kernel(const void* __restrict__ sum, bool sum_is_i
   if (i >= n) return;
   const double s = sum_is_i64 ? static_cast<double>(static_cast<const int64_t*>(sum)[i])
                               : static_cast<const double*>(sum)[i];
-  out[i] = s / static_cast<double>(count[i]);
+  out[i] = count[i] == 0 ? 0.0 : s / static_cast<double>(count[i]);  // all-null group: value is masked out
 }
 
 }  // namespace ds
@@ -336,24 +368,24 @@ ds_status ds_segment_heads_i64(const int64_t* sorted_keys, uint64_t n64, uint32_
 ds_status ds_segmented_reduce_f64(const double* vals, const uint8_t* valid, const uint32_t* idx,
                                   const uint32_t* seg_starts, uint32_t nseg, uint64_t n, int32_t op,
                                   double* out, void* ws, size_t* ws_bytes, void* stream) {
-  if (op == ds::OP_COUNT_VALID) op = -1;
-  return ds::segreduce_impl<double>(vals, valid, idx, seg_starts, nseg, n, op, out, ws, ws_bytes,
-                                    stream, __func__);
+  if (op >= ds::OP_COUNT_VALID) op = -1;
+  return ds::segreduce_impl<double, double>(vals, valid, idx, seg_starts, nseg, n, op, out, ws,
+                                            ws_bytes, stream, __func__);
 }
 
 ds_status ds_segmented_reduce_i64(const int64_t* vals, const uint8_t* valid, const uint32_t* idx,
                                   const uint32_t* seg_starts, uint32_t nseg, uint64_t n, int32_t op,
                                   int64_t* out, void* ws, size_t* ws_bytes, void* stream) {
-  if (op == ds::OP_COUNT_VALID) op = -1;
-  return ds::segreduce_impl<int64_t>(vals, valid, idx, seg_starts, nseg, n, op, out, ws, ws_bytes,
-                                     stream, __func__);
+  if (op >= ds::OP_COUNT_VALID) op = -1;
+  return ds::segreduce_impl<int64_t, int64_t>(vals, valid, idx, seg_starts, nseg, n, op, out, ws,
+                                              ws_bytes, stream, __func__);
 }
 
 ds_status ds_segmented_count_valid(const uint8_t* valid, const uint32_t* idx,
                                    const uint32_t* seg_starts, uint32_t nseg, uint64_t n,
                                    int64_t* out, void* ws, size_t* ws_bytes, void* stream) {
-  return ds::segreduce_impl<int64_t>(nullptr, valid, idx, seg_starts, nseg, n, ds::OP_COUNT_VALID,
-                                     out, ws, ws_bytes, stream, __func__);
+  return ds::segreduce_impl<int64_t, int64_t>(nullptr, valid, idx, seg_starts, nseg, n,
+                                              ds::OP_COUNT_VALID, out, ws, ws_bytes, stream, __func__);
 }
 
 ds_status ds_segment_counts(const uint32_t* seg_starts, uint32_t nseg, int64_t* out, void* stream) {
@@ -364,6 +396,60 @@ ds_status ds_segment_counts(const uint32_t* seg_starts, uint32_t nseg, int64_t* 
   }
   ds::note_launch(); ds::segment_counts_kernel<<<(nseg + 255) / 256, 256, 0, static_cast<cudaStream_t>(stream)>>>(
       seg_starts, nseg, out);
+  DS_LAUNCH_CHECK();
+  return DS_OK;
+}
+
+ds_status ds_segmented_sumsqdiff_f64(const double* vals, const uint8_t* valid, const int64_t* weights,
+                                     const double* addend, const uint32_t* idx,
+                                     const uint32_t* seg_starts, uint32_t nseg, uint64_t n,
+                                     const double* means, double* out, void* ws, size_t* ws_bytes,
+                                     void* stream) {
+  if (ws && !means) {
+    ds::set_error("%s: means must not be NULL", __func__);
+    return DS_ERR_INVALID_ARG;
+  }
+  return ds::segreduce_impl<double, double>(vals, valid, idx, seg_starts, nseg, n, ds::OP_SUMSQDIFF, out,
+                                            ws, ws_bytes, stream, __func__,
+                                            ds::SqDiffArgs{means, weights, addend});
+}
+
+ds_status ds_segmented_sumsqdiff_i64(const int64_t* vals, const uint8_t* valid, const uint32_t* idx,
+                                     const uint32_t* seg_starts, uint32_t nseg, uint64_t n,
+                                     const double* means, double* out, void* ws, size_t* ws_bytes,
+                                     void* stream) {
+  if (ws && !means) {
+    ds::set_error("%s: means must not be NULL", __func__);
+    return DS_ERR_INVALID_ARG;
+  }
+  return ds::segreduce_impl<int64_t, double>(vals, valid, idx, seg_starts, nseg, n, ds::OP_SUMSQDIFF, out,
+                                             ws, ws_bytes, stream, __func__,
+                                             ds::SqDiffArgs{means, nullptr, nullptr});
+}
+
+ds_status ds_scale_f64_by_i64(const double* a, const int64_t* w, uint64_t n, double* out, void* stream) {
+  if (n == 0) return DS_OK;
+  if (!a || !w || !out || n > 0xFFFFFFFFull) {
+    ds::set_error("%s: bad argument", __func__);
+    return DS_ERR_INVALID_ARG;
+  }
+  ds::note_launch();
+  ds::scale_kernel<<<(uint32_t)((n + 255) / 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      a, w, static_cast<uint32_t>(n), out);
+  DS_LAUNCH_CHECK();
+  return DS_OK;
+}
+
+ds_status ds_finalize_std(const double* m2, const int64_t* count, uint64_t n, int32_t ddof, double* out,
+                          void* stream) {
+  if (n == 0) return DS_OK;
+  if (!m2 || !count || !out || n > 0xFFFFFFFFull) {
+    ds::set_error("%s: bad argument", __func__);
+    return DS_ERR_INVALID_ARG;
+  }
+  ds::note_launch();
+  ds::finalize_std_kernel<<<(uint32_t)((n + 255) / 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      m2, count, static_cast<uint32_t>(n), ddof, out);
   DS_LAUNCH_CHECK();
   return DS_OK;
 }

@@ -7,7 +7,7 @@ boundaries, per-partition combine on the map side, merge + finalize on the reduc
 from typing import List, Optional, Tuple, Union
 
 from . import sort
-from .aggregate import AbsMax, AggregateFn, Count, Max, Mean, Min, Sum
+from .aggregate import AbsMax, AggregateFn, Count, Max, Mean, Min, Std, Sum
 from .block import Block, BlockAccessor, BlockExecStats, BlockList, BlockMetadata
 from .context import DatasetContext
 from .shuffle import DeviceShufflePlan, ShuffleOp
@@ -94,3 +94,6 @@ class GroupedDataset:
 
     def mean(self, on: str, ignore_nulls: bool = True):
         return self.aggregate(Mean(on, ignore_nulls))
+
+    def std(self, on: str, ddof: int = 1, ignore_nulls: bool = True):
+        return self.aggregate(Std(on, ddof, ignore_nulls))

@@ -33,7 +33,8 @@ def _tabs(g):
 def test_groupby_null_policy_golden(ds, golden, ignore):
     g = golden("nulls")
     aggs = (ds.Sum("vf", ignore), ds.Mean("vf", ignore), ds.Min("vi", ignore), ds.Max("vi", ignore),
-            ds.Sum("vi", ignore), ds.Mean("vi", ignore), ds.Count(), ds.AbsMax("vi", ignore))
+            ds.Sum("vi", ignore), ds.Mean("vi", ignore), ds.Count(), ds.AbsMax("vi", ignore),
+            ds.Std("vf", ignore_nulls=ignore), ds.Std("vi", ddof=0, ignore_nulls=ignore))
     out = ds.Dataset.from_arrow(_tabs(g)).groupby("k").aggregate(*aggs).to_arrow_concat()
     tag = "ign" if ignore else "strict"
     assert out.column_names == list(g[f"{tag}_names"])
@@ -96,3 +97,22 @@ def test_reference_sum_with_nulls_known_answers(ds):
         {"A": 0, "mean(B)": None}, {"A": 1, "mean(B)": None}, {"A": 2, "mean(B)": None}]
     # Count counts rows, nulls included (aggregate.py:104-106)
     assert [r["count()"] for r in d.groupby("A").count().iter_rows()] == [34, 33, 33]
+
+
+def test_std_matches_pandas_like_reference_test(ds):
+    # test_dataset.py:3542-3599 of the reference compares Std with pandas (ddof 1 and 0)
+    import pandas as pd
+
+    rng = np.random.default_rng(4)
+    n = 40_000
+    df = pd.DataFrame({"A": rng.integers(0, 37, n), "B": rng.standard_normal(n) * 100 + 1e6})
+    tabs = [pa.Table.from_pandas(df.iloc[i::5], preserve_index=False) for i in range(5)]
+    d = ds.Dataset.from_arrow(tabs)
+    for ddof in (1, 0):
+        got = d.groupby("A").std("B", ddof=ddof).to_arrow_concat().to_pandas()
+        want = df.groupby("A")["B"].std(ddof=ddof).reset_index()
+        assert np.array_equal(got["A"].to_numpy(), want["A"].to_numpy())
+        assert np.allclose(got["std(B)"].to_numpy(), want["B"].to_numpy(), rtol=1e-6, atol=0)
+    # single-row groups give 0.0 (aggregate.py:273-274)
+    t = pa.table({"A": np.arange(5, dtype=np.int64), "B": np.arange(5, dtype=np.float64)})
+    assert ds.Dataset.from_arrow([t]).groupby("A").std("B").to_arrow_concat()["std(B)"].to_pylist() == [0.0] * 5
