@@ -295,6 +295,25 @@ ds_status ds_finalize_validity(const int64_t* nvalid, const int64_t* nrows, uint
 ds_status ds_finalize_mean(const void* sum, int32_t sum_is_i64, const int64_t* count,
                            uint64_t n, double* out, void* stream);
 
+/* ------------------------------------------------------- GraySort records ---- */
+
+/* On-disk GraySort layout (records of record_bytes back to back, key first;
+ * experimental/raysort/constants.py:8 RECORD_SIZE = 100) <-> the two Arrow columns
+ * {key: fixed_size_binary(key_bytes), payload: fixed_size_binary(record_bytes-key_bytes)}.
+ * The reference reads and writes such files through gensort/valsort subprocesses
+ * (experimental/raysort/main.py:148-176,399-432); there is no in-tree parser to replace. */
+ds_status ds_split_records(const uint8_t* records, uint32_t record_bytes, uint32_t key_bytes,
+                           uint64_t n, uint8_t* key_out, uint8_t* payload_out, void* stream);
+ds_status ds_join_records(const uint8_t* key, const uint8_t* payload, uint32_t record_bytes,
+                          uint32_t key_bytes, uint64_t n, uint8_t* records_out, void* stream);
+
+/* valsort-style summary of a (key, payload) block, ADDED to out3 (device, zero it first):
+ * out3[0] += sum over records of CRC-32(record) (order independent, so equal before and
+ * after a correct sort), out3[1] += records whose key is below the previous record's,
+ * out3[2] += records whose key equals the previous record's. */
+ds_status ds_validate_records(const uint8_t* key, const uint8_t* payload, uint32_t record_bytes,
+                              uint32_t key_bytes, uint64_t n, uint64_t* out3, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -217,6 +217,21 @@ def random_shuffle_dataset(
     )
 
 
+def repartition_dataset(tables: Sequence[pa.Table], num_blocks: int) -> List[pa.Table]:
+    """Dataset.repartition(shuffle=True): _ShufflePartitionOp with random_shuffle=False
+    (_internal/stage_impl.py:27-69, _internal/shuffle_and_partition.py:29-97)."""
+
+    def _map(i, t, nb):
+        slice_sz = max(1, math.ceil(num_rows(t) / nb))
+        return [t.slice(j * slice_sz, slice_sz) for j in range(nb)]
+
+    def _reduce(*parts):
+        parts = [p for p in parts if p.num_columns > 0]
+        return pa.concat_tables(parts) if parts else empty_table()
+
+    return simple_shuffle(_map, _reduce, tables, num_blocks)
+
+
 # ----------------------------------------------------------------------------
 # groupby / aggregate.  aggs: sequence of (kind, on) with kind in
 # {"count","sum","mean","min","max"}; ``on`` is None for count.

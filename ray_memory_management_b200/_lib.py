@@ -56,6 +56,9 @@ _PROTOS = {
     "ds_searchsorted_fsb": [_P, c_uint32, c_uint64, _P, c_uint32, c_int32, _P, _P],
     "ds_partition_hist_scatter_i64": [_P, c_uint64, _P, c_uint32, c_int32, _P, _P, _P, _P, _SZP, _P],
     "ds_partition_hist_scatter_fsb": [_P, c_uint32, c_uint64, _P, c_uint32, c_int32, _P, _P, _P, _P, _SZP, _P],
+    "ds_split_records": [_P, c_uint32, c_uint32, c_uint64, _P, _P, _P],
+    "ds_join_records": [_P, _P, c_uint32, c_uint32, c_uint64, _P, _P],
+    "ds_validate_records": [_P, _P, c_uint32, c_uint32, c_uint64, _P, _P],
     "ds_sample_rows": [_P, c_uint32, c_uint64, c_uint32, c_uint64, _P, _P],
     "ds_random_permutation": [c_uint64, c_uint64, c_uint64, _P, _P, _SZP, _P],
     "ds_segment_heads_i64": [_P, c_uint64, _P, _P, _P, _SZP, _P],

@@ -48,6 +48,18 @@ class Dataset:
         out, stage_info = op.execute(self._blocks.copy(), n, False)
         return Dataset(out, {"random_shuffle": stage_info})
 
+    def repartition(self, num_blocks: int, *, shuffle: bool = True) -> "Dataset":
+        """Dataset.repartition(shuffle=True) (python/ray/data/_internal/stage_impl.py:27-69): the
+        shuffle op without the random permutations -- every block is cut into ``num_blocks``
+        slices and output block j concatenates slice j of every input block."""
+        if not shuffle:
+            raise NotImplementedError("repartition(shuffle=False) (fast_repartition) is not on the device path")
+        if self._blocks.initial_num_blocks() == 0:
+            return self
+        op = DeviceShufflePartitionOp(None, random_shuffle=False, random_seed=None)
+        out, stage_info = op.execute(self._blocks.copy(), num_blocks, False)
+        return Dataset(out, {"repartition": stage_info})
+
     def groupby(self, key: Optional[str]) -> GroupedDataset:
         if key is not None and not isinstance(key, str):
             raise ValueError("Table datasets can only be grouped by a column name or None")
