@@ -293,7 +293,7 @@ def run_ours(args):
                         f"(10-byte key fixed_size_binary(10) + 90-byte payload), "
                         f"{world * n * ROW_BYTES / 1e9:.1f} GB total, BASELINE.json configs[1] per GPU",
             "rows_per_gpu": n, "blocks_per_gpu": 1,
-            "l2": "inputs (10 GB/GPU) far exceed the 126 MB L2; no flush needed",
+            "l2": f"inputs ({n * ROW_BYTES / 1e9:.1f} GB/GPU) far exceed the 126 MB L2; no flush needed",
             "parallelism": f"range-partitioned x{world}" if world > 1 else "single GPU",
         },
         "clocks": clocks,
