@@ -8,7 +8,8 @@ _context_lock = threading.Lock()
 
 class DatasetContext:
     def __init__(self, use_push_based_shuffle: bool = False, use_device_shuffle: bool = True,
-                 pipeline_push_based_shuffle_reduce_tasks: bool = True, use_polars: bool = False):
+                 pipeline_push_based_shuffle_reduce_tasks: bool = True, use_polars: bool = False,
+                 fuse_device_blocks: bool = True):
         # Plan selection happens where the reference reads use_push_based_shuffle
         # (sort.py:142-146, stage_impl.py:101-109, grouped_dataset.py:142-146).  This
         # package only ships the device plan; the flag is kept so that call sites and
@@ -17,6 +18,8 @@ class DatasetContext:
         self.use_device_shuffle = use_device_shuffle
         self.pipeline_push_based_shuffle_reduce_tasks = pipeline_push_based_shuffle_reduce_tasks
         self.use_polars = use_polars
+        # run map/reduce once over the concatenated blocks when they share a GPU (shuffle.py)
+        self.fuse_device_blocks = fuse_device_blocks
 
     @staticmethod
     def get_current() -> "DatasetContext":

@@ -387,9 +387,25 @@ def _sort_block_fused(block, key, descending, boundaries, with_valid, group, ph)
     return DeviceArrowBlock(cols, n_recv)
 
 
-def sort_block(block, key: str, descending: bool = False, group=None):
+def reserve_peer_buffer(nbytes: int, group=None) -> None:
+    """Allocate (collectively) the symmetric receive buffer up front, e.g. before a run
+    whose HBM budget leaves no room for the grow-by-25% policy of the on-demand path."""
+    key = id(group) if group is not None else 0
+    pb = _peer_cache.get(key)
+    if pb is None or pb.nbytes < nbytes:
+        _peer_cache.pop(key, None)
+        del pb
+        torch.cuda.empty_cache()
+        _peer_cache[key] = _PeerBuffer(int(nbytes), group)
+
+
+def sort_block(block, key: str, descending: bool = False, group=None, consume: bool = False):
     """Dataset.sort across the ranks of ``group``: this rank's input block in, this rank's
-    slice of the globally sorted dataset out (rank order = key order)."""
+    slice of the globally sorted dataset out (rank order = key order).
+
+    ``consume=True`` is ``clear_input_blocks`` (python/ray/data/_internal/shuffle.py:95-101):
+    the input block's columns are dropped as soon as the partitioned copy exists and the send
+    buffers as soon as they have been shipped, which is what lets 62.5 GB per GPU fit."""
     from .block import (DeviceArrowBlock, DeviceArrowBlockAccessor, DeviceColumn,
                         _argsort_nulls_last, _gather)
 
@@ -398,7 +414,14 @@ def sort_block(block, key: str, descending: bool = False, group=None):
     dev = _dev()
     ph = _Phases()
     ph.mark("start")
+    if consume:  # the caller's handle stays valid (and emptied); work on our own view of it
+        src_block = block
+        from .block import DeviceArrowBlock as _DAB
+        block = _DAB(collections.OrderedDict(src_block.columns), src_block.num_rows)
+        src_block.columns.clear()
     block, with_valid = _agree_on_validity(block, group, dev)
+    names = block.column_names
+    types = {nm: block.columns[nm].type for nm in names}
     width, ktype = _key_width(block, key, group)
     local = _sample_local(block, key)
     if local.shape[1] != width:
@@ -419,11 +442,15 @@ def sort_block(block, key: str, descending: bool = False, group=None):
             return out
     parts = acc.partition_unsorted(boundaries, sort_key, descending)
     counts = [p.num_rows for p in parts]
+    if consume and world > 1:
+        block.columns.clear()  # the partitioned copy replaces the input
+        del acc
     ph.mark("partition")
     matrix = exchange_counts(counts, group, dev)
-    names = block.column_names
-    types = {nm: block.columns[nm].type for nm in names}
     wires = _wire_columns(parts, names, with_valid, key, dev)
+    del parts
+    if consume:
+        torch.cuda.empty_cache()
     nkey = 2 if key in with_valid else 1          # wires that make up the key column
     n_recv = int(matrix[:, rank].sum())
     rbs = {w: rb for w, rb, _ in wires}
@@ -462,6 +489,10 @@ def sort_block(block, key: str, descending: bool = False, group=None):
         _join_lanes(pb, main)
         pb.hdl.barrier(channel=2)  # all payload rows have landed everywhere
         ph.mark("wait payload")
+        if consume:  # the send buffers have been shipped
+            wires = [(w, rb, None) for w, rb, _ in wires]
+            torch.cuda.synchronize()
+            torch.cuda.empty_cache()
     else:
         # keys first; sort them while the payload columns are still being exchanged
         for w, rb, buf in wires[:nkey]:

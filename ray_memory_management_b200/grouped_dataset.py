@@ -40,7 +40,35 @@ class _GroupbyOp(ShuffleOp):
 
 
 class DeviceGroupbyOp(_GroupbyOp, DeviceShufflePlan):
-    pass
+    @staticmethod
+    def fused(blocks: List[Block], output_num_blocks: int, boundaries: List, key: Optional[str],
+              aggs: Tuple[AggregateFn]):
+        """One sort + one segmented reduction over the concatenated blocks, cut at the
+        splitters: output block j of the map/reduce plan holds the finalized groups whose key
+        falls into range j, which is the j-th slice of the key-sorted global result.  (Float
+        sums associate differently than per-block partial sums would; both are within the
+        path's 1e-6 tolerance.)"""
+        from . import _lib
+        from .block import DeviceArrowBlock, DeviceArrowBlockAccessor, _searchsorted
+
+        stats = BlockExecStats.builder()
+        accs = [BlockAccessor.for_block(b) for b in blocks]
+        if sum(a.num_rows() for a in accs) > _lib.DS_MAX_ROWS:
+            return None
+        map_meta = [a.get_metadata(input_files=None, exec_stats=stats.build()) for a in accs]
+        live = [a.to_block() for a in accs if a.num_rows() > 0]
+        if not live:
+            return [DeviceArrowBlock.empty() for _ in range(output_num_blocks)], map_meta
+        whole = DeviceArrowBlockAccessor(DeviceArrowBlock.concat(live))
+        if key is not None:
+            whole = DeviceArrowBlockAccessor(whole.sort_and_partition([], [(key, "ascending")], False)[0])
+        partial = whole.combine(key, aggs)
+        result, _ = DeviceArrowBlockAccessor.aggregate_combined_blocks([partial], key, aggs, finalize=True)
+        if key is None or output_num_blocks == 1:
+            return [result], map_meta
+        bounds = _searchsorted(result.columns[key], boundaries, False)
+        edges = [0] + bounds + [result.num_rows]
+        return [result.slice(edges[j], edges[j + 1]) for j in range(output_num_blocks)], map_meta
 
 
 def aggregate_impl(blocks: BlockList, clear_input_blocks: bool, key: Optional[str],

@@ -16,7 +16,8 @@ all-to-all over NCCL (see distributed.py).
 """
 from typing import Any, Dict, List, Optional, Tuple, Union
 
-from .block import Block, BlockList, BlockMetadata
+from .block import Block, BlockAccessor, BlockList, BlockMetadata
+from .context import DatasetContext
 
 
 class ShuffleOp:
@@ -50,6 +51,27 @@ class DeviceShufflePlan(ShuffleOp):
         input_blocks_list = input_blocks.get_blocks()
         input_num_blocks = len(input_blocks_list)
         in_blocks_owned_by_consumer = input_blocks._owned_by_consumer
+
+        # All blocks of a single-process plan live in this GPU's HBM, so an op may run its
+        # map and reduce functions once over the concatenated input instead of M + N times
+        # over small blocks (same output blocks; see each op's ``fused`` for the argument).
+        # With the reference's default of ~76 blocks for 10 M rows this is the difference
+        # between ~100 ms of launch overhead and one 1 ms sort.
+        fused = getattr(self, "fused", None)
+        if fused is not None and DatasetContext.get_current().fuse_device_blocks and input_num_blocks > 1:
+            res = fused(input_blocks_list, output_num_blocks, *self._map_args)
+            if res is not None:
+                new_blocks, map_meta = res
+                del input_blocks_list
+                if clear_input_blocks:
+                    input_blocks.clear()
+                new_metadata = [
+                    BlockAccessor.for_block(b).get_metadata(None, exec_stats=None) for b in new_blocks
+                ]
+                return (
+                    BlockList(new_blocks, new_metadata, owned_by_consumer=in_blocks_owned_by_consumer),
+                    {"map": map_meta, "reduce": new_metadata},
+                )
 
         shuffle_map_out = []
         shuffle_map_metadata = []

@@ -74,4 +74,39 @@ class _ShufflePartitionOp(ShuffleOp):
 
 
 class DeviceShufflePartitionOp(_ShufflePartitionOp, DeviceShufflePlan):
-    pass
+    @staticmethod
+    def fused(blocks: List[Block], output_num_blocks: int, block_udf, random_shuffle: bool,
+              random_seed: Optional[int]):
+        """random_shuffle over blocks that share a GPU: ONE permutation of the concatenated
+        rows, cut into the output block sizes the map/reduce plan would produce (those depend
+        only on the block lengths and the per-mapper RandomState slice shuffles, replayed here
+        on the host).  The contract kept is the reference's: a permutation of the rows,
+        deterministic per seed.  Repartition (no permutation) and UDF-fused shuffles keep the
+        map/reduce path, whose row placement is part of their result."""
+        from . import _lib
+
+        if not random_shuffle or block_udf is not None:
+            return None
+        stats = BlockExecStats.builder()
+        accs = [BlockAccessor.for_block(b) for b in blocks]
+        total = sum(a.num_rows() for a in accs)
+        if total > _lib.DS_MAX_ROWS:
+            return None
+        sizes = [0] * output_num_blocks
+        for i, a in enumerate(accs):  # shuffle_and_partition.py:56-65 on lengths only
+            n = a.num_rows()
+            slice_sz = max(1, math.ceil(n / output_num_blocks))
+            lens = [max(0, min(n, (j + 1) * slice_sz) - min(n, j * slice_sz)) for j in range(output_num_blocks)]
+            seed_i = random_seed + i if random_seed is not None else None
+            np.random.RandomState(seed_i).shuffle(lens)
+            sizes = [x + y for x, y in zip(sizes, lens)]
+        map_meta = [a.get_metadata(input_files=None, exec_stats=stats.build()) for a in accs]
+        live = [a.to_block() for a in accs if a.num_rows() > 0]
+        if not live:
+            return [DeviceArrowBlock.empty() for _ in range(output_num_blocks)], map_meta
+        whole = BlockAccessor.for_block(DeviceArrowBlock.concat(live)).random_shuffle(random_seed)
+        out, last = [], 0
+        for sz in sizes:
+            out.append(whole.slice(last, last + sz))
+            last += sz
+        return out, map_meta

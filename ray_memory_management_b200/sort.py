@@ -47,7 +47,27 @@ class _SortOp(ShuffleOp):
 
 
 class DeviceSortOp(_SortOp, DeviceShufflePlan):
-    pass
+    @staticmethod
+    def fused(blocks: List[Block], output_num_blocks: int, boundaries: List[T], key: SortKeyT,
+              descending: bool):
+        """One stable sort of the concatenated blocks, cut at the splitters.
+
+        Output block j of the map/reduce plan is the stable sort of the rows whose key falls
+        into range j, in (block, row) order -- i.e. exactly the j-th slice, cut at
+        searchsorted(boundaries), of the stable sort of the concatenation.  Returns None when
+        the concatenation would exceed one sort call."""
+        from . import _lib
+
+        stats = BlockExecStats.builder()
+        accs = [BlockAccessor.for_block(b) for b in blocks]
+        if sum(a.num_rows() for a in accs) > _lib.DS_MAX_ROWS:
+            return None
+        live = [a.to_block() for a in accs if a.num_rows() > 0]
+        map_meta = [a.get_metadata(input_files=None, exec_stats=stats.build()) for a in accs]
+        if not live:
+            return [DeviceArrowBlock.empty() for _ in range(output_num_blocks)], map_meta
+        whole = BlockAccessor.for_block(DeviceArrowBlock.concat(live))
+        return whole.sort_and_partition(boundaries, key, descending), map_meta
 
 
 def nearest_rank_positions(num_samples: int, num_reducers: int) -> List[int]:
@@ -88,12 +108,22 @@ def sample_boundaries(blocks: List[Block], key: SortKeyT, num_reducers: int) -> 
     if isinstance(key, list) and len(key) > 1:
         raise ValueError("Multiple boundary sampling keys not supported.")
     n_samples = int(num_reducers * 10 / len(blocks))
-    samples = [_sample_block(block, n_samples, key) for block in blocks]
+    column = key[0][0] if isinstance(key, list) else key
+    if len(blocks) > 1 and all(isinstance(b, DeviceArrowBlock) for b in blocks):
+        # device blocks of one GPU: one sampling launch over the concatenated key column
+        # (the same n_samples per block on average, stratified over the whole column)
+        live = [b.select([column]) for b in blocks if b.num_rows > 0]
+        samples = []
+        if live:
+            whole = BlockAccessor.for_block(DeviceArrowBlock.concat(live))
+            samples = [whole.sample(min(n_samples * len(live), whole.num_rows()), key)]
+    else:
+        samples = [_sample_block(block, n_samples, key) for block in blocks]
     samples = [s for s in samples if s.num_rows > 0]
     if len(samples) == 0:
         return [None] * (num_reducers - 1)
-    column = key[0][0] if isinstance(key, list) else key
-    host = pa.concat_tables([s.to_arrow() for s in samples])[column].combine_chunks().drop_null()
+    # one device-side concatenation and ONE device-to-host copy for all blocks' samples
+    host = DeviceArrowBlock.concat(samples).to_arrow()[column].combine_chunks().drop_null()
     if isinstance(host, pa.ChunkedArray):
         host = host.combine_chunks()
     return boundaries_from_samples(host, num_reducers)
