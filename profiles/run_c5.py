@@ -5,7 +5,11 @@
 
 One timed distributed sort with ``consume=True`` (the input is released as the reference
 releases its input refs with clear_input_blocks), after a small warm-up that sets up NCCL and
-reserves the symmetric receive buffer.  Validation (not timed): every rank's output is sorted,
+reserves the symmetric receive buffer.  At 62.5 GB per GPU the send-buffer staging of the
+copy-engine exchange does not fit beside the input and the receive buffer (190 GB), so run it
+with DS_EXCHANGE=fused: the partition kernel stores rows straight into the peers' buffers.
+The single timed run includes first-use cudaMalloc of its temporaries (no same-size warm-up
+fits in HBM next to a second input).  Validation (not timed): every rank's output is sorted,
 rank boundaries are ordered, and the order-independent CRC-32 checksum and the record count of
 the whole dataset are unchanged.  Rank 0 prints one JSON line.
 """

@@ -301,7 +301,7 @@ def _wire_columns(parts, names, with_valid, key, dev):
     return wires
 
 
-def _sort_block_fused(block, key, descending, boundaries, with_valid, group, ph):
+def _sort_block_fused(block, key, descending, boundaries, with_valid, group, ph, consume=False):
     """Peer-memory sort plan whose map side is ONE kernel per column that slices the block by
     destination and stores every row straight into the destination GPU's receive buffer
     (ds_scatter_rows_to_parts over peer-mapped pointers): no send buffer, no copy pass.
@@ -379,6 +379,12 @@ def _sort_block_fused(block, key, descending, boundaries, with_valid, group, ph)
     main.wait_stream(pb.side)
     pb.hdl.barrier(channel=2)  # all payload rows have landed everywhere
     ph.mark("wait payload")
+    if consume:  # every row of the input now lives in some rank's receive buffer
+        wires = None
+        block.columns.clear()
+        del perm
+        torch.cuda.synchronize()
+        torch.cuda.empty_cache()
     cols = collections.OrderedDict()
     for name in names:
         cols[name] = sorted_key if name == key else _gather(column(name), idx)
@@ -437,7 +443,7 @@ def sort_block(block, key: str, descending: bool = False, group=None, consume: b
     sort_key = [(key, "descending" if descending else "ascending")]
     ph.mark("sample+splitters")
     if _EXCHANGE == "fused" and 1 < world <= 16 and dist.get_backend(group) == "nccl":
-        out = _sort_block_fused(block, key, descending, boundaries, with_valid, group, ph)
+        out = _sort_block_fused(block, key, descending, boundaries, with_valid, group, ph, consume)
         if out is not None:
             return out
     parts = acc.partition_unsorted(boundaries, sort_key, descending)
