@@ -230,8 +230,14 @@ class DeviceArrowBlock:
         return DeviceArrowBlock(cols, num_rows)
 
     def to_host_buffers(self, out: Sequence[torch.Tensor]) -> None:
-        """D2H export into caller-provided (ideally pinned) uint8 buffers."""
+        """D2H export of the data buffers into caller-provided (ideally pinned) uint8 buffers
+        (columns with nulls need ``to_arrow``, which also exports validity)."""
+        for name, c in self.columns.items():
+            if c.valid is not None and not bool(c.valid.all()):
+                raise NotImplementedError(f"to_host_buffers: column {name!r} has nulls; use to_arrow()")
         for c, host in zip(self.columns.values(), out):
+            if host.numel() < c.data.numel():
+                raise ValueError(f"host buffer too small: {host.numel()} < {c.data.numel()} bytes")
             host[: c.data.numel()].copy_(c.data, non_blocking=True)
 
     def to_arrow(self) -> pa.Table:
@@ -619,7 +625,8 @@ class DeviceArrowBlockAccessor:
         view = self._block.slice(start, end)
         if copy:
             cols = collections.OrderedDict(
-                (n, DeviceColumn(c.type, c.data.clone())) for n, c in view.columns.items()
+                (n, DeviceColumn(c.type, c.data.clone(), c.valid.clone() if c.valid is not None else None))
+                for n, c in view.columns.items()
             )
             view = DeviceArrowBlock(cols, view.num_rows)
         return view

@@ -116,3 +116,15 @@ def test_std_matches_pandas_like_reference_test(ds):
     # single-row groups give 0.0 (aggregate.py:273-274)
     t = pa.table({"A": np.arange(5, dtype=np.int64), "B": np.arange(5, dtype=np.float64)})
     assert ds.Dataset.from_arrow([t]).groupby("A").std("B").to_arrow_concat()["std(B)"].to_pylist() == [0.0] * 5
+
+
+def test_slice_copy_and_take_keep_validity(ds):
+    t = pa.table({"a": pa.array([1, None, 3, None, 5], pa.int64())})
+    acc = ds.BlockAccessor.for_block(t)
+    assert acc.slice(1, 4, copy=True).to_arrow().equals(t.slice(1, 3))
+    assert acc.slice(1, 4, copy=False).to_arrow().equals(t.slice(1, 3))
+    assert acc.take([4, 1, 0]).to_arrow().equals(t.take([4, 1, 0]))
+    import torch
+
+    with pytest.raises(NotImplementedError):
+        acc.to_block().to_host_buffers([torch.empty(40, dtype=torch.uint8)])
