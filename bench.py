@@ -11,8 +11,10 @@ configs[1]: 100 M records = 10 GB per GPU).  Rank 0 prints ONE JSON line:
   value     sort GB/s (input bytes / device time), inputs resident in HBM, whole job
   e2e       the same through the public API from pinned HOST buffers: H2D copy of the
             batch + sort + D2H copy of the sorted batch inside the timed region
-  roofline  the onesweep pass kernel: algorithmic bytes per launch / CUDA-event
-            duration of each launch, against MEASURED_PEAKS.json's hbm_gbs
+  roofline  the dominant kernel of the step (the payload gather; the radix pass kernel is
+            reported next to it as roofline_second_kernel): algorithmic bytes per launch /
+            CUDA-event duration of each launch (events recorded inside the library around
+            the launches), against MEASURED_PEAKS.json's hbm_gbs
   cpu_baseline  the CPU restatement of the reference path (oracle/, kind "port") on a
             bounded sample, all host cores
 
@@ -243,8 +245,11 @@ def run_ours(args):
     lib.ds_debug_pass_timing(0)
     launches = int(lib.ds_debug_launch_count() - launches0)
     ms = ev0.elapsed_time(ev1)
-    tot_ms, cnt = ctypes.c_double(0), ctypes.c_int32(0)
-    lib.ds_debug_collect_pass_timing(ctypes.byref(tot_ms), ctypes.byref(cnt))
+    timed = {}
+    for kind, name in ((0, "pass"), (1, "gather")):
+        t_ms, t_cnt, t_bytes = ctypes.c_double(0), ctypes.c_int32(0), ctypes.c_double(0)
+        lib.ds_debug_collect_timing(kind, ctypes.byref(t_ms), ctypes.byref(t_cnt), ctypes.byref(t_bytes))
+        timed[name] = (t_ms.value, t_cnt.value, t_bytes.value)
     if world > 1:
         t = torch.tensor([ms], dtype=torch.float64, device="cuda")
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
@@ -252,17 +257,36 @@ def run_ours(args):
     ms_per_step = ms / args.steps
     value = world * n * ROW_BYTES / (ms_per_step * 1e-3) / 1e9
 
-    traffic = None
-    try:
-        with open(os.path.join(ROOT, "profiles", "r01_pass_kernel_traffic.json")) as f:
-            tj = json.load(f)
-        # ncu-measured DRAM bytes per row of one pass launch, scaled to this launch's rows
-        traffic = tj["traffic_bytes_per_row"] * n_pass_rows(world, n)
-    except Exception:
-        pass
-    pass_ms = tot_ms.value / max(cnt.value, 1)
     peak, peak_src = measured_peak()
-    achieved = n_pass_rows(world, n) * PASS_BYTES_PER_ROW / (pass_ms * 1e-3) / 1e9 if cnt.value else None
+    try:
+        with open(os.path.join(ROOT, "profiles", "r01_kernel_traffic.json")) as f:
+            traffic_per_alg_byte = json.load(f)
+    except Exception:
+        traffic_per_alg_byte = {}
+
+    def roofline_of(name, label):
+        t_ms, t_cnt, t_bytes = timed[name]
+        if not t_cnt:
+            return None
+        achieved = t_bytes / (t_ms * 1e-3) / 1e9           # algorithmic bytes / CUDA-event time
+        ratio = traffic_per_alg_byte.get(name, {}).get("dram_bytes_per_algorithmic_byte")
+        return {
+            "kernel": label, "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
+            "frac": achieved / peak, "frac_of_8TBs_spec": achieved / 8000.0,
+            "traffic": (t_bytes / t_cnt * ratio) if ratio else None,
+            "traffic_source": "ncu dram__bytes_read.sum+dram__bytes_write.sum per launch (profiles/r01_kernel_traffic.json), "
+                              "scaled to this launch's rows",
+            "peak_source": peak_src, "launches_timed": t_cnt, "avg_launch_ms": t_ms / t_cnt,
+            "algorithmic_bytes_per_launch": t_bytes / t_cnt,
+            "share_of_step": t_ms / ms if world == 1 else None,
+        }
+
+    roof_gather = roofline_of("gather", "gather_rows_kernel<uint16> (payload gather by permutation, 4 + 2*90 B per row)")
+    roof_pass = roofline_of("pass", "onesweep_pass_kernel_v3 (one 8-bit LSD pass over key80+idx32, 28 B per row)")
+    # the dominant kernel is the one with the larger share of the timed region
+    dominant, other = (roof_gather, roof_pass)
+    if roof_gather is None or (roof_pass is not None and timed["pass"][0] > timed["gather"][0]):
+        dominant, other = roof_pass, roof_gather
 
     if world > 1 and os.environ.get("DS_DIST_TIMING") == "1":
         from ray_memory_management_b200 import distributed as _D
@@ -298,15 +322,8 @@ def run_ours(args):
         },
         "clocks": clocks,
         "gpu_launches": launches,
-        "roofline": {
-            "kernel": "onesweep_pass_kernel (one 8-bit LSD pass over key80+idx32)",
-            "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
-            "frac": (achieved / peak) if achieved else None, "traffic": traffic,
-            "traffic_source": "ncu dram__bytes_read.sum+dram__bytes_write.sum per launch, "
-                              "profiles/r01_pass_kernel_traffic.json",
-            "peak_source": peak_src, "launches_timed": cnt.value, "avg_launch_ms": pass_ms,
-            "bytes_per_row_per_launch": PASS_BYTES_PER_ROW,
-        },
+        "roofline": dominant,
+        "roofline_second_kernel": other,
         "e2e": e2e,
     }
     if not args.no_cpu_baseline and world == 1:
@@ -315,12 +332,6 @@ def run_ours(args):
     print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()
-
-
-def n_pass_rows(world, n):
-    # rows one pass launch processes on rank 0; with W ranks the received partition is
-    # ~n rows for uniform keys (exact count is data dependent)
-    return n
 
 
 def run_e2e(args, ds, block, n, world, rank, barrier):

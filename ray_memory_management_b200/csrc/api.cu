@@ -3,6 +3,7 @@
 #include <stdarg.h>
 
 #include <atomic>
+#include <vector>
 
 #include "ds_common.cuh"
 #include "ds_keys.cuh"
@@ -21,6 +22,27 @@ void set_error(const char* fmt, ...) {
 static std::atomic<unsigned long long> g_launches{0};
 void note_launch() { g_launches.fetch_add(1, std::memory_order_relaxed); }
 unsigned long long launch_count() { return g_launches.load(std::memory_order_relaxed); }
+
+static bool g_timing = false;
+struct TimedLaunch {
+  cudaEvent_t a, b;
+  double bytes;
+};
+static std::vector<TimedLaunch> g_timed[TIMED_KINDS];
+
+LaunchTimer::LaunchTimer(int k, cudaStream_t st, double algorithmic_bytes) : kind(k), s(st), bytes(algorithmic_bytes) {
+  if (!g_timing) return;
+  if (cudaEventCreate(&a) != cudaSuccess || cudaEventCreate(&b) != cudaSuccess) {
+    a = b = nullptr;
+    return;
+  }
+  cudaEventRecord(a, s);
+}
+void LaunchTimer::stop() {
+  if (!a) return;
+  cudaEventRecord(b, s);
+  g_timed[kind].push_back(TimedLaunch{a, b, bytes});
+}
 
 int sm_count() {
   static int cached[64] = {0};
@@ -56,6 +78,32 @@ extern "C" {
 int32_t ds_version(void) { return 100; /* 0.1.0 */ }
 
 const char* ds_last_error(void) { return ds::g_err; }
+
+// Per-launch timing of a kernel class (0 = radix pass, 1 = row gather), see LaunchTimer.
+void ds_debug_pass_timing(int32_t enable) { ds::g_timing = enable != 0; }
+
+// Sums duration (ms) and algorithmic bytes of the recorded launches of `kind` and clears the
+// record.  The caller must have synchronised the stream(s) first.
+int32_t ds_debug_collect_timing(int32_t kind, double* total_ms, int32_t* launches, double* bytes) {
+  double tot = 0, by = 0;
+  int cnt = 0;
+  if (kind < 0 || kind >= ds::TIMED_KINDS) return -1;
+  for (auto& ev : ds::g_timed[kind]) {
+    float ms = 0;
+    if (cudaEventElapsedTime(&ms, ev.a, ev.b) == cudaSuccess) {
+      tot += ms;
+      by += ev.bytes;
+      ++cnt;
+    }
+    cudaEventDestroy(ev.a);
+    cudaEventDestroy(ev.b);
+  }
+  ds::g_timed[kind].clear();
+  if (total_ms) *total_ms = tot;
+  if (launches) *launches = cnt;
+  if (bytes) *bytes = by;
+  return 0;
+}
 
 // Number of kernels this library has launched in this process (bench.py: gpu_launches).
 uint64_t ds_debug_launch_count(void) { return ds::launch_count(); }

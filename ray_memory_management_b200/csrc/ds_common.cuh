@@ -77,6 +77,19 @@ inline int ws_resolve(const Workspace& w, void* ws, size_t* ws_bytes, const char
 }
 
 void note_launch();  // counts kernel launches (ds_debug_launch_count)
+
+// Optional per-launch timing for bench.py's roofline figures: CUDA events recorded on the
+// launching stream around a launch, per kernel class, read back by ds_debug_collect_timing
+// after the caller has synchronised.  Measurement aid: not thread safe, off by default.
+enum TimedKernel { TIMED_PASS = 0, TIMED_GATHER = 1, TIMED_KINDS = 2 };
+struct LaunchTimer {
+  int kind;
+  cudaStream_t s;
+  cudaEvent_t a = nullptr, b = nullptr;
+  double bytes;
+  LaunchTimer(int kind, cudaStream_t s, double algorithmic_bytes);
+  void stop();
+};
 int sm_count();  // SMs of the current device (cached per device)
 
 __device__ __forceinline__ uint32_t lane_id() { return threadIdx.x & 31; }

@@ -466,6 +466,7 @@ ds_status gather_rows_impl(const void* src, uint32_t row_bytes, uint64_t src_row
   const uint32_t n = static_cast<uint32_t>(n64);
   const uintptr_t bits = reinterpret_cast<uintptr_t>(src) | reinterpret_cast<uintptr_t>(dst) | row_bytes;
   cudaError_t e;
+  LaunchTimer timer(TIMED_GATHER, s, static_cast<double>(n) * (4.0 + 2.0 * row_bytes));
   // rows that are not 16-byte multiples: aligned-vector staging through shared memory
   if ((row_bytes & 15) != 0 && row_bytes >= 16 && row_bytes <= 2048 && src_rows > 0 &&
       (reinterpret_cast<uintptr_t>(dst) & 15) == 0 && g_gather_mode >= 3)
@@ -475,6 +476,7 @@ ds_status gather_rows_impl(const void* src, uint32_t row_bytes, uint64_t src_row
   else if ((bits & 3) == 0) e = launch_gather<uint32_t>(src, idx, dst, n, row_bytes, s);
   else if ((bits & 1) == 0) e = launch_gather<uint16_t>(src, idx, dst, n, row_bytes, s);
   else e = launch_gather<uint8_t>(src, idx, dst, n, row_bytes, s);
+  timer.stop();
   if (e != cudaSuccess) {
     set_error("ds_gather_rows: launch failed: %s", cudaGetErrorString(e));
     return DS_ERR_CUDA;

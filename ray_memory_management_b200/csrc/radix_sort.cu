@@ -455,29 +455,6 @@ __global__ void __launch_bounds__(256)
 }
 
 // ---------------------------------------------------------------- host driver
-// Optional per-launch timing of the pass kernel (bench.py's roofline figure): CUDA events
-// recorded on the launching stream around each launch; read back by
-// ds_debug_collect_pass_timing after the caller has synchronised.
-static bool g_timing = false;
-static std::vector<std::pair<cudaEvent_t, cudaEvent_t>> g_events;
-struct PassTimer {
-  cudaStream_t s;
-  cudaEvent_t a = nullptr, b = nullptr;
-  explicit PassTimer(cudaStream_t st) : s(st) {
-    if (!g_timing) return;
-    if (cudaEventCreate(&a) != cudaSuccess || cudaEventCreate(&b) != cudaSuccess) { a = b = nullptr; return; }
-    cudaEventRecord(a, s);
-  }
-  void stop() {
-    if (!a) return;
-    cudaEventRecord(b, s);
-    g_events.emplace_back(a, b);
-  }
-};
-
-struct PassConfig {
-  int threads, items;
-};
 static int g_cfg = 18;  // tuning knob (ds_debug_set_radix_config); 18 = v3 table match <384 x 12>, best measured
 
 template <typename K>
@@ -501,7 +478,7 @@ static cudaError_t launch_pass_t(const uint64_t* hi_in, const uint16_t* lo_in,
   static unsigned long long done_a = 0, done_b = 0;  // per instantiation, one bit per device
   const uint32_t tiles = (n + S::TILE - 1) / S::TILE;
   cudaError_t e;
-  PassTimer timer(s);
+  LaunchTimer timer(TIMED_PASS, s, static_cast<double>(n) * (HAS_LO ? 28.0 : 24.0));
   if (VARIANT == 1) {
     auto k = onesweep_pass_kernel<THREADS, ITEMS, MIN_BLOCKS, HAS_LO, DIGIT_LO, GEN_IDX>;
     if ((e = set_smem_attr(k, S::BYTES, &done_a)) != cudaSuccess) return e;
@@ -874,29 +851,6 @@ ds_status ds_random_permutation(uint64_t seed, uint64_t subsequence, uint64_t n,
   // colliding 64-bit keys are ordered by row index, which keeps the result a permutation.
   return ds::sort_indices_impl(ds::KIND_PHILOX, nullptr, 8, n, 0, perm_out, nullptr, 0, ws,
                                ws_bytes, stream, __func__, seed, subsequence);
-}
-
-// Measurement hooks used by bench.py; not part of the reference-facing surface.
-void ds_debug_pass_timing(int32_t enable) { ds::g_timing = enable != 0; }
-
-// Sums the recorded pass-kernel durations (ms) and clears the record.  The caller must
-// have synchronised the stream(s) first.
-int32_t ds_debug_collect_pass_timing(double* total_ms, int32_t* launches) {
-  double tot = 0;
-  int cnt = 0;
-  for (auto& ev : ds::g_events) {
-    float ms = 0;
-    if (cudaEventElapsedTime(&ms, ev.first, ev.second) == cudaSuccess) {
-      tot += ms;
-      ++cnt;
-    }
-    cudaEventDestroy(ev.first);
-    cudaEventDestroy(ev.second);
-  }
-  ds::g_events.clear();
-  if (total_ms) *total_ms = tot;
-  if (launches) *launches = cnt;
-  return 0;
 }
 
 // Tuning hook used by bench.py --sweep; not part of the reference-facing surface.
