@@ -161,15 +161,13 @@ __global__ void scan_hist_kernel(const uint32_t* __restrict__ ghist, uint32_t n,
 // falls back to the full LSD sort).
 constexpr int REPAIR_MAX_RUN = 16;
 
+// Slow path of the repair: the run of equal prefixes that starts at row i (its head) is
+// ordered by the full key with a stable insertion sort in local memory.
 template <bool HAS_LO>
-__global__ void __launch_bounds__(256)
-    repair_runs_kernel(uint64_t* __restrict__ hi, uint16_t* __restrict__ lo, uint32_t* __restrict__ idx,
-                       uint32_t n, int prefix_shift, uint32_t* __restrict__ too_long) {
-  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= n) return;
+__device__ __noinline__ void repair_one_run(uint64_t* __restrict__ hi, uint16_t* __restrict__ lo,
+                                            uint32_t* __restrict__ idx, uint32_t i, uint32_t n,
+                                            int prefix_shift, uint32_t* __restrict__ too_long) {
   const uint64_t pfx = hi[i] >> prefix_shift;
-  if (i > 0 && (hi[i - 1] >> prefix_shift) == pfx) return;        // not a run head
-  if (i + 1 >= n || (hi[i + 1] >> prefix_shift) != pfx) return;   // singleton run
   uint32_t len = 2;
   while (i + len < n && len <= REPAIR_MAX_RUN && (hi[i + len] >> prefix_shift) == pfx) ++len;
   if (len > REPAIR_MAX_RUN) {
@@ -204,6 +202,49 @@ __global__ void __launch_bounds__(256)
     hi[i + k] = h[k];
     if (HAS_LO) lo[i + k] = static_cast<uint16_t>(l[k]);
     idx[i + k] = x[k];
+  }
+}
+
+// Each thread classifies REPAIR_VEC consecutive rows from two 16-byte loads (plus its two
+// neighbours) and calls the slow path only for rows that head a run of two or more equal
+// prefixes.  Runs never overlap, and only the thread that holds a run's head writes it, so
+// the in-place update is race free; a neighbouring thread may read a prefix while the run
+// is being rewritten, but prefixes of all members of a run are equal by definition.
+constexpr int REPAIR_VEC = 4;
+template <bool HAS_LO>
+__global__ void __launch_bounds__(256)
+    repair_runs_kernel(uint64_t* __restrict__ hi, uint16_t* __restrict__ lo, uint32_t* __restrict__ idx,
+                       uint32_t n, int prefix_shift, uint32_t* __restrict__ too_long) {
+  const uint32_t i0 = (blockIdx.x * blockDim.x + threadIdx.x) * REPAIR_VEC;
+  if (i0 >= n) return;
+  uint64_t p[REPAIR_VEC + 2];  // p[k + 1] = prefix of row i0 + k
+  const bool whole = i0 + REPAIR_VEC <= n;
+  if (whole) {
+    const ulonglong2 a = *reinterpret_cast<const ulonglong2*>(hi + i0);
+    const ulonglong2 b = *reinterpret_cast<const ulonglong2*>(hi + i0 + 2);
+    p[1] = a.x >> prefix_shift;
+    p[2] = a.y >> prefix_shift;
+    p[3] = b.x >> prefix_shift;
+    p[4] = b.y >> prefix_shift;
+  } else {
+#pragma unroll
+    for (int k = 0; k < REPAIR_VEC; ++k) p[k + 1] = i0 + k < n ? hi[i0 + k] >> prefix_shift : 0;
+  }
+  const bool has_prev = i0 > 0, has_next = i0 + REPAIR_VEC < n;
+  p[0] = has_prev ? hi[i0 - 1] >> prefix_shift : 0;
+  p[REPAIR_VEC + 1] = has_next ? hi[i0 + REPAIR_VEC] >> prefix_shift : 0;
+  uint32_t heads = 0;
+#pragma unroll
+  for (int k = 0; k < REPAIR_VEC; ++k) {
+    const uint32_t i = i0 + k;
+    const bool same_prev = (k > 0 || has_prev) && p[k] == p[k + 1];
+    const bool same_next = (k + 1 < REPAIR_VEC ? (whole || i + 1 < n) : has_next) && p[k + 1] == p[k + 2];
+    if (i < n && !same_prev && same_next) heads |= 1u << k;
+  }
+  while (heads) {  // one divergent region per warp instead of one per k
+    const int k = __ffs(heads) - 1;
+    heads &= heads - 1;
+    repair_one_run<HAS_LO>(hi, lo, idx, i0 + k, n, prefix_shift, too_long);
   }
 }
 
@@ -420,34 +461,59 @@ __global__ void decode_kernel(const uint64_t* __restrict__ hi, const uint16_t* _
   }
 }
 
-// fixed_size_binary decode with coalesced 16-byte stores: 256 rows are laid out in shared
-// memory exactly as they appear in the output buffer, then copied out as uint4.
+// fixed_size_binary decode with coalesced 16-byte stores: DECODE_ROWS rows are laid out in
+// shared memory exactly as they appear in the output buffer, then copied out as uint4.
+// Each thread decodes DECODE_ROWS / 256 rows so that several loads are in flight.
+constexpr int DECODE_ROWS = 1024;
+__device__ __forceinline__ uint64_t bswap64(uint64_t v) {
+  const uint32_t lo32 = static_cast<uint32_t>(v), hi32 = static_cast<uint32_t>(v >> 32);
+  return (static_cast<uint64_t>(__byte_perm(lo32, 0, 0x0123)) << 32) | __byte_perm(hi32, 0, 0x0123);
+}
+template <bool W10>
 __global__ void __launch_bounds__(256)
     decode_fsb_staged_kernel(const uint64_t* __restrict__ hi, const uint16_t* __restrict__ lo,
                              uint32_t width, uint32_t n, bool desc, uint8_t* __restrict__ out) {
-  __shared__ __align__(16) uint8_t buf[256 * DS_MAX_KEY_BYTES];
-  const uint32_t row0 = blockIdx.x * 256u;
-  const uint32_t i = row0 + threadIdx.x;
-  if (i < n) {
-    uint64_t h = ld_stream(hi + i);
-    uint32_t l = width > 8 ? ld_stream(lo + i) : 0;
-    if (desc) {
-      h = ~h;
-      l = ~l;
-    }
-    uint8_t* p = buf + threadIdx.x * width;
+  constexpr int PER = DECODE_ROWS / 256;
+  __shared__ __align__(16) uint8_t buf[DECODE_ROWS * DS_MAX_KEY_BYTES];
+  const uint32_t row0 = blockIdx.x * static_cast<uint32_t>(DECODE_ROWS);
+  uint64_t h[PER];
+  uint32_t l[PER];
 #pragma unroll
-    for (int b = 0; b < 8; ++b)
-      if (b < (int)width) p[b] = static_cast<uint8_t>(h >> (56 - 8 * b));
-    if (width == 9) p[8] = static_cast<uint8_t>(l);
-    if (width == 10) {
-      p[8] = static_cast<uint8_t>(l >> 8);
-      p[9] = static_cast<uint8_t>(l);
+  for (int k = 0; k < PER; ++k) {
+    const uint32_t i = row0 + k * 256 + threadIdx.x;
+    h[k] = i < n ? ld_stream(hi + i) : 0;
+    l[k] = (i < n && width > 8) ? ld_stream(lo + i) : 0;
+  }
+#pragma unroll
+  for (int k = 0; k < PER; ++k) {
+    if (desc) {
+      h[k] = ~h[k];
+      l[k] = ~l[k];
+    }
+    const uint32_t r = k * 256 + threadIdx.x;
+    if (W10) {  // rows start on 2-byte boundaries: five 16-bit stores
+      const uint64_t be = bswap64(h[k]);
+      uint16_t* q = reinterpret_cast<uint16_t*>(buf + r * 10);
+      q[0] = static_cast<uint16_t>(be);
+      q[1] = static_cast<uint16_t>(be >> 16);
+      q[2] = static_cast<uint16_t>(be >> 32);
+      q[3] = static_cast<uint16_t>(be >> 48);
+      q[4] = static_cast<uint16_t>(((l[k] >> 8) & 0xffu) | ((l[k] & 0xffu) << 8));
+    } else {
+      uint8_t* q = buf + r * width;
+#pragma unroll
+      for (int b = 0; b < 8; ++b)
+        if (b < (int)width) q[b] = static_cast<uint8_t>(h[k] >> (56 - 8 * b));
+      if (width == 9) q[8] = static_cast<uint8_t>(l[k]);
+      if (width == 10) {
+        q[8] = static_cast<uint8_t>(l[k] >> 8);
+        q[9] = static_cast<uint8_t>(l[k]);
+      }
     }
   }
   __syncthreads();
-  const uint32_t nbytes = min(256u, n - row0) * width;
-  uint8_t* dst = out + static_cast<uint64_t>(row0) * width;  // 16-byte aligned: 256*width % 16 == 0
+  const uint32_t nbytes = min(static_cast<uint32_t>(DECODE_ROWS), n - row0) * width;
+  uint8_t* dst = out + static_cast<uint64_t>(row0) * width;  // 16-byte aligned: 1024*width % 16 == 0
   const uint32_t vec = nbytes >> 4;
   for (uint32_t v = threadIdx.x; v < vec; v += 256)
     st_stream(reinterpret_cast<uint4*>(dst) + v, reinterpret_cast<const uint4*>(buf)[v]);
@@ -781,10 +847,11 @@ static ds_status sort_indices_impl(int kind, const void* col, uint32_t width, ui
   }
   if (prefix_shift >= 0) {
     ds::note_launch();
+    const uint32_t repair_blocks = (n + 256 * REPAIR_VEC - 1) / (256 * REPAIR_VEC);
     if (has_lo)
-      repair_runs_kernel<true><<<(n + 255) / 256, 256, 0, s>>>(hi[cur], lo[cur], idx_out, n, prefix_shift, too_long);
+      repair_runs_kernel<true><<<repair_blocks, 256, 0, s>>>(hi[cur], lo[cur], idx_out, n, prefix_shift, too_long);
     else
-      repair_runs_kernel<false><<<(n + 255) / 256, 256, 0, s>>>(hi[cur], lo[cur], idx_out, n, prefix_shift, too_long);
+      repair_runs_kernel<false><<<repair_blocks, 256, 0, s>>>(hi[cur], lo[cur], idx_out, n, prefix_shift, too_long);
     DS_LAUNCH_CHECK();
     uint32_t flag = 0;
     DS_CUDA(cudaMemcpyAsync(&flag, too_long, sizeof(flag), cudaMemcpyDeviceToHost, s));
@@ -801,10 +868,15 @@ static ds_status sort_indices_impl(int kind, const void* col, uint32_t width, ui
       case KIND_F64: return gather_rows_impl(col, 8, n, idx_out, n, sorted_out, s);
       default:
         ds::note_launch();
-        if ((reinterpret_cast<uintptr_t>(sorted_out) & 15) == 0)
-          decode_fsb_staged_kernel<<<blocks, 256, 0, s>>>(hi[cur], lo[cur], width, n, desc,
-                                                          static_cast<uint8_t*>(sorted_out));
-        else
+        if ((reinterpret_cast<uintptr_t>(sorted_out) & 15) == 0) {
+          const int sblocks = static_cast<int>((n + DECODE_ROWS - 1) / DECODE_ROWS);
+          if (width == 10)
+            decode_fsb_staged_kernel<true><<<sblocks, 256, 0, s>>>(hi[cur], lo[cur], width, n, desc,
+                                                                   static_cast<uint8_t*>(sorted_out));
+          else
+            decode_fsb_staged_kernel<false><<<sblocks, 256, 0, s>>>(hi[cur], lo[cur], width, n, desc,
+                                                                    static_cast<uint8_t*>(sorted_out));
+        } else
           decode_kernel<KIND_FSB><<<blocks, threads, 0, s>>>(hi[cur], lo[cur], width, n, desc, sorted_out);
         break;
     }
