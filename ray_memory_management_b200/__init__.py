@@ -16,15 +16,19 @@ from .block import (
 )
 from .context import DatasetContext
 from .dataset import Dataset
+from .dataset_pipeline import DatasetPipeline
 from .grouped_dataset import DeviceGroupbyOp, GroupedDataset, aggregate_impl
 from .shuffle import DeviceShufflePlan, ShuffleOp
 from .shuffle_and_partition import DeviceShufflePartitionOp
+from .read_api import from_arrow, from_pandas, range_table, read_arrow_ipc, read_parquet, write_arrow_ipc
 from .sort import DeviceSortOp, sample_boundaries, sort_impl
+from .stats import DatasetStats
 
 __all__ = [
     "AbsMax", "AggregateFn", "Count", "Max", "Mean", "Min", "Std", "Sum", "BlockAccessor", "BlockExecStats",
     "BlockList", "BlockMetadata", "DeviceArrowBlock", "DeviceArrowBlockAccessor", "DeviceColumn",
     "DatasetContext", "Dataset", "DeviceGroupbyOp", "GroupedDataset", "aggregate_impl",
     "DeviceShufflePlan", "ShuffleOp", "DeviceShufflePartitionOp", "DeviceSortOp",
-    "sample_boundaries", "sort_impl",
+    "sample_boundaries", "sort_impl", "DatasetPipeline", "DatasetStats", "from_arrow", "from_pandas",
+    "range_table", "read_arrow_ipc", "read_parquet", "write_arrow_ipc",
 ]

@@ -5,7 +5,7 @@ shapes: Dataset.sort (python/ray/data/dataset.py:1714-1754), Dataset.random_shuf
 (:750-783) and Dataset.groupby (:1321-1353), plus the few inspection helpers the
 reference's tests use (count, take, _block_num_rows, iter_rows, to_arrow).
 """
-from typing import Any, Dict, List, Optional, Sequence
+from typing import List, Optional, Sequence
 
 import pyarrow as pa
 
@@ -13,12 +13,16 @@ from .block import BlockAccessor, BlockList, DeviceArrowBlock
 from .grouped_dataset import GroupedDataset
 from .shuffle_and_partition import DeviceShufflePartitionOp
 from .sort import sort_impl
+from .stats import DatasetStats
 
 
 class Dataset:
-    def __init__(self, blocks: BlockList, stats: Optional[Dict[str, Any]] = None):
+    def __init__(self, blocks: BlockList, stats: Optional[DatasetStats] = None, epoch: Optional[int] = None):
         self._blocks = blocks
-        self._stats = stats or {}
+        # the reference's source stage is "read" or "from_arrow_refs"; every later stage
+        # hangs its DatasetStats off this one
+        self._stats = stats or DatasetStats(stages={"from_blocks": blocks.get_metadata()}, parent=None)
+        self._epoch = epoch  # set by repeat(); read by DatasetPipeline.iter_epochs
 
     # -- construction ----------------------------------------------------------------
     @staticmethod
@@ -37,16 +41,18 @@ class Dataset:
             return self
         if key is None or callable(key):
             raise ValueError("Table datasets need a column name as sort key")
+        builder = self._stats.child_builder("sort")
         out, stage_info = sort_impl(self._blocks.copy(), False, key, descending)
-        return Dataset(out, {"sort": stage_info})
+        return Dataset(out, builder.build_multistage(stage_info), self._epoch)
 
     def random_shuffle(self, *, seed: Optional[int] = None, num_blocks: Optional[int] = None) -> "Dataset":
         if self._blocks.initial_num_blocks() == 0:
             return self
         n = num_blocks or self._blocks.initial_num_blocks()
+        builder = self._stats.child_builder("random_shuffle")
         op = DeviceShufflePartitionOp(None, random_shuffle=True, random_seed=seed)
         out, stage_info = op.execute(self._blocks.copy(), n, False)
-        return Dataset(out, {"random_shuffle": stage_info})
+        return Dataset(out, builder.build_multistage(stage_info), self._epoch)
 
     def repartition(self, num_blocks: int, *, shuffle: bool = True) -> "Dataset":
         """Dataset.repartition(shuffle=True) (python/ray/data/_internal/stage_impl.py:27-69): the
@@ -56,9 +62,46 @@ class Dataset:
             raise NotImplementedError("repartition(shuffle=False) (fast_repartition) is not on the device path")
         if self._blocks.initial_num_blocks() == 0:
             return self
+        builder = self._stats.child_builder("repartition")
         op = DeviceShufflePartitionOp(None, random_shuffle=False, random_seed=None)
         out, stage_info = op.execute(self._blocks.copy(), num_blocks, False)
-        return Dataset(out, {"repartition": stage_info})
+        return Dataset(out, builder.build_multistage(stage_info), self._epoch)
+
+    # -- pipelines: the per-window callers of sort / random_shuffle ----------------------
+    def window(self, *, blocks_per_window: Optional[int] = None,
+               bytes_per_window: Optional[int] = None) -> "DatasetPipeline":
+        """Dataset.window (python/ray/data/dataset.py:3198-3330): one pipeline window per
+        ``blocks_per_window`` blocks (default 10) or per ``bytes_per_window`` bytes."""
+        from .dataset_pipeline import DatasetPipeline, split_block_list, split_block_list_by_bytes
+
+        if blocks_per_window is not None and bytes_per_window is not None:
+            raise ValueError("Only one windowing scheme can be specified.")
+        if blocks_per_window is None:
+            blocks_per_window = 10
+        if bytes_per_window is not None:
+            splits = split_block_list_by_bytes(self._blocks, bytes_per_window)
+        else:
+            splits = split_block_list(self._blocks, blocks_per_window)
+        epoch = self._epoch
+        return DatasetPipeline([lambda b=b: Dataset(b, epoch=epoch) for b in splits], length=len(splits))
+
+    def repeat(self, times: Optional[int] = None) -> "DatasetPipeline":
+        """Dataset.repeat (dataset.py:3112-3196): the same blocks once per epoch; stages added
+        to the pipeline (a per-epoch random_shuffle, typically) run once per epoch."""
+        from .dataset_pipeline import DatasetPipeline
+
+        if times is not None and times < 1:
+            raise ValueError("`times` must be >= 1, got {}".format(times))
+        blocks = self._blocks
+
+        class _Epochs:
+            def __iter__(self_inner):
+                i = 0
+                while times is None or i < times:
+                    yield (lambda e=i: Dataset(blocks.copy(), epoch=e))
+                    i += 1
+
+        return DatasetPipeline(_Epochs(), length=times or float("inf"))
 
     def groupby(self, key: Optional[str]) -> GroupedDataset:
         if key is not None and not isinstance(key, str):
@@ -102,7 +145,9 @@ class Dataset:
                 break
         return out
 
-    def stats(self) -> Dict[str, Any]:
-        """{stage: {"map": [BlockMetadata...], "reduce": [...]}} -- the substage naming of
-        python/ray/data/_internal/stats.py:60-75 (<stage>_map, <stage>_reduce)."""
-        return self._stats
+    def stats(self) -> str:
+        """The execution summary of this dataset and its ancestors as text
+        (Dataset.stats, python/ray/data/dataset.py:3545-3553); substages are named
+        ``<stage>_map`` / ``<stage>_reduce`` as in _internal/stats.py:60-75.  The structured
+        form is ``self._stats`` (a ``DatasetStats``: ``.stages``, ``.parents``)."""
+        return self._stats.summary_string()

@@ -6,6 +6,8 @@ boundaries, per-partition combine on the map side, merge + finalize on the reduc
 """
 from typing import List, Optional, Tuple, Union
 
+import pyarrow as pa
+
 from . import sort
 from .aggregate import AbsMax, AggregateFn, Count, Max, Mean, Min, Std, Sum
 from .block import Block, BlockAccessor, BlockExecStats, BlockList, BlockMetadata
@@ -71,6 +73,43 @@ class DeviceGroupbyOp(_GroupbyOp, DeviceShufflePlan):
         return [result.slice(edges[j], edges[j + 1]) for j in range(output_num_blocks)], map_meta
 
 
+def _group_ends(block, key: Optional[str]) -> List[int]:
+    """End offsets of the runs of equal keys of a key-sorted block (get_key_boundaries,
+    grouped_dataset.py:266-275).  int64 keys: one boundary-flag + compaction kernel on the
+    device; other key types: compared on the host copy that map_groups needs anyway."""
+    import numpy as np
+
+    from .block import _key_kind, _segment_heads
+
+    n = block.num_rows
+    if key is None:
+        return [n]
+    col = block.column(key)
+    if col.valid is not None and not bool(col.valid.all()):
+        raise NotImplementedError("null groupby keys are not supported on device yet")
+    if _key_kind(col.type) == "i64":
+        starts, nseg = _segment_heads(col)
+        return starts[1:nseg + 1].cpu().tolist()
+    w = col.data.numel() // n
+    rows = col.data.cpu().numpy().reshape(n, w)
+    change = np.flatnonzero((rows[1:] != rows[:-1]).any(axis=1)) + 1
+    return change.tolist() + [n]
+
+
+def _batch_to_arrow(batch) -> pa.Table:
+    """What BlockBuilder.add_block accepts from a map_groups UDF, as an Arrow table."""
+    import pandas as pd
+
+    if isinstance(batch, pa.Table):
+        return batch
+    if isinstance(batch, pd.DataFrame):
+        return pa.Table.from_pandas(batch, preserve_index=False)
+    raise TypeError(  # BlockAccessor.for_block's error for a non-block (block.py:359-375)
+        "The map_groups UDF must return a pandas.DataFrame or a pyarrow.Table on the device "
+        f"path, got: {type(batch)}"
+    )
+
+
 def aggregate_impl(blocks: BlockList, clear_input_blocks: bool, key: Optional[str],
                    aggs: Tuple[AggregateFn]):
     """do_agg of the reference (grouped_dataset.py:118-154)."""
@@ -105,8 +144,50 @@ class GroupedDataset:
 
         for agg in aggs:
             agg._validate(self._dataset)
-        out, stats = aggregate_impl(self._dataset._blocks.copy(), False, self._key, aggs)
-        return Dataset(out, {"aggregate": stats})
+        builder = self._dataset._stats.child_builder("aggregate")
+        out, stage_info = aggregate_impl(self._dataset._blocks.copy(), False, self._key, aggs)
+        if not stage_info:  # empty input: nothing ran
+            return Dataset(out, self._dataset._stats)
+        return Dataset(out, builder.build_multistage(stage_info))
+
+    def map_groups(self, fn, *, compute=None, batch_format: str = "native", **ray_remote_args):
+        """python/ray/data/grouped_dataset.py:183-310: sort by the key (equal keys never
+        straddle output blocks, because the range partition sends equal keys to one
+        partition), cut every sorted block at its group boundaries and apply ``fn`` to each
+        group in key order; the outputs are concatenated per block.
+
+        The sort and the group boundaries are computed on the device; ``fn`` is a host UDF
+        over pandas / pyarrow batches in the reference too, so each sorted block is exported
+        once and the result imported once.  ``batch_format``: "native"/"pandas" hand ``fn`` a
+        ``pandas.DataFrame`` (the reference promotes Arrow to pandas for "native"), "pyarrow" a
+        ``pyarrow.Table``.  ``compute`` / ``ray_remote_args`` are accepted and unused."""
+        from .dataset import Dataset
+
+        if batch_format not in ("native", "pandas", "pyarrow"):
+            raise ValueError(f"The batch format must be one of 'native', 'pandas', or 'pyarrow', got: {batch_format}")
+        if self._key is not None:
+            sorted_ds = self._dataset.sort(self._key)
+        else:
+            sorted_ds = self._dataset.repartition(1)
+        builder = sorted_ds._stats.child_builder("map_batches")  # the reference's stage name
+        out_blocks = []
+        for block in sorted_ds.get_blocks():
+            n = BlockAccessor.for_block(block).num_rows()
+            if n == 0:
+                continue
+            ends = _group_ends(block, self._key)
+            table = block.to_arrow()
+            pieces, start = [], 0
+            for end in ends:
+                group = table.slice(start, end - start)
+                applied = fn(group if batch_format == "pyarrow" else group.to_pandas())
+                pieces.append(_batch_to_arrow(applied))
+                start = end
+            pieces = [p for p in pieces if p.num_columns > 0]
+            if pieces:
+                out_blocks.append(pa.concat_tables(pieces))
+        out = BlockList.from_blocks(out_blocks)
+        return Dataset(out, builder.build(out))
 
     def count(self):
         return self.aggregate(Count())

@@ -16,7 +16,7 @@ all-to-all over NCCL (see distributed.py).
 """
 from typing import Any, Dict, List, Optional, Tuple, Union
 
-from .block import Block, BlockAccessor, BlockList, BlockMetadata
+from .block import Block, BlockAccessor, BlockExecStats, BlockList, BlockMetadata
 from .context import DatasetContext
 
 
@@ -59,14 +59,17 @@ class DeviceShufflePlan(ShuffleOp):
         # between ~100 ms of launch overhead and one 1 ms sort.
         fused = getattr(self, "fused", None)
         if fused is not None and DatasetContext.get_current().fuse_device_blocks and input_num_blocks > 1:
+            stats = BlockExecStats.builder()
             res = fused(input_blocks_list, output_num_blocks, *self._map_args)
             if res is not None:
                 new_blocks, map_meta = res
                 del input_blocks_list
                 if clear_input_blocks:
                     input_blocks.clear()
+                # one set of launches produced every output block: they share its host times
+                fused_stats = stats.build()
                 new_metadata = [
-                    BlockAccessor.for_block(b).get_metadata(None, exec_stats=None) for b in new_blocks
+                    BlockAccessor.for_block(b).get_metadata(None, exec_stats=fused_stats) for b in new_blocks
                 ]
                 return (
                     BlockList(new_blocks, new_metadata, owned_by_consumer=in_blocks_owned_by_consumer),
