@@ -41,18 +41,17 @@ class AggregateFn:
 
 class _AggregateOnKeyBase(AggregateFn):
     def __init__(self, on: Optional[str], ignore_nulls: bool, kind: str):
-        if on is not None and not isinstance(on, str):
-            raise ValueError(
-                f"on must be a string when aggregating on Arrow blocks, but got:{type(on)}."
-            )
+        # a bad ``on`` is reported by _validate (TypeError for a non-key type, ValueError for a
+        # callable or an unknown column), as in the reference (aggregate.py:93-94)
         self._key_fn = on
         self._ignore_nulls = ignore_nulls
         self._kind = kind
         self.name = f"{kind}({str(on)})"
 
     def _validate(self, ds) -> None:
-        if self._key_fn is None:
-            raise ValueError("aggregation on a table dataset needs a column name (on=...)")
+        from .block import _validate_key_fn
+
+        _validate_key_fn(ds, self._key_fn)  # aggregate.py:93-94
 
 
 class Count(AggregateFn):

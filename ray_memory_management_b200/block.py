@@ -835,6 +835,23 @@ def resolve_agg_names(aggs) -> List[str]:
     return out
 
 
+def _validate_key_fn(ds, key) -> None:
+    """python/ray/data/block.py:60-93 for table datasets: a key is a column name that exists
+    in the schema; ``None`` and callables belong to simple (list) datasets."""
+    schema = ds.schema()
+    if schema is None:  # empty or cleared dataset: validation not possible
+        return
+    if isinstance(key, str):
+        if len(schema.names) > 0 and key not in schema.names:
+            raise ValueError("The column '{}' does not exist in the schema '{}'.".format(key, schema))
+    elif key is None:
+        raise ValueError("The `None` key '{}' requires dataset format to be 'simple', was 'arrow'.".format(key))
+    elif callable(key):
+        raise ValueError("Callable key '{}' requires dataset format to be 'simple', was 'arrow'.".format(key))
+    else:
+        raise TypeError("Invalid key type {} ({}).".format(key, type(key)))
+
+
 class BlockAccessor:
     """python/ray/data/block.py:370-394: dispatch on the block kind."""
 

@@ -9,7 +9,8 @@ from typing import List, Optional, Sequence
 
 import pyarrow as pa
 
-from .block import BlockAccessor, BlockList, DeviceArrowBlock
+from .aggregate import Max, Mean, Min, Std, Sum
+from .block import BlockAccessor, BlockList, DeviceArrowBlock, _validate_key_fn
 from .grouped_dataset import GroupedDataset
 from .shuffle_and_partition import DeviceShufflePartitionOp
 from .sort import sort_impl
@@ -104,13 +105,58 @@ class Dataset:
         return DatasetPipeline(_Epochs(), length=times or float("inf"))
 
     def groupby(self, key: Optional[str]) -> GroupedDataset:
-        if key is not None and not isinstance(key, str):
-            raise ValueError("Table datasets can only be grouped by a column name or None")
+        """dataset.py:1321-1353: the key is validated here (unknown column, callable key)."""
+        if key is not None:
+            _validate_key_fn(self, key)
         return GroupedDataset(self, key)
 
     def aggregate(self, *aggs):
         ret = self.groupby(None).aggregate(*aggs).take(1)
         return ret[0] if ret else None
+
+    # -- global aggregations (python/ray/data/dataset.py:1386-1712) ------------------------
+    # ``on``: a column name -> a scalar; a list of names -> a dict with one entry per column;
+    # None -> every column.  None is returned for an empty dataset, an all-null column, or any
+    # null with ignore_nulls=False.
+    def sum(self, on=None, ignore_nulls: bool = True):
+        return self._aggregate_result(self._aggregate_on(Sum, on, ignore_nulls))
+
+    def min(self, on=None, ignore_nulls: bool = True):
+        return self._aggregate_result(self._aggregate_on(Min, on, ignore_nulls))
+
+    def max(self, on=None, ignore_nulls: bool = True):
+        return self._aggregate_result(self._aggregate_on(Max, on, ignore_nulls))
+
+    def mean(self, on=None, ignore_nulls: bool = True):
+        return self._aggregate_result(self._aggregate_on(Mean, on, ignore_nulls))
+
+    def std(self, on=None, ddof: int = 1, ignore_nulls: bool = True):
+        return self._aggregate_result(self._aggregate_on(Std, on, ignore_nulls, ddof=ddof))
+
+    def _aggregate_on(self, agg_cls: type, on, *args, **kwargs):
+        """dataset.py:3585-3596."""
+        aggs = self._build_multicolumn_aggs(agg_cls, on, *args, **kwargs)
+        return self.aggregate(*aggs)
+
+    def _build_multicolumn_aggs(self, agg_cls: type, on, ignore_nulls: bool, *args,
+                                skip_cols: Optional[List[str]] = None, **kwargs):
+        """dataset.py:3598-3629: one aggregation per column; ``on=None`` expands to every
+        column of the schema except ``skip_cols`` (the groupby key)."""
+        if on is None:
+            schema = self.schema()
+            if schema is not None and len(schema.names) > 0:
+                skip = [skip_cols] if isinstance(skip_cols, str) else (skip_cols or [])
+                on = [col for col in schema.names if col not in skip]
+        if not isinstance(on, list):
+            on = [on]
+        return [agg_cls(on_, *args, ignore_nulls=ignore_nulls, **kwargs) for on_ in on]
+
+    @staticmethod
+    def _aggregate_result(result):
+        """dataset.py:3631-3641: a one-column result row is unwrapped to its value."""
+        if result is not None and len(result) == 1:
+            return list(result.values())[0]
+        return result
 
     # -- inspection --------------------------------------------------------------------
     def num_blocks(self) -> int:
@@ -124,6 +170,30 @@ class Dataset:
 
     def get_blocks(self) -> List[DeviceArrowBlock]:
         return self._blocks.get_blocks()
+
+    def schema(self) -> Optional[pa.Schema]:
+        """Schema of the first block that has columns; None for an empty dataset."""
+        if self._blocks.is_cleared():
+            return None
+        for b in self._blocks.get_blocks():
+            s = BlockAccessor.for_block(b).schema()
+            if len(s.names) > 0:
+                return s
+        return None
+
+    def to_pandas(self, limit: int = 100000):
+        if self.count() > limit:
+            raise ValueError(f"The dataset has more than the given limit of {limit} records.")
+        return self.to_arrow_concat().to_pandas()
+
+    def take_all(self, limit: int = 100000) -> List[dict]:
+        if self.count() > limit:
+            raise ValueError(f"The dataset has more than the given limit of {limit} records.")
+        return list(self.iter_rows())
+
+    def show(self, limit: int = 20) -> None:
+        for row in self.take(limit):
+            print(row)
 
     def to_arrow(self) -> List[pa.Table]:
         return [BlockAccessor.for_block(b).to_arrow() for b in self._blocks.get_blocks()]

@@ -189,20 +189,28 @@ class GroupedDataset:
         out = BlockList.from_blocks(out_blocks)
         return Dataset(out, builder.build(out))
 
+    def _aggregate_on(self, agg_cls: type, on, ignore_nulls: bool, *args, **kwargs):
+        """grouped_dataset.py:163-181: ``on`` may be a column, a list of columns, or None for
+        every column except the key."""
+        aggs = self._dataset._build_multicolumn_aggs(
+            agg_cls, on, ignore_nulls, *args, skip_cols=self._key, **kwargs
+        )
+        return self.aggregate(*aggs)
+
     def count(self):
         return self.aggregate(Count())
 
-    def sum(self, on: str, ignore_nulls: bool = True):
-        return self.aggregate(Sum(on, ignore_nulls))
+    def sum(self, on=None, ignore_nulls: bool = True):
+        return self._aggregate_on(Sum, on, ignore_nulls)
 
-    def min(self, on: str, ignore_nulls: bool = True):
-        return self.aggregate(Min(on, ignore_nulls))
+    def min(self, on=None, ignore_nulls: bool = True):
+        return self._aggregate_on(Min, on, ignore_nulls)
 
-    def max(self, on: str, ignore_nulls: bool = True):
-        return self.aggregate(Max(on, ignore_nulls))
+    def max(self, on=None, ignore_nulls: bool = True):
+        return self._aggregate_on(Max, on, ignore_nulls)
 
-    def mean(self, on: str, ignore_nulls: bool = True):
-        return self.aggregate(Mean(on, ignore_nulls))
+    def mean(self, on=None, ignore_nulls: bool = True):
+        return self._aggregate_on(Mean, on, ignore_nulls)
 
-    def std(self, on: str, ddof: int = 1, ignore_nulls: bool = True):
-        return self.aggregate(Std(on, ddof, ignore_nulls))
+    def std(self, on=None, ddof: int = 1, ignore_nulls: bool = True):
+        return self._aggregate_on(Std, on, ignore_nulls, ddof=ddof)
