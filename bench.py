@@ -52,7 +52,7 @@ def parse_args():
                    help="rows of the bounded CPU-baseline sample")
     p.add_argument("--no-e2e", action="store_true")
     p.add_argument("--e2e-inflight", type=int, default=2,
-                   help="single-GPU e2e: steps in flight (2 = H2D of step k+1 overlaps D2H of step k)")
+                   help="single-GPU e2e: steps in flight, 1..4 (>= 2: H2D of step k+1 overlaps D2H of step k)")
     p.add_argument("--no-cpu-baseline", action="store_true")
     p.add_argument("--radix-config", type=int, default=-1, help="tuning: pass-kernel variant")
     p.add_argument("--gather-mode", type=int, default=-1, help="tuning: see csrc/gather.cu g_gather_mode")
@@ -360,15 +360,17 @@ def run_e2e(args, ds, block, n, world, rank, barrier):
         out.to_host_buffers([ok, op])
         return out.num_rows
 
-    # Single GPU: two steps in flight on two streams, each with its own pinned output
-    # buffers, so step k's D2H overlaps step k+1's H2D (PCIe is full duplex).  Every step
-    # still copies its whole input in and its whole result out inside the timed region.
-    inflight = 2 if (world == 1 and args.e2e_inflight >= 2) else 1
+    # Single GPU: several steps in flight, each on its own stream with its own pinned output
+    # buffers, so step k's D2H overlaps step k+1's H2D (PCIe is full duplex) and, with three,
+    # step k+2's H2D does not have to wait for step k's D2H either.  Every step still copies
+    # its whole input in and its whole result out inside the timed region.
+    inflight = max(1, min(args.e2e_inflight, 4)) if world == 1 else 1
     outs = [(ok, op)]
     streams = [torch.cuda.current_stream()]
-    if inflight == 2:
-        outs.append((torch.empty_like(ok, pin_memory=True), torch.empty_like(op, pin_memory=True)))
-        streams = [torch.cuda.Stream(), torch.cuda.Stream()]
+    if inflight >= 2:
+        for _ in range(inflight - 1):
+            outs.append((torch.empty_like(ok, pin_memory=True), torch.empty_like(op, pin_memory=True)))
+        streams = [torch.cuda.Stream() for _ in range(inflight)]
 
     def step_on(i):
         nonlocal ok, op
