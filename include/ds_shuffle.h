@@ -314,6 +314,65 @@ ds_status ds_join_records(const uint8_t* key, const uint8_t* payload, uint32_t r
 ds_status ds_validate_records(const uint8_t* key, const uint8_t* payload, uint32_t record_bytes,
                               uint32_t key_bytes, uint64_t n, uint64_t* out3, void* stream);
 
+/* ----------------------------------------- variable-length keys and columns ---- */
+
+/* Arrow `binary` / `string` (and large_*) columns on the path: n+1 offsets into a byte
+ * buffer.  On the device offsets are int64 whatever the Arrow offset width and may start
+ * anywhere in the buffer (a slice keeps its parent's bytes).  In the reference these
+ * columns go through pyarrow on the CPU: `take` for every permutation of rows
+ * (_internal/arrow_block.py:258-267, arrow_ops/transform_pyarrow.py:46-60),
+ * `pyarrow.compute.sort_indices` for the sort (transform_pyarrow.py:15,74 called from
+ * arrow_block.py:353-394,474-486) and `np.searchsorted` on the sorted key column for the
+ * partition cuts (arrow_block.py:376-386).
+ *
+ * take = two calls: ds_varlen_take_offsets writes the n+1 offsets of the rows idx[0..n)
+ * (idx NULL = rows 0..n-1 in order, i.e. a compaction of a slice) by a 64-bit scan of their
+ * lengths (workspace protocol); the caller reads dst_offsets[n], allocates that many bytes
+ * and calls ds_varlen_take_bytes. */
+ds_status ds_varlen_take_offsets(const int64_t* src_offsets, uint64_t src_rows, const uint32_t* idx,
+                                 uint64_t n, int64_t* dst_offsets, void* ws, size_t* ws_bytes,
+                                 void* stream);
+ds_status ds_varlen_take_bytes(const int64_t* src_offsets, const uint8_t* src_data,
+                               const uint32_t* idx, uint64_t n, const int64_t* dst_offsets,
+                               uint8_t* dst_data, void* stream);
+
+/* The 64-bit parts a variable-length key is radix sorted by (least significant first: the
+ * length, then 8-byte chunks from the last to the first; every part sorted with the stable
+ * ds_sort_indices_u64 in the direction of the sort).  Together they order rows like
+ * memcmp-then-length, which is pyarrow's sort_indices order for binary and string.
+ *   idx             rows in their current order (NULL = identity); part i is taken from
+ *                   row idx[i], so each round's keys are already permuted
+ *   lengths_out[i]  byte length of row idx[i]; *max_len_out (device) = longest row
+ *   keys_out[i]     bytes [byte_offset, byte_offset+8) of row idx[i], first byte most
+ *                   significant, zero padded past the end of the row */
+ds_status ds_varlen_key_lengths(const int64_t* offsets, const uint32_t* idx, uint64_t n,
+                                uint64_t* lengths_out, uint64_t* max_len_out, void* stream);
+ds_status ds_varlen_key_chunk(const int64_t* offsets, const uint8_t* data, const uint32_t* idx,
+                              uint64_t n, uint64_t byte_offset, uint64_t* keys_out, void* stream);
+
+/* np.searchsorted(sorted_keys, boundaries, side="left") for a sorted variable-length column
+ * (arrow_block.py:376-386; descending counts the rows greater than each boundary, which is
+ * the reference's `num_rows - searchsorted(reversed, side="right")`).  Boundaries are given
+ * in the same layout (nb+1 offsets + bytes, on the device). */
+ds_status ds_searchsorted_varlen(const int64_t* sorted_offsets, const uint8_t* sorted_data,
+                                 uint64_t n, const int64_t* bound_offsets,
+                                 const uint8_t* bound_data, uint32_t nb, int32_t descending,
+                                 int64_t* out, void* stream);
+
+/* Runs of equal keys of a key-SORTED column as an int64 column: group_ids_out[i] = number of
+ * key changes in rows (0, i].  It has the same runs as the key, so ds_segment_heads_i64 and
+ * the segmented reductions work on it for every key type; this is what replaces the
+ * row-by-row `next_row[key] != current key` scan of ArrowBlockAccessor.combine
+ * (arrow_block.py:417-440) for keys that are not int64.
+ *   ds_group_ids_fixed   rows of `width` bytes compared bytewise, or (is_float64) doubles
+ *                        compared numerically (-0.0 == 0.0; a NaN equals nothing, as in
+ *                        Python)
+ *   ds_group_ids_varlen  rows compared by length and bytes */
+ds_status ds_group_ids_fixed(const void* sorted_col, uint32_t width, int32_t is_float64, uint64_t n,
+                             int64_t* group_ids_out, void* ws, size_t* ws_bytes, void* stream);
+ds_status ds_group_ids_varlen(const int64_t* sorted_offsets, const uint8_t* sorted_data, uint64_t n,
+                              int64_t* group_ids_out, void* ws, size_t* ws_bytes, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

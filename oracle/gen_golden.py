@@ -243,8 +243,72 @@ def gen_nulls():
     np.savez_compressed(os.path.join(OUT, "nulls.npz"), **out)
 
 
+def _pack_rows(rows):
+    """list of bytes/None -> (offsets int64, data uint8, valid bool) -- npz holds no objects."""
+    lens = [0 if r is None else len(r) for r in rows]
+    offs = np.zeros(len(rows) + 1, dtype=np.int64)
+    np.cumsum(lens, out=offs[1:])
+    data = np.frombuffer(b"".join(b"" if r is None else r for r in rows), dtype=np.uint8)
+    return offs, data, np.array([r is not None for r in rows])
+
+
+def gen_varlen():
+    """string / binary keys (variable length) through the reference's sort and groupby:
+    lengths 0..19 (so up to three 8-byte chunks), shared prefixes, embedded and trailing NUL
+    bytes ("ab" vs "ab\0"), duplicates, and nulls."""
+    ns = ref_shim.load()
+    A = ns.aggregate
+    n, nb = 4000, 4
+    rng = np.random.default_rng(77)
+    alphabet = np.frombuffer(b"ab\x00\xffz", dtype=np.uint8)
+    rows = []
+    for i in range(n):
+        ln = int(rng.integers(0, 20))
+        r = alphabet[rng.integers(0, len(alphabet), ln)].tobytes()
+        if rng.random() < 0.3:  # long shared prefix: decided in the 2nd or 3rd chunk
+            r = b"prefix--prefix--" + r[:3]
+        rows.append(r)
+    for i in range(0, n, 7):  # duplicates, to see stability
+        rows[i] = rows[(i * 13) % n]
+    mask = rng.random(n) < 0.05
+    out = {"block_cuts": np.array(_split(n, nb))}
+    out["bin_offsets"], out["bin_data"], _ = _pack_rows(rows)
+    out["null_mask"] = mask
+    v = rng.integers(-100, 100, n, dtype=np.int64)
+    out["v"] = v
+    # (with null keys the reference's sample_boundaries fails in np.sort -- None < bytes --
+    # so only the null-free case can be recorded; the null case is checked against pyarrow's
+    # sort_indices, the primitive the reference sorts with, in the GPU tests)
+    for tag, with_nulls in (("plain", False),):
+        keys = pa.array([None if (with_nulls and m) else r for r, m in zip(rows, mask)], pa.binary())
+        tabs = [pa.table({"key": keys[a:b], "row": np.arange(a, b, dtype=np.int64)}) for a, b in _split(n, nb)]
+        for desc in (False, True):
+            random.seed(8)
+            blocks = ref_shim.ref_sort(tabs, "key", descending=desc)
+            cat = pa.concat_tables([b for b in blocks if b.num_rows])
+            out[f"{tag}_{'desc' if desc else 'asc'}_row_order"] = cat["row"].to_numpy()
+    # ASCII strings as pa.string(): same order as their UTF-8 bytes
+    words = ["".join(chr(97 + int(c)) for c in rng.integers(0, 4, int(rng.integers(1, 12)))) for _ in range(n)]
+    out["str_offsets"], out["str_data"], _ = _pack_rows([w.encode() for w in words])
+    tabs = [pa.table({"key": pa.array(words[a:b], pa.string()), "row": np.arange(a, b, dtype=np.int64),
+                      "v": v[a:b]}) for a, b in _split(n, nb)]
+    random.seed(9)
+    blocks = ref_shim.ref_sort(tabs, "key", descending=False)
+    out["str_asc_row_order"] = pa.concat_tables([b for b in blocks if b.num_rows])["row"].to_numpy()
+    # groupby on the string key
+    random.seed(10)
+    blocks = ref_shim.ref_groupby(tabs, "key", (A.Count(), A.Sum("v"), A.Min("v"), A.Mean("v")))
+    cat = pa.concat_tables([b for b in blocks if b.num_rows])
+    out["gb_key_offsets"], out["gb_key_data"], _ = _pack_rows([k.encode() for k in cat["key"].to_pylist()])
+    for name in cat.column_names[1:]:
+        out[f"gb::{name}"] = cat[name].to_numpy()
+    out["gb_names"] = np.array(cat.column_names)
+    np.savez_compressed(os.path.join(OUT, "varlen.npz"), **out)
+
+
 def main():
     os.makedirs(OUT, exist_ok=True)
+    gen_varlen()
     gen_nulls()
     gen_sort_int64()
     gen_sort_graysort()

@@ -73,6 +73,13 @@ _PROTOS = {
     "ds_scale_f64_by_i64": [_P, _P, c_uint64, _P, _P],
     "ds_finalize_std": [_P, _P, c_uint64, c_int32, _P, _P],
     "ds_finalize_validity": [_P, _P, c_uint64, c_int32, _P, _P],
+    "ds_varlen_take_offsets": [_P, c_uint64, _P, c_uint64, _P, _P, _SZP, _P],
+    "ds_varlen_take_bytes": [_P, _P, _P, c_uint64, _P, _P, _P],
+    "ds_varlen_key_lengths": [_P, _P, c_uint64, _P, _P, _P],
+    "ds_varlen_key_chunk": [_P, _P, _P, c_uint64, c_uint64, _P, _P],
+    "ds_searchsorted_varlen": [_P, _P, c_uint64, _P, _P, c_uint32, c_int32, _P, _P],
+    "ds_group_ids_fixed": [_P, c_uint32, c_int32, c_uint64, _P, _P, _SZP, _P],
+    "ds_group_ids_varlen": [_P, _P, c_uint64, _P, _P, _SZP, _P],
 }
 EXPORTED = ["ds_version", "ds_last_error"] + sorted(_PROTOS)
 

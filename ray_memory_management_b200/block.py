@@ -110,6 +110,11 @@ def _row_bytes(t: pa.DataType) -> int:
     return bw // 8
 
 
+def _is_varlen(t: pa.DataType) -> bool:
+    return (pa.types.is_string(t) or pa.types.is_binary(t) or pa.types.is_large_string(t)
+            or pa.types.is_large_binary(t))
+
+
 def _key_kind(t: pa.DataType) -> str:
     if pa.types.is_int64(t):
         return "i64"
@@ -117,9 +122,11 @@ def _key_kind(t: pa.DataType) -> str:
         return "f64"
     if pa.types.is_fixed_size_binary(t) and 1 <= t.byte_width <= _lib.DS_MAX_KEY_BYTES:
         return "fsb"
+    if _is_varlen(t):
+        return "var"
     raise NotImplementedError(
         f"sort/groupby key of Arrow type {t} is not supported on device "
-        f"(int64, float64, fixed_size_binary(1..{_lib.DS_MAX_KEY_BYTES}))"
+        f"(int64, float64, fixed_size_binary(1..{_lib.DS_MAX_KEY_BYTES}), string, binary)"
     )
 
 
@@ -131,6 +138,7 @@ class DeviceColumn:
     that it can be sliced and gathered like any 1-byte column.  ``None`` means "no nulls"."""
 
     __slots__ = ("type", "row_bytes", "data", "valid")
+    is_varlen = False
 
     def __init__(self, arrow_type: pa.DataType, data: torch.Tensor, valid: Optional[torch.Tensor] = None):
         self.type = arrow_type
@@ -169,6 +177,65 @@ class DeviceColumn:
             return self.data.view(torch.float64)
         return self.data.view(-1, self.row_bytes)
 
+    @property
+    def nbytes(self) -> int:
+        return self.data.numel()
+
+    def with_valid(self, valid: Optional[torch.Tensor]) -> "DeviceColumn":
+        return DeviceColumn(self.type, self.data, valid)
+
+    def clone(self) -> "DeviceColumn":
+        return DeviceColumn(self.type, self.data.clone(), self.valid.clone() if self.valid is not None else None)
+
+
+class DeviceVarColumn(DeviceColumn):
+    """A variable-length Arrow column (string / binary / large_*) in HBM: ``offsets`` are
+    n+1 int64 byte positions into ``data`` (whatever the Arrow type's offset width; the width
+    is restored at export).  ``offsets[0]`` need not be 0: a slice is a view of the parent's
+    offsets and shares its bytes, as in Arrow."""
+
+    __slots__ = ("offsets", "data_bytes")
+    is_varlen = True
+
+    def __init__(self, arrow_type: pa.DataType, offsets: torch.Tensor, data: torch.Tensor,
+                 valid: Optional[torch.Tensor] = None, data_bytes: Optional[int] = None):
+        assert _is_varlen(arrow_type), arrow_type
+        assert offsets.dtype == torch.int64 and offsets.dim() == 1 and offsets.numel() >= 1
+        assert data.dtype == torch.uint8 and data.dim() == 1
+        self.type = arrow_type
+        self.row_bytes = None  # arithmetic on it fails loudly where a path is fixed-width only
+        self.offsets = offsets
+        self.data = data
+        if valid is not None:
+            assert valid.dtype == torch.uint8 and valid.numel() == offsets.numel() - 1
+        self.valid = valid
+        # bytes the rows occupy: exact when known (import, take), else an estimate (slices)
+        self.data_bytes = data.numel() if data_bytes is None else int(data_bytes)
+
+    @property
+    def num_rows(self) -> int:
+        return self.offsets.numel() - 1
+
+    def slice(self, start: int, end: int) -> "DeviceVarColumn":
+        n = self.num_rows
+        est = self.data_bytes * (end - start) // n if n else 0
+        return DeviceVarColumn(self.type, self.offsets[start:end + 1], self.data,
+                               self.valid[start:end] if self.valid is not None else None, est)
+
+    def typed(self) -> torch.Tensor:
+        raise TypeError(f"a {self.type} column has no fixed-width view")
+
+    @property
+    def nbytes(self) -> int:
+        off_w = 8 if (pa.types.is_large_string(self.type) or pa.types.is_large_binary(self.type)) else 4
+        return self.data_bytes + off_w * (self.num_rows + 1)
+
+    def with_valid(self, valid: Optional[torch.Tensor]) -> "DeviceVarColumn":
+        return DeviceVarColumn(self.type, self.offsets, self.data, valid, self.data_bytes)
+
+    def clone(self) -> "DeviceVarColumn":
+        return _gather_varlen(self, None)
+
 
 class DeviceArrowBlock:
     """An Arrow-layout table whose column buffers live in HBM."""
@@ -200,6 +267,14 @@ class DeviceArrowBlock:
             arr = ca.combine_chunks() if ca.num_chunks != 1 else ca.chunk(0)
             if isinstance(arr, pa.ChunkedArray):
                 arr = arr.chunk(0) if arr.num_chunks else pa.array([], type=ca.type)
+            valid = None
+            if arr.null_count and n:
+                bits = np.frombuffer(arr.buffers()[0], dtype=np.uint8)
+                mask = np.unpackbits(bits, bitorder="little")[arr.offset : arr.offset + n]
+                valid = torch.from_numpy(np.ascontiguousarray(mask)).to("cuda")
+            if _is_varlen(arr.type):
+                cols[name] = _import_varlen(arr, n, valid)
+                continue
             w = _row_bytes(arr.type)
             buf = arr.buffers()[1]
             if buf is None or n == 0:
@@ -207,11 +282,6 @@ class DeviceArrowBlock:
             else:
                 host = np.frombuffer(buf, dtype=np.uint8)[arr.offset * w : (arr.offset + n) * w]
             dev = torch.from_numpy(host.copy() if not host.flags.writeable else host).to("cuda", non_blocking=False)
-            valid = None
-            if arr.null_count and n:
-                bits = np.frombuffer(arr.buffers()[0], dtype=np.uint8)
-                mask = np.unpackbits(bits, bitorder="little")[arr.offset : arr.offset + n]
-                valid = torch.from_numpy(np.ascontiguousarray(mask)).to("cuda")
             cols[name] = DeviceColumn(arr.type, dev, valid)
         return DeviceArrowBlock(cols, n)
 
@@ -236,6 +306,8 @@ class DeviceArrowBlock:
             if c.valid is not None and not bool(c.valid.all()):
                 raise NotImplementedError(f"to_host_buffers: column {name!r} has nulls; use to_arrow()")
         for c, host in zip(self.columns.values(), out):
+            if c.is_varlen:
+                raise NotImplementedError("to_host_buffers: variable-length columns need to_arrow()")
             if host.numel() < c.data.numel():
                 raise ValueError(f"host buffer too small: {host.numel()} < {c.data.numel()} bytes")
             host[: c.data.numel()].copy_(c.data, non_blocking=True)
@@ -246,15 +318,17 @@ class DeviceArrowBlock:
             return pa.Table.from_pydict({})
         arrays, fields = [], []
         for name, c in self.columns.items():
-            host = c.data.cpu().numpy()
-            buf = pa.py_buffer(host.tobytes())
             vbuf, nulls = None, 0
             if c.valid is not None:
                 mask = c.valid.cpu().numpy()
                 nulls = int(self._num_rows - np.count_nonzero(mask))
                 if nulls:
                     vbuf = pa.py_buffer(np.packbits(mask != 0, bitorder="little").tobytes())
-            arrays.append(pa.Array.from_buffers(c.type, self._num_rows, [vbuf, buf], null_count=nulls))
+            if c.is_varlen:
+                bufs = [vbuf] + _export_varlen(c)
+            else:
+                bufs = [vbuf, pa.py_buffer(c.data.cpu().numpy().tobytes())]
+            arrays.append(pa.Array.from_buffers(c.type, self._num_rows, bufs, null_count=nulls))
             fields.append(pa.field(name, c.type))
         return pa.Table.from_arrays(arrays, schema=pa.schema(fields))
 
@@ -275,7 +349,7 @@ class DeviceArrowBlock:
     def nbytes(self) -> int:
         # like pyarrow.Table.nbytes: data buffers plus validity bitmaps where present
         return sum(
-            c.data.numel() + ((self._num_rows + 7) // 8 if c.valid is not None else 0)
+            c.nbytes + ((self._num_rows + 7) // 8 if c.valid is not None else 0)
             for c in self.columns.values()
         )
 
@@ -325,10 +399,111 @@ class DeviceArrowBlock:
                     else torch.ones(b.num_rows, dtype=torch.uint8, device="cuda")
                     for b in blocks
                 ])
+            if blocks[0].columns[n].is_varlen:
+                cols[n] = _concat_varlen([b.columns[n] for b in blocks], valid)
+                continue
             cols[n] = DeviceColumn(
                 blocks[0].columns[n].type, torch.cat([b.columns[n].data for b in blocks]), valid
             )
         return DeviceArrowBlock(cols, sum(b.num_rows for b in blocks))
+
+
+# --------------------------------------------------------------------------- variable-length columns
+def _import_varlen(arr: pa.Array, n: int, valid: Optional[torch.Tensor]) -> DeviceVarColumn:
+    large = pa.types.is_large_string(arr.type) or pa.types.is_large_binary(arr.type)
+    bufs = arr.buffers()
+    if n == 0 or bufs[1] is None:
+        return DeviceVarColumn(arr.type, torch.zeros(1, dtype=torch.int64, device="cuda"), _empty_u8(0), valid, 0)
+    offs = np.frombuffer(bufs[1], dtype=np.int64 if large else np.int32)[arr.offset : arr.offset + n + 1]
+    first, last = int(offs[0]), int(offs[-1])
+    offs = offs.astype(np.int64) - first
+    if bufs[2] is None or last == first:
+        data = np.zeros(0, dtype=np.uint8)
+    else:
+        data = np.frombuffer(bufs[2], dtype=np.uint8)[first:last]
+    return DeviceVarColumn(
+        arr.type, torch.from_numpy(offs).to("cuda"),
+        torch.from_numpy(data.copy() if not data.flags.writeable else data).to("cuda"), valid, last - first)
+
+
+def _export_varlen(c: DeviceVarColumn) -> list:
+    """[offsets buffer, data buffer] for pyarrow.Array.from_buffers; offsets are rebased to 0
+    and narrowed to the Arrow type's width."""
+    large = pa.types.is_large_string(c.type) or pa.types.is_large_binary(c.type)
+    offs = c.offsets.cpu().numpy()
+    first, last = int(offs[0]), int(offs[-1])
+    offs = offs - first
+    if not large:
+        if last - first > np.iinfo(np.int32).max:
+            raise ValueError(f"{c.type} column holds {last - first} bytes, more than 32-bit offsets can address")
+        offs = offs.astype(np.int32)
+    data = c.data[first:last].cpu().numpy()
+    return [pa.py_buffer(offs.tobytes()), pa.py_buffer(data.tobytes())]
+
+
+def _concat_varlen(cols: Sequence[DeviceVarColumn], valid: Optional[torch.Tensor]) -> DeviceVarColumn:
+    # one device-to-host copy for every block's first and last offset
+    ends = torch.stack([torch.stack([c.offsets[0], c.offsets[-1]]) for c in cols]).cpu().tolist()
+    offs, data, base = [], [], 0
+    for c, (first, last) in zip(cols, ends):
+        offs.append(c.offsets[:-1] + (base - first))
+        data.append(c.data[first:last])
+        base += last - first
+    offs.append(torch.tensor([base], dtype=torch.int64, device="cuda"))
+    return DeviceVarColumn(cols[0].type, torch.cat(offs), torch.cat(data), valid, base)
+
+
+def _gather_varlen(col: DeviceVarColumn, idx: Optional[torch.Tensor]) -> DeviceVarColumn:
+    """ds_varlen_take_offsets + ds_varlen_take_bytes; ``idx`` None compacts rows 0..n-1."""
+    n = col.num_rows if idx is None else idx.numel()
+    iptr = idx.data_ptr() if idx is not None else None
+    dst_off = torch.empty(n + 1, dtype=torch.int64, device="cuda")
+    ws = _lib.call_ws("ds_varlen_take_offsets", _workspace, col.offsets.data_ptr(), col.num_rows, iptr, n,
+                      dst_off.data_ptr(), stream=_stream())
+    ws.record_stream(torch.cuda.current_stream())
+    total = int(dst_off[-1].item())  # host sync: the output byte count sizes the allocation
+    out = _empty_u8(total)
+    _lib.call("ds_varlen_take_bytes", col.offsets.data_ptr(), col.data.data_ptr(), iptr, n,
+              dst_off.data_ptr(), out.data_ptr(), _stream())
+    valid = None
+    if col.valid is not None:
+        valid = col.valid.clone() if idx is None else _gather_raw(col.valid, 1, col.num_rows, idx)
+    return DeviceVarColumn(col.type, dst_off, out, valid, total)
+
+
+def _sort_u64(keys: torch.Tensor, descending: bool) -> torch.Tensor:
+    n = keys.numel()
+    idx = torch.empty(n, dtype=torch.int32, device="cuda")
+    ws = _lib.call_ws("ds_sort_indices_u64", _workspace, keys.data_ptr(), n, int(descending), idx.data_ptr(),
+                      None, 0, stream=_stream())
+    ws.record_stream(torch.cuda.current_stream())
+    return idx
+
+
+def _argsort_varlen(col: DeviceVarColumn, descending: bool, want_sorted: bool):
+    """Stable sort of a variable-length key: LSD over 64-bit parts (length, then 8-byte
+    chunks from the last to the first), each part one stable radix sort; see csrc/varlen.cu."""
+    n = col.num_rows
+    stream = _stream()
+    keys = torch.empty(n, dtype=torch.int64, device="cuda")
+    max_len = torch.empty(1, dtype=torch.int64, device="cuda")
+    _lib.call("ds_varlen_key_lengths", col.offsets.data_ptr(), None, n, keys.data_ptr(), max_len.data_ptr(), stream)
+    longest = int(max_len.item())  # host sync: number of chunk rounds
+    perm = _sort_u64(keys, descending)
+    for chunk in range((longest + 7) // 8 - 1, -1, -1):
+        _lib.call("ds_varlen_key_chunk", col.offsets.data_ptr(), col.data.data_ptr(), perm.data_ptr(), n,
+                  8 * chunk, keys.data_ptr(), stream)
+        order = _sort_u64(keys, descending)
+        perm = _gather_raw(perm.view(torch.uint8), 4, n, order).view(torch.int32)
+    return perm, (_gather_varlen(DeviceVarColumn(col.type, col.offsets, col.data), perm) if want_sorted else None)
+
+
+def _varlen_bounds_to_device(boundaries: Sequence):
+    raw = [b.encode("utf-8") if isinstance(b, str) else bytes(b) for b in boundaries]
+    offs = np.zeros(len(raw) + 1, dtype=np.int64)
+    np.cumsum([len(r) for r in raw], out=offs[1:])
+    data = np.frombuffer(b"".join(raw), dtype=np.uint8)
+    return torch.from_numpy(offs).to("cuda"), torch.from_numpy(data.copy()).to("cuda")
 
 
 Block = Union[DeviceArrowBlock, pa.Table]
@@ -339,6 +514,8 @@ def _argsort(col: DeviceColumn, descending: bool, want_sorted: bool, options: in
     """ds_sort_indices_* -> (idx int32 tensor holding uint32 values, sorted key column or None)."""
     n = col.num_rows
     kind = _key_kind(col.type)
+    if kind == "var":
+        return _argsort_varlen(col, descending, want_sorted)
     idx = torch.empty(n, dtype=torch.int32, device="cuda")
     out = _empty_u8(n * col.row_bytes) if want_sorted else None
     optr = out.data_ptr() if out is not None else None
@@ -360,6 +537,8 @@ def _gather_raw(src: torch.Tensor, row_bytes: int, src_rows: int, idx: torch.Ten
 
 
 def _gather(col: DeviceColumn, idx: torch.Tensor) -> DeviceColumn:
+    if col.is_varlen:
+        return _gather_varlen(col, idx)
     out = _gather_raw(col.data, col.row_bytes, col.num_rows, idx)
     valid = _gather_raw(col.valid, 1, col.num_rows, idx) if col.valid is not None else None
     return DeviceColumn(col.type, out, valid)
@@ -382,22 +561,22 @@ def _argsort_nulls_last(col: DeviceColumn, descending: bool):
         return idx, sk, n
     perm0, nv = _split_nulls(col)
     if nv == n:
-        idx, sk = _argsort(DeviceColumn(col.type, col.data), descending, want_sorted=True)
+        idx, sk = _argsort(col.with_valid(None), descending, want_sorted=True)
         return idx, sk, n
-    rb = col.row_bytes
-    head = DeviceColumn(col.type, _gather_raw(col.data, rb, n, perm0[:nv]))
+    bare = col.with_valid(None)
     idx = torch.empty(n, dtype=torch.int32, device="cuda")
+    pieces = []
     if nv:
-        idx2, sk = _argsort(head, descending, want_sorted=True)
+        idx2, sk = _argsort(_gather(bare, perm0[:nv]), descending, want_sorted=True)
         idx[:nv] = _gather_raw(perm0.view(torch.uint8), 4, n, idx2).view(torch.int32)
-        skd = sk.data
-    else:
-        skd = _empty_u8(0)
+        pieces.append(sk)
     idx[nv:] = perm0[nv:]
-    tail = _gather_raw(col.data, rb, n, perm0[nv:])
+    pieces.append(_gather(bare, perm0[nv:]))
     valid = torch.zeros(n, dtype=torch.uint8, device="cuda")
     valid[:nv] = 1
-    return idx, DeviceColumn(col.type, torch.cat([skd, tail]), valid), nv
+    if col.is_varlen:
+        return idx, _concat_varlen(pieces, valid), nv
+    return idx, DeviceColumn(col.type, torch.cat([p.data for p in pieces]), valid), nv
 
 
 def _take_block(block: DeviceArrowBlock, idx: torch.Tensor, ready: Optional[Dict[str, DeviceColumn]] = None) -> DeviceArrowBlock:
@@ -424,8 +603,14 @@ def _boundaries_to_device(boundaries: Sequence, col: DeviceColumn) -> torch.Tens
 def _searchsorted(sorted_col: DeviceColumn, boundaries: Sequence, descending: bool) -> List[int]:
     nb = len(boundaries)
     kind = _key_kind(sorted_col.type)
-    b = _boundaries_to_device(boundaries, sorted_col)
     out = torch.empty(nb, dtype=torch.int64, device="cuda")
+    if kind == "var":
+        boff, bdata = _varlen_bounds_to_device(boundaries)
+        _lib.call("ds_searchsorted_varlen", sorted_col.offsets.data_ptr(), sorted_col.data.data_ptr(),
+                  sorted_col.num_rows, boff.data_ptr(), bdata.data_ptr(), nb, int(descending),
+                  out.data_ptr(), _stream())
+        return [int(x) for x in out.cpu().tolist()]
+    b = _boundaries_to_device(boundaries, sorted_col)
     if kind == "fsb":
         _lib.call("ds_searchsorted_fsb", sorted_col.ptr, sorted_col.row_bytes, sorted_col.num_rows,
                   b.data_ptr(), nb, int(descending), out.data_ptr(), _stream())
@@ -438,8 +623,13 @@ def _searchsorted(sorted_col: DeviceColumn, boundaries: Sequence, descending: bo
 def _range_partition(col: DeviceColumn, boundaries: Sequence, descending: bool):
     """ds_partition_hist_scatter_* -> (perm tensor, counts list)."""
     kind = _key_kind(col.type)
-    if kind == "f64":
-        raise NotImplementedError("range partition of float64 keys is not supported on device yet")
+    if kind in ("f64", "var"):
+        # no one-pass bucket kernel for these key types: a stable sort and a searchsorted give
+        # a partition that is also ordered inside each part (the reducer's stable sort makes
+        # the final result the same either way)
+        idx, sorted_key = _argsort(col, descending, want_sorted=True)
+        edges = [0] + _searchsorted(sorted_key, boundaries, descending) + [col.num_rows]
+        return idx, [edges[i + 1] - edges[i] for i in range(len(boundaries) + 1)]
     n, nb = col.num_rows, len(boundaries)
     b = _boundaries_to_device(boundaries, col)
     counts = torch.empty(nb + 1, dtype=torch.int64, device="cuda")
@@ -463,7 +653,23 @@ def _random_permutation(n: int, seed: int, subsequence: int = 0) -> torch.Tensor
     return perm
 
 
+def _group_ids(sorted_keys: DeviceColumn) -> DeviceColumn:
+    """int64 column with the same runs of equal values as the sorted key column."""
+    n = sorted_keys.num_rows
+    gids = torch.empty(n, dtype=torch.int64, device="cuda")
+    if sorted_keys.is_varlen:
+        ws = _lib.call_ws("ds_group_ids_varlen", _workspace, sorted_keys.offsets.data_ptr(),
+                          sorted_keys.data.data_ptr(), n, gids.data_ptr(), stream=_stream())
+    else:
+        ws = _lib.call_ws("ds_group_ids_fixed", _workspace, sorted_keys.ptr, sorted_keys.row_bytes,
+                          int(pa.types.is_float64(sorted_keys.type)), n, gids.data_ptr(), stream=_stream())
+    ws.record_stream(torch.cuda.current_stream())
+    return DeviceColumn(pa.int64(), gids.view(torch.uint8))
+
+
 def _segment_heads(sorted_keys: DeviceColumn):
+    if not pa.types.is_int64(sorted_keys.type):
+        sorted_keys = _group_ids(sorted_keys)
     n = sorted_keys.num_rows
     starts = torch.empty(n + 1, dtype=torch.int32, device="cuda")
     nseg = torch.empty(1, dtype=torch.int32, device="cuda")
@@ -624,10 +830,7 @@ class DeviceArrowBlockAccessor:
         """arrow_block.py:178-182.  Device slices are views; ``copy=True`` clones."""
         view = self._block.slice(start, end)
         if copy:
-            cols = collections.OrderedDict(
-                (n, DeviceColumn(c.type, c.data.clone(), c.valid.clone() if c.valid is not None else None))
-                for n, c in view.columns.items()
-            )
+            cols = collections.OrderedDict((n, c.clone()) for n, c in view.columns.items())
             view = DeviceArrowBlock(cols, view.num_rows)
         return view
 
@@ -654,6 +857,13 @@ class DeviceArrowBlockAccessor:
         cols = collections.OrderedDict()
         for name in names:
             c = self._block.column(name)
+            if c.is_varlen:  # sample row ids with the same kernel, then take those rows
+                rows = torch.arange(c.num_rows, dtype=torch.int32, device="cuda")
+                picked = torch.empty(k, dtype=torch.int32, device="cuda")
+                if k:
+                    _lib.call("ds_sample_rows", rows.data_ptr(), 4, c.num_rows, k, seed, picked.data_ptr(), _stream())
+                cols[name] = _gather_varlen(c, picked)
+                continue
             out = _empty_u8(k * c.row_bytes)
             valid = None
             if k:
@@ -699,7 +909,7 @@ class DeviceArrowBlockAccessor:
             return _range_partition(keycol, boundaries, descending)
         n = keycol.num_rows
         perm0, nv = _split_nulls(keycol)
-        head = DeviceColumn(keycol.type, _gather_raw(keycol.data, keycol.row_bytes, n, perm0[:nv]))
+        head = _gather(keycol.with_valid(None), perm0[:nv])
         permv, counts = _range_partition(head, boundaries, descending)
         perm = torch.empty(n, dtype=torch.int32, device="cuda")
         perm[:nv] = _gather_raw(perm0.view(torch.uint8), 4, n, permv).view(torch.int32)
@@ -768,8 +978,7 @@ class DeviceArrowBlockAccessor:
             nseg = 1
         else:
             keycol = blk.column(key)
-            if _key_kind(keycol.type) != "i64":
-                raise NotImplementedError("groupby keys must be int64 on device for now")
+            _key_kind(keycol.type)  # raises for key types the device path cannot order
             if keycol.valid is not None and not bool(keycol.valid.all()):
                 raise NotImplementedError("null groupby keys are not supported on device yet")
             starts, nseg = _segment_heads(keycol)

@@ -263,6 +263,16 @@ def _key_width(block, col, group) -> Tuple[int, pa.DataType]:
 _VALID = "\x00valid"  # wire-name suffix of a column's validity bytes
 
 
+def _fixed_width_only(block, what: str) -> None:
+    """The peer-memory exchange moves rows of a fixed width; variable-length columns would
+    need a second exchange of byte counts and are single-GPU only for now."""
+    for name, c in block.columns.items():
+        if c.is_varlen:
+            raise NotImplementedError(
+                f"{what}: column {name!r} has the variable-length type {c.type}; the multi-GPU "
+                "exchange supports fixed-width columns only")
+
+
 def _agree_on_validity(block, group, dev):
     """Every rank must exchange the same set of buffers: a column carries validity on the
     wire if it has a mask on ANY rank (ranks without one send all-ones)."""
@@ -415,6 +425,7 @@ def sort_block(block, key: str, descending: bool = False, group=None, consume: b
     from .block import (DeviceArrowBlock, DeviceArrowBlockAccessor, DeviceColumn,
                         _argsort_nulls_last, _gather)
 
+    _fixed_width_only(block, "sort_block")
     world = dist.get_world_size(group)
     rank = dist.get_rank(group)
     dev = _dev()
@@ -563,6 +574,7 @@ def random_shuffle_block(block, seed: Optional[int], group=None):
 
     from .block import DeviceArrowBlock, DeviceArrowBlockAccessor, DeviceColumn
 
+    _fixed_width_only(block, "random_shuffle_block")
     world = dist.get_world_size(group)
     rank = dist.get_rank(group)
     dev = _dev()
@@ -601,6 +613,7 @@ def groupby_block(block, key: str, aggs, group=None):
     local sort + combine, range-partition the partial rows, exchange, merge + finalize."""
     from .block import DeviceArrowBlock, DeviceArrowBlockAccessor, DeviceColumn, PartialAggBlock, _searchsorted
 
+    _fixed_width_only(block, "groupby_block")
     world = dist.get_world_size(group)
     rank = dist.get_rank(group)
     dev = _dev()

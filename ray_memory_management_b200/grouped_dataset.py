@@ -75,11 +75,8 @@ class DeviceGroupbyOp(_GroupbyOp, DeviceShufflePlan):
 
 def _group_ends(block, key: Optional[str]) -> List[int]:
     """End offsets of the runs of equal keys of a key-sorted block (get_key_boundaries,
-    grouped_dataset.py:266-275).  int64 keys: one boundary-flag + compaction kernel on the
-    device; other key types: compared on the host copy that map_groups needs anyway."""
-    import numpy as np
-
-    from .block import _key_kind, _segment_heads
+    grouped_dataset.py:266-275), found on the device for every key type."""
+    from .block import _segment_heads
 
     n = block.num_rows
     if key is None:
@@ -87,13 +84,8 @@ def _group_ends(block, key: Optional[str]) -> List[int]:
     col = block.column(key)
     if col.valid is not None and not bool(col.valid.all()):
         raise NotImplementedError("null groupby keys are not supported on device yet")
-    if _key_kind(col.type) == "i64":
-        starts, nseg = _segment_heads(col)
-        return starts[1:nseg + 1].cpu().tolist()
-    w = col.data.numel() // n
-    rows = col.data.cpu().numpy().reshape(n, w)
-    change = np.flatnonzero((rows[1:] != rows[:-1]).any(axis=1)) + 1
-    return change.tolist() + [n]
+    starts, nseg = _segment_heads(col)
+    return starts[1:nseg + 1].cpu().tolist()
 
 
 def _batch_to_arrow(batch) -> pa.Table:

@@ -131,3 +131,32 @@ def test_groupby_name_conflict(golden):
     g = golden("groupby")
     aggs = (("sum", "vi"), ("sum", "vi"), ("count", None), ("count", None))
     assert ["k"] + O.resolved_names(aggs) == list(g["conflict_names"])
+
+
+def _unpack_rows(offsets, data):
+    raw = data.tobytes()
+    return [raw[offsets[i]:offsets[i + 1]] for i in range(len(offsets) - 1)]
+
+
+@pytest.mark.parametrize("desc", [False, True])
+def test_sort_varlen_binary(golden, desc):
+    """binary keys of length 0..19 with shared prefixes and NUL bytes (tests/golden/varlen.npz,
+    recorded from the reference's sort_impl)."""
+    g = golden("varlen")
+    rows = _unpack_rows(g["bin_offsets"], g["bin_data"])
+    tabs = [pa.table({"key": pa.array(rows[a:b], pa.binary()), "row": np.arange(a, b, dtype=np.int64)})
+            for a, b in g["block_cuts"]]
+    want = g[f"plain_{'desc' if desc else 'asc'}_row_order"]
+    random.seed(1)
+    blocks = O.sort_dataset(tabs, "key", desc)
+    got = pa.concat_tables([b for b in blocks if b.num_rows])["row"].to_numpy()
+    assert np.array_equal(got, want)
+    assert np.array_equal(O.global_stable_sort(tabs, "key", desc)["row"].to_numpy(), want)
+
+
+def test_sort_varlen_string(golden):
+    g = golden("varlen")
+    words = [r.decode() for r in _unpack_rows(g["str_offsets"], g["str_data"])]
+    tabs = [pa.table({"key": pa.array(words[a:b], pa.string()), "row": np.arange(a, b, dtype=np.int64)})
+            for a, b in g["block_cuts"]]
+    assert np.array_equal(O.global_stable_sort(tabs, "key", False)["row"].to_numpy(), g["str_asc_row_order"])
