@@ -43,7 +43,10 @@ struct PassList {
 };
 
 // ---------------------------------------------------------------- encode + hist
-template <int KIND, bool HAS_LO>
+// UNIFORM_CHECK: test every digit for being constant across the warp first (one atomic instead
+// of 32 colliding ones on skewed keys).  Off when the caller already knows the digits spread
+// (prefix mode, Philox keys): the four match.all per row are not free on sm_100a.
+template <int KIND, bool HAS_LO, bool UNIFORM_CHECK>
 __global__ void __launch_bounds__(512) encode_hist_kernel(const void* __restrict__ col,
                                                           uint32_t width, uint32_t n, bool desc,
                                                           uint64_t* __restrict__ hi_out,
@@ -72,8 +75,8 @@ __global__ void __launch_bounds__(512) encode_hist_kernel(const void* __restrict
       if (p < pl.count) {
         uint32_t d = (HAS_LO && pl.from_lo[p]) ? (lo >> pl.shift[p]) & 255u
                                                : static_cast<uint32_t>(hi >> pl.shift[p]) & 255u;
-        int same;
-        __match_all_sync(m, d, &same);
+        int same = 0;
+        if (UNIFORM_CHECK) __match_all_sync(m, d, &same);
         if (same) {  // constant digit across the warp: one atomic instead of 32 colliding
           if ((int)lane_id() == leader) atomicAdd(&sh[p * RADIX + d], __popc(m));
         } else {
@@ -689,18 +692,22 @@ static PassList make_passes(int kind, uint32_t width) {
 }
 
 template <int KIND>
-static cudaError_t launch_encode(bool has_lo, const void* col, uint32_t width, uint32_t n, bool desc,
-                                 uint64_t* hi, uint16_t* lo, const PassList& pl, uint32_t* ghist,
+static cudaError_t launch_encode(bool has_lo, bool uniform_check, const void* col, uint32_t width, uint32_t n,
+                                 bool desc, uint64_t* hi, uint16_t* lo, const PassList& pl, uint32_t* ghist,
                                  cudaStream_t s, uint64_t seed = 0, uint64_t subseq = 0) {
   const int threads = 512;
   int blocks = sm_count() * 4;
   const int need = (n + threads - 1) / threads;
   if (blocks > need) blocks = need;
   note_launch();
-  if (has_lo)
-    encode_hist_kernel<KIND, true><<<blocks, threads, 0, s>>>(col, width, n, desc, hi, lo, pl, ghist, seed, subseq);
+  if (has_lo && uniform_check)
+    encode_hist_kernel<KIND, true, true><<<blocks, threads, 0, s>>>(col, width, n, desc, hi, lo, pl, ghist, seed, subseq);
+  else if (has_lo)
+    encode_hist_kernel<KIND, true, false><<<blocks, threads, 0, s>>>(col, width, n, desc, hi, lo, pl, ghist, seed, subseq);
+  else if (uniform_check)
+    encode_hist_kernel<KIND, false, true><<<blocks, threads, 0, s>>>(col, width, n, desc, hi, lo, pl, ghist, seed, subseq);
   else
-    encode_hist_kernel<KIND, false><<<blocks, threads, 0, s>>>(col, width, n, desc, hi, lo, pl, ghist, seed, subseq);
+    encode_hist_kernel<KIND, false, false><<<blocks, threads, 0, s>>>(col, width, n, desc, hi, lo, pl, ghist, seed, subseq);
   return cudaGetLastError();
 }
 
@@ -809,12 +816,13 @@ static ds_status sort_indices_impl(int kind, const void* col, uint32_t width, ui
     }
   }
 
+  const bool uchk = prefix_shift < 0;  // prefix mode was chosen because the digits spread
   switch (kind) {
-    case KIND_I64: e = launch_encode<KIND_I64>(has_lo, col, width, n, desc, hi[0], lo[0], run, ghist, s); break;
-    case KIND_U64: e = launch_encode<KIND_U64>(has_lo, col, width, n, desc, hi[0], lo[0], run, ghist, s); break;
-    case KIND_F64: e = launch_encode<KIND_F64>(has_lo, col, width, n, desc, hi[0], lo[0], run, ghist, s); break;
-    case KIND_PHILOX: e = launch_encode<KIND_PHILOX>(false, nullptr, 8, n, false, hi[0], lo[0], run, ghist, s, seed, subseq); break;
-    default: e = launch_encode<KIND_FSB>(has_lo, col, width, n, desc, hi[0], lo[0], run, ghist, s); break;
+    case KIND_I64: e = launch_encode<KIND_I64>(has_lo, uchk, col, width, n, desc, hi[0], lo[0], run, ghist, s); break;
+    case KIND_U64: e = launch_encode<KIND_U64>(has_lo, uchk, col, width, n, desc, hi[0], lo[0], run, ghist, s); break;
+    case KIND_F64: e = launch_encode<KIND_F64>(has_lo, uchk, col, width, n, desc, hi[0], lo[0], run, ghist, s); break;
+    case KIND_PHILOX: e = launch_encode<KIND_PHILOX>(false, false, nullptr, 8, n, false, hi[0], lo[0], run, ghist, s, seed, subseq); break;
+    default: e = launch_encode<KIND_FSB>(has_lo, uchk, col, width, n, desc, hi[0], lo[0], run, ghist, s); break;
   }
   DS_CUDA(e);
   ds::note_launch(); scan_hist_kernel<<<run.count, RADIX, 0, s>>>(ghist, n, bin_base, skip, coll);

@@ -107,6 +107,10 @@ def sample_boundaries(blocks: List[Block], key: SortKeyT, num_reducers: int) -> 
     into ranges of about equally many rows (sort.py:80-115)."""
     if isinstance(key, list) and len(key) > 1:
         raise ValueError("Multiple boundary sampling keys not supported.")
+    if num_reducers <= 1:
+        # linspace(0, 1, 1)[1:] is empty: one output partition has no splitters, whatever the
+        # samples are -- so none are drawn (the reference samples 10 rows and discards them)
+        return []
     n_samples = int(num_reducers * 10 / len(blocks))
     column = key[0][0] if isinstance(key, list) else key
     if len(blocks) > 1 and all(isinstance(b, DeviceArrowBlock) for b in blocks):
