@@ -373,6 +373,25 @@ ds_status ds_group_ids_fixed(const void* sorted_col, uint32_t width, int32_t is_
 ds_status ds_group_ids_varlen(const int64_t* sorted_offsets, const uint8_t* sorted_data, uint64_t n,
                               int64_t* group_ids_out, void* ws, size_t* ws_bytes, void* stream);
 
+/* ------------------------------------------------------- narrow numeric keys ---- */
+
+/* pyarrow's sort_indices / searchsorted take a key column of any numeric type
+ * (transform_pyarrow.py:15, arrow_block.py:380-386); the kernels above take int64, uint64,
+ * float64 and short fixed_size_binary.  ds_widen_keys converts a narrower numeric column into
+ * the 64-bit type that orders and ties identically (integers -> int64, uint64 -> int64 biased
+ * by 2^63, float16/float32 -> float64, NaNs stay NaNs), which then stands in for the key in the calls above while the
+ * original column is what the row gather moves.  out64: n 8-byte values. */
+#define DS_KEY_INT8 0
+#define DS_KEY_INT16 1
+#define DS_KEY_INT32 2
+#define DS_KEY_UINT8 3
+#define DS_KEY_UINT16 4
+#define DS_KEY_UINT32 5
+#define DS_KEY_FLOAT32 6
+#define DS_KEY_FLOAT16 7
+#define DS_KEY_UINT64 8 /* -> int64 with the top bit flipped (same order) */
+ds_status ds_widen_keys(const void* col, int32_t src_type, uint64_t n, void* out64, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

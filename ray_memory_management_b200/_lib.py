@@ -80,6 +80,7 @@ _PROTOS = {
     "ds_searchsorted_varlen": [_P, _P, c_uint64, _P, _P, c_uint32, c_int32, _P, _P],
     "ds_group_ids_fixed": [_P, c_uint32, c_int32, c_uint64, _P, _P, _SZP, _P],
     "ds_group_ids_varlen": [_P, _P, c_uint64, _P, _P, _SZP, _P],
+    "ds_widen_keys": [_P, c_int32, c_uint64, _P, _P],
 }
 EXPORTED = ["ds_version", "ds_last_error"] + sorted(_PROTOS)
 

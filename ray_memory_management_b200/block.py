@@ -130,6 +130,42 @@ def _key_kind(t: pa.DataType) -> str:
     )
 
 
+# Arrow types that are sorted through a widened 64-bit stand-in: (ds_widen_keys code, stand-in
+# type).  64-bit temporal types are int64 underneath and are only reinterpreted.
+def _stand_in_type(t: pa.DataType):
+    T = pa.types
+    if T.is_int8(t):
+        return 0, pa.int64()
+    if T.is_int16(t):
+        return 1, pa.int64()
+    if T.is_int32(t) or T.is_date32(t) or T.is_time32(t):
+        return 2, pa.int64()
+    if T.is_uint8(t):
+        return 3, pa.int64()
+    if T.is_uint16(t):
+        return 4, pa.int64()
+    if T.is_uint32(t):
+        return 5, pa.int64()
+    if T.is_float32(t):
+        return 6, pa.float64()
+    if T.is_float16(t):
+        return 7, pa.float64()
+    if T.is_uint64(t):
+        return 8, pa.int64()
+    if T.is_timestamp(t) or T.is_date64(t) or T.is_time64(t) or T.is_duration(t):
+        return None, pa.int64()
+    return None, None
+
+
+def _stand_in_value(t: pa.DataType, v):
+    """A splitter of the original key type as a value of the stand-in type."""
+    if pa.types.is_uint64(t):
+        return int(v) - (1 << 63)
+    if isinstance(v, (np.datetime64, np.timedelta64)):
+        return int(v.astype(np.int64))
+    return v
+
+
 class DeviceColumn:
     """One fixed-width Arrow column in HBM: ``data`` is a uint8 view of n*row_bytes bytes.
 
@@ -510,8 +546,28 @@ Block = Union[DeviceArrowBlock, pa.Table]
 
 
 # --------------------------------------------------------------------------- kernels (thin wrappers)
+def _sortable(col: DeviceColumn) -> DeviceColumn:
+    """``col`` itself if the kernels take its type as a key, else a 64-bit column that orders
+    and ties like it (ds_widen_keys; a reinterpretation for 64-bit temporal types)."""
+    if col.is_varlen:
+        return col
+    code, stand_in = _stand_in_type(col.type)
+    if stand_in is None:
+        return col
+    if code is None:
+        return DeviceColumn(stand_in, col.data, col.valid)
+    n = col.num_rows
+    out = _empty_u8(n * 8)
+    _lib.call("ds_widen_keys", col.ptr, code, n, out.data_ptr(), _stream())
+    return DeviceColumn(stand_in, out, col.valid)
+
+
 def _argsort(col: DeviceColumn, descending: bool, want_sorted: bool, options: int = 0):
     """ds_sort_indices_* -> (idx int32 tensor holding uint32 values, sorted key column or None)."""
+    wide = _sortable(col)
+    if wide is not col:
+        idx, _ = _argsort(wide, descending, False, options)
+        return idx, (_gather(col.with_valid(None), idx) if want_sorted else None)
     n = col.num_rows
     kind = _key_kind(col.type)
     if kind == "var":
@@ -601,6 +657,10 @@ def _boundaries_to_device(boundaries: Sequence, col: DeviceColumn) -> torch.Tens
 
 
 def _searchsorted(sorted_col: DeviceColumn, boundaries: Sequence, descending: bool) -> List[int]:
+    wide = _sortable(sorted_col)
+    if wide is not sorted_col:
+        boundaries = [_stand_in_value(sorted_col.type, b) for b in boundaries]
+        sorted_col = wide
     nb = len(boundaries)
     kind = _key_kind(sorted_col.type)
     out = torch.empty(nb, dtype=torch.int64, device="cuda")
@@ -622,6 +682,10 @@ def _searchsorted(sorted_col: DeviceColumn, boundaries: Sequence, descending: bo
 
 def _range_partition(col: DeviceColumn, boundaries: Sequence, descending: bool):
     """ds_partition_hist_scatter_* -> (perm tensor, counts list)."""
+    wide = _sortable(col)
+    if wide is not col:
+        boundaries = [_stand_in_value(col.type, b) for b in boundaries]
+        col = wide
     kind = _key_kind(col.type)
     if kind in ("f64", "var"):
         # no one-pass bucket kernel for these key types: a stable sort and a searchsorted give
@@ -629,6 +693,8 @@ def _range_partition(col: DeviceColumn, boundaries: Sequence, descending: bool):
         # the final result the same either way)
         idx, sorted_key = _argsort(col, descending, want_sorted=True)
         edges = [0] + _searchsorted(sorted_key, boundaries, descending) + [col.num_rows]
+        for j in range(1, len(edges)):
+            edges[j] = max(edges[j], edges[j - 1])
         return idx, [edges[i + 1] - edges[i] for i in range(len(boundaries) + 1)]
     n, nb = col.num_rows, len(boundaries)
     b = _boundaries_to_device(boundaries, col)
@@ -655,6 +721,8 @@ def _random_permutation(n: int, seed: int, subsequence: int = 0) -> torch.Tensor
 
 def _group_ids(sorted_keys: DeviceColumn) -> DeviceColumn:
     """int64 column with the same runs of equal values as the sorted key column."""
+    if pa.types.is_float32(sorted_keys.type) or pa.types.is_float16(sorted_keys.type):
+        sorted_keys = _sortable(sorted_keys)  # numeric comparison (-0.0 == 0.0) needs doubles
     n = sorted_keys.num_rows
     gids = torch.empty(n, dtype=torch.int64, device="cuda")
     if sorted_keys.is_varlen:
@@ -682,8 +750,19 @@ def _segment_heads(sorted_keys: DeviceColumn):
 _OPS = {"sum": _lib.DS_OP_SUM, "min": _lib.DS_OP_MIN, "max": _lib.DS_OP_MAX, "absmax": _lib.DS_OP_ABSMAX}
 
 
+def _numeric64(vals: DeviceColumn) -> DeviceColumn:
+    """Value column as int64 / float64 for the reductions: narrower integers and floats are
+    widened (pyarrow's sum/min/max of an int32 column land in int64 rows too)."""
+    t = vals.type
+    if vals.is_varlen or pa.types.is_int64(t) or pa.types.is_float64(t) or pa.types.is_uint64(t) or pa.types.is_temporal(t):
+        return vals
+    code, stand_in = _stand_in_type(t)
+    return _sortable(vals) if code is not None else vals
+
+
 def _segmented_reduce(vals: DeviceColumn, idx: Optional[torch.Tensor], starts: torch.Tensor,
                       nseg: int, n: int, op: str) -> DeviceColumn:
+    vals = _numeric64(vals)
     if pa.types.is_float64(vals.type):
         fn = "ds_segmented_reduce_f64"
     elif pa.types.is_int64(vals.type):
@@ -710,6 +789,7 @@ def _segmented_count_valid(vals: DeviceColumn, idx: Optional[torch.Tensor], star
 def _segmented_sumsqdiff(vals: DeviceColumn, idx: Optional[torch.Tensor], starts: torch.Tensor, nseg: int,
                          n: int, means: DeviceColumn, weights: Optional[DeviceColumn] = None,
                          addend: Optional[DeviceColumn] = None) -> DeviceColumn:
+    vals = _numeric64(vals)
     out = _empty_u8(nseg * 8)
     ip = idx.data_ptr() if idx is not None else None
     if pa.types.is_float64(vals.type):
@@ -894,6 +974,7 @@ class DeviceArrowBlockAccessor:
         bounds = _searchsorted(table.column(col).slice(0, nv), boundaries, descending)
         parts, last = [], 0
         for b in bounds:
+            b = max(b, last)  # cuts never go backwards, whatever the splitters are
             parts.append(table.slice(last, b))
             last = b
         parts.append(table.slice(last, table.num_rows))
@@ -978,7 +1059,7 @@ class DeviceArrowBlockAccessor:
             nseg = 1
         else:
             keycol = blk.column(key)
-            _key_kind(keycol.type)  # raises for key types the device path cannot order
+            _key_kind(_sortable(keycol).type)  # raises for key types the device path cannot order
             if keycol.valid is not None and not bool(keycol.valid.all()):
                 raise NotImplementedError("null groupby keys are not supported on device yet")
             starts, nseg = _segment_heads(keycol)

@@ -70,6 +70,8 @@ class DeviceGroupbyOp(_GroupbyOp, DeviceShufflePlan):
             return [result], map_meta
         bounds = _searchsorted(result.columns[key], boundaries, False)
         edges = [0] + bounds + [result.num_rows]
+        for j in range(1, len(edges)):  # cuts never go backwards, whatever the splitters are
+            edges[j] = max(edges[j], edges[j - 1])
         return [result.slice(edges[j], edges[j + 1]) for j in range(output_num_blocks)], map_meta
 
 

@@ -89,6 +89,8 @@ def sort_samples(samples: pa.Array) -> list:
         rows = raw.reshape(n, w)
         order = np.lexsort(tuple(rows[:, j] for j in range(w - 1, -1, -1)))
         return [r.tobytes() for r in rows[order]]
+    if pa.types.is_temporal(t):  # splitters of temporal keys travel as their integer values
+        samples = samples.cast(pa.int32() if t.bit_width == 32 else pa.int64())
     return list(np.sort(samples.to_numpy(zero_copy_only=False)))
 
 
@@ -130,6 +132,12 @@ def sample_boundaries(blocks: List[Block], key: SortKeyT, num_reducers: int) -> 
     host = DeviceArrowBlock.concat(samples).to_arrow()[column].combine_chunks().drop_null()
     if isinstance(host, pa.ChunkedArray):
         host = host.combine_chunks()
+    if pa.types.is_floating(host.type):
+        # a NaN splitter cuts nothing sensibly (NaNs sort after every number in both directions
+        # and np.searchsorted on them is order-dependent in the reference): never pick one
+        import pyarrow.compute as pc
+
+        host = host.filter(pc.invert(pc.is_nan(host)))
     return boundaries_from_samples(host, num_reducers)
 
 
