@@ -166,16 +166,17 @@ constexpr int REPAIR_MAX_RUN = 16;
 
 // Slow path of the repair: the run of equal prefixes that starts at row i (its head) is
 // ordered by the full key with a stable insertion sort in local memory.
+// Returns the run's length if rows were moved, else 0.
 template <bool HAS_LO>
-__device__ __noinline__ void repair_one_run(uint64_t* __restrict__ hi, uint16_t* __restrict__ lo,
-                                            uint32_t* __restrict__ idx, uint32_t i, uint32_t n,
-                                            int prefix_shift, uint32_t* __restrict__ too_long) {
+__device__ __noinline__ uint32_t repair_one_run(uint64_t* __restrict__ hi, uint16_t* __restrict__ lo,
+                                                uint32_t* __restrict__ idx, uint32_t i, uint32_t n,
+                                                int prefix_shift, uint32_t* __restrict__ too_long) {
   const uint64_t pfx = hi[i] >> prefix_shift;
   uint32_t len = 2;
   while (i + len < n && len <= REPAIR_MAX_RUN && (hi[i + len] >> prefix_shift) == pfx) ++len;
   if (len > REPAIR_MAX_RUN) {
     atomicOr(too_long, 1u);
-    return;
+    return 0;
   }
   uint64_t h[REPAIR_MAX_RUN];
   uint32_t l[REPAIR_MAX_RUN], x[REPAIR_MAX_RUN];
@@ -200,12 +201,13 @@ __device__ __noinline__ void repair_one_run(uint64_t* __restrict__ hi, uint16_t*
     l[b] = kl;
     x[b] = kx;
   }
-  if (!moved) return;
+  if (!moved) return 0;
   for (uint32_t k = 0; k < len; ++k) {
     hi[i + k] = h[k];
     if (HAS_LO) lo[i + k] = static_cast<uint16_t>(l[k]);
     idx[i + k] = x[k];
   }
+  return len;
 }
 
 // Each thread classifies REPAIR_VEC consecutive rows from two 16-byte loads (plus its two
@@ -523,7 +525,131 @@ __global__ void __launch_bounds__(256)
   for (uint32_t o = (vec << 4) + threadIdx.x; o < nbytes; o += 256) dst[o] = buf[o];
 }
 
+// Prefix mode, 10-byte keys: the decode and the search for runs of equal prefixes read the
+// same sorted hi/lo stream, so one kernel does both -- it writes the key column as if no run
+// needed repair and appends the position of every run head to head_list (one global atomic
+// per block).  repair_listed_runs_kernel then visits only those heads (about 1 % of the rows),
+// orders each run by the full key and rewrites the run's 10-byte keys in the output.
+// Thread t of a block owns rows row0 + 4t .. 4t+3: two 16-byte loads of hi, one 8-byte load of
+// lo, 40 contiguous output bytes staged in shared memory as five 8-byte words.
+__global__ void __launch_bounds__(256)
+    decode10_find_runs_kernel(const uint64_t* __restrict__ hi, const uint16_t* __restrict__ lo, uint32_t n,
+                              bool desc, int prefix_shift, uint8_t* __restrict__ out,
+                              uint32_t* __restrict__ head_list, uint32_t* __restrict__ head_count) {
+  __shared__ __align__(16) uint8_t buf[DECODE_ROWS * 10];
+  __shared__ uint32_t s_warp[8];
+  __shared__ uint32_t s_base;
+  const uint32_t row0 = blockIdx.x * static_cast<uint32_t>(DECODE_ROWS);
+  const uint32_t i0 = row0 + threadIdx.x * 4;
+  uint64_t h[4] = {0, 0, 0, 0};
+  uint32_t l[4] = {0, 0, 0, 0};
+  const bool whole = i0 + 4 <= n;
+  if (whole) {
+    const ulonglong2 a = *reinterpret_cast<const ulonglong2*>(hi + i0);
+    const ulonglong2 b = *reinterpret_cast<const ulonglong2*>(hi + i0 + 2);
+    const ushort4 c = *reinterpret_cast<const ushort4*>(lo + i0);
+    h[0] = a.x; h[1] = a.y; h[2] = b.x; h[3] = b.y;
+    l[0] = c.x; l[1] = c.y; l[2] = c.z; l[3] = c.w;
+  } else {
+#pragma unroll
+    for (int k = 0; k < 4; ++k)
+      if (i0 + k < n) {
+        h[k] = hi[i0 + k];
+        l[k] = lo[i0 + k];
+      }
+  }
+  // ---- run heads among my rows (same rule as repair_runs_kernel)
+  uint32_t heads = 0;
+  if (i0 < n) {
+    uint64_t p[6];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) p[k + 1] = h[k] >> prefix_shift;
+    const bool has_prev = i0 > 0, has_next = i0 + 4 < n;
+    p[0] = has_prev ? hi[i0 - 1] >> prefix_shift : 0;
+    p[5] = has_next ? hi[i0 + 4] >> prefix_shift : 0;
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      const uint32_t i = i0 + k;
+      const bool same_prev = (k > 0 || has_prev) && p[k] == p[k + 1];
+      const bool same_next = (k + 1 < 4 ? (whole || i + 1 < n) : has_next) && p[k + 1] == p[k + 2];
+      if (i < n && !same_prev && same_next) heads |= 1u << k;
+    }
+  }
+  // ---- decode into the staging buffer: 4 rows = 40 bytes = 5 little-endian words
+  {
+    uint64_t B[4], L[4];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      const uint64_t hh = desc ? ~h[k] : h[k];
+      const uint32_t ll = (desc ? ~l[k] : l[k]) & 0xffffu;
+      B[k] = bswap64(hh);
+      L[k] = ((ll >> 8) | (ll << 8)) & 0xffffu;
+    }
+    uint64_t* q = reinterpret_cast<uint64_t*>(buf + threadIdx.x * 40);
+    q[0] = B[0];
+    q[1] = L[0] | (B[1] << 16);
+    q[2] = (B[1] >> 48) | (L[1] << 16) | (B[2] << 32);
+    q[3] = (B[2] >> 32) | (L[2] << 32) | (B[3] << 48);
+    q[4] = (B[3] >> 16) | (L[3] << 48);
+  }
+  // ---- slots for my heads: warp scan, block offsets, one global atomic per block
+  const uint32_t cnt = __popc(heads);
+  uint32_t incl = cnt;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const uint32_t v = __shfl_up_sync(0xffffffffu, incl, o);
+    if ((int)lane_id() >= o) incl += v;
+  }
+  if (lane_id() == 31) s_warp[threadIdx.x >> 5] = incl;
+  __syncthreads();  // staging buffer and warp totals complete
+  if (threadIdx.x == 0) {
+    uint32_t tot = 0;
+#pragma unroll
+    for (int w = 0; w < 8; ++w) tot += s_warp[w];
+    s_base = tot ? atomicAdd(head_count, tot) : 0u;
+  }
+  const uint32_t nbytes = min(static_cast<uint32_t>(DECODE_ROWS), n - row0) * 10u;
+  uint8_t* dst = out + static_cast<uint64_t>(row0) * 10u;
+  const uint32_t vec = nbytes >> 4;
+  for (uint32_t v = threadIdx.x; v < vec; v += 256)
+    st_stream(reinterpret_cast<uint4*>(dst) + v, reinterpret_cast<const uint4*>(buf)[v]);
+  for (uint32_t o = (vec << 4) + threadIdx.x; o < nbytes; o += 256) dst[o] = buf[o];
+  __syncthreads();  // s_base
+  if (heads) {
+    uint32_t slot = s_base + incl - cnt;
+    for (uint32_t w = 0; w < (threadIdx.x >> 5); ++w) slot += s_warp[w];
+#pragma unroll
+    for (int k = 0; k < 4; ++k)
+      if (heads >> k & 1u) head_list[slot++] = i0 + k;
+  }
+}
+
+__global__ void __launch_bounds__(256)
+    repair_listed_runs_kernel(uint64_t* __restrict__ hi, uint16_t* __restrict__ lo, uint32_t* __restrict__ idx,
+                              uint32_t n, int prefix_shift, const uint32_t* __restrict__ head_list,
+                              const uint32_t* __restrict__ head_count, bool desc, uint8_t* __restrict__ out,
+                              uint32_t* __restrict__ too_long) {
+  const uint32_t cnt = *head_count;
+  const uint32_t stride = gridDim.x * blockDim.x;
+  for (uint32_t j = blockIdx.x * blockDim.x + threadIdx.x; j < cnt; j += stride) {
+    const uint32_t i = head_list[j];
+    const uint32_t len = repair_one_run<true>(hi, lo, idx, i, n, prefix_shift, too_long);
+    for (uint32_t r = 0; r < len; ++r) {  // rewrite the keys of the rows that moved
+      const uint64_t hh = desc ? ~hi[i + r] : hi[i + r];
+      const uint32_t ll = (desc ? ~static_cast<uint32_t>(lo[i + r]) : lo[i + r]) & 0xffffu;
+      const uint64_t be = bswap64(hh);
+      uint16_t* q = reinterpret_cast<uint16_t*>(out + static_cast<uint64_t>(i + r) * 10u);
+      q[0] = static_cast<uint16_t>(be);
+      q[1] = static_cast<uint16_t>(be >> 16);
+      q[2] = static_cast<uint16_t>(be >> 32);
+      q[3] = static_cast<uint16_t>(be >> 48);
+      q[4] = static_cast<uint16_t>((ll >> 8) | ((ll & 0xffu) << 8));
+    }
+  }
+}
+
 // ---------------------------------------------------------------- host driver
+static bool g_no_fused_decode = false;  // ds_debug_set_fused_decode(0): separate repair + decode kernels
 static int g_cfg = 18;  // tuning knob (ds_debug_set_radix_config); 18 = v3 table match <384 x 12>, best measured
 
 template <typename K>
@@ -853,6 +979,29 @@ static ds_status sort_indices_impl(int kind, const void* col, uint32_t width, ui
     idx_src = idx_dst;
     cur ^= 1;
   }
+  const bool fused_decode = prefix_shift >= 0 && kind == KIND_FSB && width == 10 && sorted_out != nullptr &&
+                            (reinterpret_cast<uintptr_t>(sorted_out) & 15) == 0 && !g_no_fused_decode;
+  if (fused_decode) {
+    // the other half of the ping-pong buffers is dead now: it holds the list of run heads
+    uint32_t* head_list = reinterpret_cast<uint32_t*>(hi[cur ^ 1]);
+    uint32_t* head_count = too_long + 1;  // zeroed with the rest of ctrl
+    ds::note_launch();
+    decode10_find_runs_kernel<<<(n + DECODE_ROWS - 1) / DECODE_ROWS, 256, 0, s>>>(
+        hi[cur], lo[cur], n, desc, prefix_shift, static_cast<uint8_t*>(sorted_out), head_list, head_count);
+    DS_LAUNCH_CHECK();
+    ds::note_launch();
+    repair_listed_runs_kernel<<<sm_count() * 4, 256, 0, s>>>(hi[cur], lo[cur], idx_out, n, prefix_shift, head_list,
+                                                             head_count, desc, static_cast<uint8_t*>(sorted_out),
+                                                             too_long);
+    DS_LAUNCH_CHECK();
+    uint32_t flag = 0;
+    DS_CUDA(cudaMemcpyAsync(&flag, too_long, sizeof(flag), cudaMemcpyDeviceToHost, s));
+    DS_CUDA(cudaStreamSynchronize(s));  // host sync #2 (prefix mode only): 4 bytes
+    if (flag)
+      return sort_indices_impl(kind, col, width, n64, descending, idx_out, sorted_out,
+                               options | DS_SORT_NO_PREFIX_REPAIR, ws, ws_bytes, stream, fn, seed, subseq);
+    return DS_OK;
+  }
   if (prefix_shift >= 0) {
     ds::note_launch();
     const uint32_t repair_blocks = (n + 256 * REPAIR_VEC - 1) / (256 * REPAIR_VEC);
@@ -934,6 +1083,14 @@ ds_status ds_random_permutation(uint64_t seed, uint64_t subsequence, uint64_t n,
 }
 
 // Tuning hook used by bench.py --sweep; not part of the reference-facing surface.
+// 0: prefix mode runs repair_runs_kernel + the decode kernel separately (the older path);
+// 1 (default): the fused decode + run-head list pair.  Returns the previous setting.
+int32_t ds_debug_set_fused_decode(int32_t enable) {
+  const int old = ds::g_no_fused_decode ? 0 : 1;
+  ds::g_no_fused_decode = enable == 0;
+  return old;
+}
+
 int32_t ds_debug_set_radix_config(int32_t cfg) {
   int old = ds::g_cfg;
   if (cfg >= 0 && cfg < ds::NUM_CFGS && ds::cfg_known(cfg)) ds::g_cfg = cfg;

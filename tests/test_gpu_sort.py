@@ -388,6 +388,35 @@ def test_prefix_repair_mode_matches_full_sort(ds, desc):
     assert np.array_equal(a.astype(np.int64), _arrow_order(k, "i64", desc))
 
 
+@pytest.mark.parametrize("n", [65_536, 66_001, 400_003])
+@pytest.mark.parametrize("desc", [False, True])
+def test_fused_decode_and_listed_repair_equal_separate_kernels(ds, n, desc):
+    """prefix mode on 10-byte keys: the fused decode + run-head list + sparse repair pair
+    against the separate repair and decode kernels and against Arrow, at sizes that leave a
+    ragged last block / a ragged last 4-row group, with runs that straddle block boundaries."""
+    L = ds._lib
+    rng = np.random.default_rng(n)
+    col = rng.integers(0, 256, (n, 10), dtype=np.uint8)
+    for s in range(400):                      # runs of 2..9 rows sharing their first 7 bytes
+        rows = rng.choice(n, int(rng.integers(2, 10)), replace=False)
+        col[rows, :7] = col[rows[0], :7]
+    col[rng.choice(n, 12, replace=False)] = col[1]    # 13 equal keys (stability inside a run)
+    col[n - 3:, :7] = col[n - 4, :7]                   # a run that ends at the last row
+    col[1021:1027, :7] = col[1020, :7]                 # rows next to each other that tie on the prefix
+    want = _arrow_order(col, "fsb", desc)
+    res = {}
+    for fused in (1, 0):
+        old = L.lib.ds_debug_set_fused_decode(fused)
+        try:
+            res[fused] = _argsort_c(ds, col, "fsb", desc, width=10)
+        finally:
+            L.lib.ds_debug_set_fused_decode(old)
+    for fused in (1, 0):
+        a, sa = res[fused]
+        assert np.array_equal(a.astype(np.int64), want), fused
+        assert np.array_equal(sa.reshape(n, 10), col[want]), fused
+
+
 @pytest.mark.parametrize("width", [1, 8, 10, 90, 100])
 def test_scatter_rows_to_parts_c_abi(ds, width):
     """the fused map-side slicing kernel against numpy (local destinations; over NVLink it is
