@@ -750,8 +750,9 @@ static cudaError_t launch_pass_cfg(bool has_lo, bool digit_lo, bool gen_idx, con
 #define DS_PASS_CONFIGS(X) \
   X(0, 1, 256, 16, 2) X(4, 2, 512, 8, 2) X(6, 2, 384, 12, 2) X(7, 2, 256, 12, 3) \
   X(11, 3, 384, 12, 2) X(17, 4, 384, 12, 2) X(18, 5, 384, 12, 2) X(19, 6, 384, 12, 2) \
-  X(20, 4, 512, 8, 2) X(21, 5, 256, 12, 3) X(25, 5, 512, 8, 2)
-constexpr int NUM_CFGS = 26;  // ids are sparse: unknown ids are rejected
+  X(20, 4, 512, 8, 2) X(21, 5, 256, 12, 3) X(25, 5, 512, 8, 2) \
+  X(28, 5, 256, 16, 2)
+constexpr int NUM_CFGS = 29;  // ids are sparse: unknown ids are rejected
 
 static bool cfg_known(int cfg) {
   switch (cfg) {
