@@ -49,6 +49,7 @@ typedef int32_t ds_status;
 #define DS_SORT_NO_PASS_SKIP 1 /* never read the digit histogram back: no host sync at all
                                   (implies DS_SORT_NO_PREFIX_REPAIR) */
 #define DS_SORT_NO_PREFIX_REPAIR 2 /* always run every (non-constant) digit pass */
+#define DS_SORT_NO_HYBRID 4 /* 10-byte keys: never finish the sort with one CTA per 16-bit bucket */
 
 /* aggregation ops for ds_segmented_reduce_* */
 #define DS_OP_SUM 0

@@ -20,6 +20,7 @@ DS_MAX_KEY_BYTES = 10
 DS_MAX_PARTITIONS = 256
 DS_SORT_NO_PASS_SKIP = 1
 DS_SORT_NO_PREFIX_REPAIR = 2
+DS_SORT_NO_HYBRID = 4
 DS_OP_SUM, DS_OP_MIN, DS_OP_MAX, DS_OP_ABSMAX = 0, 1, 2, 3
 DS_SEGMENT_HEADS_STATIC_MAX_ROWS = 1 << 27
 

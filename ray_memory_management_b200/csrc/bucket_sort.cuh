@@ -1,0 +1,242 @@
+// Hybrid plan for 10-byte keys: two global onesweep passes on the two leading bytes leave the
+// rows grouped into 65536 buckets (about n / 65536 rows each, contiguous, input order kept
+// inside a bucket).  One CTA per bucket then finishes the job without further global passes:
+//   * two 8-bit counting-sort passes on key bits [32, 48) entirely in shared memory
+//     (same early-count + table-match ranking as onesweep_v3, no look-back, no global scatter),
+//   * repair of the short runs that still tie on the leading 32 bits, by the full key,
+//   * decode to the 10-byte key column and a coalesced store of keys and row ids.
+// This replaces two global passes, the repair kernel and the decode kernel of the plain
+// prefix plan.  A bucket that does not fit the CTA (skewed leading bytes) or a run longer than
+// the repair limit raises *too_long and the caller falls back to the all-global plan.
+#pragma once
+
+namespace ds {
+
+constexpr int LS_THREADS = 256;
+constexpr int LS_ITEMS = 8;
+constexpr int LS_CAP = LS_THREADS * LS_ITEMS;  // rows a CTA can hold
+constexpr int LS_WARPS = LS_THREADS / 32;
+constexpr uint32_t LS_BUCKETS = 65536;
+constexpr int LS_SMEM_BYTES = LS_CAP * 14 + LS_CAP * 10 + 16;
+
+// starts[b] = first row whose leading 16 bits are >= b, starts[65536] = n (empty buckets get the
+// next bucket's start).  `hi` is sorted by those bits.
+__global__ void __launch_bounds__(256)
+    bucket_bounds_kernel(const uint64_t* __restrict__ hi, uint32_t n, uint32_t* __restrict__ starts) {
+  const uint32_t i0 = (blockIdx.x * blockDim.x + threadIdx.x) * 4;
+  if (i0 >= n) return;
+  uint32_t b[5];  // b[k + 1] = bucket of row i0 + k, b[0] = bucket of row i0 - 1
+  if (i0 + 4 <= n) {
+    const ulonglong2 x = *reinterpret_cast<const ulonglong2*>(hi + i0);
+    const ulonglong2 y = *reinterpret_cast<const ulonglong2*>(hi + i0 + 2);
+    b[1] = static_cast<uint32_t>(x.x >> 48);
+    b[2] = static_cast<uint32_t>(x.y >> 48);
+    b[3] = static_cast<uint32_t>(y.x >> 48);
+    b[4] = static_cast<uint32_t>(y.y >> 48);
+  } else {
+#pragma unroll
+    for (int k = 0; k < 4; ++k) b[k + 1] = i0 + k < n ? static_cast<uint32_t>(hi[i0 + k] >> 48) : 0;
+  }
+  if (i0 == 0) {
+    for (uint32_t v = 0; v <= b[1]; ++v) starts[v] = 0;
+    b[0] = b[1];
+  } else {
+    b[0] = static_cast<uint32_t>(hi[i0 - 1] >> 48);
+  }
+#pragma unroll
+  for (int k = 0; k < 4; ++k) {
+    const uint32_t i = i0 + k;
+    if (i >= n) break;
+    for (uint32_t v = b[k] + 1; v <= b[k + 1]; ++v) starts[v] = i;  // usually zero or one iteration
+    if (i == n - 1)
+      for (uint32_t v = b[k + 1] + 1; v <= LS_BUCKETS; ++v) starts[v] = n;
+  }
+}
+
+__global__ void __launch_bounds__(LS_THREADS, 4)
+    bucket_local_sort_kernel(const uint64_t* __restrict__ hi_in, const uint16_t* __restrict__ lo_in,
+                             const uint32_t* __restrict__ idx_in, const uint32_t* __restrict__ starts,
+                             bool desc, uint8_t* __restrict__ keys_out, uint32_t* __restrict__ idx_out,
+                             uint32_t* __restrict__ too_long) {
+  constexpr int LOW_SHIFT = 32;  // the CTA sorts bits [32, 48); bits [48, 64) are the bucket
+  extern __shared__ __align__(16) unsigned char ls_dyn[];     // LS_SMEM_BYTES (over the 48 KB static limit)
+  unsigned char* smem = ls_dyn;                                // histograms + tables, then the rows
+  uint8_t* stage = ls_dyn + LS_CAP * 14;                       // key bytes as they lie in the output
+  __shared__ uint32_t s_warp_tot[LS_WARPS];
+  uint32_t* warp_hist = reinterpret_cast<uint32_t*>(smem);      // [WARPS][256]
+  uint32_t* match_tab = warp_hist + LS_WARPS * RADIX;            // [WARPS][2][256]
+  uint64_t* ex_hi = reinterpret_cast<uint64_t*>(smem);
+  uint32_t* ex_idx = reinterpret_cast<uint32_t*>(smem + LS_CAP * 8);
+  uint16_t* ex_lo = reinterpret_cast<uint16_t*>(smem + LS_CAP * 12);
+  static_assert(LS_WARPS * RADIX * 4 * 3 <= LS_CAP * 14, "histograms and tables overlay the rows");
+
+  const int tid = threadIdx.x;
+  const int warp = tid >> 5;
+  const uint32_t lane = tid & 31;
+  const uint32_t s = starts[blockIdx.x];
+  const uint32_t R = starts[blockIdx.x + 1] - s;
+  if (R == 0) return;
+  if (R > LS_CAP) {
+    if (tid == 0) atomicOr(too_long, 1u);
+    return;
+  }
+
+  uint64_t hi[LS_ITEMS];
+  uint32_t lo[LS_ITEMS], idx[LS_ITEMS], pos[LS_ITEMS];
+  const uint32_t wofs = warp * 32 * LS_ITEMS + lane;
+#pragma unroll
+  for (int i = 0; i < LS_ITEMS; ++i) {
+    const uint32_t lp = wofs + i * 32;
+    if (lp < R) {
+      hi[i] = ld_stream(hi_in + s + lp);
+      lo[i] = ld_stream(lo_in + s + lp);
+      idx[i] = ld_stream(idx_in + s + lp);
+    } else {
+      hi[i] = 0;
+      lo[i] = 0;
+      idx[i] = 0;
+    }
+  }
+
+  const uint32_t lt_mask = lanemask_lt();
+  const uint32_t lane_bit = 1u << lane;
+  uint32_t* wh = warp_hist + warp * RADIX;
+  volatile uint32_t* mt = match_tab + warp * 2 * RADIX;
+#pragma unroll 1
+  for (int pass = 0; pass < 2; ++pass) {
+    const int shift = LOW_SHIFT + 8 * pass;
+    for (int i = tid; i < LS_WARPS * RADIX * 3; i += LS_THREADS) warp_hist[i] = 0;
+    __syncthreads();
+    // early counts
+#pragma unroll
+    for (int i = 0; i < LS_ITEMS; ++i)
+      if (wofs + i * 32 < R) atomicAdd(&wh[static_cast<uint32_t>(hi[i] >> shift) & 255u], 1u);
+    __syncthreads();
+    // digit totals -> exclusive scan over the 256 digits -> per-warp running offsets
+    {
+      uint32_t sum = 0;
+#pragma unroll
+      for (int w = 0; w < LS_WARPS; ++w) sum += warp_hist[w * RADIX + tid];
+      uint32_t v = sum;
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        const uint32_t t = __shfl_up_sync(0xffffffffu, v, o);
+        if ((int)lane >= o) v += t;
+      }
+      if (lane == 31) s_warp_tot[warp] = v;
+      __syncthreads();
+      uint32_t run = v - sum;
+      for (int w = 0; w < warp; ++w) run += s_warp_tot[w];
+#pragma unroll
+      for (int w = 0; w < LS_WARPS; ++w) {
+        const uint32_t c = warp_hist[w * RADIX + tid];
+        warp_hist[w * RADIX + tid] = run;
+        run += c;
+      }
+    }
+    __syncthreads();
+    // rank: peers of a digit through the per-warp table, the leader advances the warp's offset
+#pragma unroll
+    for (int i = 0; i < LS_ITEMS; ++i) {
+      const bool valid = wofs + i * 32 < R;
+      const uint32_t d = static_cast<uint32_t>(hi[i] >> shift) & 255u;
+      volatile uint32_t* slot = mt + (i & 1) * RADIX + d;
+      if (valid) atomicOr(const_cast<uint32_t*>(slot), lane_bit);
+      __syncwarp();
+      const uint32_t peers = valid ? *slot : lane_bit;
+      __syncwarp();
+      if (valid) *slot = 0;
+      const uint32_t lt = __popc(peers & lt_mask);
+      uint32_t base = 0;
+      if (valid && lt == 0) base = atomicAdd(&wh[d], __popc(peers));
+      base = __shfl_sync(0xffffffffu, base, __ffs(peers) - 1);
+      pos[i] = base + lt;
+    }
+    __syncthreads();  // histograms and tables are dead: the rows overlay them
+#pragma unroll
+    for (int i = 0; i < LS_ITEMS; ++i) {
+      if (wofs + i * 32 < R) {
+        ex_hi[pos[i]] = hi[i];
+        ex_idx[pos[i]] = idx[i];
+        ex_lo[pos[i]] = static_cast<uint16_t>(lo[i]);
+      }
+    }
+    __syncthreads();
+    if (pass == 0) {  // back to registers in position order for the second digit
+#pragma unroll
+      for (int i = 0; i < LS_ITEMS; ++i) {
+        const uint32_t lp = wofs + i * 32;
+        if (lp < R) {
+          hi[i] = ex_hi[lp];
+          lo[i] = ex_lo[lp];
+          idx[i] = ex_idx[lp];
+        }
+      }
+      __syncthreads();
+    }
+  }
+
+  // ---- rows are ordered by their leading 32 bits: order the runs that tie on them
+#pragma unroll 1
+  for (int i = 0; i < LS_ITEMS; ++i) {
+    const uint32_t p = tid + i * LS_THREADS;
+    if (p + 1 >= R) continue;
+    const uint64_t pfx = ex_hi[p] >> LOW_SHIFT;
+    if ((ex_hi[p + 1] >> LOW_SHIFT) != pfx) continue;             // singleton
+    if (p > 0 && (ex_hi[p - 1] >> LOW_SHIFT) == pfx) continue;    // not the head
+    uint32_t len = 2;
+    while (p + len < R && len <= REPAIR_MAX_RUN && (ex_hi[p + len] >> LOW_SHIFT) == pfx) ++len;
+    if (len > REPAIR_MAX_RUN) {
+      atomicOr(too_long, 1u);
+      continue;
+    }
+    for (uint32_t a = 1; a < len; ++a) {  // stable insertion sort inside shared memory
+      const uint64_t kh = ex_hi[p + a];
+      const uint16_t kl = ex_lo[p + a];
+      const uint32_t kx = ex_idx[p + a];
+      uint32_t b = a;
+      while (b > 0 && (ex_hi[p + b - 1] > kh || (ex_hi[p + b - 1] == kh && ex_lo[p + b - 1] > kl))) {
+        ex_hi[p + b] = ex_hi[p + b - 1];
+        ex_lo[p + b] = ex_lo[p + b - 1];
+        ex_idx[p + b] = ex_idx[p + b - 1];
+        --b;
+      }
+      ex_hi[p + b] = kh;
+      ex_lo[p + b] = kl;
+      ex_idx[p + b] = kx;
+    }
+  }
+  __syncthreads();
+
+  // ---- decode into the staging buffer laid out like the output, then coalesced stores
+  const uint64_t out_byte = static_cast<uint64_t>(s) * 10u;
+  const uint32_t mis = static_cast<uint32_t>(out_byte & 15u);  // even: rows are 10 bytes
+#pragma unroll
+  for (int i = 0; i < LS_ITEMS; ++i) {
+    const uint32_t p = tid + i * LS_THREADS;
+    if (p < R) {
+      const uint64_t hh = desc ? ~ex_hi[p] : ex_hi[p];
+      const uint32_t ll = (desc ? ~static_cast<uint32_t>(ex_lo[p]) : ex_lo[p]) & 0xffffu;
+      const uint64_t be = bswap64(hh);
+      uint16_t* q = reinterpret_cast<uint16_t*>(stage + mis + p * 10u);
+      q[0] = static_cast<uint16_t>(be);
+      q[1] = static_cast<uint16_t>(be >> 16);
+      q[2] = static_cast<uint16_t>(be >> 32);
+      q[3] = static_cast<uint16_t>(be >> 48);
+      q[4] = static_cast<uint16_t>((ll >> 8) | ((ll & 0xffu) << 8));
+      idx_out[s + p] = ex_idx[p];
+    }
+  }
+  __syncthreads();
+  uint8_t* g = keys_out + (out_byte - mis);  // 16-byte aligned
+  const uint32_t end = mis + R * 10u;
+  const uint32_t first_vec = (mis + 15u) >> 4, last_vec = end >> 4;
+  for (uint32_t v = first_vec + tid; v < last_vec; v += LS_THREADS)
+    st_stream(reinterpret_cast<uint4*>(g) + v, reinterpret_cast<const uint4*>(stage)[v]);
+  const uint32_t head_end = min(first_vec << 4, end);
+  for (uint32_t o = mis + tid; o < head_end; o += LS_THREADS) g[o] = stage[o];
+  const uint32_t tail_begin = max(last_vec << 4, head_end);
+  for (uint32_t o = tail_begin + tid; o < end; o += LS_THREADS) g[o] = stage[o];
+}
+
+}  // namespace ds

@@ -436,6 +436,10 @@ __global__ void __launch_bounds__(THREADS, MIN_BLOCKS)
 #include "onesweep_v2.cuh"
 #include "onesweep_v3.cuh"
 namespace ds {
+__device__ __forceinline__ uint64_t bswap64(uint64_t v);
+}
+#include "bucket_sort.cuh"
+namespace ds {
 
 // ---------------------------------------------------------------- decode
 template <int KIND>
@@ -649,6 +653,7 @@ __global__ void __launch_bounds__(256)
 }
 
 // ---------------------------------------------------------------- host driver
+static int g_hybrid_mode = 1;  // ds_debug_set_hybrid: 0 never, 1 when the buckets fill a CTA, 2 whatever n (tests)
 static bool g_no_fused_decode = false;  // ds_debug_set_fused_decode(0): separate repair + decode kernels
 static int g_cfg = 18;  // tuning knob (ds_debug_set_radix_config); 18 = v3 table match <384 x 12>, best measured
 
@@ -903,6 +908,7 @@ static ds_status sort_indices_impl(int kind, const void* col, uint32_t width, ui
   // every run, and a run it cannot handle sends the call back to the all-passes plan.
   PassList run = pl;  // the digit positions that get exact histograms (and passes)
   int prefix_shift = -1;
+  bool hybrid = false;
   if (!(options & (DS_SORT_NO_PASS_SKIP | DS_SORT_NO_PREFIX_REPAIR)) && n >= (1u << 16) &&
       pl.count >= 3) {
     float coll_h[MAX_PASSES];
@@ -926,6 +932,14 @@ static ds_status sort_indices_impl(int kind, const void* col, uint32_t width, ui
       DS_CUDA(cudaMemsetAsync(ctrl, 0, ctrl_bytes, s));
       DS_CUDA(cudaStreamSynchronize(s));  // host sync: 40 bytes
     }
+    // hybrid plan (bucket_sort.cuh): 10-byte keys whose two leading bytes spread evenly and
+    // whose 65536 buckets would fill a CTA reasonably (400..1650 rows on average)
+    if (kind == KIND_FSB && width == 10 && sorted_out != nullptr && g_hybrid_mode != 0 &&
+        !(options & DS_SORT_NO_HYBRID) && (reinterpret_cast<uintptr_t>(sorted_out) & 15) == 0 &&
+        (n >= 400u * LS_BUCKETS || g_hybrid_mode == 2) && n <= 1650u * LS_BUCKETS) {
+      const float lim = 1.25f / 256.0f;
+      hybrid = coll_h[pl.count - 1] <= lim && coll_h[pl.count - 2] <= lim;
+    }
     double pairs = 0.5 * static_cast<double>(n) * static_cast<double>(n);
     for (int m = 1; m <= pl.count - 2; ++m) {
       const int p = pl.count - m;
@@ -943,6 +957,15 @@ static ds_status sort_indices_impl(int kind, const void* col, uint32_t width, ui
     }
   }
 
+  // the hybrid plan needs the prefix plan's guarantee (few ties on the leading 32 bits)
+  hybrid = hybrid && prefix_shift >= 32;
+  if (hybrid) {  // only the two leading digits run as global passes
+    run.count = 2;
+    for (int k = 0; k < 2; ++k) {
+      run.shift[k] = pl.shift[pl.count - 2 + k];
+      run.from_lo[k] = 0;
+    }
+  }
   const bool uchk = prefix_shift < 0;  // prefix mode was chosen because the digits spread
   switch (kind) {
     case KIND_I64: e = launch_encode<KIND_I64>(has_lo, uchk, col, width, n, desc, hi[0], lo[0], run, ghist, s); break;
@@ -972,13 +995,33 @@ static ds_status sort_indices_impl(int kind, const void* col, uint32_t width, ui
   const uint32_t* idx_src = nullptr;
   for (int j = 0; j < ne; ++j) {
     const int p = exec[j];
-    uint32_t* idx_dst = ((ne - 1 - j) % 2 == 0) ? idx_out : idx_alt;
+    uint32_t* idx_dst = ((ne - 1 - j) % 2 == 0) != hybrid ? idx_out : idx_alt;  // hybrid: last pass -> idx_alt
     DS_CUDA(cudaMemsetAsync(lookback, 0, sizeof(uint32_t) * static_cast<size_t>(tiles) * RADIX, s));
     DS_CUDA(launch_pass(cfg, has_lo, run.from_lo[p] != 0, j == 0, hi[cur], lo[cur], idx_src,
                         hi[cur ^ 1], lo[cur ^ 1], idx_dst, n, run.shift[p], bin_base + p * RADIX,
                         lookback, tile_counters + p, s));
     idx_src = idx_dst;
     cur ^= 1;
+  }
+  if (hybrid) {
+    // lookback is dead after the passes: its head holds the 65537 bucket starts
+    uint32_t* starts = lookback;
+    static unsigned long long attr_done = 0;
+    DS_CUDA(set_smem_attr(bucket_local_sort_kernel, LS_SMEM_BYTES, &attr_done));
+    ds::note_launch();
+    bucket_bounds_kernel<<<(n + 1023) / 1024, 256, 0, s>>>(hi[cur], n, starts);
+    DS_LAUNCH_CHECK();
+    ds::note_launch();
+    bucket_local_sort_kernel<<<LS_BUCKETS, LS_THREADS, LS_SMEM_BYTES, s>>>(
+        hi[cur], lo[cur], idx_src, starts, desc, static_cast<uint8_t*>(sorted_out), idx_out, too_long);
+    DS_LAUNCH_CHECK();
+    uint32_t flag = 0;
+    DS_CUDA(cudaMemcpyAsync(&flag, too_long, sizeof(flag), cudaMemcpyDeviceToHost, s));
+    DS_CUDA(cudaStreamSynchronize(s));  // host sync #2: 4 bytes
+    if (flag)  // a bucket or a run did not fit: the all-global prefix plan handles any data
+      return sort_indices_impl(kind, col, width, n64, descending, idx_out, sorted_out,
+                               options | DS_SORT_NO_HYBRID, ws, ws_bytes, stream, fn, seed, subseq);
+    return DS_OK;
   }
   const bool fused_decode = prefix_shift >= 0 && kind == KIND_FSB && width == 10 && sorted_out != nullptr &&
                             (reinterpret_cast<uintptr_t>(sorted_out) & 15) == 0 && !g_no_fused_decode;
@@ -1089,6 +1132,15 @@ ds_status ds_random_permutation(uint64_t seed, uint64_t subsequence, uint64_t n,
 int32_t ds_debug_set_fused_decode(int32_t enable) {
   const int old = ds::g_no_fused_decode ? 0 : 1;
   ds::g_no_fused_decode = enable == 0;
+  return old;
+}
+
+// Hybrid plan for 10-byte keys (two global passes + one CTA per 16-bit bucket): 0 never,
+// 1 (default) when n / 65536 is between 400 and 1650 rows, 2 also for smaller n (tests).
+// Returns the previous mode.
+int32_t ds_debug_set_hybrid(int32_t mode) {
+  const int old = ds::g_hybrid_mode;
+  if (mode >= 0 && mode <= 2) ds::g_hybrid_mode = mode;
   return old;
 }
 

@@ -417,6 +417,56 @@ def test_fused_decode_and_listed_repair_equal_separate_kernels(ds, n, desc):
         assert np.array_equal(sa.reshape(n, 10), col[want]), fused
 
 
+@pytest.mark.parametrize("n", [70_001, 400_003, 3_000_000])
+@pytest.mark.parametrize("desc", [False, True])
+def test_hybrid_bucket_plan_equals_arrow(ds, n, desc):
+    """10-byte keys through the hybrid plan (two global passes, then one CTA per 16-bit bucket:
+    two shared-memory passes + run repair + decode), forced for small n so that buckets are
+    tiny, empty, or unaligned in the output; against Arrow and against the all-global plan."""
+    L = ds._lib
+    rng = np.random.default_rng(n + desc)
+    col = rng.integers(0, 256, (n, 10), dtype=np.uint8)
+    for s in range(300):                      # ties on the leading 32 bits, and exact duplicates
+        rows = rng.choice(n, int(rng.integers(2, 10)), replace=False)
+        col[rows, :6] = col[rows[0], :6]
+        col[rows[-1]] = col[rows[0]]
+    col[rng.choice(n, 1500, replace=False), :2] = (5, 9)        # one well-filled bucket
+    col[col[:, 0] == 200, 0] = 201                               # 256 empty buckets in a row
+    want = _arrow_order(col, "fsb", desc)
+    old = L.lib.ds_debug_set_hybrid(2)
+    try:
+        L.lib.ds_debug_launch_count.restype = __import__("ctypes").c_uint64
+        launches0 = L.lib.ds_debug_launch_count()
+        a, sa = _argsort_c(ds, col, "fsb", desc, width=10)
+        launches = L.lib.ds_debug_launch_count() - launches0
+    finally:
+        L.lib.ds_debug_set_hybrid(old)
+    b, sb = _argsort_c(ds, col, "fsb", desc, width=10, options=L.DS_SORT_NO_HYBRID)
+    assert np.array_equal(a.astype(np.int64), want) and np.array_equal(a, b)
+    assert np.array_equal(sa, sb) and np.array_equal(sa.reshape(n, 10), col[want])
+    assert launches <= 12, launches            # sample, scan, encode, scan, 2 x (pass [+ ragged]), bounds, local
+
+
+def test_hybrid_bucket_plan_falls_back(ds):
+    """a bucket that does not fit a CTA, or a long run inside a bucket, sends the call back to
+    the all-global plan; the result is the same."""
+    L = ds._lib
+    n = 500_000
+    rng = np.random.default_rng(3)
+    for kind in ("bucket", "run"):
+        col = rng.integers(0, 256, (n, 10), dtype=np.uint8)
+        rows = rng.choice(n, 3000 if kind == "bucket" else 40, replace=False)
+        col[rows, :2 if kind == "bucket" else 5] = 77
+        want = _arrow_order(col, "fsb", False)
+        old = L.lib.ds_debug_set_hybrid(2)
+        try:
+            a, sa = _argsort_c(ds, col, "fsb", False, width=10)
+        finally:
+            L.lib.ds_debug_set_hybrid(old)
+        assert np.array_equal(a.astype(np.int64), want), kind
+        assert np.array_equal(sa.reshape(n, 10), col[want]), kind
+
+
 @pytest.mark.parametrize("width", [1, 8, 10, 90, 100])
 def test_scatter_rows_to_parts_c_abi(ds, width):
     """the fused map-side slicing kernel against numpy (local destinations; over NVLink it is
