@@ -1,9 +1,9 @@
 // Hybrid plan for 10-byte keys: two global onesweep passes on the two leading bytes leave the
 // rows grouped into 65536 buckets (about n / 65536 rows each, contiguous, input order kept
 // inside a bucket).  One CTA per bucket then finishes the job without further global passes:
-//   * two 8-bit counting-sort passes on key bits [32, 48) entirely in shared memory
-//     (same early-count + table-match ranking as onesweep_v3, no look-back, no global scatter),
-//   * repair of the short runs that still tie on the leading 32 bits, by the full key,
+//   * one counting sort on key bits [36, 48) (4096 bins for ~1500 rows) entirely in shared
+//     memory, positions handed out by shared-memory atomics,
+//   * ordering of the short runs of rows that share a bin by (full key, position on entry),
 //   * decode to the 10-byte key column and a coalesced store of keys and row ids.
 // This replaces two global passes, the repair kernel and the decode kernel of the plain
 // prefix plan.  A bucket that does not fit the CTA (skewed leading bytes) or a run longer than
@@ -17,7 +17,9 @@ constexpr int LS_ITEMS = 8;
 constexpr int LS_CAP = LS_THREADS * LS_ITEMS;  // rows a CTA can hold
 constexpr int LS_WARPS = LS_THREADS / 32;
 constexpr uint32_t LS_BUCKETS = 65536;
-constexpr int LS_SMEM_BYTES = LS_CAP * 14 + LS_CAP * 10 + 16;
+constexpr int LS_BINS = 4096;                  // bins of the CTA's counting sort ...
+constexpr int LS_BIN_SHIFT = 36;               // ... = key bits [36, 48)
+constexpr int LS_SMEM_BYTES = LS_CAP * 16 + LS_CAP * 10 + 16;
 
 // starts[b] = first row whose leading 16 bits are >= b, starts[65536] = n (empty buckets get the
 // next bucket's start).  `hi` is sorted by those bits.
@@ -58,17 +60,21 @@ __global__ void __launch_bounds__(LS_THREADS, 4)
                              const uint32_t* __restrict__ idx_in, const uint32_t* __restrict__ starts,
                              bool desc, uint8_t* __restrict__ keys_out, uint32_t* __restrict__ idx_out,
                              uint32_t* __restrict__ too_long) {
-  constexpr int LOW_SHIFT = 32;  // the CTA sorts bits [32, 48); bits [48, 64) are the bucket
-  extern __shared__ __align__(16) unsigned char ls_dyn[];     // LS_SMEM_BYTES (over the 48 KB static limit)
-  unsigned char* smem = ls_dyn;                                // histograms + tables, then the rows
-  uint8_t* stage = ls_dyn + LS_CAP * 14;                       // key bytes as they lie in the output
+  // The CTA's ~1500 rows are spread over LS_BINS bins by key bits [LS_BIN_SHIFT, 48) with one
+  // counting sort whose scatter takes positions from shared-memory atomics -- NOT stable, so
+  // every row also carries its position in the bucket (the stable order so far), and the runs
+  // of rows that share a bin (about a third of the rows, runs of 2-4) are then ordered by
+  // (full key, that position).  Rows of different bins never tie on the leading 32 bits' worth
+  // of order that the bins already decide, so the result is the stable full-key order.
+  extern __shared__ __align__(16) unsigned char ls_dyn[];  // LS_SMEM_BYTES (over the 48 KB static limit)
+  uint64_t* ex_hi = reinterpret_cast<uint64_t*>(ls_dyn);                    // rows by position
+  uint32_t* ex_idx = reinterpret_cast<uint32_t*>(ls_dyn + LS_CAP * 8);
+  uint16_t* ex_lo = reinterpret_cast<uint16_t*>(ls_dyn + LS_CAP * 12);
+  uint16_t* ex_pos = reinterpret_cast<uint16_t*>(ls_dyn + LS_CAP * 14);      // position in the bucket on entry
+  uint8_t* stage = ls_dyn + LS_CAP * 16;             // key bytes as they lie in the output ...
+  uint32_t* hist = reinterpret_cast<uint32_t*>(stage);  // ... and, before that, the bin counters
   __shared__ uint32_t s_warp_tot[LS_WARPS];
-  uint32_t* warp_hist = reinterpret_cast<uint32_t*>(smem);      // [WARPS][256]
-  uint32_t* match_tab = warp_hist + LS_WARPS * RADIX;            // [WARPS][2][256]
-  uint64_t* ex_hi = reinterpret_cast<uint64_t*>(smem);
-  uint32_t* ex_idx = reinterpret_cast<uint32_t*>(smem + LS_CAP * 8);
-  uint16_t* ex_lo = reinterpret_cast<uint16_t*>(smem + LS_CAP * 12);
-  static_assert(LS_WARPS * RADIX * 4 * 3 <= LS_CAP * 14, "histograms and tables overlay the rows");
+  static_assert(LS_BINS * 4 <= LS_CAP * 10 + 16, "the bin counters overlay the staging buffer");
 
   const int tid = threadIdx.x;
   const int warp = tid >> 5;
@@ -82,7 +88,7 @@ __global__ void __launch_bounds__(LS_THREADS, 4)
   }
 
   uint64_t hi[LS_ITEMS];
-  uint32_t lo[LS_ITEMS], idx[LS_ITEMS], pos[LS_ITEMS];
+  uint32_t lo[LS_ITEMS], idx[LS_ITEMS];
   const uint32_t wofs = warp * 32 * LS_ITEMS + lane;
 #pragma unroll
   for (int i = 0; i < LS_ITEMS; ++i) {
@@ -97,116 +103,97 @@ __global__ void __launch_bounds__(LS_THREADS, 4)
       idx[i] = 0;
     }
   }
-
-  const uint32_t lt_mask = lanemask_lt();
-  const uint32_t lane_bit = 1u << lane;
-  uint32_t* wh = warp_hist + warp * RADIX;
-  volatile uint32_t* mt = match_tab + warp * 2 * RADIX;
-#pragma unroll 1
-  for (int pass = 0; pass < 2; ++pass) {
-    const int shift = LOW_SHIFT + 8 * pass;
-    for (int i = tid; i < LS_WARPS * RADIX * 3; i += LS_THREADS) warp_hist[i] = 0;
+  for (int i = tid; i < LS_BINS; i += LS_THREADS) hist[i] = 0;
+  __syncthreads();
+#pragma unroll
+  for (int i = 0; i < LS_ITEMS; ++i)
+    if (wofs + i * 32 < R) atomicAdd(&hist[static_cast<uint32_t>(hi[i] >> LS_BIN_SHIFT) & (LS_BINS - 1)], 1u);
+  __syncthreads();
+  {  // exclusive scan of the bin counts: LS_BINS / LS_THREADS consecutive bins per thread
+    constexpr int PER = LS_BINS / LS_THREADS;
+    uint32_t c[PER];
+    uint32_t sum = 0;
+#pragma unroll
+    for (int k = 0; k < PER; ++k) {
+      c[k] = hist[tid * PER + k];
+      sum += c[k];
+    }
+    uint32_t v = sum;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const uint32_t t = __shfl_up_sync(0xffffffffu, v, o);
+      if ((int)lane >= o) v += t;
+    }
+    if (lane == 31) s_warp_tot[warp] = v;
     __syncthreads();
-    // early counts
+    uint32_t run = v - sum;
+    for (int w = 0; w < warp; ++w) run += s_warp_tot[w];
 #pragma unroll
-    for (int i = 0; i < LS_ITEMS; ++i)
-      if (wofs + i * 32 < R) atomicAdd(&wh[static_cast<uint32_t>(hi[i] >> shift) & 255u], 1u);
-    __syncthreads();
-    // digit totals -> exclusive scan over the 256 digits -> per-warp running offsets
-    {
-      uint32_t sum = 0;
-#pragma unroll
-      for (int w = 0; w < LS_WARPS; ++w) sum += warp_hist[w * RADIX + tid];
-      uint32_t v = sum;
-#pragma unroll
-      for (int o = 1; o < 32; o <<= 1) {
-        const uint32_t t = __shfl_up_sync(0xffffffffu, v, o);
-        if ((int)lane >= o) v += t;
-      }
-      if (lane == 31) s_warp_tot[warp] = v;
-      __syncthreads();
-      uint32_t run = v - sum;
-      for (int w = 0; w < warp; ++w) run += s_warp_tot[w];
-#pragma unroll
-      for (int w = 0; w < LS_WARPS; ++w) {
-        const uint32_t c = warp_hist[w * RADIX + tid];
-        warp_hist[w * RADIX + tid] = run;
-        run += c;
-      }
-    }
-    __syncthreads();
-    // rank: peers of a digit through the per-warp table, the leader advances the warp's offset
-#pragma unroll
-    for (int i = 0; i < LS_ITEMS; ++i) {
-      const bool valid = wofs + i * 32 < R;
-      const uint32_t d = static_cast<uint32_t>(hi[i] >> shift) & 255u;
-      volatile uint32_t* slot = mt + (i & 1) * RADIX + d;
-      if (valid) atomicOr(const_cast<uint32_t*>(slot), lane_bit);
-      __syncwarp();
-      const uint32_t peers = valid ? *slot : lane_bit;
-      __syncwarp();
-      if (valid) *slot = 0;
-      const uint32_t lt = __popc(peers & lt_mask);
-      uint32_t base = 0;
-      if (valid && lt == 0) base = atomicAdd(&wh[d], __popc(peers));
-      base = __shfl_sync(0xffffffffu, base, __ffs(peers) - 1);
-      pos[i] = base + lt;
-    }
-    __syncthreads();  // histograms and tables are dead: the rows overlay them
-#pragma unroll
-    for (int i = 0; i < LS_ITEMS; ++i) {
-      if (wofs + i * 32 < R) {
-        ex_hi[pos[i]] = hi[i];
-        ex_idx[pos[i]] = idx[i];
-        ex_lo[pos[i]] = static_cast<uint16_t>(lo[i]);
-      }
-    }
-    __syncthreads();
-    if (pass == 0) {  // back to registers in position order for the second digit
-#pragma unroll
-      for (int i = 0; i < LS_ITEMS; ++i) {
-        const uint32_t lp = wofs + i * 32;
-        if (lp < R) {
-          hi[i] = ex_hi[lp];
-          lo[i] = ex_lo[lp];
-          idx[i] = ex_idx[lp];
-        }
-      }
-      __syncthreads();
-    }
-  }
-
-  // ---- rows are ordered by their leading 32 bits: order the runs that tie on them
-#pragma unroll 1
-  for (int i = 0; i < LS_ITEMS; ++i) {
-    const uint32_t p = tid + i * LS_THREADS;
-    if (p + 1 >= R) continue;
-    const uint64_t pfx = ex_hi[p] >> LOW_SHIFT;
-    if ((ex_hi[p + 1] >> LOW_SHIFT) != pfx) continue;             // singleton
-    if (p > 0 && (ex_hi[p - 1] >> LOW_SHIFT) == pfx) continue;    // not the head
-    uint32_t len = 2;
-    while (p + len < R && len <= REPAIR_MAX_RUN && (ex_hi[p + len] >> LOW_SHIFT) == pfx) ++len;
-    if (len > REPAIR_MAX_RUN) {
-      atomicOr(too_long, 1u);
-      continue;
-    }
-    for (uint32_t a = 1; a < len; ++a) {  // stable insertion sort inside shared memory
-      const uint64_t kh = ex_hi[p + a];
-      const uint16_t kl = ex_lo[p + a];
-      const uint32_t kx = ex_idx[p + a];
-      uint32_t b = a;
-      while (b > 0 && (ex_hi[p + b - 1] > kh || (ex_hi[p + b - 1] == kh && ex_lo[p + b - 1] > kl))) {
-        ex_hi[p + b] = ex_hi[p + b - 1];
-        ex_lo[p + b] = ex_lo[p + b - 1];
-        ex_idx[p + b] = ex_idx[p + b - 1];
-        --b;
-      }
-      ex_hi[p + b] = kh;
-      ex_lo[p + b] = kl;
-      ex_idx[p + b] = kx;
+    for (int k = 0; k < PER; ++k) {
+      hist[tid * PER + k] = run;
+      run += c[k];
     }
   }
   __syncthreads();
+#pragma unroll
+  for (int i = 0; i < LS_ITEMS; ++i) {
+    const uint32_t lp = wofs + i * 32;
+    if (lp < R) {
+      const uint32_t p = atomicAdd(&hist[static_cast<uint32_t>(hi[i] >> LS_BIN_SHIFT) & (LS_BINS - 1)], 1u);
+      ex_hi[p] = hi[i];
+      ex_idx[p] = idx[i];
+      ex_lo[p] = static_cast<uint16_t>(lo[i]);
+      ex_pos[p] = static_cast<uint16_t>(lp);
+    }
+  }
+  __syncthreads();
+
+  // ---- order the runs of rows that share a bin by (key, position on entry)
+  {
+    uint32_t heads = 0;
+#pragma unroll
+    for (int i = 0; i < LS_ITEMS; ++i) {  // all shared-memory reads of the head test in flight at once
+      const uint32_t p = tid + i * LS_THREADS;
+      const uint64_t mine = p < R ? ex_hi[p] >> LS_BIN_SHIFT : 0;
+      const uint64_t next = p + 1 < R ? ex_hi[p + 1] >> LS_BIN_SHIFT : ~0ull;
+      const uint64_t prev = (p > 0 && p < R) ? ex_hi[p - 1] >> LS_BIN_SHIFT : ~0ull;
+      if (p + 1 < R && next == mine && prev != mine) heads |= 1u << i;
+    }
+    while (heads) {
+      const int i = __ffs(heads) - 1;
+      heads &= heads - 1;
+      const uint32_t p = tid + i * LS_THREADS;
+      const uint64_t bin = ex_hi[p] >> LS_BIN_SHIFT;
+      uint32_t len = 2;
+      while (p + len < R && len <= REPAIR_MAX_RUN && (ex_hi[p + len] >> LS_BIN_SHIFT) == bin) ++len;
+      if (len > REPAIR_MAX_RUN) {
+        atomicOr(too_long, 1u);
+        continue;
+      }
+      for (uint32_t a = 1; a < len; ++a) {  // insertion sort inside shared memory
+        const uint64_t kh = ex_hi[p + a];
+        const uint32_t kl = (static_cast<uint32_t>(ex_lo[p + a]) << 16) | ex_pos[p + a];  // (lo, position)
+        const uint32_t kx = ex_idx[p + a];
+        uint32_t b = a;
+        while (b > 0) {
+          const uint64_t qh = ex_hi[p + b - 1];
+          if (qh < kh) break;
+          const uint32_t ql = (static_cast<uint32_t>(ex_lo[p + b - 1]) << 16) | ex_pos[p + b - 1];
+          if (qh == kh && ql < kl) break;
+          ex_hi[p + b] = qh;
+          ex_lo[p + b] = static_cast<uint16_t>(ql >> 16);
+          ex_pos[p + b] = static_cast<uint16_t>(ql);
+          ex_idx[p + b] = ex_idx[p + b - 1];
+          --b;
+        }
+        ex_hi[p + b] = kh;
+        ex_lo[p + b] = static_cast<uint16_t>(kl >> 16);
+        ex_pos[p + b] = static_cast<uint16_t>(kl);
+        ex_idx[p + b] = kx;
+      }
+    }
+  }
+  __syncthreads();  // also: the bin counters are dead, the staging buffer may overwrite them
 
   // ---- decode into the staging buffer laid out like the output, then coalesced stores
   const uint64_t out_byte = static_cast<uint64_t>(s) * 10u;
