@@ -1,4 +1,4 @@
-// Hybrid plan for 10-byte keys: two global onesweep passes on the two leading bytes leave the
+// Hybrid plan (10-byte keys and 64-bit keys): two global onesweep passes on the two leading bytes leave the
 // rows grouped into 65536 buckets (about n / 65536 rows each, contiguous, input order kept
 // inside a bucket).  One CTA per bucket then finishes the job without further global passes:
 //   * one counting sort on key bits [36, 48) (4096 bins for ~1500 rows) entirely in shared
@@ -55,11 +55,18 @@ __global__ void __launch_bounds__(256)
   }
 }
 
+// OUT: what is written besides the row ids -- LS_OUT_FSB10: the 10-byte key column (HAS_LO);
+// LS_OUT_I64 / LS_OUT_U64: the 64-bit key column decoded from `hi`; LS_OUT_NONE: nothing
+// (permutations; float64 keys, whose column is gathered by the caller).
+enum { LS_OUT_NONE = 0, LS_OUT_FSB10 = 1, LS_OUT_I64 = 2, LS_OUT_U64 = 3 };
+
+template <bool HAS_LO, int OUT>
 __global__ void __launch_bounds__(LS_THREADS, 4)
     bucket_local_sort_kernel(const uint64_t* __restrict__ hi_in, const uint16_t* __restrict__ lo_in,
                              const uint32_t* __restrict__ idx_in, const uint32_t* __restrict__ starts,
                              bool desc, uint8_t* __restrict__ keys_out, uint32_t* __restrict__ idx_out,
                              uint32_t* __restrict__ too_long) {
+  static_assert(OUT != LS_OUT_FSB10 || HAS_LO, "10-byte keys carry their last two bytes in lo");
   // The CTA's ~1500 rows are spread over LS_BINS bins by key bits [LS_BIN_SHIFT, 48) with one
   // counting sort whose scatter takes positions from shared-memory atomics -- NOT stable, so
   // every row also carries its position in the bucket (the stable order so far), and the runs
@@ -95,7 +102,7 @@ __global__ void __launch_bounds__(LS_THREADS, 4)
     const uint32_t lp = wofs + i * 32;
     if (lp < R) {
       hi[i] = ld_stream(hi_in + s + lp);
-      lo[i] = ld_stream(lo_in + s + lp);
+      lo[i] = HAS_LO ? ld_stream(lo_in + s + lp) : 0;
       idx[i] = ld_stream(idx_in + s + lp);
     } else {
       hi[i] = 0;
@@ -142,7 +149,7 @@ __global__ void __launch_bounds__(LS_THREADS, 4)
       const uint32_t p = atomicAdd(&hist[static_cast<uint32_t>(hi[i] >> LS_BIN_SHIFT) & (LS_BINS - 1)], 1u);
       ex_hi[p] = hi[i];
       ex_idx[p] = idx[i];
-      ex_lo[p] = static_cast<uint16_t>(lo[i]);
+      if (HAS_LO) ex_lo[p] = static_cast<uint16_t>(lo[i]);
       ex_pos[p] = static_cast<uint16_t>(lp);
     }
   }
@@ -172,22 +179,22 @@ __global__ void __launch_bounds__(LS_THREADS, 4)
       }
       for (uint32_t a = 1; a < len; ++a) {  // insertion sort inside shared memory
         const uint64_t kh = ex_hi[p + a];
-        const uint32_t kl = (static_cast<uint32_t>(ex_lo[p + a]) << 16) | ex_pos[p + a];  // (lo, position)
+        const uint32_t kl = ((HAS_LO ? static_cast<uint32_t>(ex_lo[p + a]) : 0u) << 16) | ex_pos[p + a];  // (lo, position)
         const uint32_t kx = ex_idx[p + a];
         uint32_t b = a;
         while (b > 0) {
           const uint64_t qh = ex_hi[p + b - 1];
           if (qh < kh) break;
-          const uint32_t ql = (static_cast<uint32_t>(ex_lo[p + b - 1]) << 16) | ex_pos[p + b - 1];
+          const uint32_t ql = ((HAS_LO ? static_cast<uint32_t>(ex_lo[p + b - 1]) : 0u) << 16) | ex_pos[p + b - 1];
           if (qh == kh && ql < kl) break;
           ex_hi[p + b] = qh;
-          ex_lo[p + b] = static_cast<uint16_t>(ql >> 16);
+          if (HAS_LO) ex_lo[p + b] = static_cast<uint16_t>(ql >> 16);
           ex_pos[p + b] = static_cast<uint16_t>(ql);
           ex_idx[p + b] = ex_idx[p + b - 1];
           --b;
         }
         ex_hi[p + b] = kh;
-        ex_lo[p + b] = static_cast<uint16_t>(kl >> 16);
+        if (HAS_LO) ex_lo[p + b] = static_cast<uint16_t>(kl >> 16);
         ex_pos[p + b] = static_cast<uint16_t>(kl);
         ex_idx[p + b] = kx;
       }
@@ -195,6 +202,18 @@ __global__ void __launch_bounds__(LS_THREADS, 4)
   }
   __syncthreads();  // also: the bin counters are dead, the staging buffer may overwrite them
 
+  if (OUT != LS_OUT_FSB10) {  // 64-bit keys (or none): plain coalesced stores
+#pragma unroll
+    for (int i = 0; i < LS_ITEMS; ++i) {
+      const uint32_t p = tid + i * LS_THREADS;
+      if (p < R) {
+        idx_out[s + p] = ex_idx[p];
+        if (OUT == LS_OUT_I64) reinterpret_cast<int64_t*>(keys_out)[s + p] = dec_i64(ex_hi[p], desc);
+        if (OUT == LS_OUT_U64) reinterpret_cast<uint64_t*>(keys_out)[s + p] = desc ? ~ex_hi[p] : ex_hi[p];
+      }
+    }
+    return;
+  }
   // ---- decode into the staging buffer laid out like the output, then coalesced stores
   const uint64_t out_byte = static_cast<uint64_t>(s) * 10u;
   const uint32_t mis = static_cast<uint32_t>(out_byte & 15u);  // even: rows are 10 bytes

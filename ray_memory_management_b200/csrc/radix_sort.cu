@@ -934,8 +934,10 @@ static ds_status sort_indices_impl(int kind, const void* col, uint32_t width, ui
     }
     // hybrid plan (bucket_sort.cuh): 10-byte keys whose two leading bytes spread evenly and
     // whose 65536 buckets would fill a CTA reasonably (400..1650 rows on average)
-    if (kind == KIND_FSB && width == 10 && sorted_out != nullptr && g_hybrid_mode != 0 &&
-        !(options & DS_SORT_NO_HYBRID) && (reinterpret_cast<uintptr_t>(sorted_out) & 15) == 0 &&
+    const bool fsb10 = kind == KIND_FSB && width == 10 && sorted_out != nullptr &&
+                       (reinterpret_cast<uintptr_t>(sorted_out) & 15) == 0;
+    const bool key64 = kind != KIND_FSB;  // i64 / u64 / f64 / Philox: the whole key is `hi`
+    if ((fsb10 || key64) && g_hybrid_mode != 0 && !(options & DS_SORT_NO_HYBRID) &&
         (n >= 400u * LS_BUCKETS || g_hybrid_mode == 2) && n <= 1650u * LS_BUCKETS) {
       const float lim = 1.25f / 256.0f;
       hybrid = coll_h[pl.count - 1] <= lim && coll_h[pl.count - 2] <= lim;
@@ -1006,14 +1008,30 @@ static ds_status sort_indices_impl(int kind, const void* col, uint32_t width, ui
   if (hybrid) {
     // lookback is dead after the passes: its head holds the 65537 bucket starts
     uint32_t* starts = lookback;
-    static unsigned long long attr_done = 0;
-    DS_CUDA(set_smem_attr(bucket_local_sort_kernel, LS_SMEM_BYTES, &attr_done));
     ds::note_launch();
     bucket_bounds_kernel<<<(n + 1023) / 1024, 256, 0, s>>>(hi[cur], n, starts);
     DS_LAUNCH_CHECK();
-    ds::note_launch();
-    bucket_local_sort_kernel<<<LS_BUCKETS, LS_THREADS, LS_SMEM_BYTES, s>>>(
-        hi[cur], lo[cur], idx_src, starts, desc, static_cast<uint8_t*>(sorted_out), idx_out, too_long);
+    int out_kind = LS_OUT_NONE;  // float64 keys: the caller's gather below produces the column
+    if (sorted_out != nullptr) {
+      if (kind == KIND_FSB) out_kind = LS_OUT_FSB10;
+      if (kind == KIND_I64) out_kind = LS_OUT_I64;
+      if (kind == KIND_U64) out_kind = LS_OUT_U64;
+    }
+    static unsigned long long attr_done[4] = {0, 0, 0, 0};
+#define DS_BUCKET_LAUNCH(HL, OUT)                                                                      \
+  do {                                                                                                 \
+    DS_CUDA(set_smem_attr(bucket_local_sort_kernel<HL, OUT>, LS_SMEM_BYTES, &attr_done[OUT]));         \
+    ds::note_launch();                                                                                 \
+    bucket_local_sort_kernel<HL, OUT><<<LS_BUCKETS, LS_THREADS, LS_SMEM_BYTES, s>>>(                   \
+        hi[cur], lo[cur], idx_src, starts, desc, static_cast<uint8_t*>(sorted_out), idx_out, too_long); \
+  } while (0)
+    switch (out_kind) {
+      case LS_OUT_FSB10: DS_BUCKET_LAUNCH(true, LS_OUT_FSB10); break;
+      case LS_OUT_I64: DS_BUCKET_LAUNCH(false, LS_OUT_I64); break;
+      case LS_OUT_U64: DS_BUCKET_LAUNCH(false, LS_OUT_U64); break;
+      default: DS_BUCKET_LAUNCH(false, LS_OUT_NONE); break;
+    }
+#undef DS_BUCKET_LAUNCH
     DS_LAUNCH_CHECK();
     uint32_t flag = 0;
     DS_CUDA(cudaMemcpyAsync(&flag, too_long, sizeof(flag), cudaMemcpyDeviceToHost, s));
@@ -1021,6 +1039,7 @@ static ds_status sort_indices_impl(int kind, const void* col, uint32_t width, ui
     if (flag)  // a bucket or a run did not fit: the all-global prefix plan handles any data
       return sort_indices_impl(kind, col, width, n64, descending, idx_out, sorted_out,
                                options | DS_SORT_NO_HYBRID, ws, ws_bytes, stream, fn, seed, subseq);
+    if (kind == KIND_F64 && sorted_out != nullptr) return gather_rows_impl(col, 8, n, idx_out, n, sorted_out, s);
     return DS_OK;
   }
   const bool fused_decode = prefix_shift >= 0 && kind == KIND_FSB && width == 10 && sorted_out != nullptr &&

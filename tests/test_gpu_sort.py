@@ -447,6 +447,45 @@ def test_hybrid_bucket_plan_equals_arrow(ds, n, desc):
     assert launches <= 12, launches            # sample, scan, encode, scan, 2 x (pass [+ ragged]), bounds, local
 
 
+@pytest.mark.parametrize("desc", [False, True])
+def test_hybrid_bucket_plan_64bit_keys(ds, desc):
+    """the same plan for keys that are one 64-bit word: int64, uint64, float64 (finite, from
+    random bit patterns so that the leading bytes spread) and the Philox permutation keys."""
+    L = ds._lib
+    n = 300_007
+    rng = np.random.default_rng(21 + desc)
+    bits = rng.integers(-(2**63), 2**63 - 1, n, dtype=np.int64)
+    for g in range(300):                                   # groups of equal keys: stability
+        rows = rng.choice(n, int(rng.integers(2, 9)), replace=False)
+        bits[rows] = bits[rows[0]]
+    f = bits.view(np.float64).copy()
+    bad = ~np.isfinite(f)
+    f[bad] = np.arange(bad.sum()) + 0.5                    # distinct, so no long run of equal keys
+    cases = {"i64": bits, "u64": bits.view(np.uint64), "f64": f}
+    stream = torch.cuda.current_stream().cuda_stream
+    old = L.lib.ds_debug_set_hybrid(2)
+    try:
+        for kind, col in cases.items():
+            a, sa = _argsort_c(ds, col, kind, desc)
+            b, sb = _argsort_c(ds, col, kind, desc, options=L.DS_SORT_NO_HYBRID)
+            assert np.array_equal(a.astype(np.int64), _arrow_order(col, kind, desc)), kind
+            assert np.array_equal(a, b) and np.array_equal(sa, sb), kind
+            assert np.array_equal(sa.view(col.dtype), col[a.astype(np.int64)]), kind
+        perms = []
+        for mode in (2, 0):
+            L.lib.ds_debug_set_hybrid(mode)
+            perm = torch.empty(n, dtype=torch.int32, device="cuda")
+            ws = L.call_ws("ds_random_permutation", lambda nb: torch.empty(nb, dtype=torch.uint8, device="cuda"),
+                           1234, 7, n, perm.data_ptr(), stream=stream)
+            torch.cuda.synchronize()
+            del ws
+            perms.append(perm.cpu().numpy())
+        assert np.array_equal(perms[0], perms[1])
+        assert np.array_equal(np.sort(perms[0]), np.arange(n))
+    finally:
+        L.lib.ds_debug_set_hybrid(old)
+
+
 def test_hybrid_bucket_plan_falls_back(ds):
     """a bucket that does not fit a CTA, or a long run inside a bucket, sends the call back to
     the all-global plan; the result is the same."""
