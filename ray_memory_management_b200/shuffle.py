@@ -58,7 +58,10 @@ class DeviceShufflePlan(ShuffleOp):
         # With the reference's default of ~76 blocks for 10 M rows this is the difference
         # between ~100 ms of launch overhead and one 1 ms sort.
         fused = getattr(self, "fused", None)
-        if fused is not None and DatasetContext.get_current().fuse_device_blocks and input_num_blocks > 1:
+        # (an op whose map + reduce over ONE block still does redundant work -- random_shuffle
+        # permutes on both sides -- asks for the fused form from one block on)
+        min_blocks = 1 if getattr(self, "fuse_single_block", False) else 2
+        if fused is not None and DatasetContext.get_current().fuse_device_blocks and input_num_blocks >= min_blocks:
             stats = BlockExecStats.builder()
             res = fused(input_blocks_list, output_num_blocks, *self._map_args)
             if res is not None:

@@ -74,6 +74,9 @@ class _ShufflePartitionOp(ShuffleOp):
 
 
 class DeviceShufflePartitionOp(_ShufflePartitionOp, DeviceShufflePlan):
+    # one block: the map side's and the reduce side's permutation compose to one permutation
+    fuse_single_block = True
+
     @staticmethod
     def fused(blocks: List[Block], output_num_blocks: int, block_udf, random_shuffle: bool,
               random_seed: Optional[int]):
