@@ -73,11 +73,13 @@ __global__ void __launch_bounds__(LS_THREADS, 4)
   // of rows that share a bin (about a third of the rows, runs of 2-4) are then ordered by
   // (full key, that position).  Rows of different bins never tie on the leading 32 bits' worth
   // of order that the bins already decide, so the result is the stable full-key order.
+  // Shared-memory wavefronts are what bounds this kernel (ncu: l1tex 91 % busy, half of the
+  // wavefronts bank conflicts), so a row is two 8-byte words -- the key's hi word and a meta
+  // word (lo:16 | entry position:16 | row id:32, compared as one integer it orders by (lo,
+  // position)) -- which halves the scattered stores and the moves of the insertion sort.
   extern __shared__ __align__(16) unsigned char ls_dyn[];  // LS_SMEM_BYTES (over the 48 KB static limit)
-  uint64_t* ex_hi = reinterpret_cast<uint64_t*>(ls_dyn);                    // rows by position
-  uint32_t* ex_idx = reinterpret_cast<uint32_t*>(ls_dyn + LS_CAP * 8);
-  uint16_t* ex_lo = reinterpret_cast<uint16_t*>(ls_dyn + LS_CAP * 12);
-  uint16_t* ex_pos = reinterpret_cast<uint16_t*>(ls_dyn + LS_CAP * 14);      // position in the bucket on entry
+  uint64_t* ex_hi = reinterpret_cast<uint64_t*>(ls_dyn);                  // rows by position
+  uint64_t* ex_meta = reinterpret_cast<uint64_t*>(ls_dyn + LS_CAP * 8);
   uint8_t* stage = ls_dyn + LS_CAP * 16;             // key bytes as they lie in the output ...
   uint32_t* hist = reinterpret_cast<uint32_t*>(stage);  // ... and, before that, the bin counters
   __shared__ uint32_t s_warp_tot[LS_WARPS];
@@ -94,20 +96,18 @@ __global__ void __launch_bounds__(LS_THREADS, 4)
     return;
   }
 
-  uint64_t hi[LS_ITEMS];
-  uint32_t lo[LS_ITEMS], idx[LS_ITEMS];
+  uint64_t hi[LS_ITEMS], meta[LS_ITEMS];
   const uint32_t wofs = warp * 32 * LS_ITEMS + lane;
 #pragma unroll
   for (int i = 0; i < LS_ITEMS; ++i) {
     const uint32_t lp = wofs + i * 32;
     if (lp < R) {
       hi[i] = ld_stream(hi_in + s + lp);
-      lo[i] = HAS_LO ? ld_stream(lo_in + s + lp) : 0;
-      idx[i] = ld_stream(idx_in + s + lp);
+      const uint64_t l = HAS_LO ? ld_stream(lo_in + s + lp) : 0;
+      meta[i] = (l << 48) | (static_cast<uint64_t>(lp) << 32) | ld_stream(idx_in + s + lp);
     } else {
       hi[i] = 0;
-      lo[i] = 0;
-      idx[i] = 0;
+      meta[i] = 0;
     }
   }
   for (int i = tid; i < LS_BINS; i += LS_THREADS) hist[i] = 0;
@@ -121,9 +121,10 @@ __global__ void __launch_bounds__(LS_THREADS, 4)
     uint32_t c[PER];
     uint32_t sum = 0;
 #pragma unroll
-    for (int k = 0; k < PER; ++k) {
-      c[k] = hist[tid * PER + k];
-      sum += c[k];
+    for (int k = 0; k < PER; k += 4) {
+      const uint4 q = *reinterpret_cast<const uint4*>(hist + tid * PER + k);
+      c[k] = q.x; c[k + 1] = q.y; c[k + 2] = q.z; c[k + 3] = q.w;
+      sum += q.x + q.y + q.z + q.w;
     }
     uint32_t v = sum;
 #pragma unroll
@@ -136,34 +137,40 @@ __global__ void __launch_bounds__(LS_THREADS, 4)
     uint32_t run = v - sum;
     for (int w = 0; w < warp; ++w) run += s_warp_tot[w];
 #pragma unroll
-    for (int k = 0; k < PER; ++k) {
-      hist[tid * PER + k] = run;
-      run += c[k];
+    for (int k = 0; k < PER; k += 4) {
+      uint4 q;
+      q.x = run; run += c[k];
+      q.y = run; run += c[k + 1];
+      q.z = run; run += c[k + 2];
+      q.w = run; run += c[k + 3];
+      *reinterpret_cast<uint4*>(hist + tid * PER + k) = q;
     }
   }
   __syncthreads();
 #pragma unroll
   for (int i = 0; i < LS_ITEMS; ++i) {
-    const uint32_t lp = wofs + i * 32;
-    if (lp < R) {
+    if (wofs + i * 32 < R) {
       const uint32_t p = atomicAdd(&hist[static_cast<uint32_t>(hi[i] >> LS_BIN_SHIFT) & (LS_BINS - 1)], 1u);
       ex_hi[p] = hi[i];
-      ex_idx[p] = idx[i];
-      if (HAS_LO) ex_lo[p] = static_cast<uint16_t>(lo[i]);
-      ex_pos[p] = static_cast<uint16_t>(lp);
+      ex_meta[p] = meta[i];
     }
   }
   __syncthreads();
 
-  // ---- order the runs of rows that share a bin by (key, position on entry)
+  // ---- order the runs of rows that share a bin by (key, position on entry): the thread that
+  // holds a run's first row sorts it by insertion.  (Letting every member count its rank and
+  // move after a barrier was measured slower: 1.41 against 1.20 ms.)
   {
     uint32_t heads = 0;
 #pragma unroll
-    for (int i = 0; i < LS_ITEMS; ++i) {  // all shared-memory reads of the head test in flight at once
+    for (int i = 0; i < LS_ITEMS; ++i) {  // one load per row; the neighbours' bins come by shuffle
       const uint32_t p = tid + i * LS_THREADS;
-      const uint64_t mine = p < R ? ex_hi[p] >> LS_BIN_SHIFT : 0;
-      const uint64_t next = p + 1 < R ? ex_hi[p + 1] >> LS_BIN_SHIFT : ~0ull;
-      const uint64_t prev = (p > 0 && p < R) ? ex_hi[p - 1] >> LS_BIN_SHIFT : ~0ull;
+      const uint32_t none = 0xffffffffu;   // bins have 28 bits
+      const uint32_t mine = p < R ? static_cast<uint32_t>(ex_hi[p] >> LS_BIN_SHIFT) : none;
+      uint32_t next = __shfl_down_sync(0xffffffffu, mine, 1);
+      uint32_t prev = __shfl_up_sync(0xffffffffu, mine, 1);
+      if (lane == 31) next = p + 1 < R ? static_cast<uint32_t>(ex_hi[p + 1] >> LS_BIN_SHIFT) : none;
+      if (lane == 0) prev = (p > 0 && p < R) ? static_cast<uint32_t>(ex_hi[p - 1] >> LS_BIN_SHIFT) : none;
       if (p + 1 < R && next == mine && prev != mine) heads |= 1u << i;
     }
     while (heads) {
@@ -179,24 +186,19 @@ __global__ void __launch_bounds__(LS_THREADS, 4)
       }
       for (uint32_t a = 1; a < len; ++a) {  // insertion sort inside shared memory
         const uint64_t kh = ex_hi[p + a];
-        const uint32_t kl = ((HAS_LO ? static_cast<uint32_t>(ex_lo[p + a]) : 0u) << 16) | ex_pos[p + a];  // (lo, position)
-        const uint32_t kx = ex_idx[p + a];
+        const uint64_t km = ex_meta[p + a];
         uint32_t b = a;
         while (b > 0) {
           const uint64_t qh = ex_hi[p + b - 1];
           if (qh < kh) break;
-          const uint32_t ql = ((HAS_LO ? static_cast<uint32_t>(ex_lo[p + b - 1]) : 0u) << 16) | ex_pos[p + b - 1];
-          if (qh == kh && ql < kl) break;
+          const uint64_t qm = ex_meta[p + b - 1];
+          if (qh == kh && (qm >> 32) < (km >> 32)) break;
           ex_hi[p + b] = qh;
-          if (HAS_LO) ex_lo[p + b] = static_cast<uint16_t>(ql >> 16);
-          ex_pos[p + b] = static_cast<uint16_t>(ql);
-          ex_idx[p + b] = ex_idx[p + b - 1];
+          ex_meta[p + b] = qm;
           --b;
         }
         ex_hi[p + b] = kh;
-        if (HAS_LO) ex_lo[p + b] = static_cast<uint16_t>(kl >> 16);
-        ex_pos[p + b] = static_cast<uint16_t>(kl);
-        ex_idx[p + b] = kx;
+        ex_meta[p + b] = km;
       }
     }
   }
@@ -207,30 +209,38 @@ __global__ void __launch_bounds__(LS_THREADS, 4)
     for (int i = 0; i < LS_ITEMS; ++i) {
       const uint32_t p = tid + i * LS_THREADS;
       if (p < R) {
-        idx_out[s + p] = ex_idx[p];
+        idx_out[s + p] = static_cast<uint32_t>(ex_meta[p]);
         if (OUT == LS_OUT_I64) reinterpret_cast<int64_t*>(keys_out)[s + p] = dec_i64(ex_hi[p], desc);
         if (OUT == LS_OUT_U64) reinterpret_cast<uint64_t*>(keys_out)[s + p] = desc ? ~ex_hi[p] : ex_hi[p];
       }
     }
     return;
   }
-  // ---- decode into the staging buffer laid out like the output, then coalesced stores
+  // ---- decode into the staging buffer laid out like the output, then coalesced stores.
+  // A row's 10 bytes start on an even address: two 4-byte stores and one 2-byte store, in
+  // the order its alignment allows.
   const uint64_t out_byte = static_cast<uint64_t>(s) * 10u;
   const uint32_t mis = static_cast<uint32_t>(out_byte & 15u);  // even: rows are 10 bytes
 #pragma unroll
   for (int i = 0; i < LS_ITEMS; ++i) {
     const uint32_t p = tid + i * LS_THREADS;
     if (p < R) {
+      const uint64_t m = ex_meta[p];
       const uint64_t hh = desc ? ~ex_hi[p] : ex_hi[p];
-      const uint32_t ll = (desc ? ~static_cast<uint32_t>(ex_lo[p]) : ex_lo[p]) & 0xffffu;
-      const uint64_t be = bswap64(hh);
-      uint16_t* q = reinterpret_cast<uint16_t*>(stage + mis + p * 10u);
-      q[0] = static_cast<uint16_t>(be);
-      q[1] = static_cast<uint16_t>(be >> 16);
-      q[2] = static_cast<uint16_t>(be >> 32);
-      q[3] = static_cast<uint16_t>(be >> 48);
-      q[4] = static_cast<uint16_t>((ll >> 8) | ((ll & 0xffu) << 8));
-      idx_out[s + p] = ex_idx[p];
+      const uint32_t ll = static_cast<uint32_t>((desc ? ~m : m) >> 48);
+      const uint64_t be = bswap64(hh);                                   // bytes 0..7 of the row
+      const uint32_t t2 = ((ll >> 8) | ((ll & 0xffu) << 8)) & 0xffffu;   // bytes 8..9
+      const uint32_t o = mis + p * 10u;
+      if ((o & 3u) == 0) {
+        *reinterpret_cast<uint32_t*>(stage + o) = static_cast<uint32_t>(be);
+        *reinterpret_cast<uint32_t*>(stage + o + 4) = static_cast<uint32_t>(be >> 32);
+        *reinterpret_cast<uint16_t*>(stage + o + 8) = static_cast<uint16_t>(t2);
+      } else {
+        *reinterpret_cast<uint16_t*>(stage + o) = static_cast<uint16_t>(be);
+        *reinterpret_cast<uint32_t*>(stage + o + 2) = static_cast<uint32_t>(be >> 16);
+        *reinterpret_cast<uint32_t*>(stage + o + 6) = static_cast<uint32_t>(be >> 48) | (t2 << 16);
+      }
+      idx_out[s + p] = static_cast<uint32_t>(m);
     }
   }
   __syncthreads();
