@@ -110,14 +110,17 @@ def splitters_from_samples(samples: np.ndarray, arrow_type: pa.DataType, world: 
     so its last partition is almost empty and the others are uneven ("splitter
     quality").  Output block sizes are not part of its contract -- only the concatenation
     is -- so the multi-GPU plan uses evenly spaced quantiles of 2048 samples per rank."""
-    from .sort import sort_samples
+    from .sort import fsb_order_statistics, sort_samples
 
     n, w = samples.shape
     if n == 0:
         return [None] * (world - 1)
+    picks = [min(n - 1, (i * n) // world) for i in range(1, world)]
+    if pa.types.is_fixed_size_binary(arrow_type):  # only the W-1 picked rows become Python objects
+        return fsb_order_statistics(np.ascontiguousarray(samples), picks)
     buf = pa.py_buffer(np.ascontiguousarray(samples).tobytes())
     srt = sort_samples(pa.Array.from_buffers(arrow_type, n, [None, buf]))
-    return [srt[min(n - 1, (i * n) // world)] for i in range(1, world)]
+    return [srt[i] for i in picks]
 
 
 # ----------------------------------------------------------------------------- peer-memory exchange

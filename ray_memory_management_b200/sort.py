@@ -78,6 +78,43 @@ def nearest_rank_positions(num_samples: int, num_reducers: int) -> List[int]:
     return [int(np.around((num_samples - 1) * q)) for q in qs][1:]
 
 
+def fsb_order(rows: np.ndarray) -> np.ndarray:
+    """Stable memcmp order of n fixed-width byte rows ((n, w) uint8): the rows are compared as
+    big-endian integers, 8 bytes at a time (least significant chunk first for lexsort)."""
+    n, w = rows.shape
+    keys = []
+    for b in range(0, w, 8):
+        chunk = np.zeros((n, 8), dtype=np.uint8)
+        chunk[:, : min(8, w - b)] = rows[:, b : b + 8]
+        keys.append(chunk.view(">u8").ravel())
+    return np.argsort(keys[0], kind="stable") if len(keys) == 1 else np.lexsort(tuple(reversed(keys)))
+
+
+def fsb_order_statistics(rows: np.ndarray, picks) -> list:
+    """rows[order][i] for i in picks, where order is the memcmp order of the (n, w <= 16) byte
+    rows, WITHOUT sorting them: a selection (np.partition) on the leading 8 bytes, then the
+    rank inside the group of rows that tie on those (the multi-GPU plan needs W-1 splitters
+    out of thousands of samples on every step)."""
+    n, w = rows.shape
+    if w > 16:
+        order = fsb_order(rows)
+        return [rows[order[i]].tobytes() for i in picks]
+    pad = np.zeros((n, 16), dtype=np.uint8)
+    pad[:, :w] = rows
+    hi = pad[:, :8].copy().view(">u8").ravel().astype(np.uint64)
+    lo = pad[:, 8:].copy().view(">u8").ravel().astype(np.uint64)
+    picks = [int(i) for i in picks]
+    by_hi = np.partition(hi, sorted(set(picks))) if picks else hi
+    out = []
+    for i in picks:
+        v = by_hi[i]
+        tie = lo[hi == v]
+        below = int(np.count_nonzero(hi < v))
+        l = np.partition(tie, i - below)[i - below] if len(tie) > 1 else tie[0]
+        out.append((int(v).to_bytes(8, "big") + int(l).to_bytes(8, "big"))[:w])
+    return out
+
+
 def sort_samples(samples: pa.Array) -> list:
     """Host sort of the few sampled keys (np.sort at sort.py:110); fixed_size_binary keys
     are ordered bytewise (memcmp), as Arrow orders them."""
@@ -87,8 +124,7 @@ def sort_samples(samples: pa.Array) -> list:
         w = t.byte_width
         raw = np.frombuffer(samples.buffers()[1], dtype=np.uint8)[samples.offset * w : (samples.offset + n) * w]
         rows = raw.reshape(n, w)
-        order = np.lexsort(tuple(rows[:, j] for j in range(w - 1, -1, -1)))
-        return [r.tobytes() for r in rows[order]]
+        return [r.tobytes() for r in rows[fsb_order(rows)]]
     if pa.types.is_temporal(t):  # splitters of temporal keys travel as their integer values
         samples = samples.cast(pa.int32() if t.bit_width == 32 else pa.int64())
     return list(np.sort(samples.to_numpy(zero_copy_only=False)))

@@ -194,3 +194,21 @@ def test_stats_summary_matches_reference():
     ref = _stats_chain(rs.DatasetStats, lambda parent, name: parent.child_builder(name)).summary_string()
     mine = _stats_chain(DatasetStats, lambda parent, name: DatasetStatsBuilder(name, parent)).summary_string()
     assert mine == ref
+
+
+# ------------------------------------------------------------------ splitter selection
+@pytest.mark.parametrize("w", [1, 2, 8, 9, 10, 16, 20])
+@pytest.mark.parametrize("spread", [3, 256])
+def test_fsb_order_statistics_equal_sorted_picks(w, spread):
+    """the multi-GPU plan picks its W-1 splitters by selection, not by sorting the samples:
+    the picks must be the same rows a full memcmp sort would give (heavy ties included)."""
+    from ray_memory_management_b200.sort import fsb_order, fsb_order_statistics
+
+    rng = np.random.default_rng(w * 1000 + spread)
+    rows = rng.integers(0, spread, (3000, w), dtype=np.uint8)
+    srt = sorted(r.tobytes() for r in rows)
+    picks = [0, 1, 374, 1499, 1500, 2999, 374]
+    assert fsb_order_statistics(rows, picks) == [srt[i] for i in picks]
+    order = fsb_order(rows)
+    assert [rows[i].tobytes() for i in order] == srt
+    assert all(order[i] < order[i + 1] for i in range(2999) if srt[i] == srt[i + 1])   # stable
