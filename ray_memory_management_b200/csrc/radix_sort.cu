@@ -880,6 +880,7 @@ static ds_status sort_indices_impl(int kind, const void* col, uint32_t width, ui
   uint32_t* idx_alt = w.take<uint32_t>(n);
   uint32_t* ctrl = w.take<uint32_t>(MAX_PASSES * RADIX * 2 + 4 * MAX_PASSES);
   uint32_t* lookback = w.take<uint32_t>(static_cast<size_t>(tiles) * RADIX);
+  uint32_t* bucket_starts = w.take<uint32_t>(LS_BUCKETS + 1);  // hybrid plan only (257 KB)
   ds_status st;
   if (ws_resolve(w, ws, ws_bytes, fn, &st)) return st;
   if (n == 0) return DS_OK;
@@ -1006,8 +1007,7 @@ static ds_status sort_indices_impl(int kind, const void* col, uint32_t width, ui
     cur ^= 1;
   }
   if (hybrid) {
-    // lookback is dead after the passes: its head holds the 65537 bucket starts
-    uint32_t* starts = lookback;
+    uint32_t* starts = bucket_starts;
     ds::note_launch();
     bucket_bounds_kernel<<<(n + 1023) / 1024, 256, 0, s>>>(hi[cur], n, starts);
     DS_LAUNCH_CHECK();
