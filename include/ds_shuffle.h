@@ -83,7 +83,11 @@ const char* ds_last_error(void);
  *                  histograms show that they separate almost all rows, then order the
  *                  remaining short runs of equal prefixes by the full key (verified on
  *                  device; a second 4-byte host sync; falls back to all passes if a run
- *                  is long).  The result is identical in every mode.
+ *                  is long).  Unless DS_SORT_NO_HYBRID is set, keys whose two leading bytes
+ *                  spread evenly (and 26 M <= n <= 108 M) run only those two digits as global
+ *                  passes and finish with one thread block per 16-bit bucket in shared
+ *                  memory (same verification, same fallback).  The result is identical in
+ *                  every mode.
  * float64 order: -inf < ... < -0.0 == 0.0 ... < +inf < NaN (NaNs last in ascending
  * and in descending order, like Arrow); -0.0 and 0.0 compare equal (stable). */
 ds_status ds_sort_indices_i64(const int64_t* col, uint64_t n, int32_t descending,
