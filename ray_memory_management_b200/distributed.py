@@ -266,14 +266,51 @@ def _key_width(block, col, group) -> Tuple[int, pa.DataType]:
 _VALID = "\x00valid"  # wire-name suffix of a column's validity bytes
 
 
-def _fixed_width_only(block, what: str) -> None:
-    """The peer-memory exchange moves rows of a fixed width; variable-length columns would
-    need a second exchange of byte counts and are single-GPU only for now."""
+_LEN = "\x00len"  # wire-name suffix of a variable-length column's row lengths
+
+
+def _fixed_width_only(block, what: str, key: Optional[str] = None, payload_ok: bool = False) -> List[str]:
+    """Variable-length columns: payload columns travel as a fixed-width wire of row lengths
+    plus one all-to-all-v of their bytes (``payload_ok``); a variable-length KEY would also
+    need variable-length splitters and samples on the wire and is single-GPU only for now.
+    Returns the names of the variable-length payload columns."""
+    names = []
     for name, c in block.columns.items():
-        if c.is_varlen:
-            raise NotImplementedError(
-                f"{what}: column {name!r} has the variable-length type {c.type}; the multi-GPU "
-                "exchange supports fixed-width columns only")
+        if not c.is_varlen:
+            continue
+        if payload_ok and name != key:
+            names.append(name)
+            continue
+        raise NotImplementedError(
+            f"{what}: column {name!r} has the variable-length type {c.type}; the multi-GPU "
+            "plans take variable-length columns as payload of sort / random_shuffle only")
+    return names
+
+
+def _varlen_send(whole, row_bounds: Sequence[int], dev):
+    """``whole``: a variable-length column in send order, partition d = rows
+    row_bounds[d]:row_bounds[d+1].  Returns (row lengths as an 8-byte-per-row wire, the bytes
+    in the same order, bytes per destination)."""
+    off = whole.offsets
+    lens = (off[1:] - off[:-1]).contiguous()
+    at = torch.as_tensor(list(row_bounds), dtype=torch.int64, device=dev)
+    byte_bounds = [int(x) for x in off[at].cpu().tolist()]  # host sync: W + 1 numbers
+    data = whole.data[byte_bounds[0]: byte_bounds[-1]]
+    return lens.view(torch.uint8), data, [byte_bounds[d + 1] - byte_bounds[d] for d in range(len(row_bounds) - 1)]
+
+
+def _varlen_recv(arrow_type, len_wire: torch.Tensor, n_recv: int, data, byte_counts, valid, group, dev):
+    """Received lengths (chunks of ranks 0..W-1 back to back) -> offsets; the bytes follow in
+    the same order through one all-to-all-v with byte granularity."""
+    from .block import DeviceVarColumn
+
+    lens = len_wire[: n_recv * 8].view(torch.int64)
+    offsets = torch.zeros(n_recv + 1, dtype=torch.int64, device=dev)
+    if n_recv:
+        torch.cumsum(lens, 0, out=offsets[1:])
+    bm = exchange_counts(byte_counts, group, dev)
+    recv, _ = alltoallv_rows(data.contiguous(), 1, bm, group)
+    return DeviceVarColumn(arrow_type, offsets, recv, valid, int(bm[:, dist.get_rank(group)].sum()))
 
 
 def _agree_on_validity(block, group, dev):
@@ -291,7 +328,7 @@ def _agree_on_validity(block, group, dev):
     cols = collections.OrderedDict()
     for (name, c), nd in zip(block.columns.items(), need):
         if nd and c.valid is None:
-            c = DeviceColumn(c.type, c.data, torch.ones(c.num_rows, dtype=torch.uint8, device=dev))
+            c = c.with_valid(torch.ones(c.num_rows, dtype=torch.uint8, device=dev))
         cols[name] = c
     return DeviceArrowBlock(cols, block.num_rows), {n for n, nd in zip(block.columns, need) if nd}
 
@@ -428,7 +465,7 @@ def sort_block(block, key: str, descending: bool = False, group=None, consume: b
     from .block import (DeviceArrowBlock, DeviceArrowBlockAccessor, DeviceColumn,
                         _argsort_nulls_last, _gather)
 
-    _fixed_width_only(block, "sort_block")
+    var_names = _fixed_width_only(block, "sort_block", key, payload_ok=True)
     world = dist.get_world_size(group)
     rank = dist.get_rank(group)
     dev = _dev()
@@ -456,7 +493,7 @@ def sort_block(block, key: str, descending: bool = False, group=None, consume: b
     acc = DeviceArrowBlockAccessor(block)
     sort_key = [(key, "descending" if descending else "ascending")]
     ph.mark("sample+splitters")
-    if _EXCHANGE == "fused" and 1 < world <= 16 and dist.get_backend(group) == "nccl":
+    if _EXCHANGE == "fused" and 1 < world <= 16 and dist.get_backend(group) == "nccl" and not var_names:
         out = _sort_block_fused(block, key, descending, boundaries, with_valid, group, ph, consume)
         if out is not None:
             return out
@@ -467,7 +504,25 @@ def sort_block(block, key: str, descending: bool = False, group=None, consume: b
         del acc
     ph.mark("partition")
     matrix = exchange_counts(counts, group, dev)
-    wires = _wire_columns(parts, names, with_valid, key, dev)
+    wires = _wire_columns(parts, [nm for nm in names if nm not in var_names], with_valid, key, dev)
+    var_send = {}
+    for nm in var_names:  # lengths ride with the fixed-width wires, the bytes follow below
+        from .block import DeviceVarColumn, _concat_varlen
+
+        pcs = [p.columns[nm] for p in parts if p.num_rows]
+        if not pcs:  # this rank holds no rows
+            whole = DeviceVarColumn(types[nm], torch.zeros(1, dtype=torch.int64, device=dev),
+                                    torch.empty(0, dtype=torch.uint8, device=dev),
+                                    torch.empty(0, dtype=torch.uint8, device=dev) if nm in with_valid else None)
+        elif len(pcs) == 1:
+            whole = pcs[0]
+        else:
+            whole = _concat_varlen(pcs, torch.cat([c.valid for c in pcs]) if nm in with_valid else None)
+        len_wire, data, byte_counts = _varlen_send(whole, np.concatenate([[0], np.cumsum(counts)]), dev)
+        wires.append((nm + _LEN, 8, len_wire))
+        if nm in with_valid:
+            wires.append((nm + _VALID, 1, whole.valid.contiguous()))
+        var_send[nm] = (data, byte_counts)
     del parts
     if consume:
         torch.cuda.empty_cache()
@@ -530,6 +585,13 @@ def sort_block(block, key: str, descending: bool = False, group=None, consume: b
         ph.mark("wait payload")
     cols = collections.OrderedDict()
     for name in names:
+        if name in var_names:
+            data, byte_counts = var_send[name]
+            v = recv.get(name + _VALID)
+            src = _varlen_recv(types[name], recv[name + _LEN], n_recv, data, byte_counts,
+                               v[:n_recv] if v is not None else None, group, dev)
+            cols[name] = _gather(src, idx)
+            continue
         cols[name] = sorted_key if name == key else _gather(column(name), idx)
     ph.mark("gather payload")
     ph.finish()
@@ -577,7 +639,7 @@ def random_shuffle_block(block, seed: Optional[int], group=None):
 
     from .block import DeviceArrowBlock, DeviceArrowBlockAccessor, DeviceColumn
 
-    _fixed_width_only(block, "random_shuffle_block")
+    var_names = _fixed_width_only(block, "random_shuffle_block", None, payload_ok=True)
     world = dist.get_world_size(group)
     rank = dist.get_rank(group)
     dev = _dev()
@@ -593,9 +655,18 @@ def random_shuffle_block(block, seed: Optional[int], group=None):
     matrix = exchange_counts(counts, group, dev)
     cols = collections.OrderedDict()
     wires = []
+    var_send = {}
     for name, c in shuffled.columns.items():
-        rb = c.row_bytes
-        wires.append((name, rb, torch.cat([c.data[slices[order[d]][0] * rb: slices[order[d]][1] * rb] for d in range(world)])))
+        if name in var_names:
+            from .block import _concat_varlen
+
+            whole = _concat_varlen([c.with_valid(None).slice(*slices[order[d]]) for d in range(world)], None)
+            len_wire, data, byte_counts = _varlen_send(whole, np.concatenate([[0], np.cumsum(counts)]), dev)
+            wires.append((name + _LEN, 8, len_wire))
+            var_send[name] = (data, byte_counts)
+        else:
+            rb = c.row_bytes
+            wires.append((name, rb, torch.cat([c.data[slices[order[d]][0] * rb: slices[order[d]][1] * rb] for d in range(world)])))
         if name in with_valid:
             wires.append((name + _VALID, 1, torch.cat([c.valid[slices[order[d]][0]: slices[order[d]][1]] for d in range(world)])))
     rbs = {w: rb for w, rb, _ in wires}
@@ -603,9 +674,16 @@ def random_shuffle_block(block, seed: Optional[int], group=None):
     recv = {}
     for w, rb, buf in wires:
         recv[w] = got[w] if got is not None else alltoallv_rows(buf, rb, matrix, group)[0]
+    n_recv = int(matrix[:, rank].sum())
     for name, c in shuffled.columns.items():
-        cols[name] = DeviceColumn(c.type, recv[name], recv.get(name + _VALID))
-    out = DeviceArrowBlock(cols, int(matrix[:, rank].sum()))
+        v = recv.get(name + _VALID)
+        if name in var_names:
+            data, byte_counts = var_send[name]
+            cols[name] = _varlen_recv(c.type, recv[name + _LEN], n_recv, data, byte_counts,
+                                      v[:n_recv].clone() if v is not None else None, group, dev)
+        else:
+            cols[name] = DeviceColumn(c.type, recv[name], v)
+    out = DeviceArrowBlock(cols, n_recv)
     # every reducer permutes with the same seed in the reference (:86-89); the
     # subsequence keeps the streams of different ranks apart without changing that contract
     return DeviceArrowBlockAccessor(out).random_shuffle(seed) if out.num_rows else out
@@ -616,7 +694,7 @@ def groupby_block(block, key: str, aggs, group=None):
     local sort + combine, range-partition the partial rows, exchange, merge + finalize."""
     from .block import DeviceArrowBlock, DeviceArrowBlockAccessor, DeviceColumn, PartialAggBlock, _searchsorted
 
-    _fixed_width_only(block, "groupby_block")
+    _fixed_width_only(block, "groupby_block", key)
     world = dist.get_world_size(group)
     rank = dist.get_rank(group)
     dev = _dev()

@@ -71,6 +71,31 @@ def main():
         want = O.global_stable_sort(inputs_n, "k", desc)
         assert got.equals(want), f"distributed sort with nulls mismatch desc={desc}"
 
+    # ---- variable-length payload columns (strings, with nulls on one rank) through sort and shuffle
+    words = ["r%d-%d-" % (rank, i) + "x" * int(i % 7) for i in range(30_000 + 500 * rank)]
+    smask = (rng.random(len(words)) < 0.1) if rank == 1 else None
+    ts = pa.table({"k": rng.integers(-500, 500, len(words), dtype=np.int64),
+                   "s": pa.array(words, pa.string(), mask=smask),
+                   "b": pa.array([w.encode()[::-1] for w in words], pa.large_binary())})
+    inputs_s = gather_tables(ts, rank, world)
+    for desc in (False, True):
+        out = D.sort_block(ds.DeviceArrowBlock.from_arrow(ts), "k", descending=desc)
+        got = pa.concat_tables(gather_tables(out.to_arrow(), rank, world))
+        want = O.global_stable_sort(inputs_s, "k", desc)
+        assert got.equals(want), f"distributed sort with string payload mismatch desc={desc}"
+    sh = D.random_shuffle_block(ds.DeviceArrowBlock.from_arrow(ts), 7)
+    gs = pa.concat_tables(gather_tables(sh.to_arrow(), rank, world))
+    alls = pa.concat_tables(inputs_s)
+    assert gs.num_rows == alls.num_rows
+    key = lambda tb: sorted(zip(tb["b"].to_pylist(), tb["k"].to_pylist(), tb["s"].to_pylist()),  # noqa: E731
+                            key=lambda r: r[0])
+    assert key(gs) == key(alls), "shuffle lost or mixed up variable-length rows"
+    try:
+        D.sort_block(ds.DeviceArrowBlock.from_arrow(ts), "s")
+        raise AssertionError("a variable-length key must be refused")
+    except NotImplementedError:
+        pass
+
     # ---- random_shuffle: permutation + determinism
     a = D.random_shuffle_block(ds.DeviceArrowBlock.from_arrow(ti), 42)
     b = D.random_shuffle_block(ds.DeviceArrowBlock.from_arrow(ti), 42)
