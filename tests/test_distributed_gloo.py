@@ -91,3 +91,50 @@ def test_two_rank_exchange_reproduces_global_stable_sort(descending):
     got_p = np.concatenate([r[4] for r in res])
     assert np.array_equal(got_k, O.fsb_to_numpy(want["key"]))
     assert np.array_equal(got_p, O.fsb_to_numpy(want["payload"]))  # ties keep (rank, row) order
+
+
+def _varlen_worker(rank, world, port, q):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    from ray_memory_management_b200 import distributed as D
+    from ray_memory_management_b200.block import DeviceVarColumn
+
+    # rows of this rank in send order: partition 0 first, then partition 1 (ragged, one empty string)
+    rows = [b"r%d-%d" % (rank, i) + b"x" * (i % 5) for i in range(7 + 3 * rank)] + [b""]
+    counts = [3 + rank, len(rows) - 3 - rank]
+    offs = np.concatenate([[0], np.cumsum([len(r) for r in rows])]).astype(np.int64) + 11   # a slice: offsets start at 11
+    data = np.frombuffer(b"\xee" * 11 + b"".join(rows), dtype=np.uint8).copy()
+    col = DeviceVarColumn(pa.binary(), torch.from_numpy(offs), torch.from_numpy(data))
+    len_wire, payload, byte_counts = D._varlen_send(col, np.concatenate([[0], np.cumsum(counts)]), "cpu")
+    assert byte_counts == [sum(len(r) for r in rows[: counts[0]]), sum(len(r) for r in rows[counts[0]:])]
+    matrix = D.exchange_counts(counts, None, None)
+    lens_recv, _ = D.alltoallv_rows(len_wire.clone(), 8, matrix)
+    n_recv = int(matrix[:, rank].sum())
+    got = D._varlen_recv(pa.binary(), lens_recv, n_recv, payload, byte_counts, None, None, "cpu")
+    o, d = got.offsets.numpy(), got.data.numpy().tobytes()
+    q.put((rank, rows, counts, [d[o[i]:o[i + 1]] for i in range(n_recv)]))
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def test_two_rank_variable_length_wire():
+    """row lengths on a fixed-width wire + byte-granular all-to-all-v rebuild the strings in
+    (source rank, row) order on the receiver."""
+    world, port = 2, _free_port()
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    procs = [ctx.Process(target=_varlen_worker, args=(r, world, port, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    res = sorted([q.get(timeout=120) for _ in range(world)], key=lambda x: x[0])
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    for dst in range(world):
+        want = []
+        for src in range(world):
+            rows, counts = res[src][1], res[src][2]
+            start = sum(counts[:dst])
+            want += rows[start:start + counts[dst]]
+        assert res[dst][3] == want
