@@ -9,11 +9,13 @@
 // threads read consecutive granules of the same source row.  Algorithmic bytes per
 // row: 4 (index) + 2*row_bytes.
 #include "ds_common.cuh"
+#include "gather_bulk.cuh"
 
 namespace ds {
 
-static int g_gather_mode = 0;  // 0 auto (= granules + L2::64B, the fastest measured), 1 plain, 2 plain + L2::64B, 3 staged,
-// 4 staged + L2::64B, 5 direct (no smem idx), 6 32-bit word path for rows of 4k+2 bytes.
+static int g_gather_mode = 0;  // 0 auto, 1 plain, 2 plain + L2::64B, 3 staged,
+// 4 staged + L2::64B, 5 direct (no smem idx), 6 32-bit word path for rows of 4k+2 bytes,
+// 7 asynchronous bulk copies per row (gather_bulk.cuh, UBLKCP), 8 the same with 16-byte cp.async.
 // Measured on 100 M x 90-byte rows (ms per sort step): 2: 10.46, 5: 11.0, 3: 12.7, 6: 14.0
 
 // Read-only loads that ask L2 to fetch only 64 bytes around a miss: random rows gain
@@ -524,7 +526,9 @@ ds_status gather_rows_impl(const void* src, uint32_t row_bytes, uint64_t src_row
   const uintptr_t bits = reinterpret_cast<uintptr_t>(src) | reinterpret_cast<uintptr_t>(dst) | row_bytes;
   cudaError_t e;
   LaunchTimer timer(TIMED_GATHER, s, static_cast<double>(n) * (4.0 + 2.0 * row_bytes));
-  if (g_gather_mode == 6 && (row_bytes & 3) == 2 && row_bytes >= 6 && row_bytes <= 4096 &&
+  if ((g_gather_mode == 7 || g_gather_mode == 8) && gather_bulk_eligible(src, row_bytes, src_rows, dst)) {
+    e = launch_gather_bulk(g_gather_mode == 7 ? FETCH_BULK : FETCH_LDGSTS, src, row_bytes, src_rows, idx, n, dst, s);
+  } else if (g_gather_mode == 6 && (row_bytes & 3) == 2 && row_bytes >= 6 && row_bytes <= 4096 &&
       src_rows > 0 && (reinterpret_cast<uintptr_t>(src) & 1) == 0 && (reinterpret_cast<uintptr_t>(dst) & 3) == 0) {
     uint32_t rows = (8192 * 2 / row_bytes) & ~1u;  // even: every block's span starts 4-byte aligned
     if (rows < 2) rows = 2;
@@ -613,6 +617,13 @@ extern "C" int32_t ds_debug_set_gather_mode(int32_t mode) {
   int old = ds::g_gather_mode;
   ds::g_gather_mode = mode;
   return old;
+}
+
+// Tuning hook for the asynchronous-copy gather: rows per tile, ring depth, CTAs per SM (0 = default).
+extern "C" void ds_debug_set_gather_bulk(uint32_t rows, uint32_t stages, uint32_t ctas_per_sm) {
+  ds::g_gb_rows = rows;
+  ds::g_gb_stages = stages;
+  ds::g_gb_ctas = ctas_per_sm;
 }
 
 // Tuning hook: cudaLimitMaxL2FetchGranularity of the current device (32 / 64 / 128).

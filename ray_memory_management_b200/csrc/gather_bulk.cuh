@@ -1,0 +1,242 @@
+// Row gather for even-sized rows that are not a multiple of 16 bytes (the 90-byte GraySort
+// payload), built on asynchronous copies instead of per-thread global loads and stores.
+//
+// A persistent CTA walks tiles of R output rows through a ring of STAGES shared-memory
+// stages.  For every source row it fetches the 16-byte-aligned span that covers the row
+// (W + misalignment rounded up to 16 bytes) into the row's slot of a stage:
+//   FETCH_BULK    one cp.async.bulk per row (SASS UBLKCP), completion counted on the stage's
+//                 mbarrier through expect_tx / complete_tx;
+//   FETCH_LDGSTS  16-byte cp.async chunks with a 64-byte L2 fetch hint (SASS LDGSTS),
+//                 consecutive lanes taking consecutive chunks of a row, completion by
+//                 cp.async groups.
+// While later stages are in flight, one thread per row copies the row from its slot, at
+// whatever 2-byte alignment it arrived with, into the tile's packed output image in shared
+// memory (aligned 32-bit words, byte_perm for the half-word shift), and the image leaves as
+// ONE bulk store (cp.async.bulk shared -> global).  Global memory therefore only sees aligned
+// 16-byte-multiple transfers issued by the SM's copy engine; the odd row alignment is
+// confined to shared memory, and a row costs ~70 instructions instead of the ~270 of the
+// per-granule kernels.  Rows whose aligned span would leave [src, src + src_bytes) (first /
+// last rows of the buffer) are fetched byte by byte.
+//
+// Algorithmic bytes per row: 4 (index) + 2 * W.
+#pragma once
+#include "ds_async.cuh"
+#include "ds_common.cuh"
+
+namespace ds {
+
+constexpr int GB_THREADS = 256;
+constexpr int GB_MAX_STAGES = 4;
+enum { FETCH_BULK = 0, FETCH_LDGSTS = 1 };
+
+struct GatherBulkPlan {
+  uint32_t rows;    // R: output rows per tile (multiple of 16, <= GB_THREADS)
+  uint32_t stages;  // ring depth
+  uint32_t slot;    // bytes of shared memory per fetched row (odd multiple of 16)
+  uint32_t chunks;  // 16-byte chunks per slot
+  uint32_t smem;    // dynamic shared memory per CTA
+  uint32_t ctas_per_sm;
+};
+
+__device__ __forceinline__ uint32_t gb_warp_sum(uint32_t v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+
+// Copies one row of W bytes (W even) between two locations of the CTA's dynamic shared memory
+// given as byte offsets from its 16-byte-aligned base, both 2-byte aligned: aligned 32-bit
+// stores, each word assembled from the two aligned source words that cover it.  May read (not
+// use) one aligned word past the row's last byte.
+__device__ __forceinline__ void copy_row_even(uint8_t* __restrict__ sm, uint32_t s, uint32_t d, uint32_t W) {
+  uint32_t left = W;
+  if (d & 2) {  // leading half word up to the next aligned word of the destination
+    *reinterpret_cast<uint16_t*>(sm + d) = *reinterpret_cast<const uint16_t*>(sm + s);
+    s += 2;
+    d += 2;
+    left -= 2;
+  }
+  const uint32_t sel = (s & 2) ? 0x5432u : 0x3210u;
+  const uint32_t* w = reinterpret_cast<const uint32_t*>(sm) + (s >> 2);
+  uint32_t* o = reinterpret_cast<uint32_t*>(sm) + (d >> 2);
+  const uint32_t nw = left >> 2;
+  uint32_t prev = w[0];
+#pragma unroll 8
+  for (uint32_t k = 0; k < nw; ++k) {
+    const uint32_t cur = w[k + 1];
+    o[k] = __byte_perm(prev, cur, sel);
+    prev = cur;
+  }
+  if (left & 2)  // sel 0x5432: bytes 2..3 of the last word read; 0x3210: its bytes 0..1
+    *reinterpret_cast<uint16_t*>(sm + d + (nw << 2)) = static_cast<uint16_t>(__byte_perm(prev, 0, sel));
+}
+
+template <int FETCH>
+__global__ void __launch_bounds__(GB_THREADS)
+    gather_bulk_kernel(const uint8_t* __restrict__ src, uint64_t src_bytes, uint32_t W,
+                       const uint32_t* __restrict__ idx, uint32_t n, uint8_t* __restrict__ dst, uint32_t R,
+                       uint32_t stages, uint32_t slot, uint32_t chunks, uint32_t magic_c, uint32_t tiles) {
+  extern __shared__ __align__(128) uint8_t gb_sm[];
+  uint64_t* bars = reinterpret_cast<uint64_t*>(gb_sm);        // [GB_MAX_STAGES]
+  uint32_t* rowoff = reinterpret_cast<uint32_t*>(gb_sm + 64);  // [stages][R]: byte offset of the row in its stage
+  uint8_t* data = gb_sm + 64 + stages * R * 4;                 // [stages][R * slot] (+16 spare), 16-byte aligned
+  const uint32_t image_bytes = R * W;                          // multiple of 16 (R is)
+  uint8_t* image = data + stages * R * slot + 16;              // [2][image_bytes]: packed output tiles
+  const uint32_t tid = threadIdx.x;
+  const uint32_t lane = tid & 31;
+  const uintptr_t base = reinterpret_cast<uintptr_t>(src);
+  const uintptr_t safe_lo = (base + 15) & ~uintptr_t(15);
+  const uintptr_t safe_hi = (base + src_bytes) & ~uintptr_t(15);
+
+  if (FETCH == FETCH_BULK) {
+    if (tid == 0) {
+      for (uint32_t s = 0; s < stages; ++s) mbar_init(&bars[s], GB_THREADS / 32);
+      mbar_fence_init();
+    }
+    __syncthreads();
+  }
+
+  auto issue = [&](uint32_t t, uint32_t s) {
+    const uint32_t row0 = t * R;
+    const uint32_t rows = min(R, n - row0);
+    uint8_t* d = data + s * R * slot;
+    uint32_t* ro = rowoff + s * R;
+    if (FETCH == FETCH_BULK) {  // R <= GB_THREADS: at most one row per thread
+      uintptr_t a0 = 0;
+      uint32_t bytes = 0;
+      if (tid < rows) {
+        const uintptr_t a = base + static_cast<uint64_t>(ld_stream(idx + row0 + tid)) * W;
+        const uint32_t sh = static_cast<uint32_t>(a & 15);
+        a0 = a - sh;
+        bytes = (sh + W + 15u) & ~15u;
+        ro[tid] = tid * slot + sh;
+        if (a0 < safe_lo || a0 + bytes > safe_hi) {
+          uint8_t* q = d + tid * slot + sh;
+          for (uint32_t b = 0; b < W; ++b) q[b] = *reinterpret_cast<const uint8_t*>(a + b);
+          bytes = 0;
+        }
+      }
+      const uint32_t warp_bytes = gb_warp_sum(bytes);
+      __syncwarp();  // the lanes' shared-memory stores are ordered before lane 0's release
+      if (lane == 0) mbar_arrive_expect_tx(&bars[s], warp_bytes);
+      __syncwarp();
+      if (bytes) bulk_g2s(d + tid * slot, reinterpret_cast<const void*>(a0), bytes, &bars[s]);
+    } else {
+      const uint32_t items = rows * chunks;
+      for (uint32_t e = tid; e < items; e += GB_THREADS) {
+        const uint32_t r = __umulhi(e, magic_c);
+        const uint32_t c = e - r * chunks;
+        const uintptr_t a = base + static_cast<uint64_t>(__ldg(idx + row0 + r)) * W;
+        const uint32_t sh = static_cast<uint32_t>(a & 15);
+        if (c == 0) ro[r] = r * slot + sh;
+        if (c * 16 >= sh + W) continue;  // chunk lies wholly behind the row
+        const uintptr_t ac = a - sh + c * 16;
+        if (ac >= safe_lo && ac + 16 <= safe_hi) {
+          ldgsts16_64B(d + r * slot + c * 16, reinterpret_cast<const void*>(ac));
+        } else {  // first / last partial vector of the source buffer
+          for (uint32_t b = 0; b < 16; ++b) {
+            const uintptr_t p = ac + b;
+            if (p >= a && p < a + W) d[r * slot + c * 16 + b] = *reinterpret_cast<const uint8_t*>(p);
+          }
+        }
+      }
+      ldgsts_commit();
+    }
+  };
+
+  const uint32_t first = blockIdx.x;
+  const uint32_t my_tiles = tiles > first ? (tiles - first + gridDim.x - 1) / gridDim.x : 0;
+  for (uint32_t k = 0; k + 1 < stages; ++k) {
+    if (k < my_tiles) issue(first + k * gridDim.x, k);
+    else if (FETCH == FETCH_LDGSTS) ldgsts_commit();  // keep the group count uniform
+  }
+  for (uint32_t it = 0; it < my_tiles; ++it) {
+    const uint32_t nxt = it + stages - 1;
+    if (nxt < my_tiles) issue(first + nxt * gridDim.x, nxt % stages);
+    else if (FETCH == FETCH_LDGSTS) ldgsts_commit();
+    const uint32_t s = it % stages;
+    if (FETCH == FETCH_BULK) {
+      mbar_wait(&bars[s], (it / stages) & 1u);
+    } else {
+      switch (stages) {  // all but the newest stages-1 groups are complete
+        case 1: ldgsts_wait<0>(); break;
+        case 2: ldgsts_wait<1>(); break;
+        case 3: ldgsts_wait<2>(); break;
+        default: ldgsts_wait<3>(); break;
+      }
+    }
+    // the bulk store that read image[it & 1] two tiles ago must have drained
+    if (tid == 0 && it >= 2) bulk_wait_read<1>();
+    __syncthreads();
+
+    // ---- realign: one thread per row, slot -> packed image
+    const uint32_t t = first + it * gridDim.x;
+    const uint32_t rows = min(R, n - t * R);
+    uint8_t* img = image + (it & 1u) * image_bytes;
+    if (tid < rows)
+      copy_row_even(gb_sm, static_cast<uint32_t>(data - gb_sm) + s * R * slot + rowoff[s * R + tid],
+                    static_cast<uint32_t>(img - gb_sm) + tid * W, W);
+    fence_proxy_async_smem();
+    __syncthreads();  // image complete; the stage may be refilled
+    if (tid == 0) {
+      uint8_t* out = dst + static_cast<uint64_t>(t) * R * W;
+      const uint32_t nbytes = rows * W;
+      const uint32_t body = nbytes & ~15u;
+      if (body) bulk_s2g(out, img, body);
+      bulk_commit();
+      for (uint32_t b = body; b < nbytes; ++b) out[b] = img[b];  // ragged last tile only
+    }
+  }
+  if (tid == 0) bulk_wait<0>();
+}
+
+// Tunables (ds_debug_set_gather_bulk): rows per tile, ring depth, CTAs per SM; 0 = default.
+static uint32_t g_gb_rows = 0, g_gb_stages = 0, g_gb_ctas = 0;
+
+static bool gather_bulk_plan(uint32_t W, GatherBulkPlan* p) {
+  p->chunks = (W + 14 + 15) / 16;  // widest aligned span of a W-byte row that starts on an even address
+  if ((p->chunks & 1) == 0) ++p->chunks;  // odd multiple of 16: neighbouring slots start in different banks
+  p->slot = p->chunks * 16;
+  p->stages = g_gb_stages ? g_gb_stages : 2;
+  if (p->stages > GB_MAX_STAGES) p->stages = GB_MAX_STAGES;
+  uint32_t rows = g_gb_rows ? g_gb_rows : 128;
+  if (rows > GB_THREADS) rows = GB_THREADS;
+  rows &= ~15u;
+  const uint32_t budget = 110 * 1024;  // per CTA: stages + two output images
+  auto need = [&](uint32_t r) { return 64 + p->stages * r * (p->slot + 4) + 16 + 2 * r * W; };
+  while (rows > 16 && need(rows) > budget) rows -= 16;
+  if (rows < 16 || need(rows) > 200 * 1024) return false;
+  p->rows = rows;
+  p->smem = need(rows);
+  uint32_t ctas = (224u * 1024) / (p->smem + 1024);
+  if (ctas > 8) ctas = 8;
+  if (ctas < 1) ctas = 1;
+  if (g_gb_ctas && g_gb_ctas < ctas) ctas = g_gb_ctas;
+  p->ctas_per_sm = ctas;
+  return true;
+}
+
+static bool gather_bulk_eligible(const void* src, uint32_t W, uint64_t src_rows, const void* dst) {
+  return (W & 1) == 0 && (W & 15) != 0 && W >= 18 && W <= 1024 && src_rows > 0 &&
+         (reinterpret_cast<uintptr_t>(src) & 1) == 0 && (reinterpret_cast<uintptr_t>(dst) & 15) == 0;
+}
+
+static cudaError_t launch_gather_bulk(int fetch, const void* src, uint32_t W, uint64_t src_rows,
+                                      const uint32_t* idx, uint32_t n, void* dst, cudaStream_t s) {
+  GatherBulkPlan p;
+  if (!gather_bulk_plan(W, &p)) return cudaErrorInvalidConfiguration;
+  const uint32_t tiles = (n + p.rows - 1) / p.rows;
+  uint32_t blocks = static_cast<uint32_t>(sm_count()) * p.ctas_per_sm;
+  if (blocks > tiles) blocks = tiles;
+  const uint32_t magic_c = static_cast<uint32_t>((0x100000000ull + p.chunks - 1) / p.chunks);
+  auto k = fetch == FETCH_BULK ? gather_bulk_kernel<FETCH_BULK> : gather_bulk_kernel<FETCH_LDGSTS>;
+  cudaError_t e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(p.smem));
+  if (e != cudaSuccess) return e;
+  ds::note_launch();
+  k<<<blocks, GB_THREADS, p.smem, s>>>(static_cast<const uint8_t*>(src), src_rows * W, W, idx, n,
+                                       static_cast<uint8_t*>(dst), p.rows, p.stages, p.slot, p.chunks, magic_c,
+                                       tiles);
+  return cudaGetLastError();
+}
+
+}  // namespace ds
