@@ -132,6 +132,47 @@ ds_status ds_scatter_rows_to_parts(const void* src, uint32_t row_bytes, uint64_t
                                    const uint64_t* part_offsets, void* const* dst_bases,
                                    void* stream);
 
+/* Streaming split -- the map side of the exchange as ONE pass over the input, rows kept in
+ * input order (no permutation, no partitioned copy of the block).
+ * Replaces the per-mapper slicing of sort_and_partition (_internal/arrow_block.py:387-393),
+ * the M x N map outputs of SimpleShufflePlan.execute (_internal/shuffle.py:81-104) and their
+ * pull by the reduce tasks (_internal/shuffle.py:106-112;
+ * src/ray/object_manager/object_manager.cc:336-559).
+ *
+ * ds_split_plan: destination of every row and the per-tile placement table.
+ *   key_kind          DS_KEY_*; width = key bytes for DS_KEY_FSB (ignored otherwise)
+ *   valid             optional validity bytes (NULL = no nulls); null keys go to the LAST
+ *                     destination (the reducer's sort puts them at the end)
+ *   boundaries        nb keys (device) in the column's own encoding, ordered like the sort
+ *                     (same rule as ds_partition_hist_scatter_*); nb + 1 <= DS_MAX_SPLIT_PARTS
+ *   dest_out          n bytes: destination of row i
+ *   tile_offsets_out  (nb+1) * (ntiles+1) uint32, ntiles = ceil(n / DS_SPLIT_TILE_ROWS):
+ *                     entry [d*(ntiles+1) + t] = rows of destination d in tiles < t;
+ *                     entry [d*(ntiles+1) + ntiles] = all rows of destination d
+ *   counts_out        nb+1 uint64 rows per destination (device)
+ * ds_split_rows: moves one column.  Row i (destination d = dest[i]) is stored at
+ *   dst_bases[d] + (number of earlier rows with destination d) * row_bytes; dst_bases[d] may
+ *   be peer-mapped memory of another GPU (the rows then cross NVLink as bulk stores issued
+ *   from shared memory) or local memory.
+ *   dst_bases   HOST array of nparts device pointers
+ *   max_ctas    upper bound on the persistent grid (0 = one CTA per SM), so that a caller can
+ *               leave SMs to work running beside the transfer
+ *   row_bytes <= DS_SPLIT_MAX_ROW_BYTES. */
+#define DS_KEY_I64 0
+#define DS_KEY_U64 1
+#define DS_KEY_F64 2
+#define DS_KEY_FSB 3
+#define DS_SPLIT_TILE_ROWS 256
+#define DS_MAX_SPLIT_PARTS 32
+#define DS_SPLIT_MAX_ROW_BYTES 256
+ds_status ds_split_plan(int32_t key_kind, const void* col, uint32_t width, const uint8_t* valid,
+                        uint64_t n, const void* boundaries, uint32_t nb, int32_t descending,
+                        uint8_t* dest_out, uint32_t* tile_offsets_out, uint64_t* counts_out,
+                        void* stream);
+ds_status ds_split_rows(const void* src, uint32_t row_bytes, uint64_t n, const uint8_t* dest,
+                        const uint32_t* tile_offsets, uint32_t nparts, void* const* dst_bases,
+                        uint32_t max_ctas, void* stream);
+
 /* ----------------------------------------------------------- partition ---- */
 
 /* Cut positions of a SORTED key column at the given boundaries.

@@ -18,6 +18,10 @@ DS_ERR_INVALID_ARG, DS_ERR_UNSUPPORTED, DS_ERR_WORKSPACE, DS_ERR_CUDA, DS_ERR_TO
 DS_MAX_ROWS = (1 << 30) - 1
 DS_MAX_KEY_BYTES = 10
 DS_MAX_PARTITIONS = 256
+DS_KEY_I64, DS_KEY_U64, DS_KEY_F64, DS_KEY_FSB = 0, 1, 2, 3
+DS_SPLIT_TILE_ROWS = 256
+DS_MAX_SPLIT_PARTS = 32
+DS_SPLIT_MAX_ROW_BYTES = 256
 DS_SORT_NO_PASS_SKIP = 1
 DS_SORT_NO_PREFIX_REPAIR = 2
 DS_SORT_NO_HYBRID = 4
@@ -52,6 +56,8 @@ _PROTOS = {
     "ds_sort_indices_fsb": [_P, c_uint32, c_uint64, c_int32, _P, _P, c_int32, _P, _SZP, _P],
     "ds_gather_rows": [_P, c_uint32, c_uint64, _P, c_uint64, _P, _P],
     "ds_scatter_rows_to_parts": [_P, c_uint32, c_uint64, _P, c_uint64, c_uint32, _P, _P, _P],
+    "ds_split_plan": [c_int32, _P, c_uint32, _P, c_uint64, _P, c_uint32, c_int32, _P, _P, _P, _P],
+    "ds_split_rows": [_P, c_uint32, c_uint64, _P, _P, c_uint32, _P, c_uint32, _P],
     "ds_searchsorted_i64": [_P, c_uint64, _P, c_uint32, c_int32, _P, _P],
     "ds_searchsorted_f64": [_P, c_uint64, _P, c_uint32, c_int32, _P, _P],
     "ds_searchsorted_fsb": [_P, c_uint32, c_uint64, _P, c_uint32, c_int32, _P, _P],

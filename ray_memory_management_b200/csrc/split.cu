@@ -1,0 +1,407 @@
+// Streaming split: the map side of the all-to-all exchange as one pass over the input.
+//
+// Replaces the M x N map-output objects of the reference's shuffle and their pull by the
+// reducers (python/ray/data/_internal/shuffle.py:81-112, _internal/arrow_block.py:387-393;
+// src/ray/object_manager/object_manager.cc:336-559): the rows of a block go, in input order,
+// straight into the receive buffer of the GPU that owns their key range -- no partitioned copy
+// of the block, no permutation, no random reads.
+//
+//   ds_split_plan   reads the key column once: destination of every row (one byte, binary
+//                   search over the splitters in shared memory, null keys -> last partition)
+//                   and, per tile of DS_SPLIT_TILE_ROWS rows and per destination, how many of
+//                   the destination's rows lie in earlier tiles (exclusive scan, in place).
+//   ds_split_rows   one launch per column.  A persistent CTA per SM walks tiles of T rows:
+//                   the tile arrives with ONE bulk copy (cp.async.bulk global -> shared,
+//                   mbarrier tracked) while the CTA ranks the rows stably per destination
+//                   (warp ballots); one thread per row then moves the row inside shared memory
+//                   to its place in its destination's span (laid out with the byte alignment
+//                   of the span's global address), and every span leaves with one bulk store
+//                   (cp.async.bulk shared -> global) to dst_bases[d] + offset -- peer-mapped
+//                   memory of another GPU over NVLink, or this GPU's own buffer.  A split is a
+//                   radix pass on whole rows with digit = destination; it is stable by
+//                   construction, which is what makes the global result the stable sort.
+//
+// Algorithmic bytes per row: plan K (key) + 1; split 1 + 2 * W (W over NVLink for remote rows).
+#include "ds_async.cuh"
+#include "ds_common.cuh"
+#include "ds_keys.cuh"
+#include "gather_bulk.cuh"
+
+namespace ds {
+
+constexpr int SP_THREADS = 256;
+constexpr int SP_TILE0 = DS_SPLIT_TILE_ROWS;  // granularity of the tile offsets
+constexpr int SP_MAX_PARTS = DS_MAX_SPLIT_PARTS;
+static_assert(SP_TILE0 == SP_THREADS, "one row per thread and plan tile");
+static_assert(SP_MAX_PARTS <= 32, "one lane per destination");
+
+// ---------------------------------------------------------------- plan
+template <int KIND>
+__global__ void __launch_bounds__(SP_THREADS)
+    split_plan_kernel(const void* __restrict__ col, uint32_t width, const uint8_t* __restrict__ valid,
+                      uint32_t n, const void* __restrict__ bounds, uint32_t nb, bool desc,
+                      uint8_t* __restrict__ dest_out, uint32_t* __restrict__ tile_counts, uint32_t ntiles) {
+  __shared__ uint64_t s_bh[SP_MAX_PARTS];
+  __shared__ uint32_t s_bl[SP_MAX_PARTS];
+  __shared__ uint32_t s_wc[2][SP_THREADS / 32][SP_MAX_PARTS];
+  const uint32_t tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const uint32_t nparts = nb + 1;
+  if (tid < nb) {
+    uint64_t h;
+    uint32_t l;
+    load_key<KIND>(bounds, width, tid, desc, h, l);
+    s_bh[tid] = h;
+    s_bl[tid] = l;
+  }
+  __syncthreads();
+  uint32_t flip = 0;
+  for (uint32_t t = blockIdx.x; t < ntiles; t += gridDim.x, flip ^= 1u) {
+    const uint32_t i = t * SP_TILE0 + tid;
+    uint32_t d = 0xffffffffu;
+    if (i < n) {
+      if (valid != nullptr && valid[i] == 0) {
+        d = nb;  // null keys travel to the last partition
+      } else {
+        uint64_t kh;
+        uint32_t kl;
+        load_key<KIND>(col, width, i, desc, kh, kl);
+        uint32_t lo = 0, hi = nb;
+        while (lo < hi) {
+          const uint32_t mid = (lo + hi) >> 1;
+          // asc: count splitters <= key; desc: count splitters strictly before key (encoded)
+          const bool go_right = desc ? key_less(s_bh[mid], s_bl[mid], kh, kl)
+                                     : !key_less(kh, kl, s_bh[mid], s_bl[mid]);
+          if (go_right) lo = mid + 1;
+          else hi = mid;
+        }
+        d = lo;
+      }
+      dest_out[i] = static_cast<uint8_t>(d);
+    }
+    uint32_t mine = 0;
+    for (uint32_t b = 0; b < nparts; ++b) {
+      const uint32_t m = __ballot_sync(0xffffffffu, d == b);
+      if (lane == b) mine = __popc(m);
+    }
+    if (lane < nparts) s_wc[flip][warp][lane] = mine;
+    __syncthreads();  // one barrier per tile: the counters alternate between two copies
+    if (tid < nparts) {
+      uint32_t c = 0;
+#pragma unroll
+      for (int w = 0; w < SP_THREADS / 32; ++w) c += s_wc[flip][w][tid];
+      tile_counts[static_cast<size_t>(tid) * (ntiles + 1) + t] = c;
+    }
+  }
+}
+
+// One CTA per destination: exclusive scan of its ntiles counts in place; entry ntiles and
+// counts_out get the total.
+__global__ void __launch_bounds__(1024)
+    split_scan_kernel(uint32_t* __restrict__ tile_counts, uint32_t ntiles, uint64_t* __restrict__ counts_out) {
+  __shared__ uint32_t s_warp[32];
+  uint32_t* row = tile_counts + static_cast<size_t>(blockIdx.x) * (ntiles + 1);
+  const uint32_t tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const uint32_t per = (ntiles + 1023) / 1024;
+  const uint32_t lo = min(tid * per, ntiles), hi = min(lo + per, ntiles);
+  uint32_t sum = 0;
+  for (uint32_t i = lo; i < hi; ++i) sum += row[i];
+  uint32_t v = sum;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const uint32_t t = __shfl_up_sync(0xffffffffu, v, o);
+    if ((int)lane >= o) v += t;
+  }
+  if (lane == 31) s_warp[warp] = v;
+  __syncthreads();
+  uint32_t run = v - sum;
+  for (uint32_t w = 0; w < warp; ++w) run += s_warp[w];
+  for (uint32_t i = lo; i < hi; ++i) {
+    const uint32_t c = row[i];
+    row[i] = run;
+    run += c;
+  }
+  if (tid == 1023) {
+    row[ntiles] = run;
+    counts_out[blockIdx.x] = run;
+  }
+}
+
+// ---------------------------------------------------------------- split
+struct SplitBases {
+  unsigned char* p[SP_MAX_PARTS];
+};
+
+// generic (any alignment, any width) row copy inside shared memory
+__device__ __forceinline__ void copy_row_bytes(uint8_t* __restrict__ sm, uint32_t s, uint32_t d, uint32_t W) {
+  for (uint32_t b = 0; b < W; ++b) sm[d + b] = sm[s + b];
+}
+
+template <int K>  // tile = K * 256 rows
+__global__ void __launch_bounds__(SP_THREADS)
+    split_rows_kernel(const uint8_t* __restrict__ src, uint32_t W, uint32_t n, const uint8_t* __restrict__ dest,
+                      const uint32_t* __restrict__ tile_offsets, uint32_t ntiles0, uint32_t nparts,
+                      SplitBases bases, uint32_t tiles, bool even_path) {
+  constexpr uint32_t T = K * SP_TILE0;
+  constexpr uint32_t CHUNKS = T / 32;
+  extern __shared__ __align__(128) uint8_t sp_sm[];
+  // layout: bar | chunk counts | span tables | A (tile as it lies in the input) | B[2] (spans)
+  uint64_t* bar = reinterpret_cast<uint64_t*>(sp_sm);
+  uint32_t* s_cc = reinterpret_cast<uint32_t*>(sp_sm + 16);             // [CHUNKS][32]
+  uint32_t* s_bstart = s_cc + CHUNKS * 32;                              // [32] byte offset of span data in B
+  const uint32_t a_off = 16 + CHUNKS * 32 * 4 + 32 * 4;                 // multiple of 16
+  const uint32_t a_bytes = T * W;                                       // multiple of 16
+  const uint32_t b_bytes = a_bytes + 32 * SP_MAX_PARTS;
+  const uint32_t b_off0 = a_off + a_bytes + 16;
+  const uint32_t tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const uint32_t lt_mask = (1u << lane) - 1u;
+  const bool src_aligned = (reinterpret_cast<uintptr_t>(src) & 15) == 0;
+
+  if (tid == 0) {
+    mbar_init(bar, 1);
+    mbar_fence_init();
+  }
+  __syncthreads();
+
+  auto load_tile = [&](uint32_t t) {  // called by every thread; the bulk path is one thread's work
+    const uint32_t row0 = t * T;
+    const uint32_t rows = min(T, n - row0);
+    const uint8_t* g = src + static_cast<uint64_t>(row0) * W;
+    if (rows == T && src_aligned) {
+      if (tid == 0) {
+        mbar_arrive_expect_tx(bar, a_bytes);
+        bulk_g2s(sp_sm + a_off, g, a_bytes, bar);
+      }
+    } else {  // ragged last tile or an unaligned column: plain loads
+      const uint32_t nbytes = rows * W;
+      for (uint32_t b = tid; b < nbytes; b += SP_THREADS) sp_sm[a_off + b] = g[b];
+      __syncthreads();
+      if (tid == 0) mbar_arrive_expect_tx(bar, 0);
+    }
+  };
+
+  const uint32_t first = blockIdx.x;
+  const uint32_t my_tiles = tiles > first ? (tiles - first + gridDim.x - 1) / gridDim.x : 0;
+  if (my_tiles) load_tile(first);
+  for (uint32_t it = 0; it < my_tiles; ++it) {
+    const uint32_t t = first + it * gridDim.x;
+    const uint32_t row0 = t * T;
+    const uint32_t rows = min(T, n - row0);
+    const uint32_t b_off = b_off0 + (it & 1u) * b_bytes;
+
+    // ---- destinations and stable ranks (row i of the tile = chunk i/32, lane i%32)
+    uint32_t d[K], rk[K];
+#pragma unroll
+    for (int k = 0; k < K; ++k) {
+      const uint32_t i = k * SP_TILE0 + tid;
+      d[k] = i < rows ? dest[row0 + i] : 0xffffffffu;
+    }
+#pragma unroll
+    for (int k = 0; k < K; ++k) {
+      uint32_t mine = 0;
+      rk[k] = 0;
+      for (uint32_t b = 0; b < nparts; ++b) {
+        const uint32_t m = __ballot_sync(0xffffffffu, d[k] == b);
+        if (d[k] == b) rk[k] = __popc(m & lt_mask);
+        if (lane == b) mine = __popc(m);
+      }
+      s_cc[(k * 8 + warp) * 32 + lane] = mine;
+    }
+    // the bulk stores that read B[it & 1] two tiles ago must have drained
+    if (tid < nparts && it >= 2) bulk_wait_read<1>();
+    __syncthreads();
+    if (warp == 0) {
+      // lane b: chunk counts -> exclusive offsets within the span; span length; span placement
+      uint32_t run = 0;
+      for (uint32_t c = 0; c < CHUNKS; ++c) {
+        const uint32_t v = s_cc[c * 32 + lane];
+        s_cc[c * 32 + lane] = run;
+        run += v;
+      }
+      uint32_t res = 0, padded = 0;
+      if (lane < nparts && run) {
+        const uint64_t ga = reinterpret_cast<uint64_t>(bases.p[lane]) +
+                            static_cast<uint64_t>(tile_offsets[static_cast<size_t>(lane) * (ntiles0 + 1) + t * K]) * W;
+        res = static_cast<uint32_t>(ga & 15);
+        padded = (res + run * W + 15u) & ~15u;
+      }
+      uint32_t incl = padded;
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        const uint32_t v = __shfl_up_sync(0xffffffffu, incl, o);
+        if ((int)lane >= o) incl += v;
+      }
+      s_bstart[lane] = incl - padded + res;
+    }
+    __syncthreads();
+    uint32_t boff[K];
+#pragma unroll
+    for (int k = 0; k < K; ++k)
+      boff[k] = d[k] < nparts ? s_bstart[d[k]] + (s_cc[(k * 8 + warp) * 32 + d[k]] + rk[k]) * W : 0;
+
+    // ---- the tile has arrived: move every row to its place in its span
+    mbar_wait(bar, it & 1u);
+#pragma unroll
+    for (int k = 0; k < K; ++k) {
+      const uint32_t i = k * SP_TILE0 + tid;
+      if (i < rows) {
+        if (even_path) copy_row_even(sp_sm, a_off + i * W, b_off + boff[k], W);
+        else copy_row_bytes(sp_sm, a_off + i * W, b_off + boff[k], W);
+      }
+    }
+    fence_proxy_async_smem();
+    __syncthreads();  // spans complete, A free
+    if (it + 1 < my_tiles) load_tile(first + (it + 1) * gridDim.x);
+
+    // ---- ship the spans: thread b owns destination b
+    if (tid < nparts) {
+      const uint32_t start = s_bstart[tid];
+      // span length = this tile's rows for the destination (difference of the scanned offsets)
+      const size_t o = static_cast<size_t>(tid) * (ntiles0 + 1);
+      const uint32_t t1 = min(t * K + K, ntiles0);
+      const uint32_t len = (tile_offsets[o + t1] - tile_offsets[o + t * K]) * W;
+      if (len) {
+        uint8_t* g = bases.p[tid] + static_cast<uint64_t>(tile_offsets[o + t * K]) * W;
+        const uint8_t* sdat = sp_sm + b_off + start;
+        const uint32_t head = min(len, (16u - (start & 15u)) & 15u);
+        const uint32_t body = (len - head) & ~15u;
+        for (uint32_t b = 0; b < head; ++b) g[b] = sdat[b];
+        if (body) bulk_s2g(g + head, sdat + head, body);
+        for (uint32_t b = head + body; b < len; ++b) g[b] = sdat[b];
+      }
+      bulk_commit();
+    }
+  }
+  if (tid < nparts) bulk_wait<0>();
+}
+
+static uint32_t g_split_ctas = 0;  // ds_debug_set_split_ctas: persistent CTAs per SM (0 = default 1)
+
+template <int K>
+static cudaError_t launch_split(const void* src, uint32_t W, uint32_t n, const uint8_t* dest,
+                                const uint32_t* tile_offsets, uint32_t nparts, const SplitBases& bases,
+                                bool even_path, uint32_t max_ctas, cudaStream_t s) {
+  constexpr uint32_t T = K * SP_TILE0;
+  const uint32_t ntiles0 = (n + SP_TILE0 - 1) / SP_TILE0;
+  const uint32_t tiles = (n + T - 1) / T;
+  const uint32_t smem = 16 + (T / 32) * 32 * 4 + 32 * 4 + T * W + 16 + 2 * (T * W + 32 * SP_MAX_PARTS) + 16;
+  auto k = split_rows_kernel<K>;
+  cudaError_t e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem));
+  if (e != cudaSuccess) return e;
+  uint32_t per_sm = g_split_ctas ? g_split_ctas : 1;
+  const uint32_t fit = (224u * 1024) / (smem + 1024);
+  if (per_sm > fit) per_sm = fit ? fit : 1;
+  uint32_t blocks = static_cast<uint32_t>(sm_count()) * per_sm;
+  if (max_ctas && blocks > max_ctas) blocks = max_ctas;
+  if (blocks > tiles) blocks = tiles;
+  note_launch();
+  k<<<blocks, SP_THREADS, smem, s>>>(static_cast<const uint8_t*>(src), W, n, dest, tile_offsets, ntiles0, nparts,
+                                     bases, tiles, even_path);
+  return cudaGetLastError();
+}
+
+}  // namespace ds
+
+extern "C" {
+
+ds_status ds_split_plan(int32_t key_kind, const void* col, uint32_t width, const uint8_t* valid, uint64_t n,
+                        const void* boundaries, uint32_t nb, int32_t descending, uint8_t* dest_out,
+                        uint32_t* tile_offsets_out, uint64_t* counts_out, void* stream) {
+  using namespace ds;
+  if (n > DS_MAX_ROWS) {
+    set_error("%s: n=%llu exceeds DS_MAX_ROWS", __func__, (unsigned long long)n);
+    return DS_ERR_TOO_LARGE;
+  }
+  if (nb + 1 > DS_MAX_SPLIT_PARTS) {
+    set_error("%s: %u destinations exceed DS_MAX_SPLIT_PARTS (%d)", __func__, nb + 1, DS_MAX_SPLIT_PARTS);
+    return DS_ERR_UNSUPPORTED;
+  }
+  if (key_kind == DS_KEY_FSB ? (width < 1 || width > DS_MAX_KEY_BYTES) : false) {
+    set_error("%s: key width %u unsupported", __func__, width);
+    return DS_ERR_UNSUPPORTED;
+  }
+  if (!tile_offsets_out || !counts_out || (n > 0 && (!col || !dest_out)) || (nb > 0 && !boundaries)) {
+    set_error("%s: NULL pointer", __func__);
+    return DS_ERR_INVALID_ARG;
+  }
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  const uint32_t n32 = static_cast<uint32_t>(n);
+  const uint32_t ntiles = (n32 + SP_TILE0 - 1) / SP_TILE0;
+  if (n32) {
+    uint32_t blocks = static_cast<uint32_t>(sm_count()) * 8;
+    if (blocks > ntiles) blocks = ntiles;
+    note_launch();
+    const bool desc = descending != 0;
+    switch (key_kind) {
+      case DS_KEY_I64:
+        split_plan_kernel<KIND_I64><<<blocks, SP_THREADS, 0, s>>>(col, 8, valid, n32, boundaries, nb, desc, dest_out, tile_offsets_out, ntiles);
+        break;
+      case DS_KEY_U64:
+        split_plan_kernel<KIND_U64><<<blocks, SP_THREADS, 0, s>>>(col, 8, valid, n32, boundaries, nb, desc, dest_out, tile_offsets_out, ntiles);
+        break;
+      case DS_KEY_F64:
+        split_plan_kernel<KIND_F64><<<blocks, SP_THREADS, 0, s>>>(col, 8, valid, n32, boundaries, nb, desc, dest_out, tile_offsets_out, ntiles);
+        break;
+      case DS_KEY_FSB:
+        split_plan_kernel<KIND_FSB><<<blocks, SP_THREADS, 0, s>>>(col, width, valid, n32, boundaries, nb, desc, dest_out, tile_offsets_out, ntiles);
+        break;
+      default:
+        set_error("%s: unknown key kind %d", __func__, key_kind);
+        return DS_ERR_INVALID_ARG;
+    }
+    DS_LAUNCH_CHECK();
+  }
+  note_launch();
+  split_scan_kernel<<<nb + 1, 1024, 0, s>>>(tile_offsets_out, ntiles, counts_out);
+  DS_LAUNCH_CHECK();
+  return DS_OK;
+}
+
+ds_status ds_split_rows(const void* src, uint32_t row_bytes, uint64_t n, const uint8_t* dest,
+                        const uint32_t* tile_offsets, uint32_t nparts, void* const* dst_bases,
+                        uint32_t max_ctas, void* stream) {
+  using namespace ds;
+  if (n == 0) return DS_OK;
+  if (n > DS_MAX_ROWS) {
+    set_error("%s: n=%llu exceeds DS_MAX_ROWS", __func__, (unsigned long long)n);
+    return DS_ERR_TOO_LARGE;
+  }
+  if (nparts == 0 || nparts > DS_MAX_SPLIT_PARTS) {
+    set_error("%s: %u destinations unsupported (1..%d)", __func__, nparts, DS_MAX_SPLIT_PARTS);
+    return DS_ERR_UNSUPPORTED;
+  }
+  if (row_bytes == 0 || row_bytes > DS_SPLIT_MAX_ROW_BYTES) {
+    set_error("%s: row_bytes=%u unsupported (1..%d)", __func__, row_bytes, DS_SPLIT_MAX_ROW_BYTES);
+    return DS_ERR_UNSUPPORTED;
+  }
+  if (!src || !dest || !tile_offsets || !dst_bases) {
+    set_error("%s: NULL pointer", __func__);
+    return DS_ERR_INVALID_ARG;
+  }
+  SplitBases bases{};
+  uintptr_t bits = reinterpret_cast<uintptr_t>(src) | row_bytes;
+  for (uint32_t d = 0; d < nparts; ++d) {
+    bases.p[d] = static_cast<unsigned char*>(dst_bases[d]);
+    bits |= reinterpret_cast<uintptr_t>(dst_bases[d]);
+  }
+  const bool even_path = (bits & 1) == 0;
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  const uint32_t n32 = static_cast<uint32_t>(n);
+  const uint8_t* dst8 = dest;
+  cudaError_t e;
+  // tile of K * 256 rows: the largest whose three shared-memory images stay under ~100 KB
+  const uint32_t per256 = 3u * SP_TILE0 * row_bytes;
+  if (per256 * 8 <= 100 * 1024) e = launch_split<8>(src, row_bytes, n32, dst8, tile_offsets, nparts, bases, even_path, max_ctas, s);
+  else if (per256 * 4 <= 100 * 1024) e = launch_split<4>(src, row_bytes, n32, dst8, tile_offsets, nparts, bases, even_path, max_ctas, s);
+  else if (per256 * 2 <= 100 * 1024) e = launch_split<2>(src, row_bytes, n32, dst8, tile_offsets, nparts, bases, even_path, max_ctas, s);
+  else e = launch_split<1>(src, row_bytes, n32, dst8, tile_offsets, nparts, bases, even_path, max_ctas, s);
+  if (e != cudaSuccess) {
+    set_error("%s: launch failed: %s", __func__, cudaGetErrorString(e));
+    return DS_ERR_CUDA;
+  }
+  return DS_OK;
+}
+
+// Tuning hook: persistent CTAs per SM of ds_split_rows (0 = default).
+void ds_debug_set_split_ctas(uint32_t per_sm) { ds::g_split_ctas = per_sm; }
+
+}  // extern "C"
