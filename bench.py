@@ -48,7 +48,7 @@ def parse_args():
     p.add_argument("--warmup", type=int, default=3)
     p.add_argument("--impl", default="ours", choices=["ours", "reference"])
     p.add_argument("--rows-per-gpu", type=int, default=100_000_000)
-    p.add_argument("--cpu-rows", type=int, default=4_000_000,
+    p.add_argument("--cpu-rows", type=int, default=20_000_000,
                    help="rows of the bounded CPU-baseline sample")
     p.add_argument("--no-e2e", action="store_true")
     p.add_argument("--e2e-inflight", type=int, default=2,
@@ -57,6 +57,11 @@ def parse_args():
     p.add_argument("--radix-config", type=int, default=-1, help="tuning: pass-kernel variant")
     p.add_argument("--gather-mode", type=int, default=-1, help="tuning: see csrc/gather.cu g_gather_mode")
     p.add_argument("--l2-fetch", type=int, default=-1, help="tuning: cudaLimitMaxL2FetchGranularity")
+    p.add_argument("--blocks-per-gpu", type=int, default=20,
+                   help="single GPU: also time the same records held as this many blocks (value_multiblock)")
+    p.add_argument("--corrupt", action="store_true",
+                   help="flip one byte of the first output before validating it: the run must exit non-zero")
+    p.add_argument("--no-validate", action="store_true")
     return p.parse_args()
 
 
@@ -117,23 +122,45 @@ class ClockSampler:
                 "reasons": sorted(reasons), "samples": len(sm)}
 
 
+def cpu_rows_that_fit(rows: int) -> int:
+    """The CPU sample needs ~6x its size in host memory (tables, pickled map outputs, sorted
+    copies in the workers); shrink it when the box is small."""
+    try:
+        with open("/proc/meminfo") as f:
+            avail_kb = next(int(ln.split()[1]) for ln in f if ln.startswith("MemAvailable"))
+        cap = int(avail_kb * 1024 / (6 * ROW_BYTES))
+        return max(1_000_000, min(rows, cap))
+    except Exception:
+        return rows
+
+
 def cpu_baseline(rows: int, steps: int = 1, warmup: int = 0):
-    """(GB/s, descriptor) of the CPU port on a bounded sample, all host cores."""
+    """(GB/s, descriptor) of the CPU port on a bounded sample, all host cores.  The worker pool
+    is started before the timed region (the reference's workers are running when Dataset.sort is
+    called) and serves every step."""
     from oracle import cpu_baseline as C
 
+    rows = cpu_rows_that_fit(rows)
     cores = C.host_cores()
     blocks = max(cores, 2)
     tabs = C.make_graysort_blocks(rows, blocks, seed=1)
-    for _ in range(warmup):
-        C.time_sort(tabs, cores)
-    secs = [C.time_sort(tabs, cores) for _ in range(max(steps, 1))]
+    pool = C.make_pool(tabs, cores) if cores > 1 else None
+    try:
+        for _ in range(warmup):
+            C.time_sort(tabs, cores, pool=pool)
+        secs = [C.time_sort(tabs, cores, pool=pool) for _ in range(max(steps, 1))]
+    finally:
+        if pool is not None:
+            pool.close()
+            pool.join()
     best = min(secs)
     gbs = rows * ROW_BYTES / best / 1e9
     desc = {"value": gbs, "unit": UNIT, "cores": cores, "kind": "port",
             "sample": f"{rows} GraySort records ({rows * ROW_BYTES / 1e9:.2f} GB) in {blocks} "
                       f"blocks, best of {len(secs)}: {best:.2f} s; oracle/datasets_oracle.py "
-                      f"(pyarrow sort_indices/take + numpy searchsorted) over a {cores}-process pool"}
-    return gbs, desc, secs
+                      f"(pyarrow sort_indices/take + numpy searchsorted) over a {cores}-process pool "
+                      f"started before the timed region"}
+    return gbs, desc, secs, rows
 
 
 # ------------------------------------------------------------------------------ ours
@@ -159,18 +186,110 @@ def make_records(n: int, seed: int):
     return ds.DeviceArrowBlock(cols, n)
 
 
-def check_sorted(block, n):
-    """Cheap on-device sanity check of one output (not timed): keys non-decreasing in
-    their first 8 bytes and row ids a permutation."""
+def _wrap64(c: int) -> int:
+    return c - (1 << 64) if c >= (1 << 63) else c
+
+
+def validate_output(ds, block_in, out, world, rank):
+    """Untimed proof that one step's output is the sort of its input, on every rank:
+    valsort's invariants on device (ds_validate_records: no record below its predecessor, the
+    sum of the records' CRC-32 equal to the input's, record count equal) summed over ranks,
+    and the ranks' key ranges in rank order.  Returns the dict that goes into the JSON line."""
+    import torch
+    import torch.distributed as dist
+
+    from ray_memory_management_b200 import graysort
+
+    vin, vout = graysort.validate(block_in), graysort.validate(out)
+    t = torch.tensor([vin["records"], _wrap64(vin["checksum"]), vout["records"], _wrap64(vout["checksum"]),
+                      vout["unordered"]], dtype=torch.int64, device="cuda")
+    n_out = out.num_rows
+    edge = torch.zeros(2 * KEY_BYTES + 1, dtype=torch.uint8, device="cuda")
+    if n_out:
+        k = out.columns["key"].data
+        edge[:KEY_BYTES] = k[:KEY_BYTES]
+        edge[KEY_BYTES: 2 * KEY_BYTES] = k[(n_out - 1) * KEY_BYTES: n_out * KEY_BYTES]
+        edge[2 * KEY_BYTES] = 1
+    edges = edge[None, :]
+    if world > 1:
+        dist.all_reduce(t)  # int64 sums wrap, like the 64-bit checksum itself
+        edges = torch.empty((world, 2 * KEY_BYTES + 1), dtype=torch.uint8, device="cuda")
+        dist.all_gather_into_tensor(edges.view(-1), edge)
+    rin, cin, rout, cout, unordered = (int(x) for x in t.cpu().tolist())
+    e = edges.cpu().numpy()
+    live = [(bytes(r[:KEY_BYTES]), bytes(r[KEY_BYTES: 2 * KEY_BYTES])) for r in e if r[2 * KEY_BYTES]]
+    rank_order = all(live[i][1] <= live[i + 1][0] for i in range(len(live) - 1))
+    res = {"records_in": rin, "records_out": rout, "crc_equal": cin == cout, "unordered": unordered,
+           "rank_order": rank_order}
+    res["ok"] = rin == rout and cin == cout and unordered == 0 and rank_order
+    return res
+
+
+def validate_tie_order(ds, block_in, out):
+    """Single GPU, full size: the step's output against a second sort of the same keys that runs
+    every radix pass (no prefix/repair, no bucket kernel): row order and sorted keys must be
+    identical, and the payload must be the gather by that order -- this pins the tie order of the
+    production plan (the bucket kernel at its production fill) bit for bit."""
     import torch
 
-    k = block.columns["key"].data.view(n, KEY_BYTES)[:, :8].contiguous()
-    # big-endian bytes -> compare as int64 after byte swap; shift to keep the sign out of it
-    be = k.flip(1).contiguous().view(torch.int64).view(n)
-    hi = (be >> 1) & 0x7FFFFFFFFFFFFFFF
-    assert bool((hi[1:] >= hi[:-1]).all()), "output keys are not sorted"
-    ids = block.columns["payload"].data.view(n, PAYLOAD_BYTES)[:, :8].contiguous().view(torch.int64).view(n)
-    assert int(ids.sum().item()) == n * (n - 1) // 2, "row ids are not a permutation"
+    from ray_memory_management_b200 import _lib
+    from ray_memory_management_b200.block import _argsort, _gather
+
+    key = block_in.columns["key"]
+    idx_a, sk_a = _argsort(key, False, True)
+    idx_b, sk_b = _argsort(key, False, True, options=_lib.DS_SORT_NO_HYBRID | _lib.DS_SORT_NO_PREFIX_REPAIR)
+    same_idx = bool(torch.equal(idx_a, idx_b)) and bool(torch.equal(sk_a.data, sk_b.data))
+    same_keys = bool(torch.equal(out.columns["key"].data, sk_b.data))
+    del idx_a, sk_a, sk_b
+    pay = _gather(block_in.columns["payload"], idx_b)
+    same_payload = bool(torch.equal(out.columns["payload"].data, pay.data))
+    return same_idx and same_keys and same_payload
+
+
+def validate_miniature(ds, world, rank, sort_fn):
+    """Every N: a ragged, tie-heavy miniature (4096 distinct keys) whose expected output -- the
+    stable sort of the ranks' inputs in rank order -- every rank recomputes with torch.sort(stable)
+    from the seeds; the rows of all ranks' outputs, in rank order, must match it exactly."""
+    import collections
+
+    import pyarrow as pa
+    import torch
+    import torch.distributed as dist
+
+    def make(r):
+        m = 120_000 + 1_000 * r
+        g = torch.Generator(device="cuda").manual_seed(1000 + r)
+        low = torch.randint(0, 4096, (m,), dtype=torch.int64, device="cuda", generator=g)
+        keys = torch.full((m, KEY_BYTES), 3, dtype=torch.uint8, device="cuda")
+        keys[:, 8] = (low >> 8).to(torch.uint8)
+        keys[:, 9] = (low & 255).to(torch.uint8)
+        ids = torch.arange(m, dtype=torch.int64, device="cuda") + (r << 32)
+        payload = torch.zeros((m, PAYLOAD_BYTES), dtype=torch.uint8, device="cuda")
+        payload[:, :8] = ids.view(torch.uint8).view(m, 8)
+        return low, ids, keys, payload
+
+    lows, idss = [], []
+    for r in range(world):
+        low, ids, keys, payload = make(r)
+        lows.append(low)
+        idss.append(ids)
+        if r == rank:
+            mine = ds.DeviceArrowBlock(collections.OrderedDict(
+                key=ds.DeviceColumn(pa.binary(KEY_BYTES), keys.view(-1)),
+                payload=ds.DeviceColumn(pa.binary(PAYLOAD_BYTES), payload.view(-1))), keys.shape[0])
+    order = torch.sort(torch.cat(lows), stable=True).indices
+    want = torch.cat(idss)[order]
+    out = sort_fn(mine)
+    got = out.columns["payload"].data.view(-1, PAYLOAD_BYTES)[:, :8].contiguous().view(torch.int64).view(-1)
+    if world > 1:
+        cap = int(want.numel())
+        pad = torch.full((cap + 1,), -1, dtype=torch.int64, device="cuda")
+        pad[0] = got.numel()
+        pad[1: 1 + got.numel()] = got
+        allp = torch.empty((world, cap + 1), dtype=torch.int64, device="cuda")
+        dist.all_gather_into_tensor(allp.view(-1), pad)
+        got = torch.cat([allp[r, 1: 1 + int(allp[r, 0])] for r in range(world)])
+    return got.numel() == want.numel() and bool(torch.equal(got, want))
 
 
 def _bind_to_gpu_numa_node(gpu_index: int) -> None:
@@ -240,48 +359,78 @@ def run_ours(args):
             out = res.get_blocks()[0]
         return out
 
+    def sort_one(blk):
+        if world > 1:
+            from ray_memory_management_b200 import distributed
+
+            return distributed.sort_block(blk, "key", descending=False)
+        return ds.Dataset.from_blocks([blk]).sort("key").get_blocks()[0]
+
     # the first exchanges on a fresh box also set up NCCL and the symmetric buffers
     warmup = args.warmup if world == 1 else max(args.warmup, 5)
+    validated = None
     for i in range(warmup):
         out = one_step()
-        if i == 0 and world == 1:
+        if i == 0 and not args.no_validate:
             torch.cuda.synchronize()
-            check_sorted(out, n)
+            if args.corrupt and rank == world - 1:
+                out.columns["payload"].data[out.num_rows * PAYLOAD_BYTES // 2] ^= 1
+            validated = validate_output(ds, block, out, world, rank)
+            if world == 1:
+                validated["idx_equal_all_passes"] = validate_tie_order(ds, block, out)
+                validated["ok"] = validated["ok"] and validated["idx_equal_all_passes"]
+            del out
+            validated["miniature_bit_exact"] = validate_miniature(ds, world, rank, sort_one)
+            validated["ok"] = validated["ok"] and validated["miniature_bit_exact"]
+            if not validated["ok"]:
+                if rank == 0:
+                    print(json.dumps({"metric": METRIC, "validated": validated, "error": "output failed validation"}),
+                          flush=True)
+                sys.exit(3)
+            continue
         del out
 
     import ctypes
 
+    if world > 1:
+        from ray_memory_management_b200 import distributed as _D
+
+        _D.EXCHANGE_LOG = []
     sampler = ClockSampler(local_rank)
     barrier()
     if rank == 0:
         sampler.start()
     launches0 = lib.ds_debug_launch_count()
     lib.ds_debug_pass_timing(1)
-    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    ev0.record()
-    for _ in range(args.steps):
+    step_ev = [torch.cuda.Event(enable_timing=True) for _ in range(args.steps + 1)]
+    step_ev[0].record()
+    for k in range(args.steps):
         out = one_step()
         del out
-    ev1.record()
+        step_ev[k + 1].record()
     barrier()
     lib.ds_debug_pass_timing(0)
     launches = int(lib.ds_debug_launch_count() - launches0)
-    ms = ev0.elapsed_time(ev1)
+    ms = step_ev[0].elapsed_time(step_ev[-1])
+    step_ms = [step_ev[k].elapsed_time(step_ev[k + 1]) for k in range(args.steps)]
     timed = {}
     for kind, name in ((0, "pass"), (1, "gather")):
         t_ms, t_cnt, t_bytes = ctypes.c_double(0), ctypes.c_int32(0), ctypes.c_double(0)
         lib.ds_debug_collect_timing(kind, ctypes.byref(t_ms), ctypes.byref(t_cnt), ctypes.byref(t_bytes))
         timed[name] = (t_ms.value, t_cnt.value, t_bytes.value)
     if world > 1:
-        t = torch.tensor([ms], dtype=torch.float64, device="cuda")
+        t = torch.tensor([ms] + step_ms, dtype=torch.float64, device="cuda")
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        ms = float(t.item())
+        ms = float(t[0].item())
+        step_ms = [float(x) for x in t[1:].cpu().tolist()]
     ms_per_step = ms / args.steps
     value = world * n * ROW_BYTES / (ms_per_step * 1e-3) / 1e9
+    ss = sorted(step_ms)
+    step_stats = {"min": ss[0], "median": ss[len(ss) // 2], "max": ss[-1]}
 
     peak, peak_src = measured_peak()
     try:
-        with open(os.path.join(ROOT, "profiles", "r01_kernel_traffic.json")) as f:
+        with open(os.path.join(ROOT, "profiles", "r02_kernel_traffic.json")) as f:
             traffic_per_alg_byte = json.load(f)
     except Exception:
         traffic_per_alg_byte = {}
@@ -291,31 +440,104 @@ def run_ours(args):
         if not t_cnt:
             return None
         achieved = t_bytes / (t_ms * 1e-3) / 1e9           # algorithmic bytes / CUDA-event time
-        ratio = traffic_per_alg_byte.get(name, {}).get("dram_bytes_per_algorithmic_byte")
+        ent = traffic_per_alg_byte.get(name, {})
+        ratio = ent.get("dram_bytes_per_algorithmic_byte")
         return {
             "kernel": label, "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
             "frac": achieved / peak, "frac_of_8TBs_spec": achieved / 8000.0,
             "traffic": (t_bytes / t_cnt * ratio) if ratio else None,
-            "traffic_source": "ncu dram__bytes_read.sum+dram__bytes_write.sum per launch (profiles/r01_kernel_traffic.json), "
-                              "scaled to this launch's rows",
+            "traffic_source": (f"ncu dram__bytes_read.sum+dram__bytes_write.sum of {ent.get('kernel')} at git "
+                               f"{ent.get('git')} (profiles/r02_kernel_traffic.json), scaled to this launch's rows")
+            if ratio else None,
             "peak_source": peak_src, "launches_timed": t_cnt, "avg_launch_ms": t_ms / t_cnt,
             "algorithmic_bytes_per_launch": t_bytes / t_cnt,
             "share_of_step": t_ms / ms if world == 1 else None,
         }
 
-    roof_gather = roofline_of("gather", "gather_rows_kernel<uint16> (payload gather by permutation, 4 + 2*90 B per row)")
+    roof_gather = roofline_of("gather", "payload gather by permutation (ds_gather_rows, 4 + 2*90 B per row)")
     roof_pass = roofline_of("pass", "onesweep_pass_kernel_v3 (one 8-bit LSD pass over key80+idx32, 28 B per row)")
     # the dominant kernel is the one with the larger share of the timed region
     dominant, other = (roof_gather, roof_pass)
     if roof_gather is None or (roof_pass is not None and timed["pass"][0] > timed["gather"][0]):
         dominant, other = roof_pass, roof_gather
 
-    if world > 1 and os.environ.get("DS_DIST_TIMING") == "1":
-        from ray_memory_management_b200 import distributed as _D
+    # ---- N > 1: the exchange against NVLink, from CUDA events inside sort_block
+    roofline_exchange = None
+    phases = None
+    if world > 1:
+        log = _D.exchange_log()
+        _D.EXCHANGE_LOG = None
+        if log:
+            k = len(log)
+            mean = {f: sum(e[f] for e in log) / k for f in log[0]}
+            # a transfer is as slow as its slowest participant: max over ranks of the durations,
+            # min over ranks of the byte counts (conservative numerator)
+            t = torch.tensor([mean["ms_keys"], mean["ms_payload"], mean["ms_exposed_wait"], mean["ms_first_to_last"],
+                              -mean["bytes_out"], -mean["bytes_in"], -mean["key_bytes_out"]],
+                             dtype=torch.float64, device="cuda")
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            mk, mp_, mw, mt, bo, bi, kbo = (float(x) for x in t.cpu().tolist())
+            bo, bi, kbo = -bo, -bi, -kbo
+            achieved = (bo - kbo) / (mp_ * 1e-3) / 1e9 if mp_ > 0 else None
+            roofline_exchange = {
+                "bound": "nvlink", "unit": "GB/s per direction per GPU", "peak": 900.0,
+                "peak_measured_peer_copy": 770.0,
+                "bytes_out_per_gpu": bo, "bytes_in_per_gpu": bi, "key_bytes_out_per_gpu": kbo,
+                "ms_keys_incl_barriers": mk, "ms_payload": mp_, "ms_exposed_wait_after_key_sort": mw,
+                "ms_total_first_key_to_last_payload": mt,
+                "overlap_hidden_ms": max(mp_ - mw, 0.0),
+                "achieved": achieved, "frac": achieved / 900.0 if achieved else None,
+                "frac_of_measured_peer_copy": achieved / 770.0 if achieved else None,
+                "achieved_whole_exchange": bo / (mt * 1e-3) / 1e9 if mt > 0 else None,
+                "how": "payload bytes this GPU stored into peers' memory / CUDA-event duration of the payload "
+                       "split kernels (ds_split_rows, bulk stores over NVLink) on their stream; mean over the "
+                       "timed steps, max over ranks; the whole-exchange figure divides all remote bytes by the "
+                       "span from the first key byte to the last payload byte, key sort included",
+                "steps": k,
+            }
+        # phases of one extra (untimed) step, and the same with the payload sent AFTER the key sort
+        _D.set_phase_timing(True)
+        one_step()
+        phases = {"concurrent": [(a, round(b, 3)) for a, b in _D.LAST_TIMING]}
+        _D.PAYLOAD_AFTER_SORT = True
+        one_step()
+        one_step()
+        phases["payload_after_key_sort"] = [(a, round(b, 3)) for a, b in _D.LAST_TIMING]
+        _D.PAYLOAD_AFTER_SORT = False
+        _D.set_phase_timing(False)
 
-        one_step()  # collective: every rank takes part, rank 0 reports
-        if rank == 0:
-            print("dist phases (ms):", [(k, round(v, 2)) for k, v in _D.LAST_TIMING], file=sys.stderr)
+    # ---- single GPU: the same records held as blocks_per_gpu blocks (sample_boundaries, the
+    # partition cuts and the merge are then inside the timed region)
+    multiblock = None
+    if world == 1 and args.blocks_per_gpu > 1:
+        nb = args.blocks_per_gpu
+        cuts = [n * i // nb for i in range(nb + 1)]
+        blocks = [block.slice(cuts[i], cuts[i + 1]) for i in range(nb)]
+
+        def multi_step():
+            res, _ = ds.sort_impl(ds.BlockList.from_blocks(blocks), False, "key")
+            return res.get_blocks()
+
+        for _ in range(3):
+            del_me = multi_step()
+        rows_out = sum(b.num_rows for b in del_me)
+        assert rows_out == n, (rows_out, n)
+        del del_me
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(args.steps):
+            del_me = multi_step()
+            del del_me
+        e1.record()
+        torch.cuda.synchronize()
+        mb_ms = e0.elapsed_time(e1) / args.steps
+        multiblock = {"value": n * ROW_BYTES / (mb_ms * 1e-3) / 1e9, "unit": UNIT, "ms_per_step": mb_ms,
+                      "blocks_per_gpu": nb, "output_blocks": nb,
+                      "what": f"the same {n} records as {nb} input blocks of {n // nb} rows "
+                              "(python/ray/data/context.py:19 targets 512 MiB blocks): splitter sampling, "
+                              "range cuts and the merge run inside the timed region"}
+        del blocks
 
     # ---- e2e: pinned host buffers in, pinned host buffers out
     e2e = None
@@ -339,6 +561,7 @@ def run_ours(args):
                         f"(10-byte key fixed_size_binary(10) + 90-byte payload), "
                         f"{world * n * ROW_BYTES / 1e9:.1f} GB total, BASELINE.json configs[1] per GPU",
             "rows_per_gpu": n, "blocks_per_gpu": 1,
+            "exchange": os.environ.get("DS_EXCHANGE", "split") if world > 1 else None,
             "l2": f"inputs ({n * ROW_BYTES / 1e9:.1f} GB/GPU) far exceed the 126 MB L2; no flush needed",
             "parallelism": f"range-partitioned x{world}" if world > 1 else "single GPU",
         },
@@ -347,9 +570,14 @@ def run_ours(args):
         "roofline": dominant,
         "roofline_second_kernel": other,
         "e2e": e2e,
+        "validated": validated,
+        "step_ms": step_stats,
+        "value_multiblock": multiblock,
+        "roofline_exchange": roofline_exchange,
+        "dist_phases_ms": phases,
     }
     if not args.no_cpu_baseline and world == 1:
-        _, desc, _ = cpu_baseline(args.cpu_rows, steps=2)
+        _, desc, _, _ = cpu_baseline(args.cpu_rows, steps=2, warmup=1)
         line["cpu_baseline"] = desc
     print(json.dumps(line), flush=True)
     if world > 1:
@@ -506,14 +734,15 @@ def run_reference(args):
     world = int(os.environ.get("WORLD_SIZE", "1"))
     if rank != 0:
         return
-    rows = args.cpu_rows
-    gbs, desc, secs = cpu_baseline(rows, steps=args.steps, warmup=min(args.warmup, 1))
+    # same warm-up count as the GPU arm, bounded so that the run ends within minutes
+    warm = min(args.warmup, 3)
+    gbs, desc, secs, rows = cpu_baseline(args.cpu_rows, steps=args.steps, warmup=warm)
     per = sum(secs) / len(secs)
     gbs_mean = rows * ROW_BYTES / per / 1e9
     desc = dict(desc, value=gbs_mean)
     line = {
         "impl": "reference", "metric": METRIC, "value": gbs_mean, "unit": UNIT, "n_gpus": world,
-        "steps": args.steps, "warmup": min(args.warmup, 1), "ms_per_step": per * 1e3,
+        "steps": args.steps, "warmup": warm, "ms_per_step": per * 1e3,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8",
         "data": "synthetic",
         "config": {"workload": f"GraySort-format Dataset.sort on host cores: bounded sample of "

@@ -36,8 +36,8 @@ def _de(b: bytes) -> pa.Table:
 
 
 def _map_task(args):
-    i, desc, ser = args
-    parts = O.sort_and_partition(_G["tables"][i], _G["boundaries"], "key", desc)
+    i, desc, ser, boundaries = args
+    parts = O.sort_and_partition(_G["tables"][i], boundaries, "key", desc)
     return [_ser(p) for p in parts] if ser else parts
 
 
@@ -48,8 +48,12 @@ def _reduce_task(args):
     return O.merge_sorted_blocks(parts, "key", desc).num_rows
 
 
-def _init(tables, boundaries):
-    _G["tables"], _G["boundaries"] = tables, boundaries
+def make_pool(tables, procs: int):
+    """The worker processes, started BEFORE any timed region (the reference's Ray workers are
+    running when Dataset.sort is called).  fork: the workers inherit the input tables, which
+    stands for blocks that are "already materialised in the object store"."""
+    _G["tables"] = tables
+    return mp.get_context("fork").Pool(procs)
 
 
 def make_graysort_blocks(n_rows: int, n_blocks: int, seed: int = 1):
@@ -58,26 +62,30 @@ def make_graysort_blocks(n_rows: int, n_blocks: int, seed: int = 1):
     return [t.slice(a, b - a) for a, b in zip(cuts[:-1], cuts[1:])]
 
 
-def time_sort(tables, procs: int, descending: bool = False) -> float:
-    """Seconds for one Dataset.sort of `tables` (sample_boundaries + map + reduce)."""
+def time_sort(tables, procs: int, descending: bool = False, pool=None) -> float:
+    """Seconds for one Dataset.sort of `tables` (sample_boundaries + map + reduce).  With
+    ``procs`` > 1 the map and reduce tasks run in ``pool`` (make_pool; created here, outside
+    the timed region, when none is given); map outputs come back pickled."""
     r = len(tables)
+    own = None
+    if procs > 1 and pool is None:
+        own = pool = make_pool(tables, procs)
+    _G["tables"] = tables
     t0 = time.perf_counter()
     random.seed(0)
     boundaries = O.sample_boundaries(tables, "key", r)
     if procs <= 1:
-        _init(tables, boundaries)
-        maps = [_map_task((i, descending, False)) for i in range(r)]
+        maps = [_map_task((i, descending, False, boundaries)) for i in range(r)]
         for j in range(r):
             _reduce_task(([maps[i][j] for i in range(r)], descending, False))
-        return time.perf_counter() - t0
-    # fork: workers inherit the input tables (inputs are "already materialised in the
-    # object store" when the reference's timer starts); map outputs come back pickled.
-    _init(tables, boundaries)
-    ctx = mp.get_context("fork")
-    with ctx.Pool(procs) as pool:
-        maps = pool.map(_map_task, [(i, descending, True) for i in range(r)], chunksize=1)
+    else:
+        maps = pool.map(_map_task, [(i, descending, True, boundaries) for i in range(r)], chunksize=1)
         pool.map(_reduce_task, [([maps[i][j] for i in range(r)], descending, True) for j in range(r)], chunksize=1)
-    return time.perf_counter() - t0
+    dt = time.perf_counter() - t0
+    if own is not None:
+        own.close()
+        own.join()
+    return dt
 
 
 def host_cores() -> int:

@@ -44,12 +44,15 @@ def bench_gather(n=100_000_000, W=90):
     def run():
         _lib.call("ds_gather_rows", src.data_ptr(), W, n, idx.data_ptr(), n, out.data_ptr(), s)
 
-    variants = [(2, 0, 0, 0)]
-    for mode in (7, 8):
-        for rows, stages, ctas in ((128, 2, 0), (128, 3, 0), (256, 2, 0), (256, 3, 0), (64, 3, 0), (64, 4, 0),
-                                   (128, 2, 2), (128, 4, 0), (96, 3, 0)):
-            variants.append((mode, rows, stages, ctas))
-    for mode, rows, stages, ctas in variants:
+    variants = [(2, 0, 0, 0, 0)]
+    for mode in (8, 7):
+        for rows, stages in ((64, 2), (64, 3), (64, 4), (96, 2), (96, 3), (128, 2), (128, 3), (128, 4), (192, 2),
+                             (256, 2), (32, 4)):
+            variants.append((mode, rows, stages, 0, 0))
+    variants += [(7, 128, 2, 0, 64), (7, 128, 2, 0, 32), (2, 0, 0, 0, 32)]
+    for mode, rows, stages, ctas, l2 in variants:
+        if l2:
+            print("  (cudaLimitMaxL2FetchGranularity", l2, "was", lib.ds_debug_set_l2_fetch_granularity(l2), ")")
         lib.ds_debug_set_gather_mode(mode)
         lib.ds_debug_set_gather_bulk(rows, stages, ctas)
         out.zero_()

@@ -30,7 +30,7 @@ constexpr int GB_MAX_STAGES = 4;
 enum { FETCH_BULK = 0, FETCH_LDGSTS = 1 };
 
 struct GatherBulkPlan {
-  uint32_t rows;    // R: output rows per tile (multiple of 16, <= GB_THREADS)
+  uint32_t rows;    // R: output rows per tile = threads per CTA (multiple of 32, <= GB_THREADS)
   uint32_t stages;  // ring depth
   uint32_t slot;    // bytes of shared memory per fetched row (odd multiple of 16)
   uint32_t chunks;  // 16-byte chunks per slot
@@ -71,6 +71,7 @@ __device__ __forceinline__ void copy_row_even(uint8_t* __restrict__ sm, uint32_t
     *reinterpret_cast<uint16_t*>(sm + d + (nw << 2)) = static_cast<uint16_t>(__byte_perm(prev, 0, sel));
 }
 
+// One thread per row of a tile: blockDim.x == R.
 template <int FETCH>
 __global__ void __launch_bounds__(GB_THREADS)
     gather_bulk_kernel(const uint8_t* __restrict__ src, uint64_t src_bytes, uint32_t W,
@@ -79,9 +80,10 @@ __global__ void __launch_bounds__(GB_THREADS)
   extern __shared__ __align__(128) uint8_t gb_sm[];
   uint64_t* bars = reinterpret_cast<uint64_t*>(gb_sm);        // [GB_MAX_STAGES]
   uint32_t* rowoff = reinterpret_cast<uint32_t*>(gb_sm + 64);  // [stages][R]: byte offset of the row in its stage
-  uint8_t* data = gb_sm + 64 + stages * R * 4;                 // [stages][R * slot] (+16 spare), 16-byte aligned
+  uint32_t* s_idx = rowoff + stages * R;                       // [R]: source rows of the tile fetched next
+  uint8_t* data = gb_sm + 64 + (stages + 1) * R * 4;           // [stages][R * slot] (+16 spare), 16-byte aligned
   const uint32_t image_bytes = R * W;                          // multiple of 16 (R is)
-  uint8_t* image = data + stages * R * slot + 16;              // [2][image_bytes]: packed output tiles
+  uint8_t* image = data + stages * R * slot + 16;              // packed output tile
   const uint32_t tid = threadIdx.x;
   const uint32_t lane = tid & 31;
   const uintptr_t base = reinterpret_cast<uintptr_t>(src);
@@ -90,22 +92,23 @@ __global__ void __launch_bounds__(GB_THREADS)
 
   if (FETCH == FETCH_BULK) {
     if (tid == 0) {
-      for (uint32_t s = 0; s < stages; ++s) mbar_init(&bars[s], GB_THREADS / 32);
+      for (uint32_t s = 0; s < stages; ++s) mbar_init(&bars[s], R / 32);
       mbar_fence_init();
     }
     __syncthreads();
   }
 
-  auto issue = [&](uint32_t t, uint32_t s) {
+  // `my` = source row of output row t * R + tid, loaded one tile ahead of its use
+  auto issue = [&](uint32_t t, uint32_t s, uint32_t my) {
     const uint32_t row0 = t * R;
     const uint32_t rows = min(R, n - row0);
     uint8_t* d = data + s * R * slot;
     uint32_t* ro = rowoff + s * R;
-    if (FETCH == FETCH_BULK) {  // R <= GB_THREADS: at most one row per thread
+    if (FETCH == FETCH_BULK) {
       uintptr_t a0 = 0;
       uint32_t bytes = 0;
       if (tid < rows) {
-        const uintptr_t a = base + static_cast<uint64_t>(ld_stream(idx + row0 + tid)) * W;
+        const uintptr_t a = base + static_cast<uint64_t>(my) * W;
         const uint32_t sh = static_cast<uint32_t>(a & 15);
         a0 = a - sh;
         bytes = (sh + W + 15u) & ~15u;
@@ -122,11 +125,13 @@ __global__ void __launch_bounds__(GB_THREADS)
       __syncwarp();
       if (bytes) bulk_g2s(d + tid * slot, reinterpret_cast<const void*>(a0), bytes, &bars[s]);
     } else {
+      // consecutive lanes take consecutive 16-byte chunks of a row: the source rows come from
+      // shared memory (written by their owners before the last barrier)
       const uint32_t items = rows * chunks;
-      for (uint32_t e = tid; e < items; e += GB_THREADS) {
+      for (uint32_t e = tid; e < items; e += R) {
         const uint32_t r = __umulhi(e, magic_c);
         const uint32_t c = e - r * chunks;
-        const uintptr_t a = base + static_cast<uint64_t>(__ldg(idx + row0 + r)) * W;
+        const uintptr_t a = base + static_cast<uint64_t>(s_idx[r]) * W;
         const uint32_t sh = static_cast<uint32_t>(a & 15);
         if (c == 0) ro[r] = r * slot + sh;
         if (c * 16 >= sh + W) continue;  // chunk lies wholly behind the row
@@ -143,17 +148,38 @@ __global__ void __launch_bounds__(GB_THREADS)
       ldgsts_commit();
     }
   };
+  auto load_idx = [&](uint32_t k) -> uint32_t {  // source row of this thread's row in my k-th tile
+    const uint32_t row = (blockIdx.x + k * gridDim.x) * R + tid;
+    return row < n ? ld_stream(idx + row) : 0u;
+  };
 
   const uint32_t first = blockIdx.x;
   const uint32_t my_tiles = tiles > first ? (tiles - first + gridDim.x - 1) / gridDim.x : 0;
+  // prologue: tiles 0 .. stages-2 are issued; `ahead` holds the source row for tile stages-1
   for (uint32_t k = 0; k + 1 < stages; ++k) {
-    if (k < my_tiles) issue(first + k * gridDim.x, k);
-    else if (FETCH == FETCH_LDGSTS) ldgsts_commit();  // keep the group count uniform
+    if (k < my_tiles) {
+      const uint32_t my = load_idx(k);
+      if (FETCH == FETCH_LDGSTS) {
+        __syncthreads();
+        s_idx[tid] = my;
+        __syncthreads();
+      }
+      issue(first + k * gridDim.x, k, my);
+    } else if (FETCH == FETCH_LDGSTS) {
+      ldgsts_commit();  // keep the group count uniform
+    }
+  }
+  uint32_t ahead = stages - 1 < my_tiles ? load_idx(stages - 1) : 0u;
+  if (FETCH == FETCH_LDGSTS) {
+    __syncthreads();
+    s_idx[tid] = ahead;
+    __syncthreads();
   }
   for (uint32_t it = 0; it < my_tiles; ++it) {
     const uint32_t nxt = it + stages - 1;
-    if (nxt < my_tiles) issue(first + nxt * gridDim.x, nxt % stages);
+    if (nxt < my_tiles) issue(first + nxt * gridDim.x, nxt % stages, ahead);
     else if (FETCH == FETCH_LDGSTS) ldgsts_commit();
+    ahead = nxt + 1 < my_tiles ? load_idx(nxt + 1) : 0u;  // in flight during this iteration
     const uint32_t s = it % stages;
     if (FETCH == FETCH_BULK) {
       mbar_wait(&bars[s], (it / stages) & 1u);
@@ -165,26 +191,25 @@ __global__ void __launch_bounds__(GB_THREADS)
         default: ldgsts_wait<3>(); break;
       }
     }
-    // the bulk store that read image[it & 1] two tiles ago must have drained
-    if (tid == 0 && it >= 2) bulk_wait_read<1>();
+    if (tid == 0 && it >= 1) bulk_wait_read<0>();  // the previous tile's image has been read out
     __syncthreads();
 
     // ---- realign: one thread per row, slot -> packed image
     const uint32_t t = first + it * gridDim.x;
     const uint32_t rows = min(R, n - t * R);
-    uint8_t* img = image + (it & 1u) * image_bytes;
     if (tid < rows)
       copy_row_even(gb_sm, static_cast<uint32_t>(data - gb_sm) + s * R * slot + rowoff[s * R + tid],
-                    static_cast<uint32_t>(img - gb_sm) + tid * W, W);
+                    static_cast<uint32_t>(image - gb_sm) + tid * W, W);
+    if (FETCH == FETCH_LDGSTS) s_idx[tid] = ahead;  // read by the next iteration's issue
     fence_proxy_async_smem();
     __syncthreads();  // image complete; the stage may be refilled
     if (tid == 0) {
       uint8_t* out = dst + static_cast<uint64_t>(t) * R * W;
       const uint32_t nbytes = rows * W;
       const uint32_t body = nbytes & ~15u;
-      if (body) bulk_s2g(out, img, body);
+      if (body) bulk_s2g(out, image, body);
       bulk_commit();
-      for (uint32_t b = body; b < nbytes; ++b) out[b] = img[b];  // ragged last tile only
+      for (uint32_t b = body; b < nbytes; ++b) out[b] = image[b];  // ragged last tile only
     }
   }
   if (tid == 0) bulk_wait<0>();
@@ -201,11 +226,11 @@ static bool gather_bulk_plan(uint32_t W, GatherBulkPlan* p) {
   if (p->stages > GB_MAX_STAGES) p->stages = GB_MAX_STAGES;
   uint32_t rows = g_gb_rows ? g_gb_rows : 128;
   if (rows > GB_THREADS) rows = GB_THREADS;
-  rows &= ~15u;
-  const uint32_t budget = 110 * 1024;  // per CTA: stages + two output images
-  auto need = [&](uint32_t r) { return 64 + p->stages * r * (p->slot + 4) + 16 + 2 * r * W; };
-  while (rows > 16 && need(rows) > budget) rows -= 16;
-  if (rows < 16 || need(rows) > 200 * 1024) return false;
+  rows &= ~31u;
+  const uint32_t budget = 110 * 1024;  // per CTA: stages + the output image
+  auto need = [&](uint32_t r) { return 64 + p->stages * r * (p->slot + 4) + r * 4 + 16 + r * W; };
+  while (rows > 32 && need(rows) > budget) rows -= 32;
+  if (rows < 32 || need(rows) > 200 * 1024) return false;
   p->rows = rows;
   p->smem = need(rows);
   uint32_t ctas = (224u * 1024) / (p->smem + 1024);
@@ -233,7 +258,7 @@ static cudaError_t launch_gather_bulk(int fetch, const void* src, uint32_t W, ui
   cudaError_t e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(p.smem));
   if (e != cudaSuccess) return e;
   ds::note_launch();
-  k<<<blocks, GB_THREADS, p.smem, s>>>(static_cast<const uint8_t*>(src), src_rows * W, W, idx, n,
+  k<<<blocks, p.rows, p.smem, s>>>(static_cast<const uint8_t*>(src), src_rows * W, W, idx, n,
                                        static_cast<uint8_t*>(dst), p.rows, p.stages, p.slot, p.chunks, magic_c,
                                        tiles);
   return cudaGetLastError();

@@ -36,6 +36,8 @@ static_assert(SP_TILE0 == SP_THREADS, "one row per thread and plan tile");
 static_assert(SP_MAX_PARTS <= 32, "one lane per destination");
 
 // ---------------------------------------------------------------- plan
+// One WARP per tile of 256 rows (8 rows per lane, all loads independent), no block barriers
+// after the splitters are staged: counts come from warp ballots.
 template <int KIND>
 __global__ void __launch_bounds__(SP_THREADS)
     split_plan_kernel(const void* __restrict__ col, uint32_t width, const uint8_t* __restrict__ valid,
@@ -43,7 +45,6 @@ __global__ void __launch_bounds__(SP_THREADS)
                       uint8_t* __restrict__ dest_out, uint32_t* __restrict__ tile_counts, uint32_t ntiles) {
   __shared__ uint64_t s_bh[SP_MAX_PARTS];
   __shared__ uint32_t s_bl[SP_MAX_PARTS];
-  __shared__ uint32_t s_wc[2][SP_THREADS / 32][SP_MAX_PARTS];
   const uint32_t tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const uint32_t nparts = nb + 1;
   if (tid < nb) {
@@ -54,43 +55,49 @@ __global__ void __launch_bounds__(SP_THREADS)
     s_bl[tid] = l;
   }
   __syncthreads();
-  uint32_t flip = 0;
-  for (uint32_t t = blockIdx.x; t < ntiles; t += gridDim.x, flip ^= 1u) {
-    const uint32_t i = t * SP_TILE0 + tid;
-    uint32_t d = 0xffffffffu;
-    if (i < n) {
-      if (valid != nullptr && valid[i] == 0) {
-        d = nb;  // null keys travel to the last partition
-      } else {
-        uint64_t kh;
-        uint32_t kl;
-        load_key<KIND>(col, width, i, desc, kh, kl);
+  constexpr int PER = SP_TILE0 / 32;
+  const uint32_t warps = gridDim.x * (SP_THREADS / 32);
+  for (uint32_t t = blockIdx.x * (SP_THREADS / 32) + warp; t < ntiles; t += warps) {
+    const uint32_t base = t * SP_TILE0 + lane;
+    uint64_t kh[PER];
+    uint32_t kl[PER], d[PER];
+#pragma unroll
+    for (int j = 0; j < PER; ++j) {
+      const uint32_t i = base + j * 32;
+      kh[j] = 0;
+      kl[j] = 0;
+      d[j] = 0xffffffffu;
+      if (i < n) {
+        d[j] = 0;
+        if (valid != nullptr && valid[i] == 0) d[j] = nb;  // null keys travel to the last partition
+        else load_key<KIND>(col, width, i, desc, kh[j], kl[j]);
+      }
+    }
+#pragma unroll
+    for (int j = 0; j < PER; ++j) {
+      if (d[j] == 0) {
         uint32_t lo = 0, hi = nb;
         while (lo < hi) {
           const uint32_t mid = (lo + hi) >> 1;
           // asc: count splitters <= key; desc: count splitters strictly before key (encoded)
-          const bool go_right = desc ? key_less(s_bh[mid], s_bl[mid], kh, kl)
-                                     : !key_less(kh, kl, s_bh[mid], s_bl[mid]);
+          const bool go_right = desc ? key_less(s_bh[mid], s_bl[mid], kh[j], kl[j])
+                                     : !key_less(kh[j], kl[j], s_bh[mid], s_bl[mid]);
           if (go_right) lo = mid + 1;
           else hi = mid;
         }
-        d = lo;
+        d[j] = lo;
       }
-      dest_out[i] = static_cast<uint8_t>(d);
+      const uint32_t i = base + j * 32;
+      if (i < n) dest_out[i] = static_cast<uint8_t>(d[j]);
     }
     uint32_t mine = 0;
     for (uint32_t b = 0; b < nparts; ++b) {
-      const uint32_t m = __ballot_sync(0xffffffffu, d == b);
-      if (lane == b) mine = __popc(m);
-    }
-    if (lane < nparts) s_wc[flip][warp][lane] = mine;
-    __syncthreads();  // one barrier per tile: the counters alternate between two copies
-    if (tid < nparts) {
       uint32_t c = 0;
 #pragma unroll
-      for (int w = 0; w < SP_THREADS / 32; ++w) c += s_wc[flip][w][tid];
-      tile_counts[static_cast<size_t>(tid) * (ntiles + 1) + t] = c;
+      for (int j = 0; j < PER; ++j) c += __popc(__ballot_sync(0xffffffffu, d[j] == b));
+      if (lane == b) mine = c;
     }
+    if (lane < nparts) tile_counts[static_cast<size_t>(lane) * (ntiles + 1) + t] = mine;
   }
 }
 
@@ -328,7 +335,7 @@ ds_status ds_split_plan(int32_t key_kind, const void* col, uint32_t width, const
   const uint32_t ntiles = (n32 + SP_TILE0 - 1) / SP_TILE0;
   if (n32) {
     uint32_t blocks = static_cast<uint32_t>(sm_count()) * 8;
-    if (blocks > ntiles) blocks = ntiles;
+    if (blocks > (ntiles + 7) / 8) blocks = (ntiles + 7) / 8;
     note_launch();
     const bool desc = descending != 0;
     switch (key_kind) {

@@ -33,6 +33,15 @@ import os as _os
 
 _TIMING = _os.environ.get("DS_DIST_TIMING", "0") == "1"
 LAST_TIMING: list = []
+# bench.py: when a list, every split-plan sort appends its exchange events here (exchange_log)
+EXCHANGE_LOG = None
+# measurement aid: issue the payload transfer AFTER the key sort instead of beside it
+PAYLOAD_AFTER_SORT = False
+
+
+def set_phase_timing(on: bool) -> None:
+    global _TIMING
+    _TIMING = bool(on)
 
 
 class _Phases:
@@ -134,7 +143,11 @@ def splitters_from_samples(samples: np.ndarray, arrow_type: pa.DataType, world: 
 # the partition into 4 row ranges and pipelined gather / copy per range was measured slower
 # on 2 and on 8 GPUs -- the ranges' gathers compete with the key sort for HBM -- and was
 # dropped; see profiles/r01_multi_gpu.md.)
-_EXCHANGE = _os.environ.get("DS_EXCHANGE", "p2p")  # "fused" | "p2p" (copy engines) | "nccl"
+# "split" (default): streaming split with bulk stores into peer memory (_sort_block_split);
+# "p2p": materialised partition + copy engines; "fused": per-thread peer stores; "nccl"
+_EXCHANGE = _os.environ.get("DS_EXCHANGE", "split")
+# persistent CTAs of the payload split that runs beside the key sort (0 = one per SM)
+_SPLIT_CTAS = int(_os.environ.get("DS_SPLIT_CTAS", "0"))
 _LANES = _os.environ.get("DS_P2P_LANES", "1") == "1"  # one copy stream per destination
 _peer_cache: dict = {}
 
@@ -219,7 +232,7 @@ def _p2p_exchange_all(names, rbs, send, matrix, group):
     receive buffer} (valid until the next exchange on this group), or None when peer memory
     cannot be used (the caller then takes the NCCL path)."""
     world = matrix.shape[0]
-    if not (_EXCHANGE in ("p2p", "fused") and world > 1 and dist.get_backend(group) == "nccl"):
+    if not (_EXCHANGE in ("p2p", "fused", "split") and world > 1 and dist.get_backend(group) == "nccl"):
         return None
     try:
         layout = _PeerLayout(names, rbs, matrix)
@@ -443,6 +456,227 @@ def _sort_block_fused(block, key, descending, boundaries, with_valid, group, ph,
     return DeviceArrowBlock(cols, n_recv)
 
 
+# Exchange measurement of the last sort_block call on this rank (always on: six CUDA events).
+# Filled by _sort_block_split; read with exchange_stats() after the stream has been synchronised.
+_last_exchange: dict = {}
+
+
+def _exchange_entry(e: dict) -> dict:
+    return {"bytes_out": e["bytes_out"], "bytes_in": e["bytes_in"], "key_bytes_out": e["key_bytes_out"],
+            "ms_keys": e["k0"].elapsed_time(e["k1"]), "ms_payload": e["p0"].elapsed_time(e["p1"]),
+            "ms_exposed_wait": e["w0"].elapsed_time(e["w1"]), "ms_first_to_last": e["k0"].elapsed_time(e["w1"])}
+
+
+def exchange_stats() -> Optional[dict]:
+    """Device-side timing of the last split-plan exchange on this rank: bytes that left this
+    GPU for peers and arrived from peers, the duration of the key and payload transfers
+    (CUDA events on the streams that ran them: ms_keys includes the two device barriers around
+    the key transfer), how long the main stream waited for the payload after the key sort, and
+    the span from the first key byte to the last payload byte.  Call after synchronising."""
+    return _exchange_entry(_last_exchange) if _last_exchange else None
+
+
+def exchange_log() -> list:
+    """exchange_stats() of every call since EXCHANGE_LOG was set to a list (synchronise first)."""
+    return [_exchange_entry(e) for e in (EXCHANGE_LOG or [])]
+
+
+def _device_splitters(block, key: str, descending: bool, group, dev):
+    """W-1 splitters chosen ON THE DEVICE, identical on every rank: each rank contributes
+    SAMPLES_PER_RANK slots (Philox-stratified rows of its key column; unused slots, null keys
+    and NaNs are replaced by a value that sorts last and do not count), the slots are
+    all-gathered, sorted with the library's own radix sort and the i/W quantiles of the m valid
+    samples are picked with a device-side index -- no host round trip.  Replaces the driver-side
+    np.sort + quantile of the reference (python/ray/data/_internal/sort.py:105-115).
+    Returns (key column as the kernels compare it, kind, key bytes, bounds tensor)."""
+    import random
+
+    from . import _lib
+    from .block import DeviceColumn, _argsort, _key_kind, _sortable
+
+    world = dist.get_world_size(group)
+    wide = _sortable(block.column(key))
+    kind = _key_kind(wide.type)
+    rb = wide.row_bytes
+    S = SAMPLES_PER_RANK
+    n = block.num_rows
+    k = min(S, n)
+    stream = torch.cuda.current_stream().cuda_stream
+    pack = torch.zeros(S * rb + S, dtype=torch.uint8, device=dev)
+    slots, flags = pack[: S * rb], pack[S * rb:]
+    if k:
+        seed = random.getrandbits(63)
+        _lib.call("ds_sample_rows", wide.ptr, rb, n, k, seed, slots.data_ptr(), stream)
+        if wide.valid is not None:  # same seed -> same rows
+            _lib.call("ds_sample_rows", wide.valid_ptr, 1, n, k, seed, flags.data_ptr(), stream)
+        else:
+            flags[:k] = 1
+    ok = flags != 0
+    if kind == "i64":
+        v = slots.view(torch.int64)
+        v.copy_(torch.where(ok, v, torch.full_like(v, torch.iinfo(torch.int64).max)))
+    elif kind == "f64":
+        v = slots.view(torch.float64)
+        ok = ok & ~torch.isnan(v)
+        flags.copy_(ok.to(torch.uint8))
+        v.copy_(torch.where(ok, v, torch.full_like(v, float("inf"))))
+    else:
+        v = slots.view(S, rb)
+        v.copy_(torch.where(ok[:, None], v, torch.full_like(v, 255)))
+    allp = torch.empty(world * pack.numel(), dtype=torch.uint8, device=dev)
+    dist.all_gather_into_tensor(allp, pack, group=group)
+    allp = allp.view(world, S * rb + S)
+    allslots = allp[:, : S * rb].reshape(world * S * rb)
+    m = allp[:, S * rb:].to(torch.int64).sum()
+    _, srt = _argsort(DeviceColumn(wide.type, allslots), False, True, options=_lib.DS_SORT_NO_PASS_SKIP)
+    picks = (torch.arange(1, world, dtype=torch.int64, device=dev) * m) // world
+    picks = picks.clamp_(0, world * S - 1)
+    bounds = srt.data.view(world * S, rb)[picks]
+    if descending:
+        bounds = bounds.flip(0)
+    return wide, kind, rb, bounds.contiguous()
+
+
+def _split_supported(block, key, world: int) -> bool:
+    from . import _lib
+
+    if world > _lib.DS_MAX_SPLIT_PARTS or block.num_columns == 0:
+        return False
+    for name, c in block.columns.items():
+        if c.is_varlen or c.row_bytes > _lib.DS_SPLIT_MAX_ROW_BYTES:
+            return False
+    return True
+
+
+def _sort_block_split(block, key, descending, group, ph, consume=False):
+    """The default multi-GPU sort plan: the map side is ONE streaming pass per column
+    (ds_split_plan + ds_split_rows) that stores every row, in input order, straight into the
+    receive buffer of the GPU that owns its key range -- bulk stores from shared memory over
+    NVLink, no partitioned copy of the block, no permutation.  Keys go first; the payload
+    columns travel on a second stream beside the radix sort of the received keys.  One host
+    read-back per call (the W x W count matrix together with the validity flags); splitters are
+    chosen on the device.  Returns None when peer memory is unavailable."""
+    import ctypes
+
+    from . import _lib
+    from .block import DeviceArrowBlock, DeviceColumn, _argsort_nulls_last, _gather
+
+    world = dist.get_world_size(group)
+    rank = dist.get_rank(group)
+    dev = _dev()
+    n = block.num_rows
+    names = block.column_names
+    types = {nm: block.columns[nm].type for nm in names}
+    stream = lambda: torch.cuda.current_stream().cuda_stream  # noqa: E731
+    wide, kind, kb, bounds = _device_splitters(block, key, descending, group, dev)
+    ph.mark("sample+splitters")
+    ntiles = (n + _lib.DS_SPLIT_TILE_ROWS - 1) // _lib.DS_SPLIT_TILE_ROWS
+    dest = torch.empty(max(n, 1), dtype=torch.uint8, device=dev)
+    offs = torch.empty(world * (ntiles + 1), dtype=torch.int32, device=dev)
+    # counts of this rank's rows per destination, followed by one "has validity" flag per column
+    info = torch.zeros(world + len(names), dtype=torch.int64, device=dev)
+    code = {"i64": _lib.DS_KEY_I64, "f64": _lib.DS_KEY_F64, "fsb": _lib.DS_KEY_FSB}[kind]
+    _lib.call("ds_split_plan", code, wide.ptr if n else None, kb, wide.valid_ptr if n else None, n,
+              bounds.data_ptr() if world > 1 else None, world - 1, int(descending), dest.data_ptr(),
+              offs.data_ptr(), info.data_ptr(), stream())
+    has_valid = [int(block.columns[nm].valid is not None) for nm in names]
+    if any(has_valid):
+        info[world:] = torch.tensor(has_valid, dtype=torch.int64, device=dev)
+    allinfo = torch.empty(world * info.numel(), dtype=torch.int64, device=dev)
+    dist.all_gather_into_tensor(allinfo, info, group=group)
+    ph.mark("plan")
+    allinfo = allinfo.cpu().numpy().reshape(world, -1)  # the one host read-back of the call
+    matrix = allinfo[:, :world]
+    need_valid = allinfo[:, world:].max(axis=0) != 0
+    with_valid = {nm for nm, f in zip(names, need_valid) if f}
+    wires = []  # (wire name, row bytes, source tensor), key column first
+    for name in [key] + [nm for nm in names if nm != key]:
+        c = block.columns[name]
+        wires.append((name, c.row_bytes, c.data))
+        if name in with_valid:
+            v = c.valid if c.valid is not None else torch.ones(n, dtype=torch.uint8, device=dev)
+            wires.append((name + _VALID, 1, v))
+    nkey = 2 if key in with_valid else 1
+    rbs = {w: rb for w, rb, _ in wires}
+    try:
+        layout = _PeerLayout([w for w, _, _ in wires], rbs, matrix)
+        pb = _peer_buffer(layout.total, group)
+    except Exception as e:  # pragma: no cover - depends on the system
+        import warnings
+
+        warnings.warn(f"peer-memory exchange unavailable ({e!r}); using NCCL all_to_all")
+        return None
+    n_recv = int(matrix[:, rank].sum())
+    ptrs = [int(p) for p in pb.hdl.buffer_ptrs]
+    before = [int(matrix[:rank, d].sum()) for d in range(world)]
+    remote_rows = int(matrix[rank].sum() - matrix[rank, rank])
+    ph.mark("counts")
+
+    def split(w, rb, src, max_ctas):
+        if n == 0:
+            return
+        bases = (ctypes.c_void_p * world)(*[ptrs[d] + layout.off[w] + before[d] * rb for d in range(world)])
+        _lib.call("ds_split_rows", src.data_ptr(), rb, n, dest.data_ptr(), offs.data_ptr(), world, bases,
+                  max_ctas, stream())
+
+    ev = {k: torch.cuda.Event(enable_timing=True) for k in ("k0", "k1", "p0", "p1", "w0", "w1")}
+    main = torch.cuda.current_stream()
+    pb.hdl.barrier(channel=0)  # every rank is done with the buffer's previous contents
+    ev["k0"].record()
+    for w, rb, src in wires[:nkey]:
+        split(w, rb, src, 0)
+    pb.hdl.barrier(channel=1)  # all keys have landed everywhere
+    ev["k1"].record()
+    ph.mark("split keys")
+    recv = {w: pb.buf[layout.off[w]: layout.off[w] + n_recv * rb] for w, rb, _ in wires}
+
+    def column(name):
+        return DeviceColumn(types[name], recv[name], recv.get(name + _VALID))
+
+    def send_payload():
+        pb.side.wait_stream(main)
+        with torch.cuda.stream(pb.side):
+            ev["p0"].record()
+            for w, rb, src in wires[nkey:]:
+                split(w, rb, src, _SPLIT_CTAS)
+                src.record_stream(pb.side)
+            dest.record_stream(pb.side)
+            offs.record_stream(pb.side)
+            ev["p1"].record()
+
+    if not PAYLOAD_AFTER_SORT:
+        send_payload()  # payload rows travel beside the key sort
+    idx, sorted_key, _ = _argsort_nulls_last(column(key), descending)
+    ph.mark("key sort")
+    if PAYLOAD_AFTER_SORT:
+        send_payload()
+    ev["w0"].record()
+    main.wait_stream(pb.side)
+    pb.hdl.barrier(channel=2)  # all payload rows have landed everywhere
+    ev["w1"].record()
+    ph.mark("wait payload")
+    _last_exchange.clear()
+    _last_exchange.update(ev)
+    _last_exchange.update(
+        bytes_out=remote_rows * sum(rbs.values()),
+        bytes_in=(n_recv - int(matrix[rank, rank])) * sum(rbs.values()),
+        key_bytes_out=remote_rows * sum(rb for _, rb, _ in wires[:nkey]))
+    if EXCHANGE_LOG is not None:
+        EXCHANGE_LOG.append(dict(_last_exchange))
+    if consume:  # every row of the input now lives in some rank's receive buffer
+        wires = None
+        block.columns.clear()
+        del dest, offs
+        torch.cuda.synchronize()
+        torch.cuda.empty_cache()
+    cols = collections.OrderedDict()
+    for name in names:
+        cols[name] = sorted_key if name == key else _gather(column(name), idx)
+    ph.mark("gather payload")
+    ph.finish()
+    return DeviceArrowBlock(cols, n_recv)
+
+
 def reserve_peer_buffer(nbytes: int, group=None) -> None:
     """Allocate (collectively) the symmetric receive buffer up front, e.g. before a run
     whose HBM budget leaves no room for the grow-by-25% policy of the on-demand path."""
@@ -476,6 +710,11 @@ def sort_block(block, key: str, descending: bool = False, group=None, consume: b
         from .block import DeviceArrowBlock as _DAB
         block = _DAB(collections.OrderedDict(src_block.columns), src_block.num_rows)
         src_block.columns.clear()
+    if (_EXCHANGE == "split" and world > 1 and dist.get_backend(group) == "nccl" and not var_names
+            and _split_supported(block, key, world)):
+        out = _sort_block_split(block, key, descending, group, ph, consume)
+        if out is not None:
+            return out
     block, with_valid = _agree_on_validity(block, group, dev)
     names = block.column_names
     types = {nm: block.columns[nm].type for nm in names}
@@ -530,7 +769,7 @@ def sort_block(block, key: str, descending: bool = False, group=None, consume: b
     n_recv = int(matrix[:, rank].sum())
     rbs = {w: rb for w, rb, _ in wires}
 
-    use_p2p = _EXCHANGE in ("p2p", "fused") and world > 1 and dist.get_backend(group) == "nccl"
+    use_p2p = _EXCHANGE in ("p2p", "fused", "split") and world > 1 and dist.get_backend(group) == "nccl"
     if use_p2p:
         try:
             layout = _PeerLayout([w for w, _, _ in wires], rbs, matrix)

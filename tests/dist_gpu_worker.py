@@ -59,6 +59,20 @@ def main():
     got = pa.concat_tables(gather_tables(out.to_arrow(), rank, world))
     assert got.equals(O.global_stable_sort(inputs, "k", False)), "int64 distributed sort mismatch"
 
+    # ---- float64 keys with NaNs, a narrow (int32) key, and one rank without rows
+    nf = 0 if rank == world - 1 else 40_000 + 77 * rank
+    kf = rng.random(nf) * 100
+    kf[rng.random(nf) < 0.05] = np.nan
+    tf = pa.table({"k": kf, "i": rng.integers(-50, 50, nf).astype(np.int32),
+                   "r": np.arange(nf, dtype=np.int64) + rank * 10**6})
+    inputs_f = gather_tables(tf, rank, world)
+    for col in ("k", "i"):
+        for desc in (False, True):
+            out = D.sort_block(ds.DeviceArrowBlock.from_arrow(tf), col, descending=desc)
+            got = pa.concat_tables(gather_tables(out.to_arrow(), rank, world))
+            want = O.global_stable_sort(inputs_f, col, desc)
+            assert got.equals(want), f"distributed sort mismatch on {col!r} desc={desc}"
+
     # ---- sort with null keys and null payload values on some ranks only
     kn = rng.integers(-1000, 1000, 50_000, dtype=np.int64)
     tn = pa.table({"k": pa.array(kn, mask=(rng.random(50_000) < 0.1) if rank % 2 == 0 else None),

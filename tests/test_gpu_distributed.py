@@ -11,9 +11,10 @@ torch = pytest.importorskip("torch")
 HERE = os.path.dirname(os.path.abspath(__file__))
 
 
-@pytest.mark.parametrize("exchange", ["p2p", "fused", "nccl"])
+@pytest.mark.parametrize("exchange", ["split", "p2p", "fused", "nccl"])
 def test_distributed_plans_over_nccl(exchange):
-    """p2p: copy engines into symmetric peer memory; fused: the partition kernel stores rows
+    """split: streaming split with bulk stores into peer memory (the default);
+    p2p: copy engines into symmetric peer memory; fused: the partition kernel stores rows
     straight into the peers' buffers; nccl: all_to_all_single fallback."""
     if not torch.cuda.is_available() or torch.cuda.device_count() < 2:
         pytest.skip("needs at least 2 GPUs")
