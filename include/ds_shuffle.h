@@ -146,9 +146,11 @@ ds_status ds_scatter_rows_to_parts(const void* src, uint32_t row_bytes, uint64_t
  *   boundaries        nb keys (device) in the column's own encoding, ordered like the sort
  *                     (same rule as ds_partition_hist_scatter_*); nb + 1 <= DS_MAX_SPLIT_PARTS
  *   dest_out          n bytes: destination of row i
- *   tile_offsets_out  (nb+1) * (ntiles+1) uint32, ntiles = ceil(n / DS_SPLIT_TILE_ROWS):
- *                     entry [d*(ntiles+1) + t] = rows of destination d in tiles < t;
- *                     entry [d*(ntiles+1) + ntiles] = all rows of destination d
+ *   tile_offsets_out  capacity ds_split_table_words(n, nb+1) uint32.  The first
+ *                     (nb+1) * (ntiles+1) words, ntiles = ceil(n / DS_SPLIT_TILE_ROWS), are the
+ *                     table: entry [d*(ntiles+1) + t] = rows of destination d in tiles < t;
+ *                     entry [d*(ntiles+1) + ntiles] = all rows of destination d.  The rest is
+ *                     scratch of the scan.
  *   counts_out        nb+1 uint64 rows per destination (device)
  * ds_split_rows: moves one column.  Row i (destination d = dest[i]) is stored at
  *   dst_bases[d] + (number of earlier rows with destination d) * row_bytes; dst_bases[d] may
@@ -165,6 +167,7 @@ ds_status ds_scatter_rows_to_parts(const void* src, uint32_t row_bytes, uint64_t
 #define DS_SPLIT_TILE_ROWS 256
 #define DS_MAX_SPLIT_PARTS 32
 #define DS_SPLIT_MAX_ROW_BYTES 256
+uint64_t ds_split_table_words(uint64_t n, uint32_t nparts);
 ds_status ds_split_plan(int32_t key_kind, const void* col, uint32_t width, const uint8_t* valid,
                         uint64_t n, const void* boundaries, uint32_t nb, int32_t descending,
                         uint8_t* dest_out, uint32_t* tile_offsets_out, uint64_t* counts_out,
@@ -256,6 +259,9 @@ ds_status ds_segment_heads_i64(const int64_t* sorted_keys, uint64_t n, uint32_t*
  *   - the first call on a device looks up the array's device address (a one-time
  *     set-up step with that device current); make that first call before any stream
  *     capture begins.
+ *     The address is cached per device for the life of the process: after a
+ *     cudaDeviceReset the cached value is stale and the entry point must not be used
+ *     again in that process.
  *   - all calls on a device share the one array and find it as the previous call
  *     left it; nothing in it needs clearing (every counter is rewritten before it is
  *     read).  Two calls whose kernels overlap on the GPU (different streams, no

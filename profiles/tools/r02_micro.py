@@ -81,7 +81,7 @@ def bench_split(n=100_000_000, nparts=8):
         bnd[i, 0] = (i + 1) * 256 // nparts
     ntiles = (n + 255) // 256
     dest = torch.empty(n, dtype=torch.uint8, device="cuda")
-    offs = torch.empty(nparts * (ntiles + 1), dtype=torch.int32, device="cuda")
+    offs = torch.empty(int(lib.ds_split_table_words(n, nparts)), dtype=torch.int32, device="cuda")
     counts = torch.empty(nparts, dtype=torch.int64, device="cuda")
     s = torch.cuda.current_stream().cuda_stream
 

@@ -8,6 +8,9 @@ import ctypes
 import os
 from ctypes import c_char_p, c_int32, c_size_t, c_uint32, c_uint64, c_void_p, POINTER
 
+from . import _nvtx
+
+_nested = [False]
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "lib", "libds_shuffle.so")
 
@@ -89,10 +92,12 @@ _PROTOS = {
     "ds_group_ids_varlen": [_P, _P, c_uint64, _P, _P, _SZP, _P],
     "ds_widen_keys": [_P, c_int32, c_uint64, _P, _P],
 }
-EXPORTED = ["ds_version", "ds_last_error"] + sorted(_PROTOS)
+EXPORTED = ["ds_version", "ds_last_error", "ds_split_table_words"] + sorted(_PROTOS)
 
 lib.ds_version.restype = c_int32
 lib.ds_version.argtypes = []
+lib.ds_split_table_words.restype = c_uint64
+lib.ds_split_table_words.argtypes = [c_uint64, c_uint32]
 lib.ds_last_error.restype = c_char_p
 lib.ds_last_error.argtypes = []
 for _name, _args in _PROTOS.items():
@@ -108,6 +113,10 @@ def check(status: int) -> None:
 
 def call(name: str, *args) -> None:
     """Call a ds_* entry point and raise on a negative status."""
+    if _nvtx._on:
+        with _nvtx.range(name):
+            check(getattr(lib, name)(*args))
+        return
     check(getattr(lib, name)(*args))
 
 
@@ -117,6 +126,13 @@ def call_ws(name: str, alloc, *args_before_ws, stream):
     ``alloc(nbytes)`` must return an object with ``data_ptr()`` that lives until the
     stream work is done (the caller keeps it).
     """
+    if _nvtx._on and not _nested[0]:
+        _nested[0] = True
+        try:
+            with _nvtx.range(name):
+                return call_ws(name, alloc, *args_before_ws, stream=stream)
+        finally:
+            _nested[0] = False
     fn = getattr(lib, name)
     need = c_size_t(0)
     check(fn(*args_before_ws, None, ctypes.byref(need), stream))

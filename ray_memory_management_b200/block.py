@@ -31,13 +31,35 @@ SortKeyT = Union[None, List[Tuple[str, str]]]
 
 # --------------------------------------------------------------------------- stats
 class BlockExecStats:
-    """python/ray/data/block.py:148-205."""
+    """python/ray/data/block.py:148-205.
+
+    In the reference a task runs synchronously, so its wall time IS the time the work took.
+    Here the map / reduce function of a block only enqueues kernels, so ``wall_time_s`` is the
+    DEVICE time of those launches: a CUDA-event pair recorded on the launching stream by the
+    builder, resolved (one event synchronise) the first time the value is read.
+    ``host_time_s`` keeps the host time spent issuing the launches."""
 
     def __init__(self):
-        self.wall_time_s: Optional[float] = None
+        self._wall: Optional[float] = None
+        self._events = None
+        self.host_time_s: Optional[float] = None
         self.cpu_time_s: Optional[float] = None
         self.node_id = f"cuda:{torch.cuda.current_device()}" if torch.cuda.is_available() else "host"
         self.max_rss_bytes: int = 0
+
+    @property
+    def wall_time_s(self) -> Optional[float]:
+        if self._events is not None:
+            a, b = self._events
+            b.synchronize()
+            self._wall = a.elapsed_time(b) / 1e3
+            self._events = None
+        return self._wall
+
+    @wall_time_s.setter
+    def wall_time_s(self, v: Optional[float]) -> None:
+        self._events = None
+        self._wall = v
 
     @staticmethod
     def builder() -> "_BlockExecStatsBuilder":
@@ -53,10 +75,19 @@ class _BlockExecStatsBuilder:
     def __init__(self):
         self.start_time = time.perf_counter()
         self.start_cpu = time.process_time()
+        self.start_event = None
+        if torch.cuda.is_available():
+            self.start_event = torch.cuda.Event(enable_timing=True)
+            self.start_event.record()
 
     def build(self) -> BlockExecStats:
         stats = BlockExecStats()
-        stats.wall_time_s = time.perf_counter() - self.start_time
+        stats.host_time_s = time.perf_counter() - self.start_time
+        stats.wall_time_s = stats.host_time_s
+        if self.start_event is not None:
+            end = torch.cuda.Event(enable_timing=True)
+            end.record()
+            stats._events = (self.start_event, end)
         stats.cpu_time_s = time.process_time() - self.start_cpu
         try:
             import resource

@@ -13,7 +13,7 @@
 
 namespace ds {
 
-static int g_gather_mode = 0;  // 0 auto, 1 plain, 2 plain + L2::64B, 3 staged,
+static int g_gather_mode = 0;  // 0 auto (8 where eligible, else 2), 1 plain, 2 plain + L2::64B, 3 staged,
 // 4 staged + L2::64B, 5 direct (no smem idx), 6 32-bit word path for rows of 4k+2 bytes,
 // 7 asynchronous bulk copies per row (gather_bulk.cuh, UBLKCP), 8 the same with 16-byte cp.async.
 // Measured on 100 M x 90-byte rows (ms per sort step): 2: 10.46, 5: 11.0, 3: 12.7, 6: 14.0
@@ -526,7 +526,12 @@ ds_status gather_rows_impl(const void* src, uint32_t row_bytes, uint64_t src_row
   const uintptr_t bits = reinterpret_cast<uintptr_t>(src) | reinterpret_cast<uintptr_t>(dst) | row_bytes;
   cudaError_t e;
   LaunchTimer timer(TIMED_GATHER, s, static_cast<double>(n) * (4.0 + 2.0 * row_bytes));
-  if ((g_gather_mode == 7 || g_gather_mode == 8) && gather_bulk_eligible(src, row_bytes, src_rows, dst)) {
+  // auto: even rows that are not 16-byte multiples take the asynchronous-copy kernel with
+  // 16-byte cp.async + 64-byte L2 fetch hint (4.54 ms per 100 M x 90 B against 4.96 ms for the
+  // granule kernel and 5.07 ms for per-row bulk copies, whose misses fetch 128-byte lines:
+  // profiles/r02_gather_summary.md)
+  if ((g_gather_mode == 0 || g_gather_mode == 7 || g_gather_mode == 8) &&
+      gather_bulk_eligible(src, row_bytes, src_rows, dst)) {
     e = launch_gather_bulk(g_gather_mode == 7 ? FETCH_BULK : FETCH_LDGSTS, src, row_bytes, src_rows, idx, n, dst, s);
   } else if (g_gather_mode == 6 && (row_bytes & 3) == 2 && row_bytes >= 6 && row_bytes <= 4096 &&
       src_rows > 0 && (reinterpret_cast<uintptr_t>(src) & 1) == 0 && (reinterpret_cast<uintptr_t>(dst) & 3) == 0) {

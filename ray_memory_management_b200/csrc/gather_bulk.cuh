@@ -224,7 +224,7 @@ static bool gather_bulk_plan(uint32_t W, GatherBulkPlan* p) {
   p->slot = p->chunks * 16;
   p->stages = g_gb_stages ? g_gb_stages : 2;
   if (p->stages > GB_MAX_STAGES) p->stages = GB_MAX_STAGES;
-  uint32_t rows = g_gb_rows ? g_gb_rows : 128;
+  uint32_t rows = g_gb_rows ? g_gb_rows : 64;
   if (rows > GB_THREADS) rows = GB_THREADS;
   rows &= ~31u;
   const uint32_t budget = 110 * 1024;  // per CTA: stages + the output image

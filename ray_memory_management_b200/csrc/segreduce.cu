@@ -16,6 +16,8 @@
 //   gather is fused.  Algorithmic bytes per row: 4 (idx) + 8 (value).
 #include <type_traits>
 
+#include <atomic>
+
 #include "ds_common.cuh"
 
 namespace ds {
@@ -498,23 +500,26 @@ static __device__ __align__(256) uint32_t g_heads_scratch[HEADS_STATIC_TILES + 1
 // kernel can use, so the device address is looked up once per device (with that
 // device current) and cached.
 static ds_status heads_scratch_address(uint32_t** out, const char* fn) {
-  static uint32_t* cached[64] = {nullptr};
+  // one slot per device; relaxed atomics: concurrent first calls store the same address
+  static std::atomic<uint32_t*> cached[64];
   int dev = 0;
   DS_CUDA(cudaGetDevice(&dev));
   if (dev < 0 || dev >= 64) {
     set_error("%s: device ordinal %d out of range", fn, dev);
     return DS_ERR_UNSUPPORTED;
   }
-  if (cached[dev] == nullptr) {
+  uint32_t* addr = cached[dev].load(std::memory_order_relaxed);
+  if (addr == nullptr) {
     void* p = nullptr;
     cudaError_t e = cudaGetSymbolAddress(&p, g_heads_scratch);
     if (e != cudaSuccess || p == nullptr) {
       set_error("%s: cudaGetSymbolAddress failed: %s", fn, cudaGetErrorString(e));
       return DS_ERR_CUDA;
     }
-    cached[dev] = static_cast<uint32_t*>(p);
+    addr = static_cast<uint32_t*>(p);
+    cached[dev].store(addr, std::memory_order_relaxed);
   }
-  *out = cached[dev];
+  *out = addr;
   return DS_OK;
 }
 

@@ -101,35 +101,94 @@ __global__ void __launch_bounds__(SP_THREADS)
   }
 }
 
-// One CTA per destination: exclusive scan of its ntiles counts in place; entry ntiles and
-// counts_out get the total.
-__global__ void __launch_bounds__(1024)
-    split_scan_kernel(uint32_t* __restrict__ tile_counts, uint32_t ntiles, uint64_t* __restrict__ counts_out) {
-  __shared__ uint32_t s_warp[32];
-  uint32_t* row = tile_counts + static_cast<size_t>(blockIdx.x) * (ntiles + 1);
-  const uint32_t tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  const uint32_t per = (ntiles + 1023) / 1024;
-  const uint32_t lo = min(tid * per, ntiles), hi = min(lo + per, ntiles);
-  uint32_t sum = 0;
-  for (uint32_t i = lo; i < hi; ++i) sum += row[i];
-  uint32_t v = sum;
+// Exclusive scan over tiles of every destination's counts, in place, as reduce-then-scan:
+//   split_seg_sum_kernel   one CTA per (segment of SCAN_SEG tiles, destination): segment total
+//   split_seg_scan_kernel  one CTA per destination: exclusive scan of its segment totals;
+//                          entry ntiles of the table and counts_out get the grand total
+//   split_seg_apply_kernel the same CTAs as the first kernel: exclusive scan inside the segment
+//                          (8 consecutive tiles per thread) plus the segment's offset
+constexpr int SCAN_THREADS = 256;
+constexpr int SCAN_PER = 8;
+constexpr int SCAN_SEG = SCAN_THREADS * SCAN_PER;
+
+__device__ __forceinline__ uint32_t scan_block_exclusive(uint32_t v, uint32_t* s_warp, uint32_t* total) {
+  const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  uint32_t incl = v;
 #pragma unroll
   for (int o = 1; o < 32; o <<= 1) {
-    const uint32_t t = __shfl_up_sync(0xffffffffu, v, o);
-    if ((int)lane >= o) v += t;
+    const uint32_t t = __shfl_up_sync(0xffffffffu, incl, o);
+    if ((int)lane >= o) incl += t;
   }
-  if (lane == 31) s_warp[warp] = v;
+  if (lane == 31) s_warp[warp] = incl;
   __syncthreads();
-  uint32_t run = v - sum;
-  for (uint32_t w = 0; w < warp; ++w) run += s_warp[w];
+  uint32_t before = 0, all = 0;
+  for (uint32_t w = 0; w < blockDim.x / 32; ++w) {
+    const uint32_t c = s_warp[w];
+    if (w < warp) before += c;
+    all += c;
+  }
+  if (total) *total = all;
+  return before + incl - v;
+}
+
+__device__ __forceinline__ void scan_load(const uint32_t* row, uint32_t ntiles, uint32_t first, uint32_t (&c)[SCAN_PER]) {
+#pragma unroll
+  for (int k = 0; k < SCAN_PER; ++k) c[k] = first + k < ntiles ? row[first + k] : 0u;
+}
+
+__global__ void __launch_bounds__(SCAN_THREADS)
+    split_seg_sum_kernel(const uint32_t* __restrict__ tile_counts, uint32_t ntiles, uint32_t nsegs,
+                         uint32_t* __restrict__ seg_sums) {
+  __shared__ uint32_t s_warp[SCAN_THREADS / 32];
+  const uint32_t* row = tile_counts + static_cast<size_t>(blockIdx.y) * (ntiles + 1);
+  uint32_t c[SCAN_PER];
+  scan_load(row, ntiles, blockIdx.x * SCAN_SEG + threadIdx.x * SCAN_PER, c);
+  uint32_t sum = 0;
+#pragma unroll
+  for (int k = 0; k < SCAN_PER; ++k) sum += c[k];
+  uint32_t total;
+  scan_block_exclusive(sum, s_warp, &total);
+  if (threadIdx.x == 0) seg_sums[blockIdx.y * nsegs + blockIdx.x] = total;
+}
+
+__global__ void __launch_bounds__(1024)
+    split_seg_scan_kernel(uint32_t* __restrict__ seg_sums, uint32_t nsegs, uint32_t* __restrict__ tile_counts,
+                          uint32_t ntiles, uint64_t* __restrict__ counts_out) {
+  __shared__ uint32_t s_warp[32];
+  uint32_t* row = seg_sums + static_cast<size_t>(blockIdx.x) * nsegs;
+  const uint32_t per = (nsegs + 1023) / 1024;
+  const uint32_t lo = min(threadIdx.x * per, nsegs), hi = min(lo + per, nsegs);
+  uint32_t sum = 0;
+  for (uint32_t i = lo; i < hi; ++i) sum += row[i];
+  uint32_t total;
+  uint32_t run = scan_block_exclusive(sum, s_warp, &total);
   for (uint32_t i = lo; i < hi; ++i) {
     const uint32_t c = row[i];
     row[i] = run;
     run += c;
   }
-  if (tid == 1023) {
-    row[ntiles] = run;
-    counts_out[blockIdx.x] = run;
+  if (threadIdx.x == 0) {
+    tile_counts[static_cast<size_t>(blockIdx.x) * (ntiles + 1) + ntiles] = total;
+    counts_out[blockIdx.x] = total;
+  }
+}
+
+__global__ void __launch_bounds__(SCAN_THREADS)
+    split_seg_apply_kernel(uint32_t* __restrict__ tile_counts, uint32_t ntiles, uint32_t nsegs,
+                           const uint32_t* __restrict__ seg_sums) {
+  __shared__ uint32_t s_warp[SCAN_THREADS / 32];
+  uint32_t* row = tile_counts + static_cast<size_t>(blockIdx.y) * (ntiles + 1);
+  const uint32_t first = blockIdx.x * SCAN_SEG + threadIdx.x * SCAN_PER;
+  uint32_t c[SCAN_PER];
+  scan_load(row, ntiles, first, c);
+  uint32_t sum = 0;
+#pragma unroll
+  for (int k = 0; k < SCAN_PER; ++k) sum += c[k];
+  uint32_t run = scan_block_exclusive(sum, s_warp, nullptr) + seg_sums[blockIdx.y * nsegs + blockIdx.x];
+#pragma unroll
+  for (int k = 0; k < SCAN_PER; ++k) {
+    if (first + k < ntiles) row[first + k] = run;
+    run += c[k];
   }
 }
 
@@ -357,10 +416,30 @@ ds_status ds_split_plan(int32_t key_kind, const void* col, uint32_t width, const
     }
     DS_LAUNCH_CHECK();
   }
+  // the segment totals of the scan live in the tail of the table's allocation
+  // (ds_split_table_words accounts for them)
+  const uint32_t nsegs = (ntiles + SCAN_SEG - 1) / SCAN_SEG;
+  uint32_t* seg_sums = tile_offsets_out + static_cast<size_t>(nb + 1) * (ntiles + 1);
+  if (nsegs) {
+    note_launch();
+    split_seg_sum_kernel<<<dim3(nsegs, nb + 1), SCAN_THREADS, 0, s>>>(tile_offsets_out, ntiles, nsegs, seg_sums);
+    DS_LAUNCH_CHECK();
+  }
   note_launch();
-  split_scan_kernel<<<nb + 1, 1024, 0, s>>>(tile_offsets_out, ntiles, counts_out);
+  split_seg_scan_kernel<<<nb + 1, 1024, 0, s>>>(seg_sums, nsegs, tile_offsets_out, ntiles, counts_out);
   DS_LAUNCH_CHECK();
+  if (nsegs) {
+    note_launch();
+    split_seg_apply_kernel<<<dim3(nsegs, nb + 1), SCAN_THREADS, 0, s>>>(tile_offsets_out, ntiles, nsegs, seg_sums);
+    DS_LAUNCH_CHECK();
+  }
   return DS_OK;
+}
+
+uint64_t ds_split_table_words(uint64_t n, uint32_t nparts) {
+  const uint64_t ntiles = (n + ds::SP_TILE0 - 1) / ds::SP_TILE0;
+  const uint64_t nsegs = (ntiles + ds::SCAN_SEG - 1) / ds::SCAN_SEG;
+  return static_cast<uint64_t>(nparts) * (ntiles + 1 + nsegs);
 }
 
 ds_status ds_split_rows(const void* src, uint32_t row_bytes, uint64_t n, const uint8_t* dest,

@@ -45,16 +45,30 @@ def set_phase_timing(on: bool) -> None:
 
 
 class _Phases:
+    """Phase boundaries of one multi-GPU plan: CUDA events when phase timing is on, and one
+    NVTX range per phase when ranges are on (each mark closes the previous phase's range)."""
+
     def __init__(self):
         self.ev = []
+        self.open = False
 
     def mark(self, name):
+        from . import _nvtx
+
+        if _nvtx.enabled():
+            if self.open:
+                torch.cuda.nvtx.range_pop()
+            torch.cuda.nvtx.range_push("after:" + name)
+            self.open = True
         if _TIMING:
             e = torch.cuda.Event(enable_timing=True)
             e.record()
             self.ev.append((name, e))
 
     def finish(self):
+        if self.open:
+            torch.cuda.nvtx.range_pop()
+            self.open = False
         if _TIMING and self.ev:
             torch.cuda.synchronize()
             LAST_TIMING[:] = [(self.ev[i + 1][0], self.ev[i][1].elapsed_time(self.ev[i + 1][1]))
@@ -572,7 +586,7 @@ def _sort_block_split(block, key, descending, group, ph, consume=False):
     ph.mark("sample+splitters")
     ntiles = (n + _lib.DS_SPLIT_TILE_ROWS - 1) // _lib.DS_SPLIT_TILE_ROWS
     dest = torch.empty(max(n, 1), dtype=torch.uint8, device=dev)
-    offs = torch.empty(world * (ntiles + 1), dtype=torch.int32, device=dev)
+    offs = torch.empty(int(_lib.lib.ds_split_table_words(n, world)), dtype=torch.int32, device=dev)
     # counts of this rank's rows per destination, followed by one "has validity" flag per column
     info = torch.zeros(world + len(names), dtype=torch.int64, device=dev)
     code = {"i64": _lib.DS_KEY_I64, "f64": _lib.DS_KEY_F64, "fsb": _lib.DS_KEY_FSB}[kind]
@@ -954,10 +968,18 @@ def groupby_block(block, key: str, aggs, group=None):
     matrix = exchange_counts(counts, group, dev)
     names = _partial_names(key, aggs, block)
     cols = collections.OrderedDict()
+    from .block import _row_bytes
+
     for name, t in names:
         c = partial.columns.get(name)
-        send = c.data if c is not None else torch.empty(0, dtype=torch.uint8, device=dev)
-        recv, _ = alltoallv_rows(send, 8, matrix, group)
+        if c is not None:
+            if c.type != t:  # the layout every rank derives must be the one this rank produced
+                raise AssertionError(f"partial column {name!r} is {c.type}, expected {t}")
+            send = c.data[: partial.num_rows * c.row_bytes]
+        else:
+            send = torch.empty(0, dtype=torch.uint8, device=dev)
+        rb = _row_bytes(t)
+        recv, _ = alltoallv_rows(send.contiguous(), rb, matrix, group)
         cols[name] = DeviceColumn(t, recv)
     n_recv = int(matrix[:, rank].sum())
     # received chunks are key-sorted per source and concatenated in rank order: hand them
@@ -974,13 +996,25 @@ def groupby_block(block, key: str, aggs, group=None):
 
 
 def _partial_names(key, aggs, block) -> List[Tuple[str, pa.DataType]]:
-    """Column layout of a combined block (needed on ranks whose partial block is empty):
-    counts are int64, sum/min/max parts have the value column's type."""
-    from .block import resolve_agg_names
+    """Column layout of a combined block, derived from the schema alone so that ranks whose
+    partial block is empty put the same buffers on the wire: run counts (count, nvalid, nrows)
+    are int64, Std's mean and m2 are float64, and the sum / min / max / absmax parts have the
+    64-bit type the reductions compute in (int64 or float64; narrower value columns are
+    widened by block._numeric64)."""
+    from .block import _stand_in_type, resolve_agg_names
+
+    def reduced_type(t: pa.DataType) -> pa.DataType:
+        code, stand_in = _stand_in_type(t)
+        return stand_in if code is not None else t
 
     out = [(key, block.column(key).type)]
     for name, agg in zip(resolve_agg_names(aggs), aggs):
         for part in agg._device_merge_ops():
-            t = pa.int64() if part == "count" else block.column(agg._key_fn).type
+            if part in ("count", "nvalid", "nrows"):
+                t = pa.int64()
+            elif part in ("mean", "m2"):
+                t = pa.float64()
+            else:
+                t = reduced_type(block.column(agg._key_fn).type)
             out.append((f"{name}#{part}", t))
     return out

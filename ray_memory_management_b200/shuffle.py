@@ -16,6 +16,7 @@ all-to-all over NCCL (see distributed.py).
 """
 from typing import Any, Dict, List, Optional, Tuple, Union
 
+from . import _nvtx
 from .block import Block, BlockAccessor, BlockExecStats, BlockList, BlockMetadata
 from .context import DatasetContext
 
@@ -63,7 +64,8 @@ class DeviceShufflePlan(ShuffleOp):
         min_blocks = 1 if getattr(self, "fuse_single_block", False) else 2
         if fused is not None and DatasetContext.get_current().fuse_device_blocks and input_num_blocks >= min_blocks:
             stats = BlockExecStats.builder()
-            res = fused(input_blocks_list, output_num_blocks, *self._map_args)
+            with _nvtx.range(f"{type(self).__name__}.fused"):
+                res = fused(input_blocks_list, output_num_blocks, *self._map_args)
             if res is not None:
                 new_blocks, map_meta = res
                 del input_blocks_list
@@ -82,7 +84,8 @@ class DeviceShufflePlan(ShuffleOp):
         shuffle_map_out = []
         shuffle_map_metadata = []
         for i, block in enumerate(input_blocks_list):
-            refs = self.map(i, block, output_num_blocks, *self._map_args)
+            with _nvtx.range(f"{type(self).__name__}.map[{i}]"):
+                refs = self.map(i, block, output_num_blocks, *self._map_args)
             assert len(refs) == 1 + output_num_blocks, (len(refs), output_num_blocks)
             shuffle_map_metadata.append(refs[-1])  # metadata is LAST (sort.py:58)
             shuffle_map_out.append(refs[:-1])
@@ -99,7 +102,8 @@ class DeviceShufflePlan(ShuffleOp):
             column = [shuffle_map_out[i][j] for i in range(input_num_blocks)]
             for i in range(input_num_blocks):
                 shuffle_map_out[i][j] = None
-            blk, meta = self.reduce(*self._reduce_args, *column)
+            with _nvtx.range(f"{type(self).__name__}.reduce[{j}]"):
+                blk, meta = self.reduce(*self._reduce_args, *column)
             del column
             new_blocks.append(blk)
             new_metadata.append(meta)

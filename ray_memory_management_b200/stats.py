@@ -1,53 +1,65 @@
-"""Per-stage execution stats with the reference's reporting surface.
+"""Per-stage execution stats behind ``Dataset.stats()``.
 
-``DatasetStats`` / ``DatasetStatsBuilder`` follow python/ray/data/_internal/stats.py:39-84
-(builder, substage naming ``<stage>_map`` / ``<stage>_reduce``) and :226-380 (the summary
-text that ``Dataset.stats()`` returns and the reference's test_stats.py canonicalises).
-What differs by construction: "Remote wall/cpu time" are host times of the stream-ordered
-launches of one block's map or reduce function (kernels run asynchronously; ``executed in``
-is the host time of the whole stage including the final synchronisation when the caller
-asked for it), "Tasks per node" counts blocks per CUDA device, and the "Peak heap memory"
-line is the process RSS as in the reference.  No stats actor: nothing here is lazy.
+The reporting surface is the reference's (python/ray/data/_internal/stats.py): a chain of
+``DatasetStats`` nodes, one per executed stage, built through ``DatasetStatsBuilder``;
+all-to-all stages carry one substage per phase named ``<stage>_<phase>`` (``sort_map``,
+``sort_reduce``, ...); ``summary_string()`` prints the text that the reference's tests
+canonicalise, and this module's output is compared with the reference's byte for byte on the
+same metadata (tests/test_host_callers.py).  The implementation is this repository's own: the
+report is assembled from small line producers driven by one table of block statistics.
+
+What the numbers mean here: "Remote wall time" of a block is the DEVICE time of the launches
+that produced it (a CUDA-event pair around the map or reduce function of that block, see
+``BlockExecStats``), "Remote cpu time" the host CPU time spent issuing them, "Tasks per node"
+counts blocks per CUDA device.  There is no stats actor: nothing on this path is lazy.
 """
-import collections
 import time
-from typing import Dict, List, Optional, Set, Union
-
-import numpy as np
+from typing import Callable, Dict, Iterable, Iterator, List, Optional, Sequence, Set, Tuple, Union
 
 from .block import BlockList, BlockMetadata
 
+# (upper bound in seconds, multiplier, suffix): the first row whose bound exceeds the value wins
+_TIME_UNITS: Tuple[Tuple[float, float, str], ...] = ((0.001, 1e6, "us"), (1.0, 1e3, "ms"))
+
 
 def fmt(seconds: float) -> str:
-    if seconds > 1:
-        return str(round(seconds, 2)) + "s"
-    elif seconds > 0.001:
-        return str(round(seconds * 1000, 2)) + "ms"
-    else:
-        return str(round(seconds * 1000 * 1000, 2)) + "us"
+    """2-decimal duration with the unit the reference prints (us up to 1 ms, ms up to 1 s)."""
+    for bound, mult, suffix in _TIME_UNITS:
+        if seconds <= bound:
+            return f"{round(seconds * mult, 2)}{suffix}"
+    return f"{round(seconds, 2)}s"
+
+
+def _mean(values: Sequence[float]) -> float:
+    return float(sum(values)) / len(values)
+
+
+def _phase_names(stage_name: str, phases: Iterable[str]) -> Iterator[str]:
+    """``a->b`` fused stage names keep their full name on the first phase only."""
+    tail = stage_name.rsplit("->", 1)[-1]
+    for i, phase in enumerate(phases):
+        yield f"{stage_name if i == 0 else tail}_{phase}"
 
 
 class DatasetStatsBuilder:
+    """Times one stage on the host from construction to ``build*``."""
+
     def __init__(self, stage_name: str, parent: Optional["DatasetStats"]):
         self.stage_name = stage_name
         self.parent = parent
         self.start_time = time.perf_counter()
 
+    def _finish(self, stages: Dict[str, List[BlockMetadata]], base_name: Optional[str]) -> "DatasetStats":
+        node = DatasetStats(stages=stages, parent=self.parent, base_name=base_name)
+        node.time_total_s = time.perf_counter() - self.start_time
+        return node
+
     def build_multistage(self, stages: Dict[str, List[BlockMetadata]]) -> "DatasetStats":
-        stage_infos = {}
-        for i, (k, v) in enumerate(stages.items()):
-            if i == 0:
-                stage_infos[self.stage_name + "_" + k] = v
-            else:
-                stage_infos[self.stage_name.split("->")[-1] + "_" + k] = v
-        stats = DatasetStats(stages=stage_infos, parent=self.parent, base_name=self.stage_name)
-        stats.time_total_s = time.perf_counter() - self.start_time
-        return stats
+        named = dict(zip(_phase_names(self.stage_name, stages), stages.values()))
+        return self._finish(named, self.stage_name)
 
     def build(self, final_blocks: BlockList) -> "DatasetStats":
-        stats = DatasetStats(stages={self.stage_name: final_blocks.get_metadata()}, parent=self.parent)
-        stats.time_total_s = time.perf_counter() - self.start_time
-        return stats
+        return self._finish({self.stage_name: final_blocks.get_metadata()}, None)
 
 
 class DatasetStats:
@@ -60,95 +72,101 @@ class DatasetStats:
         if parent is not None and not isinstance(parent, list):
             parent = [parent]
         self.parents: Optional[List["DatasetStats"]] = parent
-        self.number = 0 if not self.parents else max(p.number for p in self.parents) + 1
+        self.number = 1 + max(p.number for p in self.parents) if self.parents else 0
         self.base_name = base_name
         DatasetStats._next_uuid += 1
         self.dataset_uuid = f"ds{DatasetStats._next_uuid}"
         self.time_total_s = 0.0
 
-    def _rounded_total(self):
-        r = round(self.time_total_s, 2)
-        return 0 if r <= 0 else r  # also folds -0.0
-
     def child_builder(self, name: str) -> DatasetStatsBuilder:
         return DatasetStatsBuilder(name, self)
 
-    # -- python/ray/data/_internal/stats.py:226-282 ---------------------------------------
+    # ------------------------------------------------------------------ report
     def summary_string(self, already_printed: Optional[Set[str]] = None) -> str:
-        if already_printed is None:
-            already_printed = set()
-        out = ""
-        if self.parents:
-            for p in self.parents:
-                parent_sum = p.summary_string(already_printed)
-                if parent_sum:
-                    out += parent_sum
-                    out += "\n"
-        rounded_total = self._rounded_total()
+        seen = set() if already_printed is None else already_printed
+        chunks = []
+        for p in self.parents or ():
+            text = p.summary_string(seen)
+            if text:
+                chunks.append(text + "\n")
+        chunks.extend(self._own_lines(seen))
+        return "".join(chunks)
+
+    def _elapsed(self):
+        r = round(self.time_total_s, 2)
+        return r if r > 0 else 0  # folds -0.0 and negative clock noise
+
+    def _first_time(self, name: str, seen: Set[str]) -> bool:
+        tag = self.dataset_uuid + name
+        if tag in seen:
+            return False
+        seen.add(tag)
+        return True
+
+    def _own_lines(self, seen: Set[str]) -> Iterator[str]:
+        if not self.stages:
+            return
         if len(self.stages) == 1:
-            stage_name, metadata = next(iter(self.stages.items()))
-            stage_uuid = self.dataset_uuid + stage_name
-            out += "Stage {} {}: ".format(self.number, stage_name)
-            if stage_uuid in already_printed:
-                out += "[execution cached]\n"
+            (name, meta), = self.stages.items()
+            yield f"Stage {self.number} {name}: "
+            if self._first_time(name, seen):
+                yield _head_line(meta, self._elapsed())
+                yield from _block_lines(meta, "")
             else:
-                already_printed.add(stage_uuid)
-                out += self._summarize_blocks(metadata, is_substage=False)
-        elif len(self.stages) > 1:
-            out += "Stage {} {}: executed in {}s\n".format(self.number, self.base_name, rounded_total)
-            for n, (stage_name, metadata) in enumerate(self.stages.items()):
-                stage_uuid = self.dataset_uuid + stage_name
-                out += "\n"
-                out += "\tSubstage {} {}: ".format(n, stage_name)
-                if stage_uuid in already_printed:
-                    out += "\t[execution cached]\n"
-                else:
-                    already_printed.add(stage_uuid)
-                    out += self._summarize_blocks(metadata, is_substage=True)
-        return out
+                yield "[execution cached]\n"
+            return
+        yield f"Stage {self.number} {self.base_name}: executed in {self._elapsed()}s\n"
+        for i, (name, meta) in enumerate(self.stages.items()):
+            yield f"\n\tSubstage {i} {name}: "
+            if self._first_time(name, seen):
+                yield f"{sum(m.exec_stats is not None for m in meta)}/{len(meta)} blocks executed\n"
+                yield from _block_lines(meta, "\t")
+            else:
+                yield "\t[execution cached]\n"
 
-    # -- stats.py:305-380 --------------------------------------------------------------------
-    def _summarize_blocks(self, blocks: List[BlockMetadata], is_substage: bool) -> str:
-        exec_stats = [m.exec_stats for m in blocks if m.exec_stats is not None]
-        indent = "\t" if is_substage else ""
-        rounded_total = self._rounded_total()
-        if is_substage:
-            out = "{}/{} blocks executed\n".format(len(exec_stats), len(blocks))
-        else:
-            out = ""
-            if exec_stats:
-                out = "{}/{} blocks executed in {}s".format(len(exec_stats), len(blocks), rounded_total)
-            if len(exec_stats) < len(blocks):
-                if exec_stats:
-                    out += ", "
-                out += "{}/{} blocks split from parent".format(len(blocks) - len(exec_stats), len(blocks))
-                if not exec_stats:
-                    out += " in {}s".format(rounded_total)
-            out += "\n"
 
-        def four(label, values, f=fmt):
-            return indent + "* {}: {} min, {} max, {} mean, {} total\n".format(
-                label, f(min(values)), f(max(values)), f(np.mean(values)), f(sum(values)))
+def _head_line(meta: List[BlockMetadata], elapsed) -> str:
+    """``a/b blocks executed in Ts[, c/b blocks split from parent]`` of a plain stage."""
+    total = len(meta)
+    ran = sum(m.exec_stats is not None for m in meta)
+    parts = []
+    if ran:
+        parts.append(f"{ran}/{total} blocks executed in {elapsed}s")
+    if ran < total:
+        parts.append(f"{total - ran}/{total} blocks split from parent" + ("" if ran else f" in {elapsed}s"))
+    return ", ".join(parts) + "\n"
 
-        if exec_stats:
-            out += four("Remote wall time", [e.wall_time_s for e in exec_stats])
-            out += four("Remote cpu time", [e.cpu_time_s for e in exec_stats])
-            mem = [round(e.max_rss_bytes / (1024 * 1024), 2) for e in exec_stats]
-            out += indent + "* Peak heap memory usage (MiB): {} min, {} max, {} mean\n".format(
-                min(mem), max(mem), int(np.mean(mem)))
-        rows = [m.num_rows for m in blocks if m.num_rows is not None]
-        if rows:
-            out += indent + "* Output num rows: {} min, {} max, {} mean, {} total\n".format(
-                min(rows), max(rows), int(np.mean(rows)), sum(rows))
-        sizes = [m.size_bytes for m in blocks if m.size_bytes is not None]
-        if sizes:
-            out += indent + "* Output size bytes: {} min, {} max, {} mean, {} total\n".format(
-                min(sizes), max(sizes), int(np.mean(sizes)), sum(sizes))
-        if exec_stats:
-            node_counts = collections.defaultdict(int)
-            for s in exec_stats:
-                node_counts[s.node_id] += 1
-            out += indent + "* Tasks per node: {} min, {} max, {} mean; {} nodes used\n".format(
-                min(node_counts.values()), max(node_counts.values()),
-                int(np.mean(list(node_counts.values()))), len(node_counts))
-        return out
+
+# One row per statistic: (label, values of the blocks, how to print a number, print the total?)
+_Row = Tuple[str, List, Callable[[float], str], bool]
+
+
+def _rows(meta: List[BlockMetadata]) -> Iterator[_Row]:
+    ex = [m.exec_stats for m in meta if m.exec_stats is not None]
+    if ex:
+        yield "Remote wall time", [e.wall_time_s for e in ex], fmt, True
+        yield "Remote cpu time", [e.cpu_time_s for e in ex], fmt, True
+        yield ("Peak heap memory usage (MiB)", [round(e.max_rss_bytes / (1024 * 1024), 2) for e in ex],
+               str, False)
+    for label, attr in (("Output num rows", "num_rows"), ("Output size bytes", "size_bytes")):
+        vals = [getattr(m, attr) for m in meta if getattr(m, attr) is not None]
+        if vals:
+            yield label, vals, str, True
+
+
+def _block_lines(meta: List[BlockMetadata], indent: str) -> Iterator[str]:
+    for label, vals, show, with_total in _rows(meta):
+        mean = _mean(vals)
+        cells = [f"{show(min(vals))} min", f"{show(max(vals))} max",
+                 f"{show(mean) if show is fmt else int(mean)} mean"]
+        if with_total:
+            cells.append(f"{show(sum(vals))} total")
+        yield f"{indent}* {label}: {', '.join(cells)}\n"
+    per_node: Dict[str, int] = {}
+    for m in meta:
+        if m.exec_stats is not None:
+            per_node[m.exec_stats.node_id] = per_node.get(m.exec_stats.node_id, 0) + 1
+    if per_node:
+        c = list(per_node.values())
+        yield (f"{indent}* Tasks per node: {min(c)} min, {max(c)} max, {int(_mean(c))} mean; "
+               f"{len(c)} nodes used\n")

@@ -139,6 +139,23 @@ def main():
             assert np.allclose(x, y, rtol=1e-6, atol=0), name
         else:
             assert np.array_equal(x, y), name
+    # ---- groupby with a narrow key, narrow value columns and Std on an integer column
+    # (partial columns of different widths and types on the wire)
+    tg2 = pa.table({"k": rng.integers(0, 300, 50_000).astype(np.int32),
+                    "a": rng.integers(-1000, 1000, 50_000, dtype=np.int64),
+                    "f": rng.random(50_000).astype(np.float32),
+                    "s": rng.integers(-5, 5, 50_000).astype(np.int32)})
+    inputs2 = gather_tables(tg2, rank, world)
+    out = D.groupby_block(ds.DeviceArrowBlock.from_arrow(tg2), "k",
+                          (ds.Std("a"), ds.Sum("f"), ds.Mean("s"), ds.Min("f"), ds.Max("s")))
+    got = pa.concat_tables([o for o in gather_tables(out.to_arrow(), rank, world) if o.num_rows]).to_pandas()
+    g = pa.concat_tables(inputs2).to_pandas().groupby("k")
+    assert np.array_equal(got["k"].to_numpy(), np.array(sorted(g.groups), dtype=got["k"].dtype))
+    assert np.allclose(got["std(a)"].to_numpy(), g["a"].std(ddof=1).to_numpy(), rtol=1e-6)
+    assert np.allclose(got["sum(f)"].to_numpy(), g["f"].apply(lambda x: x.astype(np.float64).sum()).to_numpy(), rtol=1e-6)
+    assert np.allclose(got["mean(s)"].to_numpy(), g["s"].mean().to_numpy(), rtol=1e-6)
+    assert np.array_equal(got["min(f)"].to_numpy().astype(np.float32), g["f"].min().to_numpy())
+    assert np.array_equal(got["max(s)"].to_numpy(), g["s"].max().to_numpy())
     torch.cuda.synchronize()
     dist.barrier()
     if rank == 0:

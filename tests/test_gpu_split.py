@@ -33,14 +33,15 @@ def _plan(lib, kind, col_dev, width, valid_dev, n, bnd_dev, nb, desc):
     nparts = nb + 1
     ntiles = (n + lib.DS_SPLIT_TILE_ROWS - 1) // lib.DS_SPLIT_TILE_ROWS
     dest = torch.full((max(n, 1),), 255, dtype=torch.uint8, device="cuda")
-    offs = torch.zeros(nparts * (ntiles + 1), dtype=torch.int32, device="cuda")
+    offs = torch.zeros(int(lib.lib.ds_split_table_words(n, nparts)), dtype=torch.int32, device="cuda")
     counts = torch.zeros(nparts, dtype=torch.int64, device="cuda")
     lib.call("ds_split_plan", kind, col_dev.data_ptr() if n else None, width,
              valid_dev.data_ptr() if valid_dev is not None else None, n,
              bnd_dev.data_ptr() if nb else None, nb, int(desc), dest.data_ptr(), offs.data_ptr(),
              counts.data_ptr(), _stream())
     torch.cuda.synchronize()
-    return dest[:n].cpu().numpy(), offs.cpu().numpy().reshape(nparts, ntiles + 1), counts.cpu().numpy(), dest, offs
+    table = offs[: nparts * (ntiles + 1)].cpu().numpy().reshape(nparts, ntiles + 1)
+    return dest[:n].cpu().numpy(), table, counts.cpu().numpy(), dest, offs
 
 
 def _bucket_i64(col, bnd, desc):
@@ -51,7 +52,7 @@ def _bucket_i64(col, bnd, desc):
 
 
 @pytest.mark.parametrize("desc", [False, True])
-@pytest.mark.parametrize("n", [0, 1, 255, 256, 257, 70_001])
+@pytest.mark.parametrize("n", [0, 1, 255, 256, 257, 70_001, 2_100_000])
 def test_split_plan_i64(lib, desc, n):
     rng = np.random.default_rng(n * 2 + desc)
     col = rng.integers(-100, 100, n, dtype=np.int64)
