@@ -157,8 +157,8 @@ ds_status ds_scatter_rows_to_parts(const void* src, uint32_t row_bytes, uint64_t
  *   be peer-mapped memory of another GPU (the rows then cross NVLink as bulk stores issued
  *   from shared memory) or local memory.
  *   dst_bases   HOST array of nparts device pointers
- *   max_ctas    upper bound on the persistent grid (0 = one CTA per SM), so that a caller can
- *               leave SMs to work running beside the transfer
+ *   max_ctas    upper bound on the persistent grid (0 = as many CTAs per SM as fit, up to 3),
+ *               so that a caller can leave room for work that runs beside the transfer
  *   row_bytes <= DS_SPLIT_MAX_ROW_BYTES. */
 #define DS_KEY_I64 0
 #define DS_KEY_U64 1

@@ -210,73 +210,99 @@ __global__ void __launch_bounds__(SP_THREADS)
   constexpr uint32_t T = K * SP_TILE0;
   constexpr uint32_t CHUNKS = T / 32;
   extern __shared__ __align__(128) uint8_t sp_sm[];
-  // layout: bar | chunk counts | span tables | A (tile as it lies in the input) | B[2] (spans)
-  uint64_t* bar = reinterpret_cast<uint64_t*>(sp_sm);
+  // layout: bars | chunk counts | span table | A[2] (tiles as they lie in the input) | B (spans)
+  uint64_t* bars = reinterpret_cast<uint64_t*>(sp_sm);                  // [2]
   uint32_t* s_cc = reinterpret_cast<uint32_t*>(sp_sm + 16);             // [CHUNKS][32]
   uint32_t* s_bstart = s_cc + CHUNKS * 32;                              // [32] byte offset of span data in B
-  const uint32_t a_off = 16 + CHUNKS * 32 * 4 + 32 * 4;                 // multiple of 16
+  const uint32_t a_off0 = 16 + CHUNKS * 32 * 4 + 32 * 4;                // multiple of 16
   const uint32_t a_bytes = T * W;                                       // multiple of 16
-  const uint32_t b_bytes = a_bytes + 32 * SP_MAX_PARTS;
-  const uint32_t b_off0 = a_off + a_bytes + 16;
+  const uint32_t a_stride = a_bytes + 16;                               // + spare for the row copy's look-ahead word
+  const uint32_t b_off = a_off0 + 2 * a_stride;
   const uint32_t tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const uint32_t lt_mask = (1u << lane) - 1u;
   const bool src_aligned = (reinterpret_cast<uintptr_t>(src) & 15) == 0;
+  const size_t my_table = static_cast<size_t>(tid) * (ntiles0 + 1);     // thread b < nparts: its row of the table
 
   if (tid == 0) {
-    mbar_init(bar, 1);
+    mbar_init(&bars[0], 1);
+    mbar_init(&bars[1], 1);
     mbar_fence_init();
   }
   __syncthreads();
 
-  auto load_tile = [&](uint32_t t) {  // called by every thread; the bulk path is one thread's work
-    const uint32_t row0 = t * T;
+  const uint32_t first = blockIdx.x;
+  const uint32_t my_tiles = tiles > first ? (tiles - first + gridDim.x - 1) / gridDim.x : 0;
+  auto tile_of = [&](uint32_t k) { return first + k * gridDim.x; };
+
+  // tile k of this CTA -> A[k & 1]; called by every thread (the bulk path is one thread's work)
+  auto load_tile = [&](uint32_t k) {
+    const uint32_t row0 = tile_of(k) * T;
     const uint32_t rows = min(T, n - row0);
     const uint8_t* g = src + static_cast<uint64_t>(row0) * W;
+    const uint32_t a_off = a_off0 + (k & 1u) * a_stride;
     if (rows == T && src_aligned) {
       if (tid == 0) {
-        mbar_arrive_expect_tx(bar, a_bytes);
-        bulk_g2s(sp_sm + a_off, g, a_bytes, bar);
+        mbar_arrive_expect_tx(&bars[k & 1u], a_bytes);
+        bulk_g2s(sp_sm + a_off, g, a_bytes, &bars[k & 1u]);
       }
     } else {  // ragged last tile or an unaligned column: plain loads
       const uint32_t nbytes = rows * W;
       for (uint32_t b = tid; b < nbytes; b += SP_THREADS) sp_sm[a_off + b] = g[b];
       __syncthreads();
-      if (tid == 0) mbar_arrive_expect_tx(bar, 0);
+      if (tid == 0) mbar_arrive_expect_tx(&bars[k & 1u], 0);
+    }
+  };
+  // what the ranking of tile k needs from global memory, fetched one tile ahead into registers:
+  // the destinations of this thread's rows and (thread b < nparts) the table entries around the tile
+  uint32_t nd[K], noff0 = 0, noff1 = 0;
+  auto prefetch = [&](uint32_t k) {
+    const uint32_t t = tile_of(k);
+    const uint32_t row0 = t * T;
+    const uint32_t rows = min(T, n - row0);
+#pragma unroll
+    for (int q = 0; q < K; ++q) {
+      const uint32_t i = q * SP_TILE0 + tid;
+      nd[q] = i < rows ? dest[row0 + i] : 0xffffffffu;
+    }
+    if (tid < nparts) {
+      noff0 = tile_offsets[my_table + t * K];
+      noff1 = tile_offsets[my_table + min(t * K + K, ntiles0)];
     }
   };
 
-  const uint32_t first = blockIdx.x;
-  const uint32_t my_tiles = tiles > first ? (tiles - first + gridDim.x - 1) / gridDim.x : 0;
-  if (my_tiles) load_tile(first);
+  if (my_tiles) {
+    prefetch(0);
+    load_tile(0);
+    if (my_tiles > 1) load_tile(1);
+  }
   for (uint32_t it = 0; it < my_tiles; ++it) {
-    const uint32_t t = first + it * gridDim.x;
-    const uint32_t row0 = t * T;
-    const uint32_t rows = min(T, n - row0);
-    const uint32_t b_off = b_off0 + (it & 1u) * b_bytes;
-
-    // ---- destinations and stable ranks (row i of the tile = chunk i/32, lane i%32)
+    const uint32_t rows = min(T, n - tile_of(it) * T);
+    const uint32_t a_off = a_off0 + (it & 1u) * a_stride;
     uint32_t d[K], rk[K];
 #pragma unroll
-    for (int k = 0; k < K; ++k) {
-      const uint32_t i = k * SP_TILE0 + tid;
-      d[k] = i < rows ? dest[row0 + i] : 0xffffffffu;
-    }
+    for (int q = 0; q < K; ++q) d[q] = nd[q];
+    const uint32_t off0 = noff0, off1 = noff1;
+    if (it + 1 < my_tiles) prefetch(it + 1);  // lands while this tile is being processed
+
+    // ---- stable ranks (row i of the tile = chunk i/32, lane i%32)
 #pragma unroll
-    for (int k = 0; k < K; ++k) {
+    for (int q = 0; q < K; ++q) {
       uint32_t mine = 0;
-      rk[k] = 0;
+      rk[q] = 0;
       for (uint32_t b = 0; b < nparts; ++b) {
-        const uint32_t m = __ballot_sync(0xffffffffu, d[k] == b);
-        if (d[k] == b) rk[k] = __popc(m & lt_mask);
+        const uint32_t m = __ballot_sync(0xffffffffu, d[q] == b);
+        if (d[q] == b) rk[q] = __popc(m & lt_mask);
         if (lane == b) mine = __popc(m);
       }
-      s_cc[(k * 8 + warp) * 32 + lane] = mine;
+      s_cc[(q * 8 + warp) * 32 + lane] = mine;
     }
-    // the bulk stores that read B[it & 1] two tiles ago must have drained
-    if (tid < nparts && it >= 2) bulk_wait_read<1>();
+    // the bulk stores of the previous tile must have read B before it is overwritten
+    if (tid < nparts && it >= 1) bulk_wait_read<0>();
     __syncthreads();
+    uint32_t span_start = 0, span_len = 0;  // thread b < nparts: its span in B and its length
+    uint8_t* span_g = nullptr;              // ... and where it goes
     if (warp == 0) {
-      // lane b: chunk counts -> exclusive offsets within the span; span length; span placement
+      // lane b: chunk counts -> exclusive offsets within the span; then the span's placement
       uint32_t run = 0;
       for (uint32_t c = 0; c < CHUNKS; ++c) {
         const uint32_t v = s_cc[c * 32 + lane];
@@ -284,11 +310,11 @@ __global__ void __launch_bounds__(SP_THREADS)
         run += v;
       }
       uint32_t res = 0, padded = 0;
-      if (lane < nparts && run) {
-        const uint64_t ga = reinterpret_cast<uint64_t>(bases.p[lane]) +
-                            static_cast<uint64_t>(tile_offsets[static_cast<size_t>(lane) * (ntiles0 + 1) + t * K]) * W;
-        res = static_cast<uint32_t>(ga & 15);
-        padded = (res + run * W + 15u) & ~15u;
+      if (lane < nparts && run) {  // run == off1 - off0 by construction of the table
+        span_g = bases.p[lane] + static_cast<uint64_t>(off0) * W;
+        span_len = (off1 - off0) * W;
+        res = static_cast<uint32_t>(reinterpret_cast<uintptr_t>(span_g) & 15);
+        padded = (res + span_len + 15u) & ~15u;
       }
       uint32_t incl = padded;
 #pragma unroll
@@ -296,43 +322,38 @@ __global__ void __launch_bounds__(SP_THREADS)
         const uint32_t v = __shfl_up_sync(0xffffffffu, incl, o);
         if ((int)lane >= o) incl += v;
       }
-      s_bstart[lane] = incl - padded + res;
+      span_start = incl - padded + res;
+      s_bstart[lane] = span_start;
     }
     __syncthreads();
     uint32_t boff[K];
 #pragma unroll
-    for (int k = 0; k < K; ++k)
-      boff[k] = d[k] < nparts ? s_bstart[d[k]] + (s_cc[(k * 8 + warp) * 32 + d[k]] + rk[k]) * W : 0;
+    for (int q = 0; q < K; ++q)
+      boff[q] = d[q] < nparts ? s_bstart[d[q]] + (s_cc[(q * 8 + warp) * 32 + d[q]] + rk[q]) * W : 0;
 
     // ---- the tile has arrived: move every row to its place in its span
-    mbar_wait(bar, it & 1u);
+    mbar_wait(&bars[it & 1u], (it >> 1) & 1u);
 #pragma unroll
-    for (int k = 0; k < K; ++k) {
-      const uint32_t i = k * SP_TILE0 + tid;
+    for (int q = 0; q < K; ++q) {
+      const uint32_t i = q * SP_TILE0 + tid;
       if (i < rows) {
-        if (even_path) copy_row_even(sp_sm, a_off + i * W, b_off + boff[k], W);
-        else copy_row_bytes(sp_sm, a_off + i * W, b_off + boff[k], W);
+        if (even_path) copy_row_even(sp_sm, a_off + i * W, b_off + boff[q], W);
+        else copy_row_bytes(sp_sm, a_off + i * W, b_off + boff[q], W);
       }
     }
     fence_proxy_async_smem();
-    __syncthreads();  // spans complete, A free
-    if (it + 1 < my_tiles) load_tile(first + (it + 1) * gridDim.x);
+    __syncthreads();  // spans complete; A[it & 1] is free for the tile after next
+    if (it + 2 < my_tiles) load_tile(it + 2);
 
     // ---- ship the spans: thread b owns destination b
     if (tid < nparts) {
-      const uint32_t start = s_bstart[tid];
-      // span length = this tile's rows for the destination (difference of the scanned offsets)
-      const size_t o = static_cast<size_t>(tid) * (ntiles0 + 1);
-      const uint32_t t1 = min(t * K + K, ntiles0);
-      const uint32_t len = (tile_offsets[o + t1] - tile_offsets[o + t * K]) * W;
-      if (len) {
-        uint8_t* g = bases.p[tid] + static_cast<uint64_t>(tile_offsets[o + t * K]) * W;
-        const uint8_t* sdat = sp_sm + b_off + start;
-        const uint32_t head = min(len, (16u - (start & 15u)) & 15u);
-        const uint32_t body = (len - head) & ~15u;
-        for (uint32_t b = 0; b < head; ++b) g[b] = sdat[b];
-        if (body) bulk_s2g(g + head, sdat + head, body);
-        for (uint32_t b = head + body; b < len; ++b) g[b] = sdat[b];
+      if (span_len) {
+        const uint8_t* sdat = sp_sm + b_off + span_start;
+        const uint32_t head = min(span_len, (16u - (span_start & 15u)) & 15u);
+        const uint32_t body = (span_len - head) & ~15u;
+        for (uint32_t b = 0; b < head; ++b) span_g[b] = sdat[b];
+        if (body) bulk_s2g(span_g + head, sdat + head, body);
+        for (uint32_t b = head + body; b < span_len; ++b) span_g[b] = sdat[b];
       }
       bulk_commit();
     }
@@ -340,7 +361,7 @@ __global__ void __launch_bounds__(SP_THREADS)
   if (tid < nparts) bulk_wait<0>();
 }
 
-static uint32_t g_split_ctas = 0;  // ds_debug_set_split_ctas: persistent CTAs per SM (0 = default 1)
+static uint32_t g_split_ctas = 0;  // ds_debug_set_split_ctas: persistent CTAs per SM (0 = default: up to 3)
 
 template <int K>
 static cudaError_t launch_split(const void* src, uint32_t W, uint32_t n, const uint8_t* dest,
@@ -349,11 +370,12 @@ static cudaError_t launch_split(const void* src, uint32_t W, uint32_t n, const u
   constexpr uint32_t T = K * SP_TILE0;
   const uint32_t ntiles0 = (n + SP_TILE0 - 1) / SP_TILE0;
   const uint32_t tiles = (n + T - 1) / T;
-  const uint32_t smem = 16 + (T / 32) * 32 * 4 + 32 * 4 + T * W + 16 + 2 * (T * W + 32 * SP_MAX_PARTS) + 16;
+  const uint32_t smem = 16 + (T / 32) * 32 * 4 + 32 * 4 + 2 * (T * W + 16) + T * W + 32 * SP_MAX_PARTS + 16;
   auto k = split_rows_kernel<K>;
   cudaError_t e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem));
   if (e != cudaSuccess) return e;
-  uint32_t per_sm = g_split_ctas ? g_split_ctas : 1;
+  // as many persistent CTAs per SM as fit (up to 3) unless the caller bounds the grid
+  uint32_t per_sm = g_split_ctas ? g_split_ctas : 3;
   const uint32_t fit = (224u * 1024) / (smem + 1024);
   if (per_sm > fit) per_sm = fit ? fit : 1;
   uint32_t blocks = static_cast<uint32_t>(sm_count()) * per_sm;

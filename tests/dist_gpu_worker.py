@@ -24,6 +24,22 @@ def gather_tables(t: pa.Table, rank, world):
     return [pa.ipc.open_stream(b).read_all() for b in out]
 
 
+def tables_equal(a: pa.Table, b: pa.Table) -> bool:
+    """Table.equals with NaN == NaN (Arrow's equality treats NaNs as different)."""
+    if a.schema != b.schema or a.num_rows != b.num_rows:
+        return False
+    for name in a.column_names:
+        x, y = a[name].combine_chunks(), b[name].combine_chunks()
+        if pa.types.is_floating(x.type):
+            if not x.is_valid().equals(y.is_valid()):
+                return False
+            if not np.array_equal(x.fill_null(0).to_numpy(), y.fill_null(0).to_numpy(), equal_nan=True):
+                return False
+        elif not x.equals(y):
+            return False
+    return True
+
+
 def main():
     rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
     torch.cuda.set_device(int(os.environ["LOCAL_RANK"]))
@@ -71,7 +87,7 @@ def main():
             out = D.sort_block(ds.DeviceArrowBlock.from_arrow(tf), col, descending=desc)
             got = pa.concat_tables(gather_tables(out.to_arrow(), rank, world))
             want = O.global_stable_sort(inputs_f, col, desc)
-            assert got.equals(want), f"distributed sort mismatch on {col!r} desc={desc}"
+            assert tables_equal(got, want), f"distributed sort mismatch on {col!r} desc={desc}"
 
     # ---- sort with null keys and null payload values on some ranks only
     kn = rng.integers(-1000, 1000, 50_000, dtype=np.int64)
