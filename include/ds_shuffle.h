@@ -166,7 +166,7 @@ ds_status ds_scatter_rows_to_parts(const void* src, uint32_t row_bytes, uint64_t
 #define DS_KEY_FSB 3
 #define DS_SPLIT_TILE_ROWS 256
 #define DS_MAX_SPLIT_PARTS 32
-#define DS_SPLIT_MAX_ROW_BYTES 256
+#define DS_SPLIT_MAX_ROW_BYTES 200
 uint64_t ds_split_table_words(uint64_t n, uint32_t nparts);
 ds_status ds_split_plan(int32_t key_kind, const void* col, uint32_t width, const uint8_t* valid,
                         uint64_t n, const void* boundaries, uint32_t nb, int32_t descending,

@@ -24,7 +24,7 @@ DS_MAX_PARTITIONS = 256
 DS_KEY_I64, DS_KEY_U64, DS_KEY_F64, DS_KEY_FSB = 0, 1, 2, 3
 DS_SPLIT_TILE_ROWS = 256
 DS_MAX_SPLIT_PARTS = 32
-DS_SPLIT_MAX_ROW_BYTES = 256
+DS_SPLIT_MAX_ROW_BYTES = 200
 DS_SORT_NO_PASS_SKIP = 1
 DS_SORT_NO_PREFIX_REPAIR = 2
 DS_SORT_NO_HYBRID = 4

@@ -210,18 +210,18 @@ __global__ void __launch_bounds__(SP_THREADS)
   constexpr uint32_t T = K * SP_TILE0;
   constexpr uint32_t CHUNKS = T / 32;
   extern __shared__ __align__(128) uint8_t sp_sm[];
-  // layout: bars | chunk counts | span table | A[2] (tiles as they lie in the input) | B (spans)
+  // layout: bars | chunk counts | A[2] (tiles as they lie in the input) | B[2] (spans)
   uint64_t* bars = reinterpret_cast<uint64_t*>(sp_sm);                  // [2]
   uint32_t* s_cc = reinterpret_cast<uint32_t*>(sp_sm + 16);             // [CHUNKS][32]
-  uint32_t* s_bstart = s_cc + CHUNKS * 32;                              // [32] byte offset of span data in B
   const uint32_t a_off0 = 16 + CHUNKS * 32 * 4 + 32 * 4;                // multiple of 16
   const uint32_t a_bytes = T * W;                                       // multiple of 16
   const uint32_t a_stride = a_bytes + 16;                               // + spare for the row copy's look-ahead word
-  const uint32_t b_off = a_off0 + 2 * a_stride;
+  const uint32_t b_off0 = a_off0 + 2 * a_stride;
+  const uint32_t b_stride = a_bytes + 32 * SP_MAX_PARTS;
   const uint32_t tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const uint32_t lt_mask = (1u << lane) - 1u;
   const bool src_aligned = (reinterpret_cast<uintptr_t>(src) & 15) == 0;
-  const size_t my_table = static_cast<size_t>(tid) * (ntiles0 + 1);     // thread b < nparts: its row of the table
+  const size_t my_table = static_cast<size_t>(lane) * (ntiles0 + 1);    // lane b < nparts: its row of the table
 
   if (tid == 0) {
     mbar_init(&bars[0], 1);
@@ -264,7 +264,7 @@ __global__ void __launch_bounds__(SP_THREADS)
       const uint32_t i = q * SP_TILE0 + tid;
       nd[q] = i < rows ? dest[row0 + i] : 0xffffffffu;
     }
-    if (tid < nparts) {
+    if (lane < nparts) {  // every warp lays the spans out for itself
       noff0 = tile_offsets[my_table + t * K];
       noff1 = tile_offsets[my_table + min(t * K + K, ntiles0)];
     }
@@ -278,6 +278,7 @@ __global__ void __launch_bounds__(SP_THREADS)
   for (uint32_t it = 0; it < my_tiles; ++it) {
     const uint32_t rows = min(T, n - tile_of(it) * T);
     const uint32_t a_off = a_off0 + (it & 1u) * a_stride;
+    const uint32_t b_off = b_off0 + (it & 1u) * b_stride;
     uint32_t d[K], rk[K];
 #pragma unroll
     for (int q = 0; q < K; ++q) d[q] = nd[q];
@@ -296,40 +297,41 @@ __global__ void __launch_bounds__(SP_THREADS)
       }
       s_cc[(q * 8 + warp) * 32 + lane] = mine;
     }
-    // the bulk stores of the previous tile must have read B before it is overwritten
-    if (tid < nparts && it >= 1) bulk_wait_read<0>();
+    // the bulk stores that read B[it & 1] two tiles ago must have drained (lane 0 of every
+    // warp ships the spans of its destinations, one bulk group per tile)
+    if (lane == 0 && it >= 2) bulk_wait_read<1>();
     __syncthreads();
-    uint32_t span_start = 0, span_len = 0;  // thread b < nparts: its span in B and its length
-    uint8_t* span_g = nullptr;              // ... and where it goes
-    if (warp == 0) {
-      // lane b: chunk counts -> exclusive offsets within the span; then the span's placement
-      uint32_t run = 0;
-      for (uint32_t c = 0; c < CHUNKS; ++c) {
-        const uint32_t v = s_cc[c * 32 + lane];
-        s_cc[c * 32 + lane] = run;
-        run += v;
-      }
-      uint32_t res = 0, padded = 0;
-      if (lane < nparts && run) {  // run == off1 - off0 by construction of the table
-        span_g = bases.p[lane] + static_cast<uint64_t>(off0) * W;
-        span_len = (off1 - off0) * W;
-        res = static_cast<uint32_t>(reinterpret_cast<uintptr_t>(span_g) & 15);
-        padded = (res + span_len + 15u) & ~15u;
-      }
-      uint32_t incl = padded;
+    // Every warp lays the spans out for itself (no second barrier, no serial section): lane b
+    // sums destination b's chunk counts -- those of earlier chunks give the offset of this
+    // warp's rows inside the span, all of them the span's length -- and a warp scan over the
+    // padded lengths places the spans in B with the byte alignment of their global address.
+    uint32_t before[K], total = 0;
 #pragma unroll
-      for (int o = 1; o < 32; o <<= 1) {
-        const uint32_t v = __shfl_up_sync(0xffffffffu, incl, o);
-        if ((int)lane >= o) incl += v;
-      }
-      span_start = incl - padded + res;
-      s_bstart[lane] = span_start;
+    for (uint32_t c = 0; c < CHUNKS; ++c) {
+      if ((c & 7u) == warp) before[c >> 3] = total;
+      total += s_cc[c * 32 + lane];
     }
-    __syncthreads();
+    uint32_t span_len = 0, res = 0, padded = 0;
+    uint8_t* span_g = nullptr;
+    if (lane < nparts && total) {  // total == off1 - off0 by construction of the table
+      span_g = bases.p[lane] + static_cast<uint64_t>(off0) * W;
+      span_len = (off1 - off0) * W;
+      res = static_cast<uint32_t>(reinterpret_cast<uintptr_t>(span_g) & 15);
+      padded = (res + span_len + 15u) & ~15u;
+    }
+    uint32_t incl = padded;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const uint32_t v = __shfl_up_sync(0xffffffffu, incl, o);
+      if ((int)lane >= o) incl += v;
+    }
+    const uint32_t span_start = incl - padded + res;  // lane b: byte offset of span b's rows in B
     uint32_t boff[K];
 #pragma unroll
-    for (int q = 0; q < K; ++q)
-      boff[q] = d[q] < nparts ? s_bstart[d[q]] + (s_cc[(q * 8 + warp) * 32 + d[q]] + rk[q]) * W : 0;
+    for (int q = 0; q < K; ++q) {
+      const uint32_t base = __shfl_sync(0xffffffffu, span_start + before[q] * W, d[q] & 31u);
+      boff[q] = base + rk[q] * W;
+    }
 
     // ---- the tile has arrived: move every row to its place in its span
     mbar_wait(&bars[it & 1u], (it >> 1) & 1u);
@@ -345,20 +347,25 @@ __global__ void __launch_bounds__(SP_THREADS)
     __syncthreads();  // spans complete; A[it & 1] is free for the tile after next
     if (it + 2 < my_tiles) load_tile(it + 2);
 
-    // ---- ship the spans: thread b owns destination b
-    if (tid < nparts) {
-      if (span_len) {
-        const uint8_t* sdat = sp_sm + b_off + span_start;
-        const uint32_t head = min(span_len, (16u - (span_start & 15u)) & 15u);
-        const uint32_t body = (span_len - head) & ~15u;
-        for (uint32_t b = 0; b < head; ++b) span_g[b] = sdat[b];
-        if (body) bulk_s2g(span_g + head, sdat + head, body);
-        for (uint32_t b = head + body; b < span_len; ++b) span_g[b] = sdat[b];
-      }
-      bulk_commit();
+    // ---- ship the spans: warp w takes destinations w, w + 8, ...; its lanes copy the few
+    // bytes before and after the 16-byte-aligned body, lane 0 issues the body's bulk store
+    for (uint32_t b = warp; b < nparts; b += SP_THREADS / 32) {
+      const uint32_t start = __shfl_sync(0xffffffffu, span_start, b);
+      const uint32_t len = __shfl_sync(0xffffffffu, span_len, b);
+      const unsigned long long ga = __shfl_sync(0xffffffffu, reinterpret_cast<unsigned long long>(span_g), b);
+      if (len == 0) continue;
+      uint8_t* g = reinterpret_cast<uint8_t*>(ga);
+      const uint8_t* sdat = sp_sm + b_off + start;
+      const uint32_t head = min(len, (16u - (start & 15u)) & 15u);
+      const uint32_t body = (len - head) & ~15u;
+      const uint32_t tail = len - head - body;  // < 16
+      if (lane < head) g[lane] = sdat[lane];
+      if (lane >= 16 && lane - 16 < tail) g[head + body + lane - 16] = sdat[head + body + lane - 16];
+      if (lane == 0 && body) bulk_s2g(g + head, sdat + head, body);
     }
+    if (lane == 0) bulk_commit();
   }
-  if (tid < nparts) bulk_wait<0>();
+  if (lane == 0) bulk_wait<0>();
 }
 
 static uint32_t g_split_ctas = 0;  // ds_debug_set_split_ctas: persistent CTAs per SM (0 = default: up to 3)
@@ -370,7 +377,7 @@ static cudaError_t launch_split(const void* src, uint32_t W, uint32_t n, const u
   constexpr uint32_t T = K * SP_TILE0;
   const uint32_t ntiles0 = (n + SP_TILE0 - 1) / SP_TILE0;
   const uint32_t tiles = (n + T - 1) / T;
-  const uint32_t smem = 16 + (T / 32) * 32 * 4 + 32 * 4 + 2 * (T * W + 16) + T * W + 32 * SP_MAX_PARTS + 16;
+  const uint32_t smem = 16 + (T / 32) * 32 * 4 + 32 * 4 + 2 * (T * W + 16) + 2 * (T * W + 32 * SP_MAX_PARTS) + 16;
   auto k = split_rows_kernel<K>;
   cudaError_t e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem));
   if (e != cudaSuccess) return e;
@@ -496,8 +503,8 @@ ds_status ds_split_rows(const void* src, uint32_t row_bytes, uint64_t n, const u
   const uint32_t n32 = static_cast<uint32_t>(n);
   const uint8_t* dst8 = dest;
   cudaError_t e;
-  // tile of K * 256 rows: the largest whose three shared-memory images stay under ~100 KB
-  const uint32_t per256 = 3u * SP_TILE0 * row_bytes;
+  // tile of K * 256 rows: the largest whose four shared-memory images stay under ~100 KB
+  const uint32_t per256 = 4u * SP_TILE0 * row_bytes;
   if (per256 * 8 <= 100 * 1024) e = launch_split<8>(src, row_bytes, n32, dst8, tile_offsets, nparts, bases, even_path, max_ctas, s);
   else if (per256 * 4 <= 100 * 1024) e = launch_split<4>(src, row_bytes, n32, dst8, tile_offsets, nparts, bases, even_path, max_ctas, s);
   else if (per256 * 2 <= 100 * 1024) e = launch_split<2>(src, row_bytes, n32, dst8, tile_offsets, nparts, bases, even_path, max_ctas, s);

@@ -78,7 +78,7 @@ def test_split_plan_i64(lib, desc, n):
 
 @pytest.mark.parametrize("width,nparts,n", [
     (90, 8, 100_003), (10, 8, 100_003), (90, 2, 5_000), (8, 5, 33_333), (16, 3, 10_000),
-    (7, 4, 9_999), (100, 8, 4_097), (250, 3, 2_049), (2, 32, 50_000), (90, 1, 1_000), (24, 8, 255),
+    (7, 4, 9_999), (100, 8, 4_097), (200, 3, 2_049), (198, 5, 3_000), (2, 32, 50_000), (90, 1, 1_000), (24, 8, 255),
 ])
 @pytest.mark.parametrize("offset", [0, 2, 1])
 def test_split_rows_matches_numpy(lib, width, nparts, n, offset):
