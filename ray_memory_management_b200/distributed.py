@@ -360,14 +360,19 @@ def _agree_on_validity(block, group, dev):
     return DeviceArrowBlock(cols, block.num_rows), {n for n, nd in zip(block.columns, need) if nd}
 
 
-def _wire_columns(parts, names, with_valid, key, dev):
-    """[(wire name, row bytes, send buffer)] with the key column(s) first."""
+def _wire_columns(parts, names, with_valid, key, dev, row_bytes=None):
+    """[(wire name, row bytes, send buffer)] with the key column(s) first.  ``row_bytes``:
+    {column: bytes per row} from the block's schema, so that a rank without rows puts the same
+    widths on the wire as the others."""
     data = _spanning(parts, names, dev)
     wires = []
     order = [key] + [n for n in names if n != key] if key is not None else list(names)
     live = [p for p in parts if p.num_rows]
     for name in order:
-        rb = live[0].columns[name].row_bytes if live else 1
+        if row_bytes is not None:
+            rb = row_bytes[name]
+        else:
+            rb = live[0].columns[name].row_bytes if live else 1
         wires.append((name, rb, data[name]))
         if name in with_valid:
             vs = [p.columns[name].valid for p in live]
@@ -750,6 +755,7 @@ def sort_block(block, key: str, descending: bool = False, group=None, consume: b
         out = _sort_block_fused(block, key, descending, boundaries, with_valid, group, ph, consume)
         if out is not None:
             return out
+    col_rb = {nm: block.columns[nm].row_bytes for nm in names if nm not in var_names}
     parts = acc.partition_unsorted(boundaries, sort_key, descending)
     counts = [p.num_rows for p in parts]
     if consume and world > 1:
@@ -757,7 +763,7 @@ def sort_block(block, key: str, descending: bool = False, group=None, consume: b
         del acc
     ph.mark("partition")
     matrix = exchange_counts(counts, group, dev)
-    wires = _wire_columns(parts, [nm for nm in names if nm not in var_names], with_valid, key, dev)
+    wires = _wire_columns(parts, [nm for nm in names if nm not in var_names], with_valid, key, dev, col_rb)
     var_send = {}
     for nm in var_names:  # lengths ride with the fixed-width wires, the bytes follow below
         from .block import DeviceVarColumn, _concat_varlen
