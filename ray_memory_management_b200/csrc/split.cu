@@ -202,6 +202,14 @@ __device__ __forceinline__ void copy_row_bytes(uint8_t* __restrict__ sm, uint32_
   for (uint32_t b = 0; b < W; ++b) sm[d + b] = sm[s + b];
 }
 
+// one aligned store of 1 << k bytes (k = 0..3), shared -> global
+__device__ __forceinline__ void store_piece(uint8_t* g, const uint8_t* sm, uint32_t k) {
+  if (k == 0) *g = *sm;
+  else if (k == 1) *reinterpret_cast<uint16_t*>(g) = *reinterpret_cast<const uint16_t*>(sm);
+  else if (k == 2) *reinterpret_cast<uint32_t*>(g) = *reinterpret_cast<const uint32_t*>(sm);
+  else *reinterpret_cast<uint2*>(g) = *reinterpret_cast<const uint2*>(sm);
+}
+
 template <int K>  // tile = K * 256 rows
 __global__ void __launch_bounds__(SP_THREADS)
     split_rows_kernel(const uint8_t* __restrict__ src, uint32_t W, uint32_t n, const uint8_t* __restrict__ dest,
@@ -356,11 +364,26 @@ __global__ void __launch_bounds__(SP_THREADS)
       if (len == 0) continue;
       uint8_t* g = reinterpret_cast<uint8_t*>(ga);
       const uint8_t* sdat = sp_sm + b_off + start;
-      const uint32_t head = min(len, (16u - (start & 15u)) & 15u);
+      const uint32_t gap = (16u - (start & 15u)) & 15u;
+      const uint32_t head = min(len, gap);
       const uint32_t body = (len - head) & ~15u;
       const uint32_t tail = len - head - body;  // < 16
-      if (lane < head) g[lane] = sdat[lane];
-      if (lane >= 16 && lane - 16 < tail) g[head + body + lane - 16] = sdat[head + body + lane - 16];
+      if (head < gap) {  // a span shorter than the distance to the next 16-byte boundary: bytes
+        if (lane < head) g[lane] = sdat[lane];
+        continue;
+      }
+      // The bytes before and after the aligned body go out as the few widest aligned stores
+      // that cover them (8/4/2/1 bytes: every remote store is a packet of its own on NVLink).
+      // head < 16 ends on a 16-byte boundary: lane k (0..3) stores the piece of 1 << k bytes if
+      // bit k of head is set, pieces in ascending size; the tail mirrors it from its start.
+      if (lane < 4 && (head >> lane & 1u)) {
+        const uint32_t o = head & ((1u << lane) - 1u);  // bytes of smaller pieces come first
+        store_piece(g + o, sdat + o, lane);
+      } else if (lane >= 4 && lane < 8 && (tail >> (lane - 4) & 1u)) {
+        const uint32_t k = lane - 4;
+        const uint32_t o = head + body + (tail & ~((2u << k) - 1u));  // larger pieces come first
+        store_piece(g + o, sdat + o, k);
+      }
       if (lane == 0 && body) bulk_s2g(g + head, sdat + head, body);
     }
     if (lane == 0) bulk_commit();
@@ -368,6 +391,7 @@ __global__ void __launch_bounds__(SP_THREADS)
   if (lane == 0) bulk_wait<0>();
 }
 
+static uint32_t g_split_k = 0;     // ds_debug_set_split_tile: force tile = k * 256 rows (0 = by row width)
 static uint32_t g_split_ctas = 0;  // ds_debug_set_split_ctas: persistent CTAs per SM (0 = default: up to 3)
 
 template <int K>
@@ -505,7 +529,12 @@ ds_status ds_split_rows(const void* src, uint32_t row_bytes, uint64_t n, const u
   cudaError_t e;
   // tile of K * 256 rows: the largest whose four shared-memory images stay under ~100 KB
   const uint32_t per256 = 4u * SP_TILE0 * row_bytes;
-  if (per256 * 8 <= 100 * 1024) e = launch_split<8>(src, row_bytes, n32, dst8, tile_offsets, nparts, bases, even_path, max_ctas, s);
+  uint32_t kk = g_split_k;
+  if (kk && per256 * kk > 220 * 1024) kk = 0;
+  if (kk == 2) e = launch_split<2>(src, row_bytes, n32, dst8, tile_offsets, nparts, bases, even_path, max_ctas, s);
+  else if (kk == 4) e = launch_split<4>(src, row_bytes, n32, dst8, tile_offsets, nparts, bases, even_path, max_ctas, s);
+  else if (kk == 1) e = launch_split<1>(src, row_bytes, n32, dst8, tile_offsets, nparts, bases, even_path, max_ctas, s);
+  else if (per256 * 8 <= 100 * 1024) e = launch_split<8>(src, row_bytes, n32, dst8, tile_offsets, nparts, bases, even_path, max_ctas, s);
   else if (per256 * 4 <= 100 * 1024) e = launch_split<4>(src, row_bytes, n32, dst8, tile_offsets, nparts, bases, even_path, max_ctas, s);
   else if (per256 * 2 <= 100 * 1024) e = launch_split<2>(src, row_bytes, n32, dst8, tile_offsets, nparts, bases, even_path, max_ctas, s);
   else e = launch_split<1>(src, row_bytes, n32, dst8, tile_offsets, nparts, bases, even_path, max_ctas, s);
@@ -515,6 +544,9 @@ ds_status ds_split_rows(const void* src, uint32_t row_bytes, uint64_t n, const u
   }
   return DS_OK;
 }
+
+// Tuning hook: tile of ds_split_rows = k * 256 rows (1, 2, 4; 0 = chosen from the row width).
+void ds_debug_set_split_tile(uint32_t k) { ds::g_split_k = k; }
 
 // Tuning hook: persistent CTAs per SM of ds_split_rows (0 = default).
 void ds_debug_set_split_ctas(uint32_t per_sm) { ds::g_split_ctas = per_sm; }

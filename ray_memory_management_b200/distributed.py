@@ -161,7 +161,8 @@ def splitters_from_samples(samples: np.ndarray, arrow_type: pa.DataType, world: 
 # "p2p": materialised partition + copy engines; "fused": per-thread peer stores; "nccl"
 _EXCHANGE = _os.environ.get("DS_EXCHANGE", "split")
 # persistent CTAs of the payload split that runs beside the key sort (0 = one per SM)
-_SPLIT_CTAS = int(_os.environ.get("DS_SPLIT_CTAS", "0"))
+_SPLIT_CTAS = int(_os.environ.get("DS_SPLIT_CTAS", "-1"))  # -1: one per SM
+_SPLIT_TILE = int(_os.environ.get("DS_SPLIT_TILE", "0"))   # tuning: tile = k * 256 rows
 _LANES = _os.environ.get("DS_P2P_LANES", "1") == "1"  # one copy stream per destination
 _peer_cache: dict = {}
 
@@ -638,6 +639,11 @@ def _sort_block_split(block, key, descending, group, ph, consume=False):
         _lib.call("ds_split_rows", src.data_ptr(), rb, n, dest.data_ptr(), offs.data_ptr(), world, bases,
                   max_ctas, stream())
 
+    payload_ctas = _SPLIT_CTAS
+    if payload_ctas < 0:  # beside the key sort: one persistent CTA per SM keeps NVLink busy
+        payload_ctas = torch.cuda.get_device_properties(dev).multi_processor_count
+    if _SPLIT_TILE:
+        _lib.lib.ds_debug_set_split_tile(_SPLIT_TILE)
     ev = {k: torch.cuda.Event(enable_timing=True) for k in ("k0", "k1", "p0", "p1", "w0", "w1")}
     main = torch.cuda.current_stream()
     pb.hdl.barrier(channel=0)  # every rank is done with the buffer's previous contents
@@ -656,11 +662,10 @@ def _sort_block_split(block, key, descending, group, ph, consume=False):
         pb.side.wait_stream(main)
         with torch.cuda.stream(pb.side):
             ev["p0"].record()
+            # (no record_stream: the main stream waits for this stream before the function
+            # returns, so every buffer used here outlives the work that reads it)
             for w, rb, src in wires[nkey:]:
-                split(w, rb, src, _SPLIT_CTAS)
-                src.record_stream(pb.side)
-            dest.record_stream(pb.side)
-            offs.record_stream(pb.side)
+                split(w, rb, src, payload_ctas)
             ev["p1"].record()
 
     if not PAYLOAD_AFTER_SORT:
