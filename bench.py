@@ -38,6 +38,7 @@ KEY_BYTES = 10
 PAYLOAD_BYTES = 90
 PASS_BYTES_PER_ROW = 2 * (KEY_BYTES + 4)  # read + write (key + idx)
 METRIC = "sort_throughput_100B_records"
+DEFAULT_PLAN = "split"  # multi-GPU plan of a run without --plan
 UNIT = "GB/s"
 
 
@@ -62,6 +63,10 @@ def parse_args():
     p.add_argument("--corrupt", action="store_true",
                    help="flip one byte of the first output before validating it: the run must exit non-zero")
     p.add_argument("--no-validate", action="store_true")
+    p.add_argument("--plan", default="auto", choices=["auto", "split", "push"],
+                   help="N > 1: one exchange round (split) or the push-based plan in rounds (push); "
+                        "auto = the plan DESIGN.md records as the faster one")
+    p.add_argument("--rounds", type=int, default=0, help="rounds of the push-based plan (0 = library default)")
     return p.parse_args()
 
 
@@ -348,22 +353,35 @@ def run_ours(args):
             dist.barrier()
         torch.cuda.synchronize()
 
+    plan = args.plan if args.plan != "auto" else DEFAULT_PLAN
+    rounds = args.rounds or None
+
+    def dist_sort(blk):
+        """the rank's output blocks, in key order"""
+        from ray_memory_management_b200 import distributed
+
+        if plan == "push":
+            return distributed.sort_block_push(blk, "key", descending=False, rounds=rounds)[0]
+        return [distributed.sort_block(blk, "key", descending=False, rounds=1)]
+
     def one_step():
         if world > 1:
-            from ray_memory_management_b200 import distributed
-
-            out = distributed.sort_block(block, "key", descending=False)
+            out = dist_sort(block)
         else:
             bl = ds.BlockList.from_blocks([block])
             res, _ = ds.sort_impl(bl, False, "key")
             out = res.get_blocks()[0]
         return out
 
+    def one_block(res):
+        """a step's result as ONE block (validation only, untimed)"""
+        if isinstance(res, list):
+            return res[0] if len(res) == 1 else ds.DeviceArrowBlock.concat(res)
+        return res
+
     def sort_one(blk):
         if world > 1:
-            from ray_memory_management_b200 import distributed
-
-            return distributed.sort_block(blk, "key", descending=False)
+            return one_block(dist_sort(blk))
         return ds.Dataset.from_blocks([blk]).sort("key").get_blocks()[0]
 
     # the first exchanges on a fresh box also set up NCCL and the symmetric buffers
@@ -372,6 +390,7 @@ def run_ours(args):
     for i in range(warmup):
         out = one_step()
         if i == 0 and not args.no_validate:
+            out = one_block(out)
             torch.cuda.synchronize()
             if args.corrupt and rank == world - 1:
                 out.columns["payload"].data[out.num_rows * PAYLOAD_BYTES // 2] ^= 1
@@ -562,6 +581,7 @@ def run_ours(args):
                         f"{world * n * ROW_BYTES / 1e9:.1f} GB total, BASELINE.json configs[1] per GPU",
             "rows_per_gpu": n, "blocks_per_gpu": 1,
             "exchange": os.environ.get("DS_EXCHANGE", "split") if world > 1 else None,
+            "plan": (plan + (f" x{rounds}" if rounds and plan == "push" else "")) if world > 1 else None,
             "l2": f"inputs ({n * ROW_BYTES / 1e9:.1f} GB/GPU) far exceed the 126 MB L2; no flush needed",
             "parallelism": f"range-partitioned x{world}" if world > 1 else "single GPU",
         },
@@ -603,7 +623,7 @@ def run_e2e(args, ds, block, n, world, rank, barrier):
         if world > 1:
             from ray_memory_management_b200 import distributed
 
-            out = distributed.sort_block(blk, "key", descending=False)
+            out = distributed.sort_block(blk, "key", descending=False, rounds=1)
         else:
             out = ds.Dataset.from_blocks([blk]).sort("key").get_blocks()[0]
         del blk
@@ -694,7 +714,7 @@ def _run_e2e_pipelined(args, ds, schema, host_in, host_out, n, world, barrier):
                 c.data.record_stream(main)
             if k + 1 < steps:
                 nxt = upload()
-            out = distributed.sort_block(blk, "key", descending=False)
+            out = distributed.sort_block(blk, "key", descending=False, rounds=1)
             del blk
             done = torch.cuda.Event()
             done.record(main)

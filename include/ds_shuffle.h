@@ -157,6 +157,9 @@ ds_status ds_scatter_rows_to_parts(const void* src, uint32_t row_bytes, uint64_t
  *   be peer-mapped memory of another GPU (the rows then cross NVLink as bulk stores issued
  *   from shared memory) or local memory.
  *   dst_bases   HOST array of nparts device pointers
+ *   dest_mask   bit d set: the rows of destination d are moved by this call; rows of the other
+ *               destinations are left where they are (0 = every destination).  A plan that
+ *               sends its key ranges in rounds calls once per round with that round's mask.
  *   max_ctas    upper bound on the persistent grid (0 = as many CTAs per SM as fit, up to 3),
  *               so that a caller can leave room for work that runs beside the transfer
  *   row_bytes <= DS_SPLIT_MAX_ROW_BYTES. */
@@ -174,7 +177,7 @@ ds_status ds_split_plan(int32_t key_kind, const void* col, uint32_t width, const
                         void* stream);
 ds_status ds_split_rows(const void* src, uint32_t row_bytes, uint64_t n, const uint8_t* dest,
                         const uint32_t* tile_offsets, uint32_t nparts, void* const* dst_bases,
-                        uint32_t max_ctas, void* stream);
+                        uint32_t dest_mask, uint32_t max_ctas, void* stream);
 
 /* ----------------------------------------------------------- partition ---- */
 

@@ -104,7 +104,7 @@ def bench_split(n=100_000_000, nparts=8):
 
                 def rows():
                     _lib.call("ds_split_rows", col.data_ptr(), W, n, dest.data_ptr(), offs.data_ptr(), nparts, arr,
-                              max_ctas, s)
+                              0, max_ctas, s)
 
                 ms = timed(rows)
                 print(f"split rows {name} W={W} ctas/SM={per_sm} max_ctas={max_ctas}: {ms:.3f} ms  "

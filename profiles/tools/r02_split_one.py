@@ -29,6 +29,6 @@ for _ in range(2):
     for col, W in ((keys, 10), (payload, 90)):
         outs = [torch.empty(int(x) * W, dtype=torch.uint8, device="cuda") for x in c]
         arr = (ctypes.c_void_p * nparts)(*[o.data_ptr() for o in outs])
-        _lib.call("ds_split_rows", col.data_ptr(), W, n, dest.data_ptr(), offs.data_ptr(), nparts, arr, 0, s)
+        _lib.call("ds_split_rows", col.data_ptr(), W, n, dest.data_ptr(), offs.data_ptr(), nparts, arr, 0, 0, s)
         torch.cuda.synchronize()
 print("ok")

@@ -214,7 +214,7 @@ template <int K>  // tile = K * 256 rows
 __global__ void __launch_bounds__(SP_THREADS)
     split_rows_kernel(const uint8_t* __restrict__ src, uint32_t W, uint32_t n, const uint8_t* __restrict__ dest,
                       const uint32_t* __restrict__ tile_offsets, uint32_t ntiles0, uint32_t nparts,
-                      SplitBases bases, uint32_t tiles, bool even_path) {
+                      SplitBases bases, uint32_t tiles, bool even_path, uint32_t dest_mask) {
   constexpr uint32_t T = K * SP_TILE0;
   constexpr uint32_t CHUNKS = T / 32;
   extern __shared__ __align__(128) uint8_t sp_sm[];
@@ -299,6 +299,7 @@ __global__ void __launch_bounds__(SP_THREADS)
       uint32_t mine = 0;
       rk[q] = 0;
       for (uint32_t b = 0; b < nparts; ++b) {
+        if (!(dest_mask >> b & 1u)) continue;  // rows of destinations outside the mask stay behind
         const uint32_t m = __ballot_sync(0xffffffffu, d[q] == b);
         if (d[q] == b) rk[q] = __popc(m & lt_mask);
         if (lane == b) mine = __popc(m);
@@ -346,7 +347,7 @@ __global__ void __launch_bounds__(SP_THREADS)
 #pragma unroll
     for (int q = 0; q < K; ++q) {
       const uint32_t i = q * SP_TILE0 + tid;
-      if (i < rows) {
+      if (i < rows && d[q] < nparts && (dest_mask >> d[q] & 1u)) {
         if (even_path) copy_row_even(sp_sm, a_off + i * W, b_off + boff[q], W);
         else copy_row_bytes(sp_sm, a_off + i * W, b_off + boff[q], W);
       }
@@ -397,7 +398,7 @@ static uint32_t g_split_ctas = 0;  // ds_debug_set_split_ctas: persistent CTAs p
 template <int K>
 static cudaError_t launch_split(const void* src, uint32_t W, uint32_t n, const uint8_t* dest,
                                 const uint32_t* tile_offsets, uint32_t nparts, const SplitBases& bases,
-                                bool even_path, uint32_t max_ctas, cudaStream_t s) {
+                                bool even_path, uint32_t dest_mask, uint32_t max_ctas, cudaStream_t s) {
   constexpr uint32_t T = K * SP_TILE0;
   const uint32_t ntiles0 = (n + SP_TILE0 - 1) / SP_TILE0;
   const uint32_t tiles = (n + T - 1) / T;
@@ -414,7 +415,7 @@ static cudaError_t launch_split(const void* src, uint32_t W, uint32_t n, const u
   if (blocks > tiles) blocks = tiles;
   note_launch();
   k<<<blocks, SP_THREADS, smem, s>>>(static_cast<const uint8_t*>(src), W, n, dest, tile_offsets, ntiles0, nparts,
-                                     bases, tiles, even_path);
+                                     bases, tiles, even_path, dest_mask);
   return cudaGetLastError();
 }
 
@@ -497,7 +498,7 @@ uint64_t ds_split_table_words(uint64_t n, uint32_t nparts) {
 
 ds_status ds_split_rows(const void* src, uint32_t row_bytes, uint64_t n, const uint8_t* dest,
                         const uint32_t* tile_offsets, uint32_t nparts, void* const* dst_bases,
-                        uint32_t max_ctas, void* stream) {
+                        uint32_t dest_mask, uint32_t max_ctas, void* stream) {
   using namespace ds;
   if (n == 0) return DS_OK;
   if (n > DS_MAX_ROWS) {
@@ -516,11 +517,18 @@ ds_status ds_split_rows(const void* src, uint32_t row_bytes, uint64_t n, const u
     set_error("%s: NULL pointer", __func__);
     return DS_ERR_INVALID_ARG;
   }
+  if (dest_mask == 0) dest_mask = 0xffffffffu;
   SplitBases bases{};
   uintptr_t bits = reinterpret_cast<uintptr_t>(src) | row_bytes;
   for (uint32_t d = 0; d < nparts; ++d) {
     bases.p[d] = static_cast<unsigned char*>(dst_bases[d]);
-    bits |= reinterpret_cast<uintptr_t>(dst_bases[d]);
+    if (dest_mask >> d & 1u) {
+      if (dst_bases[d] == nullptr) {
+        set_error("%s: dst_bases[%u] is NULL", __func__, d);
+        return DS_ERR_INVALID_ARG;
+      }
+      bits |= reinterpret_cast<uintptr_t>(dst_bases[d]);
+    }
   }
   const bool even_path = (bits & 1) == 0;
   cudaStream_t s = static_cast<cudaStream_t>(stream);
@@ -531,13 +539,13 @@ ds_status ds_split_rows(const void* src, uint32_t row_bytes, uint64_t n, const u
   const uint32_t per256 = 4u * SP_TILE0 * row_bytes;
   uint32_t kk = g_split_k;
   if (kk && per256 * kk > 220 * 1024) kk = 0;
-  if (kk == 2) e = launch_split<2>(src, row_bytes, n32, dst8, tile_offsets, nparts, bases, even_path, max_ctas, s);
-  else if (kk == 4) e = launch_split<4>(src, row_bytes, n32, dst8, tile_offsets, nparts, bases, even_path, max_ctas, s);
-  else if (kk == 1) e = launch_split<1>(src, row_bytes, n32, dst8, tile_offsets, nparts, bases, even_path, max_ctas, s);
-  else if (per256 * 8 <= 100 * 1024) e = launch_split<8>(src, row_bytes, n32, dst8, tile_offsets, nparts, bases, even_path, max_ctas, s);
-  else if (per256 * 4 <= 100 * 1024) e = launch_split<4>(src, row_bytes, n32, dst8, tile_offsets, nparts, bases, even_path, max_ctas, s);
-  else if (per256 * 2 <= 100 * 1024) e = launch_split<2>(src, row_bytes, n32, dst8, tile_offsets, nparts, bases, even_path, max_ctas, s);
-  else e = launch_split<1>(src, row_bytes, n32, dst8, tile_offsets, nparts, bases, even_path, max_ctas, s);
+  if (kk == 2) e = launch_split<2>(src, row_bytes, n32, dst8, tile_offsets, nparts, bases, even_path, dest_mask, max_ctas, s);
+  else if (kk == 4) e = launch_split<4>(src, row_bytes, n32, dst8, tile_offsets, nparts, bases, even_path, dest_mask, max_ctas, s);
+  else if (kk == 1) e = launch_split<1>(src, row_bytes, n32, dst8, tile_offsets, nparts, bases, even_path, dest_mask, max_ctas, s);
+  else if (per256 * 8 <= 100 * 1024) e = launch_split<8>(src, row_bytes, n32, dst8, tile_offsets, nparts, bases, even_path, dest_mask, max_ctas, s);
+  else if (per256 * 4 <= 100 * 1024) e = launch_split<4>(src, row_bytes, n32, dst8, tile_offsets, nparts, bases, even_path, dest_mask, max_ctas, s);
+  else if (per256 * 2 <= 100 * 1024) e = launch_split<2>(src, row_bytes, n32, dst8, tile_offsets, nparts, bases, even_path, dest_mask, max_ctas, s);
+  else e = launch_split<1>(src, row_bytes, n32, dst8, tile_offsets, nparts, bases, even_path, dest_mask, max_ctas, s);
   if (e != cudaSuccess) {
     set_error("%s: launch failed: %s", __func__, cudaGetErrorString(e));
     return DS_ERR_CUDA;

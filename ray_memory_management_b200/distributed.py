@@ -501,11 +501,11 @@ def exchange_log() -> list:
     return [_exchange_entry(e) for e in (EXCHANGE_LOG or [])]
 
 
-def _device_splitters(block, key: str, descending: bool, group, dev):
-    """W-1 splitters chosen ON THE DEVICE, identical on every rank: each rank contributes
+def _device_splitters(block, key: str, descending: bool, group, dev, nparts: Optional[int] = None):
+    """nparts-1 (default W-1) splitters chosen ON THE DEVICE, identical on every rank: each rank contributes
     SAMPLES_PER_RANK slots (Philox-stratified rows of its key column; unused slots, null keys
     and NaNs are replaced by a value that sorts last and do not count), the slots are
-    all-gathered, sorted with the library's own radix sort and the i/W quantiles of the m valid
+    all-gathered, sorted with the library's own radix sort and the i/nparts quantiles of the m valid
     samples are picked with a device-side index -- no host round trip.  Replaces the driver-side
     np.sort + quantile of the reference (python/ray/data/_internal/sort.py:105-115).
     Returns (key column as the kernels compare it, kind, key bytes, bounds tensor)."""
@@ -549,7 +549,8 @@ def _device_splitters(block, key: str, descending: bool, group, dev):
     allslots = allp[:, : S * rb].reshape(world * S * rb)
     m = allp[:, S * rb:].to(torch.int64).sum()
     _, srt = _argsort(DeviceColumn(wide.type, allslots), False, True, options=_lib.DS_SORT_NO_PASS_SKIP)
-    picks = (torch.arange(1, world, dtype=torch.int64, device=dev) * m) // world
+    nparts = world if nparts is None else nparts
+    picks = (torch.arange(1, nparts, dtype=torch.int64, device=dev) * m) // nparts
     picks = picks.clamp_(0, world * S - 1)
     bounds = srt.data.view(world * S, rb)[picks]
     if descending:
@@ -568,14 +569,26 @@ def _split_supported(block, key, world: int) -> bool:
     return True
 
 
-def _sort_block_split(block, key, descending, group, ph, consume=False):
+def _sort_block_split(block, key, descending, group, ph, consume=False, rounds: int = 1):
     """The default multi-GPU sort plan: the map side is ONE streaming pass per column
     (ds_split_plan + ds_split_rows) that stores every row, in input order, straight into the
     receive buffer of the GPU that owns its key range -- bulk stores from shared memory over
     NVLink, no partitioned copy of the block, no permutation.  Keys go first; the payload
     columns travel on a second stream beside the radix sort of the received keys.  One host
-    read-back per call (the W x W count matrix together with the validity flags); splitters are
-    chosen on the device.  Returns None when peer memory is unavailable."""
+    read-back per call (the count matrix together with the validity flags); splitters are
+    chosen on the device.
+
+    ``rounds`` > 1 is the push-based form (python/ray/data/_internal/push_based_shuffle.py:
+    363-526): every rank's key range is cut into ``rounds`` sub-ranges by more splitters, the
+    payload travels one sub-range ("round") at a time, and the receiver finishes round r --
+    gather of the rows whose keys it sorted while they were in flight -- while round r+1 is
+    still arriving.  Where the reference merges the map outputs of a round and reduces the
+    merged runs at the end, the rounds here ARE key sub-ranges, so the "merge" of a round is
+    the sort of its received keys and the final reduce is the gather; the rounds' outputs are
+    consecutive output blocks, no re-merge.
+
+    Returns ([output block per round], {"map", "merge", "reduce"} event pairs) or None when
+    peer memory is unavailable."""
     import ctypes
 
     from . import _lib
@@ -587,27 +600,28 @@ def _sort_block_split(block, key, descending, group, ph, consume=False):
     n = block.num_rows
     names = block.column_names
     types = {nm: block.columns[nm].type for nm in names}
+    R = max(1, min(int(rounds), _lib.DS_MAX_SPLIT_PARTS // world))
+    nd = world * R  # destinations: sub-range r of rank d is destination d * R + r
     stream = lambda: torch.cuda.current_stream().cuda_stream  # noqa: E731
-    wide, kind, kb, bounds = _device_splitters(block, key, descending, group, dev)
+    wide, kind, kb, bounds = _device_splitters(block, key, descending, group, dev, nd)
     ph.mark("sample+splitters")
-    ntiles = (n + _lib.DS_SPLIT_TILE_ROWS - 1) // _lib.DS_SPLIT_TILE_ROWS
     dest = torch.empty(max(n, 1), dtype=torch.uint8, device=dev)
-    offs = torch.empty(int(_lib.lib.ds_split_table_words(n, world)), dtype=torch.int32, device=dev)
+    offs = torch.empty(int(_lib.lib.ds_split_table_words(n, nd)), dtype=torch.int32, device=dev)
     # counts of this rank's rows per destination, followed by one "has validity" flag per column
-    info = torch.zeros(world + len(names), dtype=torch.int64, device=dev)
+    info = torch.zeros(nd + len(names), dtype=torch.int64, device=dev)
     code = {"i64": _lib.DS_KEY_I64, "f64": _lib.DS_KEY_F64, "fsb": _lib.DS_KEY_FSB}[kind]
     _lib.call("ds_split_plan", code, wide.ptr if n else None, kb, wide.valid_ptr if n else None, n,
-              bounds.data_ptr() if world > 1 else None, world - 1, int(descending), dest.data_ptr(),
+              bounds.data_ptr() if nd > 1 else None, nd - 1, int(descending), dest.data_ptr(),
               offs.data_ptr(), info.data_ptr(), stream())
     has_valid = [int(block.columns[nm].valid is not None) for nm in names]
     if any(has_valid):
-        info[world:] = torch.tensor(has_valid, dtype=torch.int64, device=dev)
+        info[nd:] = torch.tensor(has_valid, dtype=torch.int64, device=dev)
     allinfo = torch.empty(world * info.numel(), dtype=torch.int64, device=dev)
     dist.all_gather_into_tensor(allinfo, info, group=group)
     ph.mark("plan")
     allinfo = allinfo.cpu().numpy().reshape(world, -1)  # the one host read-back of the call
-    matrix = allinfo[:, :world]
-    need_valid = allinfo[:, world:].max(axis=0) != 0
+    matrix = allinfo[:, :nd]                            # [source rank, destination]
+    need_valid = allinfo[:, nd:].max(axis=0) != 0
     with_valid = {nm for nm, f in zip(names, need_valid) if f}
     wires = []  # (wire name, row bytes, source tensor), key column first
     for name in [key] + [nm for nm in names if nm != key]:
@@ -618,26 +632,35 @@ def _sort_block_split(block, key, descending, group, ph, consume=False):
             wires.append((name + _VALID, 1, v))
     nkey = 2 if key in with_valid else 1
     rbs = {w: rb for w, rb, _ in wires}
+    # receive layout, identical on every rank: one region per (wire, round), each with room for
+    # the fullest (rank, round) anywhere
+    cap_rows = int(matrix.sum(axis=0).max())
+    region, total = {}, 0
+    for w, rb, _ in wires:
+        for r in range(R):
+            region[(w, r)] = total
+            total += _align(cap_rows * rb)
     try:
-        layout = _PeerLayout([w for w, _, _ in wires], rbs, matrix)
-        pb = _peer_buffer(layout.total, group)
+        pb = _peer_buffer(max(total, 256), group)
     except Exception as e:  # pragma: no cover - depends on the system
         import warnings
 
         warnings.warn(f"peer-memory exchange unavailable ({e!r}); using NCCL all_to_all")
         return None
-    n_recv = int(matrix[:, rank].sum())
     ptrs = [int(p) for p in pb.hdl.buffer_ptrs]
-    before = [int(matrix[:rank, d].sum()) for d in range(world)]
-    remote_rows = int(matrix[rank].sum() - matrix[rank, rank])
+    before = matrix[:rank].sum(axis=0)                  # rows lower ranks place, per destination
+    n_round = [int(matrix[:, rank * R + r].sum()) for r in range(R)]
+    own = sum(int(matrix[rank, rank * R + r]) for r in range(R))
+    remote_rows = int(matrix[rank].sum()) - own
     ph.mark("counts")
 
-    def split(w, rb, src, max_ctas):
+    def split(w, rb, src, mask, max_ctas):
         if n == 0:
             return
-        bases = (ctypes.c_void_p * world)(*[ptrs[d] + layout.off[w] + before[d] * rb for d in range(world)])
-        _lib.call("ds_split_rows", src.data_ptr(), rb, n, dest.data_ptr(), offs.data_ptr(), world, bases,
-                  max_ctas, stream())
+        bases = (ctypes.c_void_p * nd)(*[ptrs[j // R] + region[(w, j % R)] + int(before[j]) * rb
+                                         for j in range(nd)])
+        _lib.call("ds_split_rows", src.data_ptr(), rb, n, dest.data_ptr(), offs.data_ptr(), nd, bases,
+                  mask, max_ctas, stream())
 
     payload_ctas = _SPLIT_CTAS
     if payload_ctas < 0:  # beside the key sort: one persistent CTA per SM keeps NVLink busy
@@ -649,41 +672,75 @@ def _sort_block_split(block, key, descending, group, ph, consume=False):
     pb.hdl.barrier(channel=0)  # every rank is done with the buffer's previous contents
     ev["k0"].record()
     for w, rb, src in wires[:nkey]:
-        split(w, rb, src, 0)
+        split(w, rb, src, 0, 0)  # the keys of every round go first
     pb.hdl.barrier(channel=1)  # all keys have landed everywhere
     ev["k1"].record()
     ph.mark("split keys")
-    recv = {w: pb.buf[layout.off[w]: layout.off[w] + n_recv * rb] for w, rb, _ in wires}
 
-    def column(name):
-        return DeviceColumn(types[name], recv[name], recv.get(name + _VALID))
+    def recv(w, r):
+        rb = rbs[w]
+        return pb.buf[region[(w, r)]: region[(w, r)] + n_round[r] * rb]
+
+    def column(name, r):
+        v = recv(name + _VALID, r) if name in with_valid else None
+        return DeviceColumn(types[name], recv(name, r), v)
+
+    landed = [torch.cuda.Event() for _ in range(R)]
 
     def send_payload():
         pb.side.wait_stream(main)
         with torch.cuda.stream(pb.side):
+            # (no record_stream: the main stream waits for this stream's events before the
+            # function returns, so every buffer used here outlives the work that reads it)
             ev["p0"].record()
-            # (no record_stream: the main stream waits for this stream before the function
-            # returns, so every buffer used here outlives the work that reads it)
-            for w, rb, src in wires[nkey:]:
-                split(w, rb, src, payload_ctas)
-            ev["p1"].record()
+            for r in range(R):
+                mask = sum(1 << (d * R + r) for d in range(world)) if R > 1 else 0
+                for w, rb, src in wires[nkey:]:
+                    split(w, rb, src, mask, payload_ctas)
+                if r == R - 1:
+                    ev["p1"].record()
+                pb.hdl.barrier(channel=2 + r)  # round r has landed everywhere
+                landed[r].record()
 
     if not PAYLOAD_AFTER_SORT:
         send_payload()  # payload rows travel beside the key sort
-    idx, sorted_key, _ = _argsort_nulls_last(column(key), descending)
+    marks = {"merge": [], "reduce": []}
+    order = []
+    for r in range(R):  # "merge": the received keys of a round become a sorted run
+        a = torch.cuda.Event(enable_timing=True)
+        a.record()
+        order.append(_argsort_nulls_last(column(key, r), descending)[:2])
+        b = torch.cuda.Event(enable_timing=True)
+        b.record()
+        marks["merge"].append((a, b))
     ph.mark("key sort")
     if PAYLOAD_AFTER_SORT:
         send_payload()
-    ev["w0"].record()
+    outs = []
+    for r in range(R):  # "reduce": the round's output block, as soon as its payload is here
+        if r == R - 1:
+            ev["w0"].record()
+        main.wait_event(landed[r])
+        if r == R - 1:
+            ev["w1"].record()
+            ph.mark("wait payload")
+        a = torch.cuda.Event(enable_timing=True)
+        a.record()
+        idx, sorted_key = order[r]
+        cols = collections.OrderedDict()
+        for name in names:
+            cols[name] = sorted_key if name == key else _gather(column(name, r), idx)
+        outs.append(DeviceArrowBlock(cols, n_round[r]))
+        b = torch.cuda.Event(enable_timing=True)
+        b.record()
+        marks["reduce"].append((a, b))
     main.wait_stream(pb.side)
-    pb.hdl.barrier(channel=2)  # all payload rows have landed everywhere
-    ev["w1"].record()
-    ph.mark("wait payload")
+    marks["map"] = [(ev["k0"], ev["p1"])]
     _last_exchange.clear()
     _last_exchange.update(ev)
     _last_exchange.update(
         bytes_out=remote_rows * sum(rbs.values()),
-        bytes_in=(n_recv - int(matrix[rank, rank])) * sum(rbs.values()),
+        bytes_in=(sum(n_round) - own) * sum(rbs.values()),
         key_bytes_out=remote_rows * sum(rb for _, rb, _ in wires[:nkey]))
     if EXCHANGE_LOG is not None:
         EXCHANGE_LOG.append(dict(_last_exchange))
@@ -693,12 +750,9 @@ def _sort_block_split(block, key, descending, group, ph, consume=False):
         del dest, offs
         torch.cuda.synchronize()
         torch.cuda.empty_cache()
-    cols = collections.OrderedDict()
-    for name in names:
-        cols[name] = sorted_key if name == key else _gather(column(name), idx)
     ph.mark("gather payload")
     ph.finish()
-    return DeviceArrowBlock(cols, n_recv)
+    return outs, marks
 
 
 def reserve_peer_buffer(nbytes: int, group=None) -> None:
@@ -713,7 +767,49 @@ def reserve_peer_buffer(nbytes: int, group=None) -> None:
         _peer_cache[key] = _PeerBuffer(int(nbytes), group)
 
 
-def sort_block(block, key: str, descending: bool = False, group=None, consume: bool = False):
+PUSH_ROUNDS = int(_os.environ.get("DS_PUSH_ROUNDS", "4"))  # rounds of the push-based plan
+
+
+def sort_block_push(block, key: str, descending: bool = False, group=None, consume: bool = False,
+                    rounds: Optional[int] = None):
+    """Dataset.sort across the ranks of ``group`` with the push-based plan
+    (python/ray/data/_internal/push_based_shuffle.py:363-526): this rank's input block in,
+    (this rank's output blocks in key order, {"map", "merge", "reduce": [BlockMetadata]}) out --
+    the return shape of PushBasedShufflePlan.execute (:513-517).  Global order = rank order,
+    then block order.  See _sort_block_split for what a round is."""
+    from .block import BlockExecStats, BlockMetadata, DeviceArrowBlock
+
+    world = dist.get_world_size(group)
+    var_names = _fixed_width_only(block, "sort_block_push", key, payload_ok=True)
+    ph = _Phases()
+    ph.mark("start")
+    in_rows, in_bytes = block.num_rows, block.nbytes
+    R = PUSH_ROUNDS if rounds is None else rounds
+    ok = world > 1 and dist.get_backend(group) == "nccl" and not var_names and _split_supported(block, key, world)
+    res = _sort_block_split(block, key, descending, group, ph, consume, R) if ok else None
+    if res is None:  # inputs the split plan does not take: one round through sort_block
+        out = sort_block(block, key, descending, group, consume, rounds=1)
+        st = BlockExecStats.builder().build()
+        meta = BlockMetadata(num_rows=out.num_rows, size_bytes=out.nbytes, schema=None, input_files=None, exec_stats=st)
+        return [out], {"map": [meta], "merge": [meta], "reduce": [meta]}
+    outs, marks = res
+
+    def meta_of(rows, nbytes, pair):
+        st = BlockExecStats()
+        st.cpu_time_s = 0.0
+        st._events = pair  # device time of the phase, resolved when read
+        return BlockMetadata(num_rows=rows, size_bytes=nbytes, schema=None, input_files=None, exec_stats=st)
+
+    stats = {
+        "map": [meta_of(in_rows, in_bytes, marks["map"][0])],
+        "merge": [meta_of(o.num_rows, o.columns[key].nbytes, p) for o, p in zip(outs, marks["merge"])],
+        "reduce": [meta_of(o.num_rows, o.nbytes, p) for o, p in zip(outs, marks["reduce"])],
+    }
+    return outs, stats
+
+
+def sort_block(block, key: str, descending: bool = False, group=None, consume: bool = False,
+               rounds: Optional[int] = None):
     """Dataset.sort across the ranks of ``group``: this rank's input block in, this rank's
     slice of the globally sorted dataset out (rank order = key order).
 
@@ -729,6 +825,10 @@ def sort_block(block, key: str, descending: bool = False, group=None, consume: b
     dev = _dev()
     ph = _Phases()
     ph.mark("start")
+    if rounds is None:  # the plan selection point of the reference (sort.py:142-146)
+        from .context import DatasetContext
+
+        rounds = PUSH_ROUNDS if DatasetContext.get_current().use_push_based_shuffle else 1
     if consume:  # the caller's handle stays valid (and emptied); work on our own view of it
         src_block = block
         from .block import DeviceArrowBlock as _DAB
@@ -736,9 +836,10 @@ def sort_block(block, key: str, descending: bool = False, group=None, consume: b
         src_block.columns.clear()
     if (_EXCHANGE == "split" and world > 1 and dist.get_backend(group) == "nccl" and not var_names
             and _split_supported(block, key, world)):
-        out = _sort_block_split(block, key, descending, group, ph, consume)
-        if out is not None:
-            return out
+        res = _sort_block_split(block, key, descending, group, ph, consume, rounds)
+        if res is not None:
+            outs, _ = res
+            return outs[0] if len(outs) == 1 else DeviceArrowBlock.concat(outs)
     block, with_valid = _agree_on_validity(block, group, dev)
     names = block.column_names
     types = {nm: block.columns[nm].type for nm in names}

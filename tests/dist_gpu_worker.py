@@ -66,6 +66,29 @@ def main():
         sizes = [o.num_rows for o in outs]
         assert max(sizes) < 1.3 * sum(sizes) / world, f"unbalanced partitions {sizes}"
 
+    # ---- the push-based plan: key sub-ranges travel in rounds; several output blocks per rank
+    if os.environ.get("DS_EXCHANGE", "split") == "split":
+        inputs = gather_tables(t, rank, world)
+        for rounds in (2, 3):
+            for desc in (False, True):
+                outs, stats = D.sort_block_push(ds.DeviceArrowBlock.from_arrow(t), "key", descending=desc,
+                                                rounds=rounds)
+                assert sorted(stats) == ["map", "merge", "reduce"]
+                assert len(outs) == rounds == len(stats["merge"]) == len(stats["reduce"])
+                mine = pa.concat_tables([o.to_arrow() for o in outs])
+                got = pa.concat_tables([o for o in gather_tables(mine, rank, world) if o.num_rows])
+                assert got.equals(O.global_stable_sort(inputs, "key", desc)), f"push plan mismatch r={rounds} desc={desc}"
+                assert sum(m.num_rows for m in stats["reduce"]) == mine.num_rows
+                assert all(m.exec_stats.wall_time_s >= 0 for ms in stats.values() for m in ms)
+        # the reference's flag selects the plan inside sort_block (one concatenated block out)
+        from ray_memory_management_b200.context import DatasetContext
+
+        DatasetContext._set_current(DatasetContext(use_push_based_shuffle=True))
+        out = D.sort_block(ds.DeviceArrowBlock.from_arrow(t), "key")
+        DatasetContext._set_current(DatasetContext())
+        got = pa.concat_tables([o for o in gather_tables(out.to_arrow(), rank, world) if o.num_rows])
+        assert got.equals(O.global_stable_sort(inputs, "key", False)), "use_push_based_shuffle mismatch"
+
     # ---- int64 sort
     rng = np.random.default_rng(rank)
     ti = pa.table({"k": rng.integers(-10**6, 10**6, 150_000, dtype=np.int64),

@@ -104,7 +104,7 @@ def test_split_rows_matches_numpy(lib, width, nparts, n, offset):
         for b in bufs:
             b.fill_(0xAB)
         lib.call("ds_split_rows", src.data_ptr(), width, n, dest_dev.data_ptr(), offs_dev.data_ptr(), nparts,
-                 arr, max_ctas, _stream())
+                 arr, 0, max_ctas, _stream())
         torch.cuda.synchronize()
         for d in range(nparts):
             got = bufs[d].cpu().numpy()
@@ -135,7 +135,7 @@ def test_split_rows_unaligned_source_and_fsb_keys(lib):
         assert np.array_equal(dest.astype(np.int64), want_dest)
         outs = [torch.zeros(int(c) * width, dtype=torch.uint8, device="cuda") for c in counts]
         arr = (ctypes.c_void_p * 8)(*[o.data_ptr() for o in outs])
-        lib.call("ds_split_rows", src.data_ptr(), width, n, dest_dev.data_ptr(), offs_dev.data_ptr(), 8, arr, 0, _stream())
+        lib.call("ds_split_rows", src.data_ptr(), width, n, dest_dev.data_ptr(), offs_dev.data_ptr(), 8, arr, 0, 0, _stream())
         torch.cuda.synchronize()
         for d in range(8):
             assert np.array_equal(outs[d].cpu().numpy().reshape(-1, width), rows[want_dest == d])
@@ -144,7 +144,35 @@ def test_split_rows_unaligned_source_and_fsb_keys(lib):
 def test_split_rejects_bad_arguments(lib):
     z = torch.zeros(16, dtype=torch.uint8, device="cuda")
     arr = (ctypes.c_void_p * 1)(z.data_ptr())
-    assert lib.lib.ds_split_rows(z.data_ptr(), lib.DS_SPLIT_MAX_ROW_BYTES + 1, 1, z.data_ptr(), z.data_ptr(), 1, arr, 0, None) == lib.DS_ERR_UNSUPPORTED
-    assert lib.lib.ds_split_rows(z.data_ptr(), 8, 1, z.data_ptr(), z.data_ptr(), lib.DS_MAX_SPLIT_PARTS + 1, arr, 0, None) == lib.DS_ERR_UNSUPPORTED
+    assert lib.lib.ds_split_rows(z.data_ptr(), lib.DS_SPLIT_MAX_ROW_BYTES + 1, 1, z.data_ptr(), z.data_ptr(), 1, arr, 0, 0, None) == lib.DS_ERR_UNSUPPORTED
+    assert lib.lib.ds_split_rows(z.data_ptr(), 8, 1, z.data_ptr(), z.data_ptr(), lib.DS_MAX_SPLIT_PARTS + 1, arr, 0, 0, None) == lib.DS_ERR_UNSUPPORTED
     assert lib.lib.ds_split_plan(lib.DS_KEY_I64, z.data_ptr(), 8, None, 1, z.data_ptr(), lib.DS_MAX_SPLIT_PARTS, 0,
                                  z.data_ptr(), z.data_ptr(), z.data_ptr(), None) == lib.DS_ERR_UNSUPPORTED
+
+
+@pytest.mark.parametrize("width", [90, 10, 7])
+def test_split_rows_in_rounds(lib, width):
+    """dest_mask: three calls that each move a third of the destinations together do what one
+    call does; destinations outside a call's mask are not touched by it."""
+    rng = np.random.default_rng(width)
+    n, nparts = 60_001, 6
+    rows = rng.integers(0, 256, (n, width), dtype=np.uint8)
+    keys = rng.integers(0, 6000, n, dtype=np.int64)
+    bnd = np.arange(1000, 6000, 1000, dtype=np.int64)
+    want_dest = np.searchsorted(bnd, keys, side="right")
+    dcol, dbnd = torch.from_numpy(keys).cuda(), torch.from_numpy(bnd).cuda()
+    _, _, counts, dest_dev, offs_dev = _plan(lib, lib.DS_KEY_I64, dcol, 8, None, n, dbnd, nparts - 1, False)
+    src = torch.from_numpy(rows.reshape(-1).copy()).cuda()
+    outs = [torch.full((int(c) * width,), 0xCD, dtype=torch.uint8, device="cuda") for c in counts]
+    arr = (ctypes.c_void_p * nparts)(*[o.data_ptr() for o in outs])
+    for r in range(3):
+        mask = (1 << r) | (1 << (r + 3))
+        lib.call("ds_split_rows", src.data_ptr(), width, n, dest_dev.data_ptr(), offs_dev.data_ptr(), nparts,
+                 arr, mask, 0, _stream())
+        torch.cuda.synchronize()
+        for d in range(nparts):
+            got = outs[d].cpu().numpy().reshape(-1, width)
+            if d % 3 <= r:
+                assert np.array_equal(got, rows[want_dest == d]), (r, d)
+            else:
+                assert (got == 0xCD).all(), (r, d)
