@@ -8,12 +8,14 @@
 // OUTPUT rows, so its writes are one contiguous, fully coalesced span; consecutive
 // threads read consecutive granules of the same source row.  Algorithmic bytes per
 // row: 4 (index) + 2*row_bytes.
+#include <atomic>
+
 #include "ds_common.cuh"
 #include "gather_bulk.cuh"
 
 namespace ds {
 
-static int g_gather_mode = 0;  // 0 auto (8 where eligible, else 2), 1 plain, 2 plain + L2::64B, 3 staged,
+static std::atomic<int> g_gather_mode{0};  // 0 auto (8 where eligible, else 2), 1 plain, 2 plain + L2::64B, 3 staged,
 // 4 staged + L2::64B, 5 direct (no smem idx), 6 32-bit word path for rows of 4k+2 bytes,
 // 7 asynchronous bulk copies per row (gather_bulk.cuh, UBLKCP), 8 the same with 16-byte cp.async.
 // Measured on 100 M x 90-byte rows (ms per sort step): 2: 10.46, 5: 11.0, 3: 12.7, 6: 14.0
@@ -509,6 +511,7 @@ static cudaError_t launch_scatter_parts(const void* src, const uint32_t* perm, u
 
 ds_status gather_rows_impl(const void* src, uint32_t row_bytes, uint64_t src_rows,
                            const uint32_t* idx, uint64_t n64, void* dst, cudaStream_t s) {
+  const int g_gather_mode = ds::g_gather_mode.load(std::memory_order_relaxed);  // one snapshot per call
   if (n64 == 0) return DS_OK;
   if (n64 > 0xFFFFFFFFull) {
     set_error("ds_gather_rows: n=%llu exceeds 2^32-1", (unsigned long long)n64);
@@ -619,9 +622,7 @@ extern "C" ds_status ds_scatter_rows_to_parts(const void* src, uint32_t row_byte
 
 // Tuning hook, see g_gather_mode.
 extern "C" int32_t ds_debug_set_gather_mode(int32_t mode) {
-  int old = ds::g_gather_mode;
-  ds::g_gather_mode = mode;
-  return old;
+  return ds::g_gather_mode.exchange(mode);
 }
 
 // Tuning hook for the asynchronous-copy gather: rows per tile, ring depth, CTAs per SM (0 = default).

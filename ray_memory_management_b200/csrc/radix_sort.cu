@@ -22,6 +22,7 @@
 //                        already resident), shared-memory exchange, coalesced scatter.
 //                        Algorithmic bytes per key per pass: 2*(8[+2]+4) = 24 / 28.
 //   decode_kernel        sorted hi/lo -> sorted key column in its Arrow form.
+#include <atomic>
 #include <utility>
 #include <vector>
 
@@ -653,18 +654,20 @@ __global__ void __launch_bounds__(256)
 }
 
 // ---------------------------------------------------------------- host driver
-static int g_hybrid_mode = 1;  // ds_debug_set_hybrid: 0 never, 1 when the buckets fill a CTA, 2 whatever n (tests)
-static bool g_no_fused_decode = false;  // ds_debug_set_fused_decode(0): separate repair + decode kernels
-static int g_cfg = 18;  // tuning knob (ds_debug_set_radix_config); 18 = v3 table match <384 x 12>, best measured
+static std::atomic<int> g_hybrid_mode{1};  // ds_debug_set_hybrid: 0 never, 1 when the buckets fill a CTA, 2 whatever n (tests)
+static std::atomic<bool> g_no_fused_decode{false};  // ds_debug_set_fused_decode(0): separate repair + decode kernels
+static std::atomic<int> g_cfg{18};  // tuning knob (ds_debug_set_radix_config); 18 = v3 table match <384 x 12>, best measured
 
+// one bit per device; relaxed atomics: concurrent first launches set the same attribute twice
+using DoneMask = std::atomic<unsigned long long>;
 template <typename K>
-static cudaError_t set_smem_attr(K k, int bytes, unsigned long long* done_mask) {
+static cudaError_t set_smem_attr(K k, int bytes, DoneMask* done_mask) {
   int dev = 0;
   cudaGetDevice(&dev);
-  if (!(*done_mask >> (dev & 63) & 1ull)) {
+  if (!(done_mask->load(std::memory_order_relaxed) >> (dev & 63) & 1ull)) {
     cudaError_t e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
     if (e != cudaSuccess) return e;
-    *done_mask |= 1ull << (dev & 63);
+    done_mask->fetch_or(1ull << (dev & 63), std::memory_order_relaxed);
   }
   return cudaSuccess;
 }
@@ -675,7 +678,7 @@ static cudaError_t launch_pass_t(const uint64_t* hi_in, const uint16_t* lo_in,
                                  uint32_t* idx_out, uint32_t n, int shift, const uint32_t* bin_base,
                                  uint32_t* lookback, uint32_t* tile_counter, cudaStream_t s) {
   using S = PassSmem<THREADS, ITEMS, HAS_LO>;
-  static unsigned long long done_a = 0, done_b = 0;  // per instantiation, one bit per device
+  static DoneMask done_a{0}, done_b{0};  // per instantiation, one bit per device
   const uint32_t tiles = (n + S::TILE - 1) / S::TILE;
   cudaError_t e;
   LaunchTimer timer(TIMED_PASS, s, static_cast<double>(n) * (HAS_LO ? 28.0 : 24.0));
@@ -867,7 +870,7 @@ static ds_status sort_indices_impl(int kind, const void* col, uint32_t width, ui
   const uint32_t n = static_cast<uint32_t>(n64);
   const bool has_lo = kind == KIND_FSB && width > 8;
   const PassList pl = make_passes(kind, width);
-  const int cfg = g_cfg;
+  const int cfg = g_cfg.load(std::memory_order_relaxed);
   const uint32_t tiles = (n + cfg_tile(cfg) - 1) / cfg_tile(cfg);
 
   Workspace w(ws);
@@ -938,8 +941,9 @@ static ds_status sort_indices_impl(int kind, const void* col, uint32_t width, ui
     const bool fsb10 = kind == KIND_FSB && width == 10 && sorted_out != nullptr &&
                        (reinterpret_cast<uintptr_t>(sorted_out) & 15) == 0;
     const bool key64 = kind != KIND_FSB;  // i64 / u64 / f64 / Philox: the whole key is `hi`
-    if ((fsb10 || key64) && g_hybrid_mode != 0 && !(options & DS_SORT_NO_HYBRID) &&
-        (n >= 400u * LS_BUCKETS || g_hybrid_mode == 2) && n <= 1650u * LS_BUCKETS) {
+    const int hybrid_mode = g_hybrid_mode.load(std::memory_order_relaxed);
+    if ((fsb10 || key64) && hybrid_mode != 0 && !(options & DS_SORT_NO_HYBRID) &&
+        (n >= 400u * LS_BUCKETS || hybrid_mode == 2) && n <= 1650u * LS_BUCKETS) {
       const float lim = 1.25f / 256.0f;
       hybrid = coll_h[pl.count - 1] <= lim && coll_h[pl.count - 2] <= lim;
     }
@@ -1017,7 +1021,7 @@ static ds_status sort_indices_impl(int kind, const void* col, uint32_t width, ui
       if (kind == KIND_I64) out_kind = LS_OUT_I64;
       if (kind == KIND_U64) out_kind = LS_OUT_U64;
     }
-    static unsigned long long attr_done[4] = {0, 0, 0, 0};
+    static DoneMask attr_done[4];
 #define DS_BUCKET_LAUNCH(HL, OUT)                                                                      \
   do {                                                                                                 \
     DS_CUDA(set_smem_attr(bucket_local_sort_kernel<HL, OUT>, LS_SMEM_BYTES, &attr_done[OUT]));         \
@@ -1043,7 +1047,7 @@ static ds_status sort_indices_impl(int kind, const void* col, uint32_t width, ui
     return DS_OK;
   }
   const bool fused_decode = prefix_shift >= 0 && kind == KIND_FSB && width == 10 && sorted_out != nullptr &&
-                            (reinterpret_cast<uintptr_t>(sorted_out) & 15) == 0 && !g_no_fused_decode;
+                            (reinterpret_cast<uintptr_t>(sorted_out) & 15) == 0 && !g_no_fused_decode.load(std::memory_order_relaxed);
   if (fused_decode) {
     // the other half of the ping-pong buffers is dead now: it holds the list of run heads
     uint32_t* head_list = reinterpret_cast<uint32_t*>(hi[cur ^ 1]);
@@ -1149,8 +1153,8 @@ ds_status ds_random_permutation(uint64_t seed, uint64_t subsequence, uint64_t n,
 // 0: prefix mode runs repair_runs_kernel + the decode kernel separately (the older path);
 // 1 (default): the fused decode + run-head list pair.  Returns the previous setting.
 int32_t ds_debug_set_fused_decode(int32_t enable) {
-  const int old = ds::g_no_fused_decode ? 0 : 1;
-  ds::g_no_fused_decode = enable == 0;
+  const int old = ds::g_no_fused_decode.load() ? 0 : 1;
+  ds::g_no_fused_decode.store(enable == 0);
   return old;
 }
 
@@ -1158,14 +1162,14 @@ int32_t ds_debug_set_fused_decode(int32_t enable) {
 // 1 (default) when n / 65536 is between 400 and 1650 rows, 2 also for smaller n (tests).
 // Returns the previous mode.
 int32_t ds_debug_set_hybrid(int32_t mode) {
-  const int old = ds::g_hybrid_mode;
-  if (mode >= 0 && mode <= 2) ds::g_hybrid_mode = mode;
+  const int old = ds::g_hybrid_mode.load();
+  if (mode >= 0 && mode <= 2) ds::g_hybrid_mode.store(mode);
   return old;
 }
 
 int32_t ds_debug_set_radix_config(int32_t cfg) {
-  int old = ds::g_cfg;
-  if (cfg >= 0 && cfg < ds::NUM_CFGS && ds::cfg_known(cfg)) ds::g_cfg = cfg;
+  int old = ds::g_cfg.load();
+  if (cfg >= 0 && cfg < ds::NUM_CFGS && ds::cfg_known(cfg)) ds::g_cfg.store(cfg);
   return old;
 }
 

@@ -38,6 +38,33 @@ static_assert(SP_MAX_PARTS <= 32, "one lane per destination");
 // ---------------------------------------------------------------- plan
 // One WARP per tile of 256 rows (8 rows per lane, all loads independent), no block barriers
 // after the splitters are staged: counts come from warp ballots.
+//
+// A key is first compared on a PREFIX only -- the leading 4 bytes of a fixed_size_binary key
+// (two 16-bit loads instead of five for the 10-byte GraySort key), the whole 64-bit word for
+// the numeric kinds.  The prefix decides the destination unless it equals the prefix of the
+// splitter next to it; only such keys (a handful per million for spread keys) load the rest.
+template <int KIND>
+__device__ __forceinline__ uint64_t load_key_prefix(const void* col, uint32_t width, uint64_t i, bool desc) {
+  if (KIND != KIND_FSB) {
+    uint64_t h;
+    uint32_t l;
+    load_key<KIND>(col, width, i, desc, h, l);
+    return h;
+  }
+  const uint8_t* p = static_cast<const uint8_t*>(col) + i * width;
+  uint32_t v = 0;
+  if ((width & 1) == 0 && width >= 4) {
+    const uint16_t* q = reinterpret_cast<const uint16_t*>(p);
+    const uint32_t a = __ldg(q), b = __ldg(q + 1);  // little-endian pairs
+    v = ((a & 0xFF) << 24) | ((a >> 8) << 16) | ((b & 0xFF) << 8) | (b >> 8);
+  } else {
+#pragma unroll
+    for (int b = 0; b < 4; ++b) v = (v << 8) | (b < (int)width ? __ldg(p + b) : 0u);
+  }
+  if (desc) v = ~v & (width >= 4 ? 0xFFFFFFFFu : ~((1u << (32 - 8 * width)) - 1u));
+  return static_cast<uint64_t>(v) << 32;
+}
+
 template <int KIND>
 __global__ void __launch_bounds__(SP_THREADS)
     split_plan_kernel(const void* __restrict__ col, uint32_t width, const uint8_t* __restrict__ valid,
@@ -45,49 +72,66 @@ __global__ void __launch_bounds__(SP_THREADS)
                       uint8_t* __restrict__ dest_out, uint32_t* __restrict__ tile_counts, uint32_t ntiles) {
   __shared__ uint64_t s_bh[SP_MAX_PARTS];
   __shared__ uint32_t s_bl[SP_MAX_PARTS];
+  __shared__ uint64_t s_bp[SP_MAX_PARTS];  // the splitters' prefixes
   const uint32_t tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const uint32_t nparts = nb + 1;
+  constexpr uint64_t PMASK = KIND == KIND_FSB ? 0xFFFFFFFF00000000ull : ~0ull;
   if (tid < nb) {
     uint64_t h;
     uint32_t l;
     load_key<KIND>(bounds, width, tid, desc, h, l);
     s_bh[tid] = h;
     s_bl[tid] = l;
+    s_bp[tid] = h & PMASK;
   }
   __syncthreads();
   constexpr int PER = SP_TILE0 / 32;
   const uint32_t warps = gridDim.x * (SP_THREADS / 32);
   for (uint32_t t = blockIdx.x * (SP_THREADS / 32) + warp; t < ntiles; t += warps) {
     const uint32_t base = t * SP_TILE0 + lane;
-    uint64_t kh[PER];
-    uint32_t kl[PER], d[PER];
+    uint64_t kp[PER];
+    uint32_t d[PER];
 #pragma unroll
     for (int j = 0; j < PER; ++j) {
       const uint32_t i = base + j * 32;
-      kh[j] = 0;
-      kl[j] = 0;
+      kp[j] = 0;
       d[j] = 0xffffffffu;
       if (i < n) {
-        d[j] = 0;
+        d[j] = 0xfffffffeu;  // "to be searched"
         if (valid != nullptr && valid[i] == 0) d[j] = nb;  // null keys travel to the last partition
-        else load_key<KIND>(col, width, i, desc, kh[j], kl[j]);
+        else kp[j] = load_key_prefix<KIND>(col, width, i, desc);
       }
     }
 #pragma unroll
     for (int j = 0; j < PER; ++j) {
-      if (d[j] == 0) {
+      const uint32_t i = base + j * 32;
+      if (d[j] == 0xfffffffeu) {
+        // lo = #{splitter prefixes < key prefix}, hi = #{splitter prefixes <= key prefix}
         uint32_t lo = 0, hi = nb;
         while (lo < hi) {
           const uint32_t mid = (lo + hi) >> 1;
-          // asc: count splitters <= key; desc: count splitters strictly before key (encoded)
-          const bool go_right = desc ? key_less(s_bh[mid], s_bl[mid], kh[j], kl[j])
-                                     : !key_less(kh[j], kl[j], s_bh[mid], s_bl[mid]);
-          if (go_right) lo = mid + 1;
+          if (s_bp[mid] < kp[j]) lo = mid + 1;
           else hi = mid;
         }
-        d[j] = lo;
+        uint32_t up = lo;
+        while (up < nb && s_bp[up] == kp[j]) ++up;
+        if (up != lo) {
+          // some splitters share the prefix: the full key decides among [lo, up]
+          uint64_t kh;
+          uint32_t kl;
+          load_key<KIND>(col, width, i, desc, kh, kl);
+          uint32_t b = lo;
+          while (b < up) {
+            // asc: count splitters <= key; desc: count splitters strictly before key (encoded)
+            const bool go_right = desc ? key_less(s_bh[b], s_bl[b], kh, kl) : !key_less(kh, kl, s_bh[b], s_bl[b]);
+            if (!go_right) break;
+            ++b;
+          }
+          d[j] = b;
+        } else {
+          d[j] = lo;  // no splitter shares the prefix: every splitter below it is <= the key
+        }
       }
-      const uint32_t i = base + j * 32;
       if (i < n) dest_out[i] = static_cast<uint8_t>(d[j]);
     }
     uint32_t mine = 0;
