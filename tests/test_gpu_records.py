@@ -49,6 +49,21 @@ def test_record_file_roundtrip_and_validate(ds, tmp_path, n):
         assert v["unordered"] > n // 3  # the unsorted input is far from ordered
 
 
+def test_record_file_streamed_in_chunks(ds, tmp_path):
+    """many chunks through the pinned ring (chunk size far below the file size, ragged tail)"""
+    from ray_memory_management_b200 import graysort
+
+    n = 12_345
+    t, rec = _records(n, seed=3)
+    path = tmp_path / "in.dat"
+    rec.tofile(path)
+    blk = graysort.read_records(str(path), chunk_bytes=100 * 777)  # 16 chunks, the last one short
+    assert blk.to_arrow().equals(t)
+    out = tmp_path / "out.dat"
+    graysort.write_records(blk, str(out), chunk_bytes=100 * 500)
+    assert np.array_equal(np.fromfile(out, dtype=np.uint8), rec.reshape(-1))
+
+
 def test_validate_counts_duplicates_and_disorder(ds):
     from ray_memory_management_b200 import graysort
 
