@@ -297,21 +297,22 @@ _VALID = "\x00valid"  # wire-name suffix of a column's validity bytes
 _LEN = "\x00len"  # wire-name suffix of a variable-length column's row lengths
 
 
-def _fixed_width_only(block, what: str, key: Optional[str] = None, payload_ok: bool = False) -> List[str]:
-    """Variable-length columns: payload columns travel as a fixed-width wire of row lengths
-    plus one all-to-all-v of their bytes (``payload_ok``); a variable-length KEY would also
-    need variable-length splitters and samples on the wire and is single-GPU only for now.
-    Returns the names of the variable-length payload columns."""
+def _fixed_width_only(block, what: str, key: Optional[str] = None, payload_ok: bool = False,
+                      key_ok: bool = False) -> List[str]:
+    """Variable-length columns travel as a fixed-width wire of row lengths plus one
+    all-to-all-v of their bytes (``payload_ok``); a variable-length KEY (``key_ok``: sort only)
+    also needs variable-length splitters, which the ranks agree on through the host.
+    Returns the names of the variable-length columns."""
     names = []
     for name, c in block.columns.items():
         if not c.is_varlen:
             continue
-        if payload_ok and name != key:
+        if payload_ok and (name != key or key_ok):
             names.append(name)
             continue
         raise NotImplementedError(
             f"{what}: column {name!r} has the variable-length type {c.type}; the multi-GPU "
-            "plans take variable-length columns as payload of sort / random_shuffle only")
+            "plans take variable-length columns in sort (key or payload) and as payload of random_shuffle")
     return names
 
 
@@ -339,6 +340,27 @@ def _varlen_recv(arrow_type, len_wire: torch.Tensor, n_recv: int, data, byte_cou
     bm = exchange_counts(byte_counts, group, dev)
     recv, _ = alltoallv_rows(data.contiguous(), 1, bm, group)
     return DeviceVarColumn(arrow_type, offsets, recv, valid, int(bm[:, dist.get_rank(group)].sum()))
+
+
+def _varlen_splitters(block, key: str, world: int, group) -> list:
+    """W-1 splitters of a string / binary key column, identical on every rank: up to
+    SAMPLES_PER_RANK sampled keys per rank travel as Python objects (all_gather_object), are
+    ordered bytewise -- Arrow's order for binary and for UTF-8 strings -- and the i/W quantiles
+    are picked (python/ray/data/_internal/sort.py:105-115 does the same on the driver)."""
+    from .block import DeviceArrowBlockAccessor
+
+    mine = []
+    if block.num_rows:
+        s = DeviceArrowBlockAccessor(block).sample(min(SAMPLES_PER_RANK, block.num_rows), key)
+        mine = [v for v in s.to_arrow()[key].to_pylist() if v is not None]
+    gathered = [None] * world
+    dist.all_gather_object(gathered, mine, group=group)
+    allv = [v for part in gathered for v in part]
+    if not allv:
+        return [None] * (world - 1)
+    allv.sort(key=lambda v: v.encode("utf-8") if isinstance(v, str) else bytes(v))
+    n = len(allv)
+    return [allv[min(n - 1, (i * n) // world)] for i in range(1, world)]
 
 
 def _agree_on_validity(block, group, dev):
@@ -819,7 +841,8 @@ def sort_block(block, key: str, descending: bool = False, group=None, consume: b
     from .block import (DeviceArrowBlock, DeviceArrowBlockAccessor, DeviceColumn,
                         _argsort_nulls_last, _gather)
 
-    var_names = _fixed_width_only(block, "sort_block", key, payload_ok=True)
+    var_names = _fixed_width_only(block, "sort_block", key, payload_ok=True, key_ok=True)
+    key_is_var = key in var_names
     world = dist.get_world_size(group)
     rank = dist.get_rank(group)
     dev = _dev()
@@ -843,12 +866,15 @@ def sort_block(block, key: str, descending: bool = False, group=None, consume: b
     block, with_valid = _agree_on_validity(block, group, dev)
     names = block.column_names
     types = {nm: block.columns[nm].type for nm in names}
-    width, ktype = _key_width(block, key, group)
-    local = _sample_local(block, key)
-    if local.shape[1] != width:
-        local = np.zeros((0, width), dtype=np.uint8)
-    samples = gather_samples(local, width, group, dev)
-    boundaries = splitters_from_samples(samples, ktype, world)
+    if key_is_var:
+        boundaries = _varlen_splitters(block, key, world, group)
+    else:
+        width, ktype = _key_width(block, key, group)
+        local = _sample_local(block, key)
+        if local.shape[1] != width:
+            local = np.zeros((0, width), dtype=np.uint8)
+        samples = gather_samples(local, width, group, dev)
+        boundaries = splitters_from_samples(samples, ktype, world)
     if boundaries and boundaries[0] is None:
         return block  # no non-null key anywhere: nothing to order
     if descending:
@@ -869,7 +895,8 @@ def sort_block(block, key: str, descending: bool = False, group=None, consume: b
         del acc
     ph.mark("partition")
     matrix = exchange_counts(counts, group, dev)
-    wires = _wire_columns(parts, [nm for nm in names if nm not in var_names], with_valid, key, dev, col_rb)
+    wires = _wire_columns(parts, [nm for nm in names if nm not in var_names], with_valid,
+                          None if key_is_var else key, dev, col_rb)
     var_send = {}
     for nm in var_names:  # lengths ride with the fixed-width wires, the bytes follow below
         from .block import DeviceVarColumn, _concat_varlen
@@ -891,7 +918,8 @@ def sort_block(block, key: str, descending: bool = False, group=None, consume: b
     del parts
     if consume:
         torch.cuda.empty_cache()
-    nkey = 2 if key in with_valid else 1          # wires that make up the key column
+    # wires that make up the key column (a variable-length key is rebuilt after the exchange)
+    nkey = 0 if key_is_var else (2 if key in with_valid else 1)
     n_recv = int(matrix[:, rank].sum())
     rbs = {w: rb for w, rb, _ in wires}
 
@@ -924,7 +952,8 @@ def sort_block(block, key: str, descending: bool = False, group=None, consume: b
         ph.mark("p2p keys")
         for w, rb, _ in wires:
             recv[w] = pb.buf[layout.off[w]: layout.off[w] + n_recv * rb]
-        idx, sorted_key, _ = _argsort_nulls_last(column(key), descending)
+        if not key_is_var:
+            idx, sorted_key, _ = _argsort_nulls_last(column(key), descending)
         ph.mark("key sort")
         _join_lanes(pb, main)
         pb.hdl.barrier(channel=2)  # all payload rows have landed everywhere
@@ -943,21 +972,29 @@ def sort_block(block, key: str, descending: bool = False, group=None, consume: b
             r, work = alltoallv_rows(buf, rb, matrix, group, async_op=True)
             recv[w] = r
             pending.append(work)
-        idx, sorted_key, _ = _argsort_nulls_last(column(key), descending)
+        if not key_is_var:
+            idx, sorted_key, _ = _argsort_nulls_last(column(key), descending)
         ph.mark("key sort")
         for work in pending:
             work.wait()
         ph.mark("wait payload")
-    cols = collections.OrderedDict()
-    for name in names:
+    var_cols = {}
+    for name in names:  # the bytes of the variable-length columns follow their lengths
         if name in var_names:
             data, byte_counts = var_send[name]
             v = recv.get(name + _VALID)
-            src = _varlen_recv(types[name], recv[name + _LEN], n_recv, data, byte_counts,
-                               v[:n_recv] if v is not None else None, group, dev)
-            cols[name] = _gather(src, idx)
-            continue
-        cols[name] = sorted_key if name == key else _gather(column(name), idx)
+            var_cols[name] = _varlen_recv(types[name], recv[name + _LEN], n_recv, data, byte_counts,
+                                          v[:n_recv] if v is not None else None, group, dev)
+    if key_is_var:
+        idx, sorted_key, _ = _argsort_nulls_last(var_cols[key], descending)
+    cols = collections.OrderedDict()
+    for name in names:
+        if name == key:
+            cols[name] = sorted_key
+        elif name in var_names:
+            cols[name] = _gather(var_cols[name], idx)
+        else:
+            cols[name] = _gather(column(name), idx)
     ph.mark("gather payload")
     ph.finish()
     return DeviceArrowBlock(cols, n_recv)
