@@ -5,9 +5,9 @@
 
 One timed distributed sort with ``consume=True`` (the input is released as the reference
 releases its input refs with clear_input_blocks), after a small warm-up that sets up NCCL and
-reserves the symmetric receive buffer.  At 62.5 GB per GPU the send-buffer staging of the
-copy-engine exchange does not fit beside the input and the receive buffer (190 GB), so run it
-with DS_EXCHANGE=fused: the partition kernel stores rows straight into the peers' buffers.
+reserves the symmetric receive buffer.  The default multi-GPU plan (streaming split straight into
+the peers' receive buffers, DS_EXCHANGE=split) has no send buffer, so input (62.5 GB) + receive
+buffer (65 GB) fit; the copy-engine plan (DS_EXCHANGE=p2p) does not at this size.
 The single timed run includes first-use cudaMalloc of its temporaries (no same-size warm-up
 fits in HBM next to a second input).  Validation (not timed): every rank's output is sorted,
 rank boundaries are ordered, and the order-independent CRC-32 checksum and the record count of

@@ -13,7 +13,7 @@ src = torch.randint(0, 256, (n * W,), dtype=torch.uint8, device="cuda", generato
 idx = torch.randperm(n, device="cuda", generator=g).to(torch.int32)
 out = torch.empty(n * W, dtype=torch.uint8, device="cuda")
 s = torch.cuda.current_stream().cuda_stream
-for mode, rows, stages in ((2, 0, 0), (7, 128, 2), (8, 64, 3), (7, 64, 2)):
+for mode, rows, stages in ((0, 0, 0), (2, 0, 0), (7, 64, 2)):  # auto (= cp.async variant), old granule kernel, bulk variant
     _lib.lib.ds_debug_set_gather_mode(mode)
     _lib.lib.ds_debug_set_gather_bulk(rows, stages, 0)
     for _ in range(2):
