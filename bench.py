@@ -67,6 +67,9 @@ def parse_args():
                    help="N > 1: one exchange round (split) or the push-based plan in rounds (push); "
                         "auto = the plan DESIGN.md records as the faster one")
     p.add_argument("--rounds", type=int, default=0, help="rounds of the push-based plan (0 = library default)")
+    p.add_argument("--staged", type=int, default=-1,
+                   help="push-based plan: trailing rounds that are staged locally and shipped by the copy "
+                        "engines (-1 = library default: all but the first)")
     return p.parse_args()
 
 
@@ -361,7 +364,8 @@ def run_ours(args):
         from ray_memory_management_b200 import distributed
 
         if plan == "push":
-            return distributed.sort_block_push(blk, "key", descending=False, rounds=rounds)[0]
+            return distributed.sort_block_push(blk, "key", descending=False, rounds=rounds,
+                                               staged=args.staged if args.staged >= 0 else None)[0]
         return [distributed.sort_block(blk, "key", descending=False, rounds=1)]
 
     def one_step():

@@ -591,7 +591,8 @@ def _split_supported(block, key, world: int) -> bool:
     return True
 
 
-def _sort_block_split(block, key, descending, group, ph, consume=False, rounds: int = 1):
+def _sort_block_split(block, key, descending, group, ph, consume=False, rounds: int = 1,
+                      staged: int = 0):
     """The default multi-GPU sort plan: the map side is ONE streaming pass per column
     (ds_split_plan + ds_split_rows) that stores every row, in input order, straight into the
     receive buffer of the GPU that owns its key range -- bulk stores from shared memory over
@@ -608,6 +609,13 @@ def _sort_block_split(block, key, descending, group, ph, consume=False, rounds: 
     merged runs at the end, the rounds here ARE key sub-ranges, so the "merge" of a round is
     the sort of its received keys and the final reduce is the gather; the rounds' outputs are
     consecutive output blocks, no re-merge.
+
+    ``staged`` (< rounds): the last ``staged`` rounds do not cross NVLink during the split pass.
+    The ONE pass over the input stores the rows of the first rounds straight into the peers'
+    buffers and the rows of the staged rounds into a local staging buffer (the split kernel does
+    not care where a destination lives); the copy engines then ship the staged rounds, one after
+    the other, while the SMs gather the rounds that have landed.  With ``staged`` = 0 every round
+    is its own masked pass of the split kernel over the input.
 
     Returns ([output block per round], {"map", "merge", "reduce"} event pairs) or None when
     peer memory is unavailable."""
@@ -676,11 +684,26 @@ def _sort_block_split(block, key, descending, group, ph, consume=False, rounds: 
     remote_rows = int(matrix[rank].sum()) - own
     ph.mark("counts")
 
+    S = max(0, min(int(staged), R - 1))
+    direct_rounds = R - S
+    # staging: per payload wire and staged round, this rank's rows for ranks 0..W-1 back to back
+    stage_buf, stage_off = {}, {}
+    for r in range(direct_rounds, R):
+        cnt = [int(matrix[rank, d * R + r]) for d in range(world)]
+        stage_off[r] = np.concatenate([[0], np.cumsum(cnt)])
+        for w, rb, _ in wires[nkey:]:
+            stage_buf[(w, r)] = torch.empty(max(int(stage_off[r][-1]) * rb, 1), dtype=torch.uint8, device=dev)
+
+    def base_of(w, rb, j):
+        d, r = divmod(j, R)
+        if (w, r) in stage_buf:
+            return stage_buf[(w, r)].data_ptr() + int(stage_off[r][d]) * rb
+        return ptrs[d] + region[(w, r)] + int(before[j]) * rb
+
     def split(w, rb, src, mask, max_ctas):
         if n == 0:
             return
-        bases = (ctypes.c_void_p * nd)(*[ptrs[j // R] + region[(w, j % R)] + int(before[j]) * rb
-                                         for j in range(nd)])
+        bases = (ctypes.c_void_p * nd)(*[base_of(w, rb, j) for j in range(nd)])
         _lib.call("ds_split_rows", src.data_ptr(), rb, n, dest.data_ptr(), offs.data_ptr(), nd, bases,
                   mask, max_ctas, stream())
 
@@ -715,13 +738,40 @@ def _sort_block_split(block, key, descending, group, ph, consume=False, rounds: 
             # (no record_stream: the main stream waits for this stream's events before the
             # function returns, so every buffer used here outlives the work that reads it)
             ev["p0"].record()
-            for r in range(R):
-                mask = sum(1 << (d * R + r) for d in range(world)) if R > 1 else 0
-                for w, rb, src in wires[nkey:]:
-                    split(w, rb, src, mask, payload_ctas)
+            if S == 0:
+                for r in range(R):
+                    mask = sum(1 << (d * R + r) for d in range(world)) if R > 1 else 0
+                    for w, rb, src in wires[nkey:]:
+                        split(w, rb, src, mask, payload_ctas)
+                    if r == R - 1:
+                        ev["p1"].record()
+                    pb.hdl.barrier(channel=2 + r)  # round r has landed everywhere
+                    landed[r].record()
+                return
+            for w, rb, src in wires[nkey:]:  # one pass: direct rounds to the peers, the rest staged
+                split(w, rb, src, 0, payload_ctas)
+            pb.hdl.barrier(channel=2)
+            for r in range(direct_rounds):
+                landed[r].record()
+        for r in range(direct_rounds, R):  # the copy engines ship the staged rounds in order
+            for step in range(world):
+                d = (rank + step) % world
+                rows = int(matrix[rank, d * R + r])
+                if rows == 0:
+                    continue
+                lane = pb.lanes[d]
+                lane.wait_stream(pb.side)
+                with torch.cuda.stream(lane):
+                    for w, rb, _ in wires[nkey:]:
+                        dst = pb.hdl.get_buffer(d, (rows * rb,), torch.uint8,
+                                                region[(w, r)] + int(before[d * R + r]) * rb)
+                        o = int(stage_off[r][d]) * rb
+                        dst.copy_(stage_buf[(w, r)][o: o + rows * rb], non_blocking=True)
+            _join_lanes(pb, pb.side)
+            with torch.cuda.stream(pb.side):
                 if r == R - 1:
-                    ev["p1"].record()
-                pb.hdl.barrier(channel=2 + r)  # round r has landed everywhere
+                    ev["p1"].record()  # the last payload byte of this rank has been copied out
+                pb.hdl.barrier(channel=2 + r)  # staged round r has landed everywhere
                 landed[r].record()
 
     if not PAYLOAD_AFTER_SORT:
@@ -789,11 +839,14 @@ def reserve_peer_buffer(nbytes: int, group=None) -> None:
         _peer_cache[key] = _PeerBuffer(int(nbytes), group)
 
 
-PUSH_ROUNDS = int(_os.environ.get("DS_PUSH_ROUNDS", "4"))  # rounds of the push-based plan
+PUSH_ROUNDS = int(_os.environ.get("DS_PUSH_ROUNDS", "2"))  # rounds of the push-based plan
+
+
+PUSH_STAGED = int(_os.environ.get("DS_PUSH_STAGED", "-1"))  # staged rounds (-1: all but the first)
 
 
 def sort_block_push(block, key: str, descending: bool = False, group=None, consume: bool = False,
-                    rounds: Optional[int] = None):
+                    rounds: Optional[int] = None, staged: Optional[int] = None):
     """Dataset.sort across the ranks of ``group`` with the push-based plan
     (python/ray/data/_internal/push_based_shuffle.py:363-526): this rank's input block in,
     (this rank's output blocks in key order, {"map", "merge", "reduce": [BlockMetadata]}) out --
@@ -808,7 +861,9 @@ def sort_block_push(block, key: str, descending: bool = False, group=None, consu
     in_rows, in_bytes = block.num_rows, block.nbytes
     R = PUSH_ROUNDS if rounds is None else rounds
     ok = world > 1 and dist.get_backend(group) == "nccl" and not var_names and _split_supported(block, key, world)
-    res = _sort_block_split(block, key, descending, group, ph, consume, R) if ok else None
+    if staged is None:
+        staged = PUSH_STAGED if PUSH_STAGED >= 0 else R - 1
+    res = _sort_block_split(block, key, descending, group, ph, consume, R, staged) if ok else None
     if res is None:  # inputs the split plan does not take: one round through sort_block
         out = sort_block(block, key, descending, group, consume, rounds=1)
         st = BlockExecStats.builder().build()

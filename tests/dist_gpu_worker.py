@@ -69,15 +69,16 @@ def main():
     # ---- the push-based plan: key sub-ranges travel in rounds; several output blocks per rank
     if os.environ.get("DS_EXCHANGE", "split") == "split":
         inputs = gather_tables(t, rank, world)
-        for rounds in (2, 3):
+        # (rounds, staged): staged rounds wait in a local buffer and are shipped by the copy engines
+        for rounds, staged in ((2, None), (2, 0), (3, None), (3, 1)):
             for desc in (False, True):
                 outs, stats = D.sort_block_push(ds.DeviceArrowBlock.from_arrow(t), "key", descending=desc,
-                                                rounds=rounds)
+                                                rounds=rounds, staged=staged)
                 assert sorted(stats) == ["map", "merge", "reduce"]
                 assert len(outs) == rounds == len(stats["merge"]) == len(stats["reduce"])
                 mine = pa.concat_tables([o.to_arrow() for o in outs])
                 got = pa.concat_tables([o for o in gather_tables(mine, rank, world) if o.num_rows])
-                assert got.equals(O.global_stable_sort(inputs, "key", desc)), f"push plan mismatch r={rounds} desc={desc}"
+                assert got.equals(O.global_stable_sort(inputs, "key", desc)), f"push plan mismatch r={rounds} staged={staged} desc={desc}"
                 assert sum(m.num_rows for m in stats["reduce"]) == mine.num_rows
                 assert all(m.exec_stats.wall_time_s >= 0 for ms in stats.values() for m in ms)
         # the reference's flag selects the plan inside sort_block (one concatenated block out)
