@@ -163,6 +163,7 @@ _EXCHANGE = _os.environ.get("DS_EXCHANGE", "split")
 # persistent CTAs of the payload split that runs beside the key sort (0 = one per SM)
 _SPLIT_CTAS = int(_os.environ.get("DS_SPLIT_CTAS", "-1"))  # -1: one per SM
 _SPLIT_TILE = int(_os.environ.get("DS_SPLIT_TILE", "0"))   # tuning: tile = k * 256 rows
+_EARLY_PAYLOAD = int(_os.environ.get("DS_EARLY_PAYLOAD", "-1"))  # 1 / 0 force, -1: from the world size
 _LANES = _os.environ.get("DS_P2P_LANES", "1") == "1"  # one copy stream per destination
 _peer_cache: dict = {}
 
@@ -715,12 +716,10 @@ def _sort_block_split(block, key, descending, group, ph, consume=False, rounds: 
     ev = {k: torch.cuda.Event(enable_timing=True) for k in ("k0", "k1", "p0", "p1", "w0", "w1")}
     main = torch.cuda.current_stream()
     pb.hdl.barrier(channel=0)  # every rank is done with the buffer's previous contents
-    ev["k0"].record()
-    for w, rb, src in wires[:nkey]:
-        split(w, rb, src, 0, 0)  # the keys of every round go first
-    pb.hdl.barrier(channel=1)  # all keys have landed everywhere
-    ev["k1"].record()
-    ph.mark("split keys")
+    # When the step is bound by the payload transfer (4 GPUs and more: each GPU ships 3/4..7/8 of
+    # its rows) the payload starts at once, beside the key transfer, so that NVLink never idles;
+    # with fewer GPUs the key sort is the longer chain and the keys get the link to themselves.
+    early_payload = _EARLY_PAYLOAD == 1 or (_EARLY_PAYLOAD < 0 and world >= 4)
 
     def recv(w, r):
         rb = rbs[w]
@@ -774,7 +773,15 @@ def _sort_block_split(block, key, descending, group, ph, consume=False, rounds: 
                 pb.hdl.barrier(channel=2 + r)  # staged round r has landed everywhere
                 landed[r].record()
 
-    if not PAYLOAD_AFTER_SORT:
+    if early_payload and not PAYLOAD_AFTER_SORT:
+        send_payload()
+    ev["k0"].record()
+    for w, rb, src in wires[:nkey]:
+        split(w, rb, src, 0, 0)  # the keys of every round go first
+    pb.hdl.barrier(channel=1)  # all keys have landed everywhere
+    ev["k1"].record()
+    ph.mark("split keys")
+    if not PAYLOAD_AFTER_SORT and not early_payload:
         send_payload()  # payload rows travel beside the key sort
     marks = {"merge": [], "reduce": []}
     order = []
