@@ -720,6 +720,8 @@ def _sort_block_split(block, key, descending, group, ph, consume=False, rounds: 
     # its rows) the payload starts at once, beside the key transfer, so that NVLink never idles;
     # with fewer GPUs the key sort is the longer chain and the keys get the link to themselves.
     early_payload = _EARLY_PAYLOAD == 1 or (_EARLY_PAYLOAD < 0 and world >= 4)
+    ev_start = torch.cuda.Event(enable_timing=True)
+    ev_start.record()
 
     def recv(w, r):
         rb = rbs[w]
@@ -814,7 +816,7 @@ def _sort_block_split(block, key, descending, group, ph, consume=False, rounds: 
         b.record()
         marks["reduce"].append((a, b))
     main.wait_stream(pb.side)
-    marks["map"] = [(ev["k0"], ev["p1"])]
+    marks["map"] = [(ev_start, ev["w1"])]  # first key byte sent .. last payload byte landed (this stream)
     _last_exchange.clear()
     _last_exchange.update(ev)
     _last_exchange.update(
