@@ -163,7 +163,7 @@ _EXCHANGE = _os.environ.get("DS_EXCHANGE", "split")
 # persistent CTAs of the payload split that runs beside the key sort (0 = one per SM)
 _SPLIT_CTAS = int(_os.environ.get("DS_SPLIT_CTAS", "-1"))  # -1: one per SM
 _SPLIT_TILE = int(_os.environ.get("DS_SPLIT_TILE", "0"))   # tuning: tile = k * 256 rows
-_EARLY_PAYLOAD = int(_os.environ.get("DS_EARLY_PAYLOAD", "-1"))  # 1 / 0 force, -1: from the world size
+_EARLY_PAYLOAD = int(_os.environ.get("DS_EARLY_PAYLOAD", "0"))  # 1: payload beside the key transfer
 _LANES = _os.environ.get("DS_P2P_LANES", "1") == "1"  # one copy stream per destination
 _peer_cache: dict = {}
 
@@ -716,10 +716,11 @@ def _sort_block_split(block, key, descending, group, ph, consume=False, rounds: 
     ev = {k: torch.cuda.Event(enable_timing=True) for k in ("k0", "k1", "p0", "p1", "w0", "w1")}
     main = torch.cuda.current_stream()
     pb.hdl.barrier(channel=0)  # every rank is done with the buffer's previous contents
-    # When the step is bound by the payload transfer (4 GPUs and more: each GPU ships 3/4..7/8 of
-    # its rows) the payload starts at once, beside the key transfer, so that NVLink never idles;
-    # with fewer GPUs the key sort is the longer chain and the keys get the link to themselves.
-    early_payload = _EARLY_PAYLOAD == 1 or (_EARLY_PAYLOAD < 0 and world >= 4)
+    # DS_EARLY_PAYLOAD=1 starts the payload transfer beside the key transfer instead of after it.
+    # Measured slower on 2 and on 8 GPUs (the key split is starved by the payload kernel: 5.8
+    # instead of 1.7 ms at N=8, and the key sort starts that much later; profiles/r02_b8_early*.json),
+    # so the keys get the link to themselves by default.
+    early_payload = _EARLY_PAYLOAD == 1
     ev_start = torch.cuda.Event(enable_timing=True)
     ev_start.record()
 
