@@ -245,6 +245,40 @@ def test_stats_sort_and_aggregate(m):
     assert agg.stats().index("sort_map") < agg.stats().index("aggregate_map")   # parents first
 
 
+def test_stats_wall_time_is_device_time(m):
+    """'Remote wall time' of a sort is the DEVICE time of its launches (CUDA events recorded by
+    the BlockExecStats builder), not the host time it took to enqueue them: it agrees with a
+    CUDA-event pair around the whole sort, and NVTX ranges do not change results."""
+    import torch
+
+    from ray_memory_management_b200 import _nvtx
+
+    n = 4_000_000
+    rng = np.random.default_rng(9)
+    t = pa.table({"k": rng.integers(0, 2**62, n, dtype=np.int64), "v": np.arange(n, dtype=np.int64)})
+    blk = m.DeviceArrowBlock.from_arrow(t)
+    for _ in range(2):  # warm-up: workspace allocations
+        m.Dataset.from_blocks([blk]).sort("k")
+    torch.cuda.synchronize()
+    nvtx_on = _nvtx.enable(True)  # ranges around every stage phase and ds_* call (no-op without NVTX)
+    try:
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        ds = m.Dataset.from_blocks([blk]).sort("k")
+        e1.record()
+        torch.cuda.synchronize()
+    finally:
+        _nvtx.enable(False)
+    assert isinstance(nvtx_on, bool)
+    outer_s = e0.elapsed_time(e1) / 1e3
+    metas = ds._stats.stages["sort_reduce"]
+    dev_s = max(md.exec_stats.wall_time_s for md in metas)
+    assert dev_s > 0
+    assert 0.3 * outer_s <= dev_s <= 1.05 * outer_s, (dev_s, outer_s)
+    assert all(md.exec_stats.host_time_s is not None for md in metas)
+    assert np.array_equal(ds.to_arrow_concat()["k"].to_numpy(), np.sort(t["k"].to_numpy()))
+
+
 # ------------------------------------------------------------------------- loaders
 def test_read_parquet_and_ipc_round_trip(m, tmp_path):
     import pyarrow.parquet as pq
