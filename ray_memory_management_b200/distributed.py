@@ -663,6 +663,7 @@ def _sort_block_split(block, key, descending, group, ph, consume=False, rounds: 
             wires.append((name + _VALID, 1, v))
     nkey = 2 if key in with_valid else 1
     rbs = {w: rb for w, rb, _ in wires}
+    key_rb = sum(rb for _, rb, _ in wires[:nkey])
     # receive layout, identical on every rank: one region per (wire, round), each with room for
     # the fullest (rank, round) anywhere
     cap_rows = int(matrix.sum(axis=0).max())
@@ -798,6 +799,16 @@ def _sort_block_split(block, key, descending, group, ph, consume=False, rounds: 
     ph.mark("key sort")
     if PAYLOAD_AFTER_SORT:
         send_payload()
+    if consume:
+        # clear_input_blocks: every row of the input must have left before the input's memory can
+        # make room for the output, so the gathers wait for the whole payload here
+        main.wait_stream(pb.side)
+        torch.cuda.synchronize()
+        wires = None
+        block.columns.clear()
+        stage_buf.clear()
+        del dest, offs, wide
+        torch.cuda.empty_cache()
     outs = []
     for r in range(R):  # "reduce": the round's output block, as soon as its payload is here
         if r == R - 1:
@@ -823,15 +834,9 @@ def _sort_block_split(block, key, descending, group, ph, consume=False, rounds: 
     _last_exchange.update(
         bytes_out=remote_rows * sum(rbs.values()),
         bytes_in=(sum(n_round) - own) * sum(rbs.values()),
-        key_bytes_out=remote_rows * sum(rb for _, rb, _ in wires[:nkey]))
+        key_bytes_out=remote_rows * key_rb)
     if EXCHANGE_LOG is not None:
         EXCHANGE_LOG.append(dict(_last_exchange))
-    if consume:  # every row of the input now lives in some rank's receive buffer
-        wires = None
-        block.columns.clear()
-        del dest, offs
-        torch.cuda.synchronize()
-        torch.cuda.empty_cache()
     ph.mark("gather payload")
     ph.finish()
     return outs, marks
