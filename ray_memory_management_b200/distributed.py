@@ -25,7 +25,7 @@ import pyarrow as pa
 import torch
 import torch.distributed as dist
 
-SAMPLES_PER_RANK = 2048
+SAMPLES_PER_RANK = 8192
 
 # Optional phase timing (DS_DIST_TIMING=1): CUDA events on the current stream; the list of
 # (phase, ms) of the last call is left in LAST_TIMING.  Measurement aid only.
