@@ -44,6 +44,7 @@ def main():
     torch.cuda.synchronize()
     dist.barrier()
     free0 = torch.cuda.mem_get_info()[0]
+    torch.cuda.reset_peak_memory_stats()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
     out = D.sort_block(blk, "key", consume=True)
@@ -75,6 +76,8 @@ def main():
             "checksum_preserved": t[0] % (1 << 62) == t[1] % (1 << 62), "records_in": t[2], "records_out": t[3],
             "unordered_records": t[4], "rank_boundaries_ordered": ordered,
             "free_hbm_before_gb": free0 / 1e9,
+            "peak_torch_allocated_gb_rank0": torch.cuda.max_memory_allocated() / 1e9,
+            "exchange": os.environ.get("DS_EXCHANGE", "split"),
         }), flush=True)
     dist.destroy_process_group()
 

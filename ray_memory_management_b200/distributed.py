@@ -804,7 +804,7 @@ def _sort_block_split(block, key, descending, group, ph, consume=False, rounds: 
         # make room for the output, so the gathers wait for the whole payload here
         main.wait_stream(pb.side)
         torch.cuda.synchronize()
-        wires = None
+        wires = c = src = v = None  # (loop variables above still name the last column's tensors)
         block.columns.clear()
         stage_buf.clear()
         del dest, offs, wide
