@@ -663,12 +663,13 @@ def _sort_block_split(block, key, descending, group, ph, consume=False, rounds: 
             wires.append((name + _VALID, 1, v))
     nkey = 2 if key in with_valid else 1
     rbs = {w: rb for w, rb, _ in wires}
-    key_rb = sum(rb for _, rb, _ in wires[:nkey])
+    key_rb = sum(rb for _w, rb, _t in wires[:nkey])
     # receive layout, identical on every rank: one region per (wire, round), each with room for
     # the fullest (rank, round) anywhere
     cap_rows = int(matrix.sum(axis=0).max())
     region, total = {}, 0
-    for w, rb, _ in wires:
+    wire_rb = [(w, rb) for w, rb, _t in wires]  # names and widths only: no tensor references
+    for w, rb in wire_rb:
         for r in range(R):
             region[(w, r)] = total
             total += _align(cap_rows * rb)
@@ -693,7 +694,7 @@ def _sort_block_split(block, key, descending, group, ph, consume=False, rounds: 
     for r in range(direct_rounds, R):
         cnt = [int(matrix[rank, d * R + r]) for d in range(world)]
         stage_off[r] = np.concatenate([[0], np.cumsum(cnt)])
-        for w, rb, _ in wires[nkey:]:
+        for w, rb in wire_rb[nkey:]:
             stage_buf[(w, r)] = torch.empty(max(int(stage_off[r][-1]) * rb, 1), dtype=torch.uint8, device=dev)
 
     def base_of(w, rb, j):
@@ -765,7 +766,7 @@ def _sort_block_split(block, key, descending, group, ph, consume=False, rounds: 
                 lane = pb.lanes[d]
                 lane.wait_stream(pb.side)
                 with torch.cuda.stream(lane):
-                    for w, rb, _ in wires[nkey:]:
+                    for w, rb in wire_rb[nkey:]:
                         dst = pb.hdl.get_buffer(d, (rows * rb,), torch.uint8,
                                                 region[(w, r)] + int(before[d * R + r]) * rb)
                         o = int(stage_off[r][d]) * rb
