@@ -1,6 +1,7 @@
-// onesweep pass, third generation.  Same protocol as onesweep_v2.cuh (early counts,
-// aggregate published before ranking, batched look-back, full-tile fast path) with the two
-// per-item costs that dominated its profile replaced:
+// onesweep pass, third generation (the first two were retired after round 1; their profiles are
+// in profiles/r01_pass_kernel_v2_summary.txt).  Early per-warp digit counts, tile aggregate
+// published before ranking, batched look-back, full-tile fast path; compared with the second
+// generation the two per-item costs that dominated its profile are replaced:
 //
 //  * peer matching through shared memory instead of 8 ballots.  On B200 the ALU pipe was
 //    the busiest unit of v2 (~70 ALU instructions per key, most of them the ballot / LOP3

@@ -15,12 +15,15 @@
 //                        one global flush per block).
 //   scan_hist_kernel     exclusive scan per digit position -> global bin bases, and a
 //                        "constant digit" flag per position (such passes are skipped).
-//   onesweep_pass_kernel one 8-bit pass: warp-striped coalesced loads, per-warp digit
-//                        histograms ranked with match.any (stable), per-digit
-//                        decoupled look-back across tiles (tile ids handed out by an
-//                        atomic counter, so a tile only ever waits on tiles that are
-//                        already resident), shared-memory exchange, coalesced scatter.
+//   onesweep_pass_kernel_v3 (onesweep_v3.cuh) one 8-bit pass: warp-striped coalesced loads,
+//                        per-warp digit counts published to the look-back array before
+//                        ranking, peers of a digit found through a per-warp shared-memory
+//                        table (stable), per-digit decoupled look-back across tiles (tile ids
+//                        handed out by an atomic counter, so a tile only ever waits on tiles
+//                        that are already resident), shared-memory exchange, coalesced scatter.
 //                        Algorithmic bytes per key per pass: 2*(8[+2]+4) = 24 / 28.
+//   bucket_local_sort_kernel (bucket_sort.cuh) finishes a sort whose two leading bytes have
+//                        been sorted globally: one CTA per 16-bit bucket in shared memory.
 //   decode_kernel        sorted hi/lo -> sorted key column in its Arrow form.
 #include <atomic>
 #include <utility>
@@ -275,166 +278,27 @@ struct PassSmem {
   static constexpr int BYTES = (EXCH > HIST ? EXCH : HIST);
 };
 
-template <int THREADS, int ITEMS, int MIN_BLOCKS, bool HAS_LO, bool DIGIT_LO, bool GEN_IDX>
-__global__ void __launch_bounds__(THREADS, MIN_BLOCKS)
-    onesweep_pass_kernel(const uint64_t* __restrict__ hi_in, const uint16_t* __restrict__ lo_in,
-                         const uint32_t* __restrict__ idx_in, uint64_t* __restrict__ hi_out,
-                         uint16_t* __restrict__ lo_out, uint32_t* __restrict__ idx_out, uint32_t n,
-                         int shift, const uint32_t* __restrict__ bin_base,
-                         volatile uint32_t* lookback, uint32_t* tile_counter) {
-  static_assert(THREADS >= RADIX && THREADS % 32 == 0, "one thread per digit is required");
-  using S = PassSmem<THREADS, ITEMS, HAS_LO>;
-  constexpr int TILE = S::TILE;
-  constexpr int WARPS = S::WARPS;
-  extern __shared__ __align__(16) unsigned char smem[];
-  uint32_t* warp_hist = reinterpret_cast<uint32_t*>(smem);  // [WARPS][RADIX], then reused:
-  uint64_t* ex_hi = reinterpret_cast<uint64_t*>(smem);      // [TILE]
-  uint32_t* ex_idx = reinterpret_cast<uint32_t*>(smem + TILE * 8);
-  uint16_t* ex_lo = reinterpret_cast<uint16_t*>(smem + TILE * 12);
-  __shared__ uint32_t s_gofs[RADIX];
-  __shared__ uint32_t s_dstart[RADIX];
-  __shared__ uint32_t s_warp_tot[8];
-  __shared__ uint32_t s_tile;
-
-  const int tid = threadIdx.x;
-  const int warp = tid >> 5;
-  const uint32_t lane = tid & 31;
-  if (tid == 0) s_tile = atomicAdd(tile_counter, 1u);
+// helpers of the pass kernel (onesweep_v3.cuh)
+__device__ __forceinline__ uint32_t ballot_match8(uint32_t d) {
+  uint32_t peers = 0xffffffffu;
 #pragma unroll
-  for (int i = tid; i < WARPS * RADIX; i += THREADS) warp_hist[i] = 0;
-  __syncthreads();
-  const uint32_t tile = s_tile;
-  const uint32_t tile_base = tile * TILE;
-  const uint32_t tile_valid = min(static_cast<uint32_t>(TILE), n - tile_base);
-  const bool full = tile_valid == TILE;
-
-  // ---- load (warp-striped: item i of lane l sits at warp_base + i*32 + l)
-  uint64_t hi[ITEMS];
-  uint32_t lo[ITEMS];
-  uint32_t idx[ITEMS];
-  uint32_t rank[ITEMS];
-  const uint32_t wofs = warp * 32 * ITEMS + lane;  // tile-local position of item 0
-#pragma unroll
-  for (int i = 0; i < ITEMS; ++i) {
-    const uint32_t lp = wofs + i * 32;
-    const uint32_t gp = tile_base + lp;
-    if (full || lp < tile_valid) {
-      hi[i] = ld_stream(hi_in + gp);
-      lo[i] = HAS_LO ? ld_stream(lo_in + gp) : 0;
-      idx[i] = GEN_IDX ? gp : ld_stream(idx_in + gp);
-    } else {
-      hi[i] = 0;
-      lo[i] = 0;
-      idx[i] = 0;
-    }
+  for (int b = 0; b < 8; ++b) {
+    const bool bit = (d >> b) & 1u;
+    const uint32_t v = __ballot_sync(0xffffffffu, bit);
+    peers &= bit ? v : ~v;
   }
-
-  // ---- rank inside the warp (stable: items visited in position order, peers by lane)
-  uint32_t* wh = warp_hist + warp * RADIX;
-  const uint32_t lt_mask = lanemask_lt();
-#pragma unroll
-  for (int i = 0; i < ITEMS; ++i) {
-    const bool valid = full || (wofs + i * 32 < tile_valid);
-    const uint32_t d = valid ? digit_of<HAS_LO, DIGIT_LO>(hi[i], lo[i], shift) : 0xFFFFFFFFu;
-    const uint32_t peers = __match_any_sync(0xffffffffu, d);
-    const uint32_t lt = __popc(peers & lt_mask);
-    uint32_t prev = 0;
-    if (valid) prev = wh[d];
-    __syncwarp();
-    if (valid && lt == 0) wh[d] = prev + __popc(peers);
-    __syncwarp();
-    rank[i] = prev + lt;
-  }
-  __syncthreads();
-
-  // ---- per digit: scan over warps, scan over digits, look back over earlier tiles
-  if (tid < RADIX) {
-    uint32_t sum = 0;
-#pragma unroll
-    for (int w = 0; w < WARPS; ++w) {
-      const uint32_t c = warp_hist[w * RADIX + tid];
-      warp_hist[w * RADIX + tid] = sum;
-      sum += c;
-    }
-    // publish this tile's count as early as possible
-    volatile uint32_t* my = lookback + static_cast<size_t>(tile) * RADIX + tid;
-    if (tile == 0) {
-      *my = LB_INCLUSIVE | sum;
-    } else {
-      *my = LB_AGGREGATE | sum;
-    }
-    // block-wide exclusive scan of the 256 digit counts
-    uint32_t v = sum;
-#pragma unroll
-    for (int o = 1; o < 32; o <<= 1) {
-      uint32_t t = __shfl_up_sync(0xffffffffu, v, o);
-      if ((int)lane >= o) v += t;
-    }
-    if (lane == 31) s_warp_tot[warp] = v;
-    asm volatile("bar.sync 1, 256;");
-    uint32_t add = 0;
-#pragma unroll
-    for (int w = 0; w < 8; ++w)
-      if (w < warp) add += s_warp_tot[w];
-    const uint32_t dstart = v + add - sum;
-    s_dstart[tid] = dstart;
-    uint32_t excl = 0;
-    if (tile != 0) {
-      int t = static_cast<int>(tile) - 1;
-      while (true) {
-        uint32_t s = lookback[static_cast<size_t>(t) * RADIX + tid];
-        if ((s & ~LB_VALUE) == 0) continue;  // not published yet: that tile is resident, spin
-        excl += s & LB_VALUE;
-        if (s & LB_INCLUSIVE) break;
-        --t;
-      }
-      *my = LB_INCLUSIVE | (excl + sum);
-    }
-    s_gofs[tid] = bin_base[tid] + excl - dstart;
-  }
-  __syncthreads();
-
-  // ---- tile-local sorted position of every item
-#pragma unroll
-  for (int i = 0; i < ITEMS; ++i) {
-    const bool valid = full || (wofs + i * 32 < tile_valid);
-    if (valid) {
-      const uint32_t d = digit_of<HAS_LO, DIGIT_LO>(hi[i], lo[i], shift);
-      rank[i] += s_dstart[d] + wh[d];
-    }
-  }
-  __syncthreads();  // warp_hist is dead from here: the exchange buffers overlay it
-
-#pragma unroll
-  for (int i = 0; i < ITEMS; ++i) {
-    const bool valid = full || (wofs + i * 32 < tile_valid);
-    if (valid) {
-      ex_hi[rank[i]] = hi[i];
-      ex_idx[rank[i]] = idx[i];
-      if (HAS_LO) ex_lo[rank[i]] = static_cast<uint16_t>(lo[i]);
-    }
-  }
-  __syncthreads();
-
-  // ---- coalesced scatter: consecutive threads own consecutive sorted positions
-#pragma unroll
-  for (int i = 0; i < ITEMS; ++i) {
-    const uint32_t p = tid + i * THREADS;
-    if (full || p < tile_valid) {
-      const uint64_t h = ex_hi[p];
-      const uint32_t l = HAS_LO ? ex_lo[p] : 0;
-      const uint32_t x = ex_idx[p];
-      const uint32_t d = digit_of<HAS_LO, DIGIT_LO>(h, l, shift);
-      const uint32_t dst = s_gofs[d] + p;
-      hi_out[dst] = h;
-      if (HAS_LO) lo_out[dst] = static_cast<uint16_t>(l);
-      idx_out[dst] = x;
-    }
-  }
+  return peers;
+}
+__device__ __forceinline__ uint32_t ld_relaxed_gpu(const volatile uint32_t* p) {
+  uint32_t v;
+  asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_relaxed_gpu(volatile uint32_t* p, uint32_t v) {
+  asm volatile("st.relaxed.gpu.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
 }
 
 }  // namespace ds
-#include "onesweep_v2.cuh"
 #include "onesweep_v3.cuh"
 namespace ds {
 __device__ __forceinline__ uint64_t bswap64(uint64_t v);
@@ -682,13 +546,8 @@ static cudaError_t launch_pass_t(const uint64_t* hi_in, const uint16_t* lo_in,
   const uint32_t tiles = (n + S::TILE - 1) / S::TILE;
   cudaError_t e;
   LaunchTimer timer(TIMED_PASS, s, static_cast<double>(n) * (HAS_LO ? 28.0 : 24.0));
-  if (VARIANT == 1) {
-    auto k = onesweep_pass_kernel<THREADS, ITEMS, MIN_BLOCKS, HAS_LO, DIGIT_LO, GEN_IDX>;
-    if ((e = set_smem_attr(k, S::BYTES, &done_a)) != cudaSuccess) return e;
-    ds::note_launch();
-    k<<<tiles, THREADS, S::BYTES, s>>>(hi_in, lo_in, idx_in, hi_out, lo_out, idx_out, n, shift,
-                                       bin_base, lookback, tile_counter);
-  } else if (VARIANT >= 4) {
+  static_assert(VARIANT >= 4 && VARIANT <= 6, "the first two generations of the pass kernel are retired");
+  {
     constexpr bool TABLE = VARIANT == 4 || VARIANT == 5;
     constexpr bool PACKED = VARIANT == 4 || VARIANT == 6;
     using S3 = PassSmemV3<THREADS, ITEMS, PACKED, HAS_LO>;
@@ -696,6 +555,7 @@ static cudaError_t launch_pass_t(const uint64_t* hi_in, const uint16_t* lo_in,
     auto kt = onesweep_pass_kernel_v3<THREADS, ITEMS, MIN_BLOCKS, HAS_LO, DIGIT_LO, GEN_IDX, false, TABLE, PACKED>;
     if ((e = set_smem_attr(kf, S3::BYTES, &done_a)) != cudaSuccess) return e;
     if ((e = set_smem_attr(kt, S3::BYTES, &done_b)) != cudaSuccess) return e;
+    // full tiles first, then (stream-ordered) the ragged last tile as tile id `full_tiles`
     const uint32_t full_tiles = n / S::TILE;
     if (full_tiles) {
       ds::note_launch();
@@ -706,24 +566,6 @@ static cudaError_t launch_pass_t(const uint64_t* hi_in, const uint16_t* lo_in,
       ds::note_launch();
       kt<<<1, THREADS, S3::BYTES, s>>>(hi_in, lo_in, idx_in, hi_out, lo_out, idx_out, n, shift,
                                        bin_base, lookback, tile_counter);
-    }
-  } else {
-    // full tiles first, then (stream-ordered) the ragged last tile as tile id `full_tiles`
-    constexpr bool M = VARIANT == 3;
-    auto kf = onesweep_pass_kernel_v2<THREADS, ITEMS, MIN_BLOCKS, HAS_LO, DIGIT_LO, GEN_IDX, true, M>;
-    auto kt = onesweep_pass_kernel_v2<THREADS, ITEMS, MIN_BLOCKS, HAS_LO, DIGIT_LO, GEN_IDX, false, M>;
-    if ((e = set_smem_attr(kf, S::BYTES, &done_a)) != cudaSuccess) return e;
-    if ((e = set_smem_attr(kt, S::BYTES, &done_b)) != cudaSuccess) return e;
-    const uint32_t full_tiles = n / S::TILE;
-    if (full_tiles) {
-      ds::note_launch();
-      kf<<<full_tiles, THREADS, S::BYTES, s>>>(hi_in, lo_in, idx_in, hi_out, lo_out, idx_out, n,
-                                               shift, bin_base, lookback, tile_counter);
-    }
-    if (tiles > full_tiles) {
-      ds::note_launch();
-      kt<<<1, THREADS, S::BYTES, s>>>(hi_in, lo_in, idx_in, hi_out, lo_out, idx_out, n, shift,
-                                      bin_base, lookback, tile_counter);
     }
   }
   timer.stop();
@@ -753,11 +595,12 @@ static cudaError_t launch_pass_cfg(bool has_lo, bool digit_lo, bool gen_idx, con
 #undef DS_PASS
 }
 
-// (variant, threads, items, min blocks per SM); variant 1 = first kernel, 2 = v2 ballots,
-// 3 = v2 match.any, 4 = v3 table+packed, 5 = v3 table, 6 = v3 packed
+// (variant, threads, items, min blocks per SM) of onesweep_pass_kernel_v3: variant 4 = match
+// table + packed exchange slots, 5 = match table (the default, cfg 18), 6 = ballots + packed.
+// The first two generations of the kernel (ids 0..11) were retired after round 1; their
+// measurements are in profiles/r01_pass_kernel_v2_summary.txt.
 #define DS_PASS_CONFIGS(X) \
-  X(0, 1, 256, 16, 2) X(4, 2, 512, 8, 2) X(6, 2, 384, 12, 2) X(7, 2, 256, 12, 3) \
-  X(11, 3, 384, 12, 2) X(17, 4, 384, 12, 2) X(18, 5, 384, 12, 2) X(19, 6, 384, 12, 2) \
+  X(17, 4, 384, 12, 2) X(18, 5, 384, 12, 2) X(19, 6, 384, 12, 2) \
   X(20, 4, 512, 8, 2) X(21, 5, 256, 12, 3) X(25, 5, 512, 8, 2) \
   X(28, 5, 256, 16, 2)
 constexpr int NUM_CFGS = 29;  // ids are sparse: unknown ids are rejected

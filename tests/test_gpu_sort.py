@@ -277,9 +277,9 @@ def test_large_graysort_properties(ds):
     assert bool((keys[rowid] == out.columns["key"].data.view(n, 10)).all())
 
 
-@pytest.mark.parametrize("cfg", [0, 4, 6, 7, 11, 17, 18, 19, 20, 21, 25, 28])
+@pytest.mark.parametrize("cfg", [17, 18, 19, 20, 21, 25, 28])
 def test_every_pass_kernel_variant(ds, cfg):
-    """all tile shapes / both generations of the pass kernel give the same bit-exact order."""
+    """all tile shapes / matching and exchange variants of the pass kernel give the same bit-exact order."""
     lib = ds._lib.lib
     old = lib.ds_debug_set_radix_config(cfg)
     try:
