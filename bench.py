@@ -56,7 +56,7 @@ def parse_args():
                    help="single-GPU e2e: steps in flight, 1..4 (>= 2: H2D of step k+1 overlaps D2H of step k)")
     p.add_argument("--no-cpu-baseline", action="store_true")
     p.add_argument("--radix-config", type=int, default=-1, help="tuning: pass-kernel variant")
-    p.add_argument("--gather-mode", type=int, default=-1, help="tuning: see csrc/gather.cu g_gather_mode")
+    p.add_argument("--gather-mode", type=int, default=-1, help="tuning: see csrc/gather.cu g_gather_mode (0 auto, 1, 2, 7, 8)")
     p.add_argument("--l2-fetch", type=int, default=-1, help="tuning: cudaLimitMaxL2FetchGranularity")
     p.add_argument("--blocks-per-gpu", type=int, default=20,
                    help="single GPU: also time the same records held as this many blocks (value_multiblock)")

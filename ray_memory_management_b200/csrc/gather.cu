@@ -15,9 +15,10 @@
 
 namespace ds {
 
-static std::atomic<int> g_gather_mode{0};  // 0 auto (8 where eligible, else 2), 1 plain, 2 plain + L2::64B, 3 staged,
-// 4 staged + L2::64B, 5 direct (no smem idx), 6 32-bit word path for rows of 4k+2 bytes,
-// 7 asynchronous bulk copies per row (gather_bulk.cuh, UBLKCP), 8 the same with 16-byte cp.async.
+static std::atomic<int> g_gather_mode{0};  // 0 auto (8 where eligible, else 2), 1 granule loads,
+// 2 granule loads + L2::64B hint, 7 asynchronous bulk copies per row (gather_bulk.cuh, UBLKCP),
+// 8 the same with 16-byte cp.async.  (Modes 3..6 of round 1 -- staged, direct, 32-bit words --
+// were slower and are gone; their numbers are in profiles/r01_gather_staged_summary.txt.)
 // Measured on 100 M x 90-byte rows (ms per sort step): 2: 10.46, 5: 11.0, 3: 12.7, 6: 14.0
 
 // Read-only loads that ask L2 to fetch only 64 bytes around a miss: random rows gain
@@ -63,99 +64,6 @@ __global__ void __launch_bounds__(256) gather_single_kernel(const G* __restrict_
 constexpr int GATHER_THREADS = 256;
 constexpr int GATHER_MAX_ROWS = 1024;
 
-// Rows whose size is even but not a multiple of 4 (the 90-byte GraySort payload): the block's
-// output span is written as aligned 32-bit words (full 128-byte lines per warp store); every
-// word is assembled from the two aligned source words that cover it (byte_perm), so the global
-// instruction count per 4 bytes drops from 4 (two 16-bit loads, two 16-bit stores) to 3.
-// Requires: W even, src 2-byte aligned, dst 4-byte aligned, rows_per_block * W % 4 == 0.
-template <bool HINT>
-__global__ void __launch_bounds__(GATHER_THREADS)
-    gather_rows_w32_kernel(const uint8_t* __restrict__ src, uint64_t src_bytes,
-                           const uint32_t* __restrict__ idx, uint8_t* __restrict__ dst, uint32_t n,
-                           uint32_t W, uint32_t rows_per_block, uint32_t magic_w) {
-  __shared__ uint32_t s_idx[GATHER_MAX_ROWS + 1];
-  const uint32_t row0 = blockIdx.x * rows_per_block;
-  const uint32_t rows = min(rows_per_block, n - row0);
-  for (uint32_t r = threadIdx.x; r < rows; r += GATHER_THREADS) s_idx[r] = ld_stream(idx + row0 + r);
-  __syncthreads();
-  const uint32_t nbytes = rows * W;
-  const uint32_t nwords = nbytes >> 2;
-  uint32_t* out = reinterpret_cast<uint32_t*>(dst + static_cast<uint64_t>(row0) * W);
-  const uintptr_t base = reinterpret_cast<uintptr_t>(src);
-  const uintptr_t end = base + src_bytes;
-  auto half_at = [&](uint32_t o) -> uint32_t {  // 16 bits at span byte offset o (even)
-    const uint32_t r = __umulhi(o, magic_w);
-    return __ldg(reinterpret_cast<const uint16_t*>(base + static_cast<uint64_t>(s_idx[r]) * W + (o - r * W)));
-  };
-  auto word_at = [&](uint32_t q) -> uint32_t {
-    const uint32_t o = q << 2;
-    const uint32_t r = __umulhi(o, magic_w);
-    const uint32_t off = o - r * W;
-    const uintptr_t a = base + static_cast<uint64_t>(s_idx[r]) * W + off;
-    if (off + 4 <= W) {
-      const uintptr_t a4 = a & ~uintptr_t(3);
-      if ((a & 2) == 0) return HINT ? ld_nc_64B(reinterpret_cast<const uint32_t*>(a4)) : __ldg(reinterpret_cast<const uint32_t*>(a4));
-      if (a4 >= base && a4 + 8 <= end) {
-        const uint32_t w0 = HINT ? ld_nc_64B(reinterpret_cast<const uint32_t*>(a4)) : __ldg(reinterpret_cast<const uint32_t*>(a4));
-        const uint32_t w1 = HINT ? ld_nc_64B(reinterpret_cast<const uint32_t*>(a4 + 4)) : __ldg(reinterpret_cast<const uint32_t*>(a4 + 4));
-        return __byte_perm(w0, w1, 0x5432);
-      }
-    }
-    return half_at(o) | (half_at(o + 2) << 16);  // straddles two rows, or touches the buffer edge
-  };
-  constexpr int UNROLL = 8;
-  uint32_t q = threadIdx.x;
-  for (; q + (UNROLL - 1) * GATHER_THREADS < nwords; q += UNROLL * GATHER_THREADS) {
-    uint32_t v[UNROLL];
-#pragma unroll
-    for (int k = 0; k < UNROLL; ++k) v[k] = word_at(q + k * GATHER_THREADS);
-#pragma unroll
-    for (int k = 0; k < UNROLL; ++k) st_stream(out + q + k * GATHER_THREADS, v[k]);
-  }
-  for (; q < nwords; q += GATHER_THREADS) st_stream(out + q, word_at(q));
-  // a ragged last block may end on a half word
-  if ((nbytes & 2) && threadIdx.x == 0)
-    *reinterpret_cast<uint16_t*>(reinterpret_cast<uint8_t*>(out) + (nwords << 2)) = static_cast<uint16_t>(half_at(nwords << 2));
-}
-
-// Same work without the shared-memory index stage: every element reads its row number
-// through L1 (consecutive lanes share it), so a block never waits at a barrier.
-template <typename G, bool HINT>
-__global__ void __launch_bounds__(GATHER_THREADS)
-    gather_rows_direct_kernel(const G* __restrict__ src, const uint32_t* __restrict__ idx,
-                              G* __restrict__ dst, uint32_t n, uint32_t gpr, uint32_t rows_per_block,
-                              uint32_t magic) {
-  const uint32_t row0 = blockIdx.x * rows_per_block;
-  const uint32_t rows = min(rows_per_block, n - row0);
-  const uint32_t total = rows * gpr;
-  const uint32_t* ib = idx + row0;
-  G* out = dst + static_cast<uint64_t>(row0) * gpr;
-  constexpr int UNROLL = 16;
-  uint32_t e = threadIdx.x;
-  for (; e + (UNROLL - 1) * GATHER_THREADS < total; e += UNROLL * GATHER_THREADS) {
-    uint32_t rr[UNROLL], ii[UNROLL];
-#pragma unroll
-    for (int k = 0; k < UNROLL; ++k) {
-      rr[k] = __umulhi(e + k * GATHER_THREADS, magic);
-      ii[k] = __ldg(ib + rr[k]);
-    }
-    G v[UNROLL];
-#pragma unroll
-    for (int k = 0; k < UNROLL; ++k) {
-      const uint32_t ee = e + k * GATHER_THREADS;
-      const G* p = src + static_cast<uint64_t>(ii[k]) * gpr + (ee - rr[k] * gpr);
-      v[k] = HINT ? ld_nc_64B(p) : __ldg(p);
-    }
-#pragma unroll
-    for (int k = 0; k < UNROLL; ++k) st_stream(out + e + k * GATHER_THREADS, v[k]);
-  }
-  for (; e < total; e += GATHER_THREADS) {
-    const uint32_t r = __umulhi(e, magic);
-    const G* p = src + static_cast<uint64_t>(__ldg(ib + r)) * gpr + (e - r * gpr);
-    st_stream(out + e, HINT ? ld_nc_64B(p) : __ldg(p));
-  }
-}
-
 template <typename G, bool HINT>
 __global__ void __launch_bounds__(GATHER_THREADS)
     gather_rows_kernel(const G* __restrict__ src, const uint32_t* __restrict__ idx,
@@ -191,111 +99,13 @@ __global__ void __launch_bounds__(GATHER_THREADS)
   }
 }
 
-// ---- staged gather for rows that are not a multiple of 16 bytes (e.g. 90-byte payloads)
-// Phase 1 pulls every source row in as ALIGNED 16-byte vectors (the aligned span that
-// covers the row: at most ceil((W+15)/16)+... chunks) into a shared-memory slot; phase 2
-// re-reads the slots at their byte misalignment (two aligned 32-bit words + byte_perm per
-// output word) and writes the block's contiguous output span as aligned 16-byte vectors.
-// Global traffic is therefore all 128-bit; only shared memory sees the odd alignment.
+// ---- helpers of the staged peer scatter below (rows that are not a multiple of 16 bytes are
+// pulled in as ALIGNED 16-byte vectors and re-read from shared memory at their misalignment)
 constexpr int STAGE_THREADS = 256;
 
 __device__ __forceinline__ uint32_t smem_word_unaligned(const uint8_t* base, uint32_t byte_off) {
   const uint32_t* w = reinterpret_cast<const uint32_t*>(base + (byte_off & ~3u));
   return __byte_perm(w[0], w[1], 0x3210u + 0x1111u * (byte_off & 3u));
-}
-
-__global__ void __launch_bounds__(STAGE_THREADS)
-    gather_staged_kernel(const uint8_t* __restrict__ src, uint32_t W, uint64_t src_bytes,
-                         const uint32_t* __restrict__ idx, uint32_t n, uint8_t* __restrict__ dst,
-                         uint32_t rows_per_block, uint32_t chunks, uint32_t magic_w,
-                         uint32_t magic_c, bool hint) {
-  extern __shared__ __align__(16) uint8_t sm[];
-  const uint32_t slot = chunks * 16 + 16;  // +16: the word pair read in phase 2 may overhang
-  uint64_t* s_a0 = reinterpret_cast<uint64_t*>(sm);                       // [R] aligned source address
-  uint32_t* s_shift = reinterpret_cast<uint32_t*>(sm + rows_per_block * 8);  // [R] misalignment
-  uint8_t* data = sm + rows_per_block * 12;                                // [R][slot], 16-aligned
-  const uint32_t row0 = blockIdx.x * rows_per_block;
-  const uint32_t rows = min(rows_per_block, n - row0);
-  const uintptr_t base = reinterpret_cast<uintptr_t>(src);
-  const uintptr_t safe_lo = (base + 15) & ~uintptr_t(15);
-  const uintptr_t safe_hi = (base + src_bytes) & ~uintptr_t(15);
-
-  for (uint32_t r = threadIdx.x; r < rows; r += STAGE_THREADS) {
-    const uintptr_t a = base + static_cast<uint64_t>(ld_stream(idx + row0 + r)) * W;
-    s_a0[r] = a & ~uintptr_t(15);
-    s_shift[r] = static_cast<uint32_t>(a & 15);
-  }
-  __syncthreads();
-
-  const uint32_t items = rows * chunks;
-#pragma unroll 4
-  for (uint32_t e = threadIdx.x; e < items; e += STAGE_THREADS) {
-    const uint32_t r = __umulhi(e, magic_c);
-    const uint32_t c = e - r * chunks;
-    if (c * 16 >= s_shift[r] + W) continue;  // chunk lies wholly after the row
-    const uintptr_t a = s_a0[r] + c * 16;
-    uint4 v;
-    if (a >= safe_lo && a + 16 <= safe_hi) {
-      v = hint ? ld_nc_64B(reinterpret_cast<const uint4*>(a)) : __ldg(reinterpret_cast<const uint4*>(a));
-    } else {  // first / last partial vector of the source buffer: guarded byte loads
-      uint8_t t[16];
-#pragma unroll
-      for (int b = 0; b < 16; ++b)
-        t[b] = (a + b >= base && a + b < base + src_bytes) ? *reinterpret_cast<const uint8_t*>(a + b) : 0;
-      v = *reinterpret_cast<uint4*>(t);
-    }
-    *reinterpret_cast<uint4*>(data + r * slot + c * 16) = v;
-  }
-  __syncthreads();
-
-  const uint32_t nbytes = rows * W;
-  uint8_t* out = dst + static_cast<uint64_t>(row0) * W;  // 16-aligned (rows_per_block % 16 == 0)
-  const uint32_t nvec = nbytes >> 4;
-  for (uint32_t q = threadIdx.x; q < nvec; q += STAGE_THREADS) {
-    uint32_t w[4];
-#pragma unroll
-    for (int k = 0; k < 4; ++k) {
-      const uint32_t o = q * 16 + k * 4;
-      const uint32_t r = __umulhi(o, magic_w);
-      const uint32_t off = o - r * W;
-      if (off + 4 <= W) {
-        w[k] = smem_word_unaligned(data + r * slot, s_shift[r] + off);
-      } else {  // word straddles two rows
-        uint32_t acc = 0;
-#pragma unroll
-        for (int b = 0; b < 4; ++b) {
-          const uint32_t ob = off + b;
-          const uint32_t rr = ob >= W ? r + 1 : r;
-          const uint32_t oo = ob >= W ? ob - W : ob;
-          acc |= static_cast<uint32_t>(data[rr * slot + s_shift[rr] + oo]) << (8 * b);
-        }
-        w[k] = acc;
-      }
-    }
-    st_stream(reinterpret_cast<uint4*>(out) + q, make_uint4(w[0], w[1], w[2], w[3]));
-  }
-  for (uint32_t o = (nvec << 4) + threadIdx.x; o < nbytes; o += STAGE_THREADS) {
-    const uint32_t r = __umulhi(o, magic_w);
-    const uint32_t off = o - r * W;
-    out[o] = data[r * slot + s_shift[r] + off];
-  }
-}
-
-static cudaError_t launch_gather_staged(const void* src, uint32_t W, uint64_t src_rows,
-                                        const uint32_t* idx, uint32_t n, void* dst, cudaStream_t s) {
-  const uint32_t chunks = (W + 15 + 15) / 16;        // worst-case aligned span of a W-byte row
-  const uint32_t slot = chunks * 16 + 16;
-  uint32_t rows = 128;                               // multiple of 16 -> aligned output spans
-  while (rows > 16 && rows * (slot + 12) > 40 * 1024) rows >>= 1;
-  const uint32_t smem = rows * (slot + 12);
-  const uint32_t magic_w = static_cast<uint32_t>((0x100000000ull + W - 1) / W);
-  const uint32_t magic_c = static_cast<uint32_t>((0x100000000ull + chunks - 1) / chunks);
-  const uint32_t blocks = (n + rows - 1) / rows;
-  ds::note_launch();
-  gather_staged_kernel<<<blocks, STAGE_THREADS, smem, s>>>(
-      static_cast<const uint8_t*>(src), W, src_rows * W, idx, n, static_cast<uint8_t*>(dst), rows,
-      chunks, magic_w, magic_c, g_gather_mode == 4);
-  return cudaGetLastError();
 }
 
 template <typename G>
@@ -320,9 +130,6 @@ static cudaError_t launch_gather(const void* src, const uint32_t* idx, void* dst
   ds::note_launch();
   if (g_gather_mode == 1)
     gather_rows_kernel<G, false><<<blocks, GATHER_THREADS, 0, s>>>(
-        static_cast<const G*>(src), idx, static_cast<G*>(dst), n, gpr, rows, magic);
-  else if (g_gather_mode == 5)
-    gather_rows_direct_kernel<G, true><<<blocks, GATHER_THREADS, 0, s>>>(
         static_cast<const G*>(src), idx, static_cast<G*>(dst), n, gpr, rows, magic);
   else
     gather_rows_kernel<G, true><<<blocks, GATHER_THREADS, 0, s>>>(
@@ -532,27 +339,11 @@ ds_status gather_rows_impl(const void* src, uint32_t row_bytes, uint64_t src_row
   // auto: even rows that are not 16-byte multiples take the asynchronous-copy kernel with
   // 16-byte cp.async + 64-byte L2 fetch hint (4.54 ms per 100 M x 90 B against 4.96 ms for the
   // granule kernel and 5.07 ms for per-row bulk copies, whose misses fetch 128-byte lines:
-  // profiles/r02_gather_summary.md)
+  // profiles/r02_gather_final_summary.txt)
   if ((g_gather_mode == 0 || g_gather_mode == 7 || g_gather_mode == 8) &&
       gather_bulk_eligible(src, row_bytes, src_rows, dst)) {
     e = launch_gather_bulk(g_gather_mode == 7 ? FETCH_BULK : FETCH_LDGSTS, src, row_bytes, src_rows, idx, n, dst, s);
-  } else if (g_gather_mode == 6 && (row_bytes & 3) == 2 && row_bytes >= 6 && row_bytes <= 4096 &&
-      src_rows > 0 && (reinterpret_cast<uintptr_t>(src) & 1) == 0 && (reinterpret_cast<uintptr_t>(dst) & 3) == 0) {
-    uint32_t rows = (8192 * 2 / row_bytes) & ~1u;  // even: every block's span starts 4-byte aligned
-    if (rows < 2) rows = 2;
-    if (rows > GATHER_MAX_ROWS) rows = GATHER_MAX_ROWS;
-    const uint32_t magic_w = static_cast<uint32_t>((0x100000000ull + row_bytes - 1) / row_bytes);
-    ds::note_launch();
-    gather_rows_w32_kernel<true><<<(n + rows - 1) / rows, GATHER_THREADS, 0, s>>>(
-        static_cast<const uint8_t*>(src), src_rows * row_bytes, idx, static_cast<uint8_t*>(dst), n, row_bytes,
-        rows, magic_w);
-    e = cudaGetLastError();
-  } else
-  // rows that are not 16-byte multiples: aligned-vector staging through shared memory
-  if ((row_bytes & 15) != 0 && row_bytes >= 16 && row_bytes <= 2048 && src_rows > 0 &&
-      (reinterpret_cast<uintptr_t>(dst) & 15) == 0 && (g_gather_mode == 3 || g_gather_mode == 4))
-    e = launch_gather_staged(src, row_bytes, src_rows, idx, n, dst, s);
-  else if ((bits & 15) == 0) e = launch_gather<uint4>(src, idx, dst, n, row_bytes, s);
+  } else if ((bits & 15) == 0) e = launch_gather<uint4>(src, idx, dst, n, row_bytes, s);
   else if ((bits & 7) == 0) e = launch_gather<uint2>(src, idx, dst, n, row_bytes, s);
   else if ((bits & 3) == 0) e = launch_gather<uint32_t>(src, idx, dst, n, row_bytes, s);
   else if ((bits & 1) == 0) e = launch_gather<uint16_t>(src, idx, dst, n, row_bytes, s);

@@ -303,9 +303,9 @@ def test_every_pass_kernel_variant(ds, cfg):
 
 @pytest.mark.parametrize("width", [1, 2, 3, 8, 10, 16, 17, 18, 24, 33, 90, 100, 250, 1022])
 @pytest.mark.parametrize("start_row", [0, 1, 3])
-@pytest.mark.parametrize("mode", [0, 2, 3, 5, 7, 8])
+@pytest.mark.parametrize("mode", [0, 1, 2, 7, 8])
 def test_gather_rows_c_abi(ds, width, start_row, mode):
-    """every granule path of ds_gather_rows (incl. the staged kernel for rows that are not a
+    """every granule path of ds_gather_rows and both asynchronous-copy kernels (rows that are not a
     multiple of 16 bytes), with the source column starting at odd byte offsets."""
     lib = ds._lib
     rng = np.random.default_rng(width * 7 + start_row)
@@ -329,14 +329,14 @@ def test_gather_rows_c_abi(ds, width, start_row, mode):
     assert not got[n_out * width:].any()  # nothing written past the output
 
 
-def test_gather_staged_equals_plain(ds):
+def test_gather_variants_agree(ds):
     lib = ds._lib
     rng = np.random.default_rng(0)
     n = 300_001
     src = torch.from_numpy(rng.integers(0, 256, n * 90, dtype=np.uint8)).cuda()
     idx = torch.from_numpy(rng.permutation(n).astype(np.int32)).cuda()
     outs = []
-    for mode in (1, 2, 3, 4, 5, 6, 7, 8):
+    for mode in (1, 2, 7, 8):
         old = lib.lib.ds_debug_set_gather_mode(mode)
         out = torch.empty(n * 90, dtype=torch.uint8, device="cuda")
         lib.call("ds_gather_rows", src.data_ptr(), 90, n, idx.data_ptr(), n, out.data_ptr(),
