@@ -306,8 +306,42 @@ def gen_varlen():
     np.savez_compressed(os.path.join(OUT, "varlen.npz"), **out)
 
 
+def _ipc_bytes(t: pa.Table) -> np.ndarray:
+    sink = pa.BufferOutputStream()
+    with pa.ipc.new_stream(sink, t.schema) as w:
+        w.write_table(t)
+    return np.frombuffer(sink.getvalue().to_pybytes(), dtype=np.uint8).copy()
+
+
+def gen_partial_agg():
+    """The COMBINED (not finalised) blocks of the reference: ArrowBlockAccessor.combine
+    (arrow_block.py:396-467) and aggregate_combined_blocks(finalize=False) (:488-587) -- list
+    columns [accumulator parts..., has_data] with None for groups whose result is null
+    (null_aggregate.py:29-65).  Stored as Arrow IPC streams (npz holds no list columns)."""
+    ns = ref_shim.load()
+    A = ns.aggregate
+    AB = ns.arrow_block.ArrowBlockAccessor
+    rng = np.random.default_rng(11)
+    n = 3000
+    k = np.sort(rng.integers(0, 120, n)).astype(np.int64)
+    v = rng.integers(-50, 50, n).astype(np.float64) / 4.0           # exactly representable
+    w = rng.integers(-1000, 1000, n).astype(np.int64)
+    vmask = rng.random(n) < 0.15
+    vmask[k == 7] = True                                             # a group with no valid value
+    t = pa.table({"k": k, "v": pa.array(v, mask=vmask), "w": w})
+    aggs = (A.Sum("v"), A.Mean("v"), A.Count(), A.Max("w"), A.Min("v"), A.Std("v"),
+            A.Sum("v", ignore_nulls=False), A.Mean("w"), A.Sum("w"), A.AbsMax("w"))
+    halves = [t.slice(0, 1700), t.slice(1700)]                       # key 0..: groups straddle the cut
+    parts = [AB(h).combine("k", aggs) for h in halves]
+    merged, _ = AB.aggregate_combined_blocks(parts, "k", aggs, False)
+    out = {"input": _ipc_bytes(t), "cut": np.array([1700]), "combined_0": _ipc_bytes(parts[0]),
+           "combined_1": _ipc_bytes(parts[1]), "merged_partial": _ipc_bytes(merged)}
+    np.savez_compressed(os.path.join(OUT, "partial_agg.npz"), **out)
+
+
 def main():
     os.makedirs(OUT, exist_ok=True)
+    gen_partial_agg()
     gen_varlen()
     gen_nulls()
     gen_sort_int64()

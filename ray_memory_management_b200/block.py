@@ -890,8 +890,60 @@ class PartialAggBlock(DeviceArrowBlock):
 
     The reference stores each accumulator as an Arrow list column with a trailing
     has_data flag (python/ray/data/_internal/null_aggregate.py:29-46); on device the
-    numeric parts are kept as plain columns named ``<agg>#sum`` / ``<agg>#count`` / ...
-    and the list wrapper is not materialised."""
+    numeric parts are kept as plain columns named ``<agg>#sum`` / ``<agg>#nvalid`` / ...
+    (``to_flat_arrow``), and the list wrapper is built only at the export boundary: ``to_arrow``
+    of a block that knows its aggregations returns the reference's table."""
+
+    def __init__(self, columns, num_rows, key: Optional[str] = None, aggs=None):
+        super().__init__(columns, num_rows)
+        self.key = key
+        self.aggs = aggs
+
+    def to_flat_arrow(self) -> pa.Table:
+        return DeviceArrowBlock.to_arrow(self)
+
+    def to_arrow(self) -> pa.Table:
+        """The block as ArrowBlockAccessor.combine / aggregate_combined_blocks(finalize=False)
+        return it (arrow_block.py:396-467, 488-587): the key column, then per aggregation a
+        ``list`` column ``[accumulator parts..., has_data]`` -- ``count()`` stays int64 -- where
+        a group without any valid value holds the initial accumulator with has_data 0
+        (ignore_nulls) and a group that met a null holds None (ignore_nulls=False)
+        (null_aggregate.py:29-65, 93-138)."""
+        flat = self.to_flat_arrow()
+        if self.aggs is None:
+            return flat
+        n = self._num_rows
+        arrays, names = [], []
+        if self.key is not None:
+            arrays.append(flat[self.key].combine_chunks())
+            names.append(self.key)
+        for name, agg in zip(resolve_agg_names(self.aggs), self.aggs):
+            parts = {p: flat[f"{name}#{p}"].to_numpy(zero_copy_only=False) for p in agg._device_merge_ops()}
+            names.append(name)
+            if set(parts) == {"count"}:
+                arrays.append(pa.array(parts["count"], pa.int64()))
+                continue
+            kind = agg._kind
+            if kind == "mean":
+                cols, init = [parts["sum"], parts["nvalid"]], [0, 0]
+            elif kind == "std":
+                cols, init = [parts["m2"], parts["mean"], parts["nvalid"]], [0, 0, 0]
+            else:
+                cols = [parts[kind]]
+                init = [{"sum": 0, "absmax": 0, "min": np.inf, "max": -np.inf}[kind]]
+            has = parts["nvalid"] > 0
+            null = np.zeros(n, dtype=bool) if agg._ignore_nulls else parts["nvalid"] < parts["nrows"]
+            is_int = all(c.dtype.kind in "iu" for c in cols) and all(np.isfinite(v) for v in init)
+            dt = np.int64 if is_int else np.float64
+            width = len(cols) + 1
+            mat = np.empty((n, width), dtype=dt)
+            for c, (col, v0) in enumerate(zip(cols, init)):
+                mat[:, c] = np.where(has, col.astype(dt), dt(v0) if is_int else v0)
+            mat[:, width - 1] = has
+            offsets = pa.array(np.arange(n + 1, dtype=np.int32) * width, pa.int32())
+            arrays.append(pa.ListArray.from_arrays(offsets, pa.array(mat.reshape(-1)),
+                                                   mask=pa.array(null) if null.any() else None))
+        return pa.Table.from_arrays(arrays, names=names)
 
 
 class DeviceArrowBlockAccessor:
@@ -1084,7 +1136,7 @@ class DeviceArrowBlockAccessor:
         n = blk.num_rows
         cols = collections.OrderedDict()
         if n == 0:
-            return PartialAggBlock(cols, 0)
+            return PartialAggBlock(cols, 0, key, aggs)
         if key is None:
             starts = torch.tensor([0, n], dtype=torch.int32, device="cuda")
             nseg = 1
@@ -1098,7 +1150,7 @@ class DeviceArrowBlockAccessor:
         for name, agg in zip(resolve_agg_names(aggs), aggs):
             for part, col in agg._device_accumulate(blk, starts, nseg, n).items():
                 cols[f"{name}#{part}"] = col
-        return PartialAggBlock(cols, nseg)
+        return PartialAggBlock(cols, nseg, key, aggs)
 
     @staticmethod
     def aggregate_combined_blocks(blocks: List[PartialAggBlock], key: Optional[str],
@@ -1139,7 +1191,7 @@ class DeviceArrowBlockAccessor:
             else:
                 for p, c in parts.items():
                     cols[f"{name}#{p}"] = c
-        ret = (DeviceArrowBlock if finalize else PartialAggBlock)(cols, nseg)
+        ret = DeviceArrowBlock(cols, nseg) if finalize else PartialAggBlock(cols, nseg, key, aggs)
         return ret, DeviceArrowBlockAccessor(ret).get_metadata(None, exec_stats=stats.build())
 
 

@@ -171,3 +171,54 @@ def test_reference_tabular_groupby_known_answers(ds):
         {"A": 0, "max(B)": 99}, {"A": 1, "max(B)": 97}, {"A": 2, "max(B)": 98}]
     assert [r for r in d.groupby("A").mean("B").iter_rows()] == [
         {"A": 0, "mean(B)": 49.5}, {"A": 1, "mean(B)": 49.0}, {"A": 2, "mean(B)": 50.0}]
+
+
+# ------------------------------------------------------------------ combined (partial) blocks
+def _ipc(a):
+    return pa.ipc.open_stream(a.tobytes()).read_all()
+
+
+def _assert_partial_equal(got: pa.Table, want: pa.Table):
+    """same schema, same nulls, list contents equal (float parts to 1e-9 relative; the path allows 1e-6)"""
+    assert got.schema.equals(want.schema), (got.schema, want.schema)
+    assert got.num_rows == want.num_rows
+    for name in want.column_names:
+        g, w = got[name].combine_chunks(), want[name].combine_chunks()
+        if not pa.types.is_list(w.type):
+            assert g.equals(w), name
+            continue
+        assert g.is_valid().equals(w.is_valid()), name
+        gl, wl = g.to_pylist(), w.to_pylist()
+        for a, b in zip(gl, wl):
+            if b is None:
+                continue
+            assert len(a) == len(b), name
+            assert np.allclose(np.array(a, dtype=np.float64), np.array(b, dtype=np.float64), rtol=1e-9, atol=0,
+                               equal_nan=True), (name, a, b)
+
+
+def test_combined_blocks_export_the_reference_schema(golden):
+    """ArrowBlockAccessor.combine and aggregate_combined_blocks(finalize=False) of the reference
+    (recorded by oracle/gen_golden.py: gen_partial_agg) against the device path's combined
+    blocks at the export boundary: list columns [accumulator parts..., has_data], the initial
+    accumulator with has_data 0 for a group without valid values, None where a null was met and
+    nulls are not ignored; and _GroupbyOp.reduce(partial_reduce=True) returns such a block."""
+    import ray_memory_management_b200 as ds
+    from ray_memory_management_b200.block import DeviceArrowBlockAccessor, PartialAggBlock
+    from ray_memory_management_b200.grouped_dataset import _GroupbyOp
+
+    g = golden("partial_agg")
+    t = _ipc(g["input"])
+    cut = int(g["cut"][0])
+    aggs = (ds.Sum("v"), ds.Mean("v"), ds.Count(), ds.Max("w"), ds.Min("v"), ds.Std("v"),
+            ds.Sum("v", ignore_nulls=False), ds.Mean("w"), ds.Sum("w"), ds.AbsMax("w"))
+    halves = [t.slice(0, cut), t.slice(cut)]
+    parts = [DeviceArrowBlockAccessor(ds.DeviceArrowBlock.from_arrow(h)).combine("k", aggs) for h in halves]
+    for i, p in enumerate(parts):
+        assert isinstance(p, PartialAggBlock)
+        _assert_partial_equal(p.to_arrow(), _ipc(g[f"combined_{i}"]))
+    merged, _ = _GroupbyOp.reduce("k", aggs, *parts, partial_reduce=True)
+    assert isinstance(merged, PartialAggBlock)
+    _assert_partial_equal(merged.to_arrow(), _ipc(g["merged_partial"]))
+    # the flat (device-side) layout stays available
+    assert "sum(v)#sum" in parts[0].to_flat_arrow().column_names

@@ -160,3 +160,18 @@ def test_sort_varlen_string(golden):
     tabs = [pa.table({"key": pa.array(words[a:b], pa.string()), "row": np.arange(a, b, dtype=np.int64)})
             for a, b in g["block_cuts"]]
     assert np.array_equal(O.global_stable_sort(tabs, "key", False)["row"].to_numpy(), g["str_asc_row_order"])
+
+
+def test_partial_agg_golden_is_the_reference_schema(golden):
+    """the combined blocks recorded from the reference: list columns with a trailing has_data
+    flag, None for groups that met a null with ignore_nulls=False (null_aggregate.py:29-65)"""
+    import pyarrow as pa
+
+    g = golden("partial_agg")
+    t = pa.ipc.open_stream(g["combined_0"].tobytes()).read_all()
+    assert t.column_names[:4] == ["k", "sum(v)", "mean(v)", "count()"]
+    assert pa.types.is_list(t["sum(v)"].type) and pa.types.is_int64(t["count()"].type)
+    assert t["sum(v)_2"].null_count > 0 and t["sum(v)"].null_count == 0
+    assert all(len(x) == 3 for x in t["mean(v)"].to_pylist()) and all(len(x) == 4 for x in t["std(v)"].to_pylist())
+    m = pa.ipc.open_stream(g["merged_partial"].tobytes()).read_all()
+    assert m.schema.equals(t.schema)
