@@ -933,7 +933,12 @@ class PartialAggBlock(DeviceArrowBlock):
                 init = [{"sum": 0, "absmax": 0, "min": np.inf, "max": -np.inf}[kind]]
             has = parts["nvalid"] > 0
             null = np.zeros(n, dtype=bool) if agg._ignore_nulls else parts["nvalid"] < parts["nrows"]
-            is_int = all(c.dtype.kind in "iu" for c in cols) and all(np.isfinite(v) for v in init)
+            # integer columns keep integer accumulators (list<int64>); their min / max have no
+            # integer "empty" value (the reference holds +-inf there, which turns that one list
+            # into floats): an integer group without valid values exports 0 with has_data 0
+            is_int = all(c.dtype.kind in "iu" for c in cols)
+            if is_int:
+                init = [v if np.isfinite(v) else 0 for v in init]
             dt = np.int64 if is_int else np.float64
             width = len(cols) + 1
             mat = np.empty((n, width), dtype=dt)
