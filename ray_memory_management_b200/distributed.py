@@ -906,6 +906,9 @@ def sort_block(block, key: str, descending: bool = False, group=None, consume: b
     """Dataset.sort across the ranks of ``group``: this rank's input block in, this rank's
     slice of the globally sorted dataset out (rank order = key order).
 
+    Every rank passes a block with the dataset's columns -- a rank without rows passes a block
+    whose columns are empty, not a block without columns (the ranks do not exchange schemas).
+
     ``consume=True`` is ``clear_input_blocks`` (python/ray/data/_internal/shuffle.py:95-101):
     the input block's columns are dropped as soon as the partitioned copy exists and the send
     buffers as soon as they have been shipped, which is what lets 62.5 GB per GPU fit."""
