@@ -117,6 +117,18 @@ ds_status ds_sort_indices_fsb(const uint8_t* col, uint32_t width, uint64_t n,
 ds_status ds_gather_rows(const void* src, uint32_t row_bytes, uint64_t src_rows,
                          const uint32_t* idx, uint64_t n, void* dst, void* stream);
 
+/* The same gather when the source column lies in several buffers -- the blocks of a dataset --
+ * so that sorting a dataset of many blocks does not first copy them into one
+ * (pa.concat_tables at transform_pyarrow.py:70-75 / _internal/arrow_block.py:473-486 is free for
+ * Arrow's chunked tables; a device column has to be contiguous or gathered like this).
+ * idx[j] counts rows over the concatenation of the sources in the given order.
+ *   srcs, src_rows   HOST arrays of nsrc device pointers / row counts (nsrc <= 64)
+ * Supported for even row_bytes in 18..1024 that are not a multiple of 16, sources 2-byte and dst
+ * 16-byte aligned (the asynchronous-copy kernel); otherwise DS_ERR_UNSUPPORTED -- concatenate. */
+ds_status ds_gather_rows_multi(const void* const* srcs, const uint64_t* src_rows, uint32_t nsrc,
+                               uint32_t row_bytes, const uint32_t* idx, uint64_t n, void* dst,
+                               void* stream);
+
 /* Partition scatter: copy the rows of a column, visited in partitioned order, to where
  * each partition is consumed.  Row j (in the order of `perm`, as written by
  * ds_partition_hist_scatter_*) belongs to partition d with part_offsets[d] <= j <

@@ -58,6 +58,7 @@ _PROTOS = {
     "ds_sort_indices_f64": [_P, c_uint64, c_int32, _P, _P, c_int32, _P, _SZP, _P],
     "ds_sort_indices_fsb": [_P, c_uint32, c_uint64, c_int32, _P, _P, c_int32, _P, _SZP, _P],
     "ds_gather_rows": [_P, c_uint32, c_uint64, _P, c_uint64, _P, _P],
+    "ds_gather_rows_multi": [_P, _P, c_uint32, c_uint32, _P, c_uint64, _P, _P],
     "ds_scatter_rows_to_parts": [_P, c_uint32, c_uint64, _P, c_uint64, c_uint32, _P, _P, _P],
     "ds_split_plan": [c_int32, _P, c_uint32, _P, c_uint64, _P, c_uint32, c_int32, _P, _P, _P, _P],
     "ds_split_rows": [_P, c_uint32, c_uint64, _P, _P, c_uint32, _P, c_uint32, c_uint32, _P],

@@ -631,6 +631,34 @@ def _gather(col: DeviceColumn, idx: torch.Tensor) -> DeviceColumn:
     return DeviceColumn(col.type, out, valid)
 
 
+def _multi_gather_ok(cols: Sequence[DeviceColumn]) -> bool:
+    """ds_gather_rows_multi takes even rows of 18..1024 bytes that are not a multiple of 16 from
+    at most 64 2-byte-aligned sources (the asynchronous-copy kernel)."""
+    w = cols[0].row_bytes if not cols[0].is_varlen else 0
+    return (1 < len(cols) <= 64 and w >= 18 and w <= 1024 and w % 2 == 0 and w % 16 != 0
+            and all((not c.is_varlen) and c.type == cols[0].type and c.ptr % 2 == 0 for c in cols))
+
+
+def _gather_multi(cols: Sequence[DeviceColumn], idx: torch.Tensor) -> DeviceColumn:
+    """Row gather from a column that lies in several blocks (idx counts rows over their
+    concatenation) without concatenating them first."""
+    import ctypes
+
+    n = idx.numel()
+    rb = cols[0].row_bytes
+    live = [c for c in cols if c.num_rows]
+    out = _empty_u8(n * rb)
+    srcs = (ctypes.c_void_p * len(live))(*[c.ptr for c in live])
+    rows = (ctypes.c_uint64 * len(live))(*[c.num_rows for c in live])
+    _lib.call("ds_gather_rows_multi", srcs, rows, len(live), rb, idx.data_ptr(), n, out.data_ptr(), _stream())
+    valid = None
+    if any(c.valid is not None for c in cols):
+        v = torch.cat([c.valid if c.valid is not None else torch.ones(c.num_rows, dtype=torch.uint8, device="cuda")
+                       for c in cols])
+        valid = _gather_raw(v, 1, v.numel(), idx)
+    return DeviceColumn(cols[0].type, out, valid)
+
+
 def _split_nulls(col: DeviceColumn) -> Tuple[torch.Tensor, int]:
     """Row ids with the non-null rows first and the null rows last, input order kept in
     both groups (a stable two-way partition on the validity byte), and the non-null count."""
@@ -1067,6 +1095,45 @@ class DeviceArrowBlockAccessor:
             last = b
         parts.append(table.slice(last, table.num_rows))
         return parts
+
+    @staticmethod
+    def sort_blocks_and_partition(blocks: List[DeviceArrowBlock], boundaries: List, key: SortKeyT,
+                                  descending: bool) -> List[DeviceArrowBlock]:
+        """sort_and_partition of the CONCATENATION of ``blocks`` without building it: only the key
+        columns are concatenated (they have to be contiguous for the radix sort); every other
+        column is gathered straight from the blocks (ds_gather_rows_multi) where its shape allows,
+        which saves one full copy of the dataset."""
+        if not isinstance(key, str) and key is not None and not callable(key) and len(key) > 1:
+            raise NotImplementedError("sorting by multiple columns is not supported yet")
+        col, _ = _normalize_key(key)
+        blocks = [b for b in blocks if b.num_rows > 0]
+        names = blocks[0].column_names
+        if len(blocks) == 1 or any(b.column_names != names for b in blocks):
+            return DeviceArrowBlockAccessor(DeviceArrowBlock.concat(blocks)).sort_and_partition(
+                boundaries, key, descending)
+        keycol = DeviceArrowBlock.concat([b.select([col]) for b in blocks]).column(col)
+        idx, sorted_key, nv = _argsort_nulls_last(keycol, descending)
+        cols = collections.OrderedDict()
+        for name in names:
+            if name == col:
+                cols[name] = sorted_key
+                continue
+            parts = [b.columns[name] for b in blocks]
+            if _multi_gather_ok(parts):
+                cols[name] = _gather_multi(parts, idx)
+            else:
+                cols[name] = _gather(DeviceArrowBlock.concat([b.select([name]) for b in blocks]).column(name), idx)
+        table = DeviceArrowBlock(cols, idx.numel())
+        if len(boundaries) == 0:
+            return [table]
+        bounds = _searchsorted(table.column(col).slice(0, nv), boundaries, descending)
+        out, last = [], 0
+        for b in bounds:
+            b = max(b, last)  # cuts never go backwards, whatever the splitters are
+            out.append(table.slice(last, b))
+            last = b
+        out.append(table.slice(last, table.num_rows))
+        return out
 
     def partition_perm(self, boundaries: List, key: SortKeyT, descending: bool):
         """(perm, counts) of the stable range partition: ``perm`` lists the row ids grouped

@@ -363,6 +363,55 @@ extern "C" ds_status ds_gather_rows(const void* src, uint32_t row_bytes, uint64_
   return ds::gather_rows_impl(src, row_bytes, src_rows, idx, n, dst, static_cast<cudaStream_t>(stream));
 }
 
+extern "C" ds_status ds_gather_rows_multi(const void* const* srcs, const uint64_t* src_rows, uint32_t nsrc,
+                                          uint32_t row_bytes, const uint32_t* idx, uint64_t n, void* dst,
+                                          void* stream) {
+  using namespace ds;
+  if (n == 0) return DS_OK;
+  if (n > 0xFFFFFFFFull) {
+    set_error("%s: n=%llu exceeds 2^32-1", __func__, (unsigned long long)n);
+    return DS_ERR_TOO_LARGE;
+  }
+  if (!srcs || !src_rows || !idx || !dst || nsrc == 0) {
+    set_error("%s: NULL pointer or no source", __func__);
+    return DS_ERR_INVALID_ARG;
+  }
+  if (nsrc > GB_MAX_SOURCES) {
+    set_error("%s: %u sources exceed the limit of %d", __func__, nsrc, GB_MAX_SOURCES);
+    return DS_ERR_UNSUPPORTED;
+  }
+  GatherSources g{};
+  g.nsrc = nsrc;
+  uint64_t total = 0;
+  bool ok = true;
+  for (uint32_t b = 0; b < nsrc; ++b) {
+    g.start[b] = static_cast<uint32_t>(total);
+    g.base[b] = static_cast<const uint8_t*>(srcs[b]);
+    total += src_rows[b];
+    ok = ok && (src_rows[b] == 0 || gather_bulk_eligible(srcs[b], row_bytes, src_rows[b], dst));
+  }
+  if (total > 0xFFFFFFFFull) {
+    set_error("%s: %llu source rows exceed 2^32-1", __func__, (unsigned long long)total);
+    return DS_ERR_TOO_LARGE;
+  }
+  g.start[nsrc] = static_cast<uint32_t>(total);
+  if (!ok) {
+    set_error("%s: row_bytes=%u / alignment not supported (even rows of 18..1024 bytes that are not a multiple "
+              "of 16, sources 2-byte and dst 16-byte aligned); gather from one concatenated column instead",
+              __func__, row_bytes);
+    return DS_ERR_UNSUPPORTED;
+  }
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  LaunchTimer timer(TIMED_GATHER, s, static_cast<double>(n) * (4.0 + 2.0 * row_bytes));
+  cudaError_t e = launch_gather_bulk(FETCH_LDGSTS, g, row_bytes, idx, static_cast<uint32_t>(n), dst, s);
+  timer.stop();
+  if (e != cudaSuccess) {
+    set_error("%s: launch failed: %s", __func__, cudaGetErrorString(e));
+    return DS_ERR_CUDA;
+  }
+  return DS_OK;
+}
+
 extern "C" ds_status ds_scatter_rows_to_parts(const void* src, uint32_t row_bytes, uint64_t src_rows,
                                               const uint32_t* perm, uint64_t n, uint32_t nparts,
                                               const uint64_t* part_offsets, void* const* dst_bases,

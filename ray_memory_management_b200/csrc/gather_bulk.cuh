@@ -71,24 +71,62 @@ __device__ __forceinline__ void copy_row_even(uint8_t* __restrict__ sm, uint32_t
     *reinterpret_cast<uint16_t*>(sm + d + (nw << 2)) = static_cast<uint16_t>(__byte_perm(prev, 0, sel));
 }
 
+// The source column may lie in several buffers (the blocks of a dataset): idx counts rows over
+// their concatenation, source b holds rows [start[b], start[b+1]).
+constexpr int GB_MAX_SOURCES = 64;
+struct GatherSources {
+  uint32_t nsrc;
+  uint32_t start[GB_MAX_SOURCES + 1];
+  const uint8_t* base[GB_MAX_SOURCES];
+};
+constexpr uint64_t GB_GUARDED = 1ull << 63;  // flag in a resolved address: fetch this row byte by byte
+
 // One thread per row of a tile: blockDim.x == R.
 template <int FETCH>
 __global__ void __launch_bounds__(GB_THREADS)
-    gather_bulk_kernel(const uint8_t* __restrict__ src, uint64_t src_bytes, uint32_t W,
-                       const uint32_t* __restrict__ idx, uint32_t n, uint8_t* __restrict__ dst, uint32_t R,
-                       uint32_t stages, uint32_t slot, uint32_t chunks, uint32_t magic_c, uint32_t tiles) {
+    gather_bulk_kernel(const GatherSources srcs, uint32_t W, const uint32_t* __restrict__ idx, uint32_t n,
+                       uint8_t* __restrict__ dst, uint32_t R, uint32_t stages, uint32_t slot, uint32_t chunks,
+                       uint32_t magic_c, uint32_t tiles) {
   extern __shared__ __align__(128) uint8_t gb_sm[];
-  uint64_t* bars = reinterpret_cast<uint64_t*>(gb_sm);        // [GB_MAX_STAGES]
-  uint32_t* rowoff = reinterpret_cast<uint32_t*>(gb_sm + 64);  // [stages][R]: byte offset of the row in its stage
-  uint32_t* s_idx = rowoff + stages * R;                       // [R]: source rows of the tile fetched next
-  uint8_t* data = gb_sm + 64 + (stages + 1) * R * 4;           // [stages][R * slot] (+16 spare), 16-byte aligned
-  const uint32_t image_bytes = R * W;                          // multiple of 16 (R is)
-  uint8_t* image = data + stages * R * slot + 16;              // packed output tile
+  uint64_t* bars = reinterpret_cast<uint64_t*>(gb_sm);                       // [GB_MAX_STAGES]
+  uint64_t* s_base = reinterpret_cast<uint64_t*>(gb_sm + 64);                // [GB_MAX_SOURCES]
+  uint32_t* s_start = reinterpret_cast<uint32_t*>(gb_sm + 64 + GB_MAX_SOURCES * 8);  // [GB_MAX_SOURCES + 1]
+  constexpr uint32_t HDR = 64 + GB_MAX_SOURCES * 8 + (GB_MAX_SOURCES + 1) * 4 + 60;  // multiple of 64
+  uint64_t* s_addr = reinterpret_cast<uint64_t*>(gb_sm + HDR);               // [R]: resolved rows of the tile fetched next
+  uint32_t* rowoff = reinterpret_cast<uint32_t*>(gb_sm + HDR + R * 8);       // [stages][R]: byte offset of the row in its stage
+  uint8_t* data = gb_sm + HDR + R * 8 + stages * R * 4;                      // [stages][R * slot] (+16 spare), 16-byte aligned
+  const uint32_t image_bytes = R * W;                                        // multiple of 16 (R is)
+  uint8_t* image = data + stages * R * slot + 16;                            // packed output tile
+  (void)image_bytes;
   const uint32_t tid = threadIdx.x;
   const uint32_t lane = tid & 31;
-  const uintptr_t base = reinterpret_cast<uintptr_t>(src);
-  const uintptr_t safe_lo = (base + 15) & ~uintptr_t(15);
-  const uintptr_t safe_hi = (base + src_bytes) & ~uintptr_t(15);
+  const uint32_t nsrc = srcs.nsrc;
+  for (uint32_t b = tid; b < nsrc; b += blockDim.x) {
+    s_base[b] = reinterpret_cast<uint64_t>(srcs.base[b]);
+    s_start[b] = srcs.start[b];
+  }
+  if (tid == 0) s_start[nsrc] = srcs.start[nsrc];
+  __syncthreads();
+  // row number over the concatenated sources -> address of the row; GB_GUARDED is set when the
+  // 16-byte-aligned span around the row would leave its source buffer
+  auto resolve = [&](uint32_t row) -> uint64_t {
+    uint32_t b = 0;
+    if (nsrc > 1) {
+      uint32_t lo = 0, hi = nsrc;  // last b with start[b] <= row
+      while (hi - lo > 1) {
+        const uint32_t mid = (lo + hi) >> 1;
+        if (s_start[mid] <= row) lo = mid;
+        else hi = mid;
+      }
+      b = lo;
+    }
+    const uint64_t base = s_base[b];
+    const uint64_t a = base + static_cast<uint64_t>(row - s_start[b]) * W;
+    const uint64_t end = base + static_cast<uint64_t>(s_start[b + 1] - s_start[b]) * W;
+    const uint64_t a0 = a & ~uint64_t(15), a1 = (a + W + 15) & ~uint64_t(15);
+    const bool safe = a0 >= ((base + 15) & ~uint64_t(15)) && a1 <= (end & ~uint64_t(15));
+    return safe ? a : (a | GB_GUARDED);
+  };
 
   if (FETCH == FETCH_BULK) {
     if (tid == 0) {
@@ -98,8 +136,8 @@ __global__ void __launch_bounds__(GB_THREADS)
     __syncthreads();
   }
 
-  // `my` = source row of output row t * R + tid, loaded one tile ahead of its use
-  auto issue = [&](uint32_t t, uint32_t s, uint32_t my) {
+  // `my` = resolved source row of output row t * R + tid, loaded one tile ahead of its use
+  auto issue = [&](uint32_t t, uint32_t s, uint64_t my) {
     const uint32_t row0 = t * R;
     const uint32_t rows = min(R, n - row0);
     uint8_t* d = data + s * R * slot;
@@ -108,12 +146,12 @@ __global__ void __launch_bounds__(GB_THREADS)
       uintptr_t a0 = 0;
       uint32_t bytes = 0;
       if (tid < rows) {
-        const uintptr_t a = base + static_cast<uint64_t>(my) * W;
+        const uintptr_t a = static_cast<uintptr_t>(my & ~GB_GUARDED);
         const uint32_t sh = static_cast<uint32_t>(a & 15);
         a0 = a - sh;
         bytes = (sh + W + 15u) & ~15u;
         ro[tid] = tid * slot + sh;
-        if (a0 < safe_lo || a0 + bytes > safe_hi) {
+        if (my & GB_GUARDED) {
           uint8_t* q = d + tid * slot + sh;
           for (uint32_t b = 0; b < W; ++b) q[b] = *reinterpret_cast<const uint8_t*>(a + b);
           bytes = 0;
@@ -131,12 +169,13 @@ __global__ void __launch_bounds__(GB_THREADS)
       for (uint32_t e = tid; e < items; e += R) {
         const uint32_t r = __umulhi(e, magic_c);
         const uint32_t c = e - r * chunks;
-        const uintptr_t a = base + static_cast<uint64_t>(s_idx[r]) * W;
+        const uint64_t ra = s_addr[r];
+        const uintptr_t a = static_cast<uintptr_t>(ra & ~GB_GUARDED);
         const uint32_t sh = static_cast<uint32_t>(a & 15);
         if (c == 0) ro[r] = r * slot + sh;
         if (c * 16 >= sh + W) continue;  // chunk lies wholly behind the row
         const uintptr_t ac = a - sh + c * 16;
-        if (ac >= safe_lo && ac + 16 <= safe_hi) {
+        if (!(ra & GB_GUARDED)) {
           ldgsts16_64B(d + r * slot + c * 16, reinterpret_cast<const void*>(ac));
         } else {  // first / last partial vector of the source buffer
           for (uint32_t b = 0; b < 16; ++b) {
@@ -148,9 +187,9 @@ __global__ void __launch_bounds__(GB_THREADS)
       ldgsts_commit();
     }
   };
-  auto load_idx = [&](uint32_t k) -> uint32_t {  // source row of this thread's row in my k-th tile
+  auto load_idx = [&](uint32_t k) -> uint64_t {  // resolved source row of this thread's row in my k-th tile
     const uint32_t row = (blockIdx.x + k * gridDim.x) * R + tid;
-    return row < n ? ld_stream(idx + row) : 0u;
+    return row < n ? resolve(ld_stream(idx + row)) : 0ull;
   };
 
   const uint32_t first = blockIdx.x;
@@ -158,10 +197,10 @@ __global__ void __launch_bounds__(GB_THREADS)
   // prologue: tiles 0 .. stages-2 are issued; `ahead` holds the source row for tile stages-1
   for (uint32_t k = 0; k + 1 < stages; ++k) {
     if (k < my_tiles) {
-      const uint32_t my = load_idx(k);
+      const uint64_t my = load_idx(k);
       if (FETCH == FETCH_LDGSTS) {
         __syncthreads();
-        s_idx[tid] = my;
+        s_addr[tid] = my;
         __syncthreads();
       }
       issue(first + k * gridDim.x, k, my);
@@ -169,17 +208,17 @@ __global__ void __launch_bounds__(GB_THREADS)
       ldgsts_commit();  // keep the group count uniform
     }
   }
-  uint32_t ahead = stages - 1 < my_tiles ? load_idx(stages - 1) : 0u;
+  uint64_t ahead = stages - 1 < my_tiles ? load_idx(stages - 1) : 0ull;
   if (FETCH == FETCH_LDGSTS) {
     __syncthreads();
-    s_idx[tid] = ahead;
+    s_addr[tid] = ahead;
     __syncthreads();
   }
   for (uint32_t it = 0; it < my_tiles; ++it) {
     const uint32_t nxt = it + stages - 1;
     if (nxt < my_tiles) issue(first + nxt * gridDim.x, nxt % stages, ahead);
     else if (FETCH == FETCH_LDGSTS) ldgsts_commit();
-    ahead = nxt + 1 < my_tiles ? load_idx(nxt + 1) : 0u;  // in flight during this iteration
+    ahead = nxt + 1 < my_tiles ? load_idx(nxt + 1) : 0ull;  // in flight during this iteration
     const uint32_t s = it % stages;
     if (FETCH == FETCH_BULK) {
       mbar_wait(&bars[s], (it / stages) & 1u);
@@ -200,7 +239,7 @@ __global__ void __launch_bounds__(GB_THREADS)
     if (tid < rows)
       copy_row_even(gb_sm, static_cast<uint32_t>(data - gb_sm) + s * R * slot + rowoff[s * R + tid],
                     static_cast<uint32_t>(image - gb_sm) + tid * W, W);
-    if (FETCH == FETCH_LDGSTS) s_idx[tid] = ahead;  // read by the next iteration's issue
+    if (FETCH == FETCH_LDGSTS) s_addr[tid] = ahead;  // read by the next iteration's issue
     fence_proxy_async_smem();
     __syncthreads();  // image complete; the stage may be refilled
     if (tid == 0) {
@@ -228,7 +267,8 @@ static bool gather_bulk_plan(uint32_t W, GatherBulkPlan* p) {
   if (rows > GB_THREADS) rows = GB_THREADS;
   rows &= ~31u;
   const uint32_t budget = 110 * 1024;  // per CTA: stages + the output image
-  auto need = [&](uint32_t r) { return 64 + p->stages * r * (p->slot + 4) + r * 4 + 16 + r * W; };
+  // header (barriers + source table) + resolved rows + per-stage row offsets and slots + image
+  auto need = [&](uint32_t r) { return 896u + r * 8 + p->stages * r * (p->slot + 4) + 16 + r * W; };
   while (rows > 32 && need(rows) > budget) rows -= 32;
   if (rows < 32 || need(rows) > 200 * 1024) return false;
   p->rows = rows;
@@ -246,8 +286,8 @@ static bool gather_bulk_eligible(const void* src, uint32_t W, uint64_t src_rows,
          (reinterpret_cast<uintptr_t>(src) & 1) == 0 && (reinterpret_cast<uintptr_t>(dst) & 15) == 0;
 }
 
-static cudaError_t launch_gather_bulk(int fetch, const void* src, uint32_t W, uint64_t src_rows,
-                                      const uint32_t* idx, uint32_t n, void* dst, cudaStream_t s) {
+static cudaError_t launch_gather_bulk(int fetch, const GatherSources& srcs, uint32_t W, const uint32_t* idx,
+                                      uint32_t n, void* dst, cudaStream_t s) {
   GatherBulkPlan p;
   if (!gather_bulk_plan(W, &p)) return cudaErrorInvalidConfiguration;
   const uint32_t tiles = (n + p.rows - 1) / p.rows;
@@ -258,10 +298,19 @@ static cudaError_t launch_gather_bulk(int fetch, const void* src, uint32_t W, ui
   cudaError_t e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(p.smem));
   if (e != cudaSuccess) return e;
   ds::note_launch();
-  k<<<blocks, p.rows, p.smem, s>>>(static_cast<const uint8_t*>(src), src_rows * W, W, idx, n,
-                                       static_cast<uint8_t*>(dst), p.rows, p.stages, p.slot, p.chunks, magic_c,
-                                       tiles);
+  k<<<blocks, p.rows, p.smem, s>>>(srcs, W, idx, n, static_cast<uint8_t*>(dst), p.rows, p.stages, p.slot,
+                                   p.chunks, magic_c, tiles);
   return cudaGetLastError();
+}
+
+static cudaError_t launch_gather_bulk(int fetch, const void* src, uint32_t W, uint64_t src_rows,
+                                      const uint32_t* idx, uint32_t n, void* dst, cudaStream_t s) {
+  GatherSources srcs{};
+  srcs.nsrc = 1;
+  srcs.start[0] = 0;
+  srcs.start[1] = static_cast<uint32_t>(src_rows);
+  srcs.base[0] = static_cast<const uint8_t*>(src);
+  return launch_gather_bulk(fetch, srcs, W, idx, n, dst, s);
 }
 
 }  // namespace ds

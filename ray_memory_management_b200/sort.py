@@ -66,8 +66,9 @@ class DeviceSortOp(_SortOp, DeviceShufflePlan):
         map_meta = [a.get_metadata(input_files=None, exec_stats=stats.build()) for a in accs]
         if not live:
             return [DeviceArrowBlock.empty() for _ in range(output_num_blocks)], map_meta
-        whole = BlockAccessor.for_block(DeviceArrowBlock.concat(live))
-        return whole.sort_and_partition(boundaries, key, descending), map_meta
+        from .block import DeviceArrowBlockAccessor
+
+        return DeviceArrowBlockAccessor.sort_blocks_and_partition(live, boundaries, key, descending), map_meta
 
 
 def nearest_rank_positions(num_samples: int, num_reducers: int) -> List[int]:

@@ -141,3 +141,44 @@ def test_segment_heads_and_reductions(lib, n, groups):
     ws = lib.call_ws("ds_segmented_reduce_f64", _ws, dv.data_ptr(), None, dp.data_ptr(), starts.data_ptr(), k, n,
                      lib.DS_OP_SUM, b.data_ptr(), stream=_stream())
     assert bool((a == b).all())
+
+
+@pytest.mark.parametrize("width", [90, 18, 250, 1022])
+def test_gather_rows_multi_matches_numpy(lib, width):
+    """ds_gather_rows_multi: the source column lies in several buffers of ragged sizes (one of
+    them empty, one a single row, one starting at an odd multiple of 2 bytes); idx counts rows
+    over their concatenation, incl. the first and last row of every buffer (guarded edges)."""
+    rng = np.random.default_rng(width)
+    sizes = [1000, 1, 0, 4097, 333, 2]
+    parts = [rng.integers(0, 256, (m, width), dtype=np.uint8) for m in sizes]
+    allrows = np.concatenate(parts)
+    devs, ptrs = [], []
+    for k, p in enumerate(parts):
+        pad = 2 if k == 3 else 0  # a source that is only 2-byte aligned
+        t = torch.from_numpy(np.concatenate([np.zeros(pad, np.uint8), p.reshape(-1)])).cuda()
+        devs.append(t)
+        ptrs.append(t.data_ptr() + pad)
+    n_out = 20_011
+    idx = rng.integers(0, len(allrows), n_out, dtype=np.int64)
+    edges = np.cumsum([0] + sizes)
+    firsts_lasts = [int(x) for b in range(len(sizes)) if sizes[b] for x in (edges[b], edges[b + 1] - 1)]
+    idx[: len(firsts_lasts)] = firsts_lasts
+    idx_dev = torch.from_numpy(idx.astype(np.int32)).cuda()
+    out = torch.zeros(n_out * width + 32, dtype=torch.uint8, device="cuda")
+    live = [(p, m) for p, m in zip(ptrs, sizes) if m]
+    srcs = (ctypes.c_void_p * len(live))(*[p for p, _ in live])
+    rows = (ctypes.c_uint64 * len(live))(*[m for _, m in live])
+    lib.call("ds_gather_rows_multi", srcs, rows, len(live), width, idx_dev.data_ptr(), n_out, out.data_ptr(), _stream())
+    torch.cuda.synchronize()
+    got = out.cpu().numpy()
+    assert np.array_equal(got[: n_out * width].reshape(n_out, width), allrows[idx])
+    assert not got[n_out * width:].any()
+
+
+def test_gather_rows_multi_rejects_other_shapes(lib):
+    z = torch.zeros(4096, dtype=torch.uint8, device="cuda")
+    i = torch.zeros(4, dtype=torch.int32, device="cuda")
+    srcs = (ctypes.c_void_p * 2)(z.data_ptr(), z.data_ptr())
+    rows = (ctypes.c_uint64 * 2)(4, 4)
+    for width in (16, 17, 8, 96):
+        assert lib.lib.ds_gather_rows_multi(srcs, rows, 2, width, i.data_ptr(), 4, z.data_ptr(), None) == lib.DS_ERR_UNSUPPORTED
