@@ -1181,9 +1181,10 @@ class DeviceArrowBlockAccessor:
             ret = DeviceArrowBlock.empty()
         else:
             col, desc_from_key = _normalize_key(key)
-            ret = DeviceArrowBlockAccessor(DeviceArrowBlock.concat(blocks))._sorted(
-                col, desc_from_key if not isinstance(key, str) else _descending
-            )
+            # (no concatenated copy of the payload: the columns are gathered from the blocks)
+            ret = DeviceArrowBlockAccessor.sort_blocks_and_partition(
+                blocks, [], col, desc_from_key if not isinstance(key, str) else _descending
+            )[0]
         return ret, DeviceArrowBlockAccessor(ret).get_metadata(None, exec_stats=stats.build())
 
     # -- random_shuffle (arrow_block.py:184-186) ----------------------------------------
