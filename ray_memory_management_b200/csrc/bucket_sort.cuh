@@ -24,26 +24,27 @@ constexpr int LS_SMEM_BYTES = LS_CAP * 16 + LS_CAP * 10 + 16;
 // starts[b] = first row whose leading 16 bits are >= b, starts[65536] = n (empty buckets get the
 // next bucket's start).  `hi` is sorted by those bits.
 __global__ void __launch_bounds__(256)
-    bucket_bounds_kernel(const uint64_t* __restrict__ hi, uint32_t n, uint32_t* __restrict__ starts) {
+    bucket_bounds_kernel(const uint64_t* __restrict__ hi, uint32_t n, uint32_t* __restrict__ starts,
+                         const KeyXform xf) {
   const uint32_t i0 = (blockIdx.x * blockDim.x + threadIdx.x) * 4;
   if (i0 >= n) return;
   uint32_t b[5];  // b[k + 1] = bucket of row i0 + k, b[0] = bucket of row i0 - 1
   if (i0 + 4 <= n) {
     const ulonglong2 x = *reinterpret_cast<const ulonglong2*>(hi + i0);
     const ulonglong2 y = *reinterpret_cast<const ulonglong2*>(hi + i0 + 2);
-    b[1] = static_cast<uint32_t>(x.x >> 48);
-    b[2] = static_cast<uint32_t>(x.y >> 48);
-    b[3] = static_cast<uint32_t>(y.x >> 48);
-    b[4] = static_cast<uint32_t>(y.y >> 48);
+    b[1] = g28(x.x, xf) >> 12;
+    b[2] = g28(x.y, xf) >> 12;
+    b[3] = g28(y.x, xf) >> 12;
+    b[4] = g28(y.y, xf) >> 12;
   } else {
 #pragma unroll
-    for (int k = 0; k < 4; ++k) b[k + 1] = i0 + k < n ? static_cast<uint32_t>(hi[i0 + k] >> 48) : 0;
+    for (int k = 0; k < 4; ++k) b[k + 1] = i0 + k < n ? g28(hi[i0 + k], xf) >> 12 : 0;
   }
   if (i0 == 0) {
     for (uint32_t v = 0; v <= b[1]; ++v) starts[v] = 0;
     b[0] = b[1];
   } else {
-    b[0] = static_cast<uint32_t>(hi[i0 - 1] >> 48);
+    b[0] = g28(hi[i0 - 1], xf) >> 12;
   }
 #pragma unroll
   for (int k = 0; k < 4; ++k) {
@@ -60,12 +61,12 @@ __global__ void __launch_bounds__(256)
 // (permutations; float64 keys, whose column is gathered by the caller).
 enum { LS_OUT_NONE = 0, LS_OUT_FSB10 = 1, LS_OUT_I64 = 2, LS_OUT_U64 = 3 };
 
-template <bool HAS_LO, int OUT>
+template <bool HAS_LO, int OUT, bool XF>
 __global__ void __launch_bounds__(LS_THREADS, 4)
     bucket_local_sort_kernel(const uint64_t* __restrict__ hi_in, const uint16_t* __restrict__ lo_in,
                              const uint32_t* __restrict__ idx_in, const uint32_t* __restrict__ starts,
                              bool desc, uint8_t* __restrict__ keys_out, uint32_t* __restrict__ idx_out,
-                             uint32_t* __restrict__ too_long) {
+                             uint32_t* __restrict__ too_long, const KeyXform xf) {
   static_assert(OUT != LS_OUT_FSB10 || HAS_LO, "10-byte keys carry their last two bytes in lo");
   // The CTA's ~1500 rows are spread over LS_BINS bins by key bits [LS_BIN_SHIFT, 48) with one
   // counting sort whose scatter takes positions from shared-memory atomics -- NOT stable, so
@@ -114,7 +115,7 @@ __global__ void __launch_bounds__(LS_THREADS, 4)
   __syncthreads();
 #pragma unroll
   for (int i = 0; i < LS_ITEMS; ++i)
-    if (wofs + i * 32 < R) atomicAdd(&hist[static_cast<uint32_t>(hi[i] >> LS_BIN_SHIFT) & (LS_BINS - 1)], 1u);
+    if (wofs + i * 32 < R) atomicAdd(&hist[g28t<XF>(hi[i], xf) & (LS_BINS - 1)], 1u);
   __syncthreads();
   {  // exclusive scan of the bin counts: LS_BINS / LS_THREADS consecutive bins per thread
     constexpr int PER = LS_BINS / LS_THREADS;
@@ -150,7 +151,7 @@ __global__ void __launch_bounds__(LS_THREADS, 4)
 #pragma unroll
   for (int i = 0; i < LS_ITEMS; ++i) {
     if (wofs + i * 32 < R) {
-      const uint32_t p = atomicAdd(&hist[static_cast<uint32_t>(hi[i] >> LS_BIN_SHIFT) & (LS_BINS - 1)], 1u);
+      const uint32_t p = atomicAdd(&hist[g28t<XF>(hi[i], xf) & (LS_BINS - 1)], 1u);
       ex_hi[p] = hi[i];
       ex_meta[p] = meta[i];
     }
@@ -166,20 +167,20 @@ __global__ void __launch_bounds__(LS_THREADS, 4)
     for (int i = 0; i < LS_ITEMS; ++i) {  // one load per row; the neighbours' bins come by shuffle
       const uint32_t p = tid + i * LS_THREADS;
       const uint32_t none = 0xffffffffu;   // bins have 28 bits
-      const uint32_t mine = p < R ? static_cast<uint32_t>(ex_hi[p] >> LS_BIN_SHIFT) : none;
+      const uint32_t mine = p < R ? g28t<XF>(ex_hi[p], xf) : none;
       uint32_t next = __shfl_down_sync(0xffffffffu, mine, 1);
       uint32_t prev = __shfl_up_sync(0xffffffffu, mine, 1);
-      if (lane == 31) next = p + 1 < R ? static_cast<uint32_t>(ex_hi[p + 1] >> LS_BIN_SHIFT) : none;
-      if (lane == 0) prev = (p > 0 && p < R) ? static_cast<uint32_t>(ex_hi[p - 1] >> LS_BIN_SHIFT) : none;
+      if (lane == 31) next = p + 1 < R ? g28t<XF>(ex_hi[p + 1], xf) : none;
+      if (lane == 0) prev = (p > 0 && p < R) ? g28t<XF>(ex_hi[p - 1], xf) : none;
       if (p + 1 < R && next == mine && prev != mine) heads |= 1u << i;
     }
     while (heads) {
       const int i = __ffs(heads) - 1;
       heads &= heads - 1;
       const uint32_t p = tid + i * LS_THREADS;
-      const uint64_t bin = ex_hi[p] >> LS_BIN_SHIFT;
+      const uint32_t bin = g28t<XF>(ex_hi[p], xf);
       uint32_t len = 2;
-      while (p + len < R && len <= REPAIR_MAX_RUN && (ex_hi[p + len] >> LS_BIN_SHIFT) == bin) ++len;
+      while (p + len < R && len <= REPAIR_MAX_RUN && g28t<XF>(ex_hi[p + len], xf) == bin) ++len;
       if (len > REPAIR_MAX_RUN) {
         atomicOr(too_long, 1u);
         continue;
@@ -210,8 +211,9 @@ __global__ void __launch_bounds__(LS_THREADS, 4)
       const uint32_t p = tid + i * LS_THREADS;
       if (p < R) {
         idx_out[s + p] = static_cast<uint32_t>(ex_meta[p]);
-        if (OUT == LS_OUT_I64) reinterpret_cast<int64_t*>(keys_out)[s + p] = dec_i64(ex_hi[p], desc);
-        if (OUT == LS_OUT_U64) reinterpret_cast<uint64_t*>(keys_out)[s + p] = desc ? ~ex_hi[p] : ex_hi[p];
+        const uint64_t h0 = XF ? (ex_hi[p] >> xf.s) + xf.base : ex_hi[p];  // the key's own encoding
+        if (OUT == LS_OUT_I64) reinterpret_cast<int64_t*>(keys_out)[s + p] = dec_i64(h0, desc);
+        if (OUT == LS_OUT_U64) reinterpret_cast<uint64_t*>(keys_out)[s + p] = desc ? ~h0 : h0;
       }
     }
     return;
@@ -226,7 +228,8 @@ __global__ void __launch_bounds__(LS_THREADS, 4)
     const uint32_t p = tid + i * LS_THREADS;
     if (p < R) {
       const uint64_t m = ex_meta[p];
-      const uint64_t hh = desc ? ~ex_hi[p] : ex_hi[p];
+      const uint64_t h0 = XF ? (ex_hi[p] >> xf.s) + xf.base : ex_hi[p];  // the key's own encoding
+      const uint64_t hh = desc ? ~h0 : h0;
       const uint32_t ll = static_cast<uint32_t>((desc ? ~m : m) >> 48);
       const uint64_t be = bswap64(hh);                                   // bytes 0..7 of the row
       const uint32_t t2 = ((ll >> 8) | ((ll & 0xffu) << 8)) & 0xffffu;   // bytes 8..9

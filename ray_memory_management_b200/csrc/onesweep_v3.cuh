@@ -27,13 +27,13 @@ struct PassSmemV3 {
 };
 
 template <int THREADS, int ITEMS, int MIN_BLOCKS, bool HAS_LO, bool DIGIT_LO, bool GEN_IDX,
-          bool FULL, bool TABLE, bool PACKED>
+          bool FULL, bool TABLE, bool PACKED, bool XF>
 __global__ void __launch_bounds__(THREADS, MIN_BLOCKS)
     onesweep_pass_kernel_v3(const uint64_t* __restrict__ hi_in, const uint16_t* __restrict__ lo_in,
                             const uint32_t* __restrict__ idx_in, uint64_t* __restrict__ hi_out,
                             uint16_t* __restrict__ lo_out, uint32_t* __restrict__ idx_out,
                             uint32_t n, int shift, const uint32_t* __restrict__ bin_base,
-                            volatile uint32_t* lookback, uint32_t* tile_counter) {
+                            volatile uint32_t* lookback, uint32_t* tile_counter, const KeyXform xf) {
   static_assert(THREADS >= RADIX && THREADS % 32 == 0, "one thread per digit is required");
   using S = PassSmemV3<THREADS, ITEMS, PACKED, HAS_LO>;
   constexpr int TILE = S::TILE;
@@ -87,7 +87,7 @@ __global__ void __launch_bounds__(THREADS, MIN_BLOCKS)
 #pragma unroll
   for (int i = 0; i < ITEMS; ++i) {
     if (full || (wofs + i * 32 < tile_valid))
-      atomicAdd(&wh[digit_of<HAS_LO, DIGIT_LO>(hi[i], lo[i], shift)], 1u);
+      atomicAdd(&wh[digit_x<HAS_LO, DIGIT_LO, XF>(hi[i], lo[i], shift, xf)], 1u);
   }
   __syncthreads();
 
@@ -130,7 +130,7 @@ __global__ void __launch_bounds__(THREADS, MIN_BLOCKS)
 #pragma unroll
   for (int i = 0; i < ITEMS; ++i) {
     const bool valid = full || (wofs + i * 32 < tile_valid);
-    const uint32_t d = digit_of<HAS_LO, DIGIT_LO>(hi[i], lo[i], shift);
+    const uint32_t d = digit_x<HAS_LO, DIGIT_LO, XF>(hi[i], lo[i], shift, xf);
     uint32_t peers;
     if (TABLE) {
       volatile uint32_t* slot = mt + (i & 1) * RADIX + d;
@@ -209,7 +209,7 @@ __global__ void __launch_bounds__(THREADS, MIN_BLOCKS)
         l = HAS_LO ? ex_lo[p] : 0;
         x = ex_idx[p];
       }
-      const uint32_t d = digit_of<HAS_LO, DIGIT_LO>(h, l, shift);
+      const uint32_t d = digit_x<HAS_LO, DIGIT_LO, XF>(h, l, shift, xf);
       const uint32_t dst = s_gofs[d] + p;
       hi_out[dst] = h;
       if (HAS_LO) lo_out[dst] = static_cast<uint16_t>(l);

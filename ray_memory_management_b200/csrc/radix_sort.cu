@@ -46,6 +46,33 @@ struct PassList {
   int from_lo[MAX_PASSES];
 };
 
+// Keys that occupy a SUB-RANGE of the key space (one rank's share of a range-partitioned
+// dataset, clustered ids, time stamps): the hybrid plan wants 65536 evenly filled buckets, which
+// the two leading bytes of such keys do not give.  The encode kernel then stores
+//   hi' = (hi - base) << s        (monotone and injective on [base, base + span))
+// instead of hi, and every kernel of the plan takes its bucket / bin digits from the 28-bit
+//   G = umul64hi(hi', R),  R = floor((2^92 - 1) / (span << s)),
+// which spreads [0, span) over [0, 2^28) evenly (G is only monotone, not injective: ties inside a
+// bin are ordered by the full hi' as before).  With on == 0, G is hi >> 36 and nothing changes.
+// base and span come from the sampled minimum and maximum plus a margin; a key outside
+// [base, base + span) raises the fallback flag.
+struct KeyXform {
+  uint64_t base;
+  uint64_t span;
+  uint64_t R;
+  uint32_t s;
+  uint32_t on;
+};
+__device__ __forceinline__ uint32_t g28(uint64_t hix, const KeyXform& x) {
+  return x.on ? static_cast<uint32_t>(__umul64hi(hix, x.R)) : static_cast<uint32_t>(hix >> 36);
+}
+// the same with the choice made at compile time (pass and bucket kernels: no cost when off)
+template <bool XF>
+__device__ __forceinline__ uint32_t g28t(uint64_t hix, const KeyXform& x) {
+  return XF ? static_cast<uint32_t>(__umul64hi(hix, x.R)) : static_cast<uint32_t>(hix >> 36);
+}
+static thread_local KeyXform t_xf = {0, 0, 0, 0, 0};  // of the sort call running on this thread
+
 // ---------------------------------------------------------------- encode + hist
 // UNIFORM_CHECK: test every digit for being constant across the warp first (one atomic instead
 // of 32 colliding ones on skewed keys).  Off when the caller already knows the digits spread
@@ -56,7 +83,8 @@ __global__ void __launch_bounds__(512) encode_hist_kernel(const void* __restrict
                                                           uint64_t* __restrict__ hi_out,
                                                           uint16_t* __restrict__ lo_out, PassList pl,
                                                           uint32_t* __restrict__ ghist,
-                                                          uint64_t seed, uint64_t subseq) {
+                                                          uint64_t seed, uint64_t subseq, KeyXform xf,
+                                                          uint32_t* __restrict__ out_of_range) {
   __shared__ uint32_t sh[MAX_PASSES * RADIX];
   for (int i = threadIdx.x; i < pl.count * RADIX; i += blockDim.x) sh[i] = 0;
   __syncthreads();
@@ -70,6 +98,14 @@ __global__ void __launch_bounds__(512) encode_hist_kernel(const void* __restrict
     } else {
       load_key<KIND>(col, width, i, desc, hi, lo);
     }
+    if (xf.on) {  // sub-range keys: store hi' (see KeyXform)
+      uint64_t d0 = hi - xf.base;
+      if (hi < xf.base || d0 >= xf.span) {
+        atomicOr(out_of_range, 1u);
+        d0 = hi < xf.base ? 0 : xf.span - 1;
+      }
+      hi = d0 << xf.s;
+    }
     st_stream(hi_out + i, hi);
     if (HAS_LO) st_stream(lo_out + i, static_cast<uint16_t>(lo));
     const unsigned m = __activemask();
@@ -79,6 +115,7 @@ __global__ void __launch_bounds__(512) encode_hist_kernel(const void* __restrict
       if (p < pl.count) {
         uint32_t d = (HAS_LO && pl.from_lo[p]) ? (lo >> pl.shift[p]) & 255u
                                                : static_cast<uint32_t>(hi >> pl.shift[p]) & 255u;
+        if (xf.on) d = (g28(hi, xf) >> pl.shift[p]) & 255u;  // shift = 12 / 20: the two bucket digits
         int same = 0;
         if (UNIFORM_CHECK) __match_all_sync(m, d, &same);
         if (same) {  // constant digit across the warp: one atomic instead of 32 colliding
@@ -101,25 +138,42 @@ __global__ void __launch_bounds__(512) encode_hist_kernel(const void* __restrict
 template <int KIND>
 __global__ void __launch_bounds__(256) sample_hist_kernel(const void* __restrict__ col, uint32_t width,
                                                           uint32_t n, bool desc, uint32_t stride,
-                                                          PassList pl, uint32_t* __restrict__ ghist) {
+                                                          PassList pl, uint32_t* __restrict__ ghist,
+                                                          unsigned long long* __restrict__ minmax, KeyXform xf) {
   __shared__ uint32_t sh[MAX_PASSES * RADIX];
+  // minmax[0] = max(~hi) (i.e. ~min), minmax[1] = max(hi) over the sample; both start at 0
+  __shared__ unsigned long long s_mm[2];
+  if (threadIdx.x < 2) s_mm[threadIdx.x] = 0;
   for (int i = threadIdx.x; i < pl.count * RADIX; i += blockDim.x) sh[i] = 0;
   __syncthreads();
   const uint32_t ns = (n + stride - 1) / stride;
+  unsigned long long t_inv_min = 0, t_max = 0;
   for (uint32_t j = blockIdx.x * blockDim.x + threadIdx.x; j < ns; j += gridDim.x * blockDim.x) {
     uint64_t hi;
     uint32_t lo;
     load_key<KIND>(col, width, static_cast<uint64_t>(j) * stride, desc, hi, lo);
+    t_inv_min = max(t_inv_min, static_cast<unsigned long long>(~hi));
+    t_max = max(t_max, static_cast<unsigned long long>(hi));
+    if (xf.on) {
+      const uint64_t d0 = hi - xf.base;
+      hi = ((hi < xf.base) ? 0 : (d0 >= xf.span ? xf.span - 1 : d0)) << xf.s;
+    }
 #pragma unroll
     for (int p = 0; p < MAX_PASSES; ++p) {
       if (p < pl.count) {
-        const uint32_t d = pl.from_lo[p] ? (lo >> pl.shift[p]) & 255u
-                                         : static_cast<uint32_t>(hi >> pl.shift[p]) & 255u;
+        uint32_t d = pl.from_lo[p] ? (lo >> pl.shift[p]) & 255u
+                                   : static_cast<uint32_t>(hi >> pl.shift[p]) & 255u;
+        if (xf.on) d = (g28(hi, xf) >> pl.shift[p]) & 255u;
         atomicAdd(&sh[p * RADIX + d], 1u);
       }
     }
   }
+  if (minmax != nullptr) {
+    atomicMax(&s_mm[0], t_inv_min);
+    atomicMax(&s_mm[1], t_max);
+  }
   __syncthreads();
+  if (minmax != nullptr && threadIdx.x < 2) atomicMax(minmax + threadIdx.x, s_mm[threadIdx.x]);
   for (int i = threadIdx.x; i < pl.count * RADIX; i += blockDim.x) {
     const uint32_t c = sh[i];
     if (c) atomicAdd(&ghist[i], c);
@@ -266,6 +320,11 @@ __global__ void iota_kernel(uint32_t* out, uint32_t n) {
 template <bool HAS_LO, bool DIGIT_LO>
 __device__ __forceinline__ uint32_t digit_of(uint64_t hi, uint32_t lo, int shift) {
   return DIGIT_LO && HAS_LO ? (lo >> shift) & 255u : static_cast<uint32_t>(hi >> shift) & 255u;
+}
+// the same with the sub-range transform: shift then counts bits of G (12 / 20)
+template <bool HAS_LO, bool DIGIT_LO, bool XF>
+__device__ __forceinline__ uint32_t digit_x(uint64_t hi, uint32_t lo, int shift, const KeyXform& xf) {
+  return XF ? (g28t<true>(hi, xf) >> shift) & 255u : digit_of<HAS_LO, DIGIT_LO>(hi, lo, shift);
 }
 
 template <int THREADS, int ITEMS, bool HAS_LO>
@@ -519,6 +578,8 @@ __global__ void __launch_bounds__(256)
 
 // ---------------------------------------------------------------- host driver
 static std::atomic<int> g_hybrid_mode{1};  // ds_debug_set_hybrid: 0 never, 1 when the buckets fill a CTA, 2 whatever n (tests)
+static std::atomic<bool> g_no_subrange{false};  // ds_debug_set_subrange(0): no hybrid plan on a sub-range of the key space
+static std::atomic<int> g_last_plan{-1};        // ds_debug_last_sort_plan
 static std::atomic<bool> g_no_fused_decode{false};  // ds_debug_set_fused_decode(0): separate repair + decode kernels
 static std::atomic<int> g_cfg{18};  // tuning knob (ds_debug_set_radix_config); 18 = v3 table match <384 x 12>, best measured
 
@@ -551,22 +612,39 @@ static cudaError_t launch_pass_t(const uint64_t* hi_in, const uint16_t* lo_in,
     constexpr bool TABLE = VARIANT == 4 || VARIANT == 5;
     constexpr bool PACKED = VARIANT == 4 || VARIANT == 6;
     using S3 = PassSmemV3<THREADS, ITEMS, PACKED, HAS_LO>;
-    auto kf = onesweep_pass_kernel_v3<THREADS, ITEMS, MIN_BLOCKS, HAS_LO, DIGIT_LO, GEN_IDX, true, TABLE, PACKED>;
-    auto kt = onesweep_pass_kernel_v3<THREADS, ITEMS, MIN_BLOCKS, HAS_LO, DIGIT_LO, GEN_IDX, false, TABLE, PACKED>;
-    if ((e = set_smem_attr(kf, S3::BYTES, &done_a)) != cudaSuccess) return e;
-    if ((e = set_smem_attr(kt, S3::BYTES, &done_b)) != cudaSuccess) return e;
     // full tiles first, then (stream-ordered) the ragged last tile as tile id `full_tiles`
     const uint32_t full_tiles = n / S::TILE;
-    if (full_tiles) {
-      ds::note_launch();
-      kf<<<full_tiles, THREADS, S3::BYTES, s>>>(hi_in, lo_in, idx_in, hi_out, lo_out, idx_out, n,
-                                                shift, bin_base, lookback, tile_counter);
+    auto launch = [&](auto kf, auto kt, DoneMask* da, DoneMask* db) -> cudaError_t {
+      cudaError_t e2;
+      if ((e2 = set_smem_attr(kf, S3::BYTES, da)) != cudaSuccess) return e2;
+      if ((e2 = set_smem_attr(kt, S3::BYTES, db)) != cudaSuccess) return e2;
+      if (full_tiles) {
+        ds::note_launch();
+        kf<<<full_tiles, THREADS, S3::BYTES, s>>>(hi_in, lo_in, idx_in, hi_out, lo_out, idx_out, n,
+                                                  shift, bin_base, lookback, tile_counter, t_xf);
+      }
+      if (tiles > full_tiles) {
+        ds::note_launch();
+        kt<<<1, THREADS, S3::BYTES, s>>>(hi_in, lo_in, idx_in, hi_out, lo_out, idx_out, n, shift,
+                                         bin_base, lookback, tile_counter, t_xf);
+      }
+      return cudaSuccess;
+    };
+    if (t_xf.on) {  // sub-range hybrid plan: digits of G, always taken from `hi`
+      if constexpr (!DIGIT_LO) {
+        static DoneMask done_c{0}, done_d{0};
+        e = launch(onesweep_pass_kernel_v3<THREADS, ITEMS, MIN_BLOCKS, HAS_LO, false, GEN_IDX, true, TABLE, PACKED, true>,
+                   onesweep_pass_kernel_v3<THREADS, ITEMS, MIN_BLOCKS, HAS_LO, false, GEN_IDX, false, TABLE, PACKED, true>,
+                   &done_c, &done_d);
+      } else {
+        e = cudaErrorInvalidValue;
+      }
+    } else {
+      e = launch(onesweep_pass_kernel_v3<THREADS, ITEMS, MIN_BLOCKS, HAS_LO, DIGIT_LO, GEN_IDX, true, TABLE, PACKED, false>,
+                 onesweep_pass_kernel_v3<THREADS, ITEMS, MIN_BLOCKS, HAS_LO, DIGIT_LO, GEN_IDX, false, TABLE, PACKED, false>,
+                 &done_a, &done_b);
     }
-    if (tiles > full_tiles) {
-      ds::note_launch();
-      kt<<<1, THREADS, S3::BYTES, s>>>(hi_in, lo_in, idx_in, hi_out, lo_out, idx_out, n, shift,
-                                       bin_base, lookback, tile_counter);
-    }
+    if (e != cudaSuccess) return e;
   }
   timer.stop();
   return cudaGetLastError();
@@ -672,20 +750,21 @@ static PassList make_passes(int kind, uint32_t width) {
 template <int KIND>
 static cudaError_t launch_encode(bool has_lo, bool uniform_check, const void* col, uint32_t width, uint32_t n,
                                  bool desc, uint64_t* hi, uint16_t* lo, const PassList& pl, uint32_t* ghist,
-                                 cudaStream_t s, uint64_t seed = 0, uint64_t subseq = 0) {
+                                 cudaStream_t s, uint64_t seed = 0, uint64_t subseq = 0,
+                                 uint32_t* out_of_range = nullptr) {
   const int threads = 512;
   int blocks = sm_count() * 4;
   const int need = (n + threads - 1) / threads;
   if (blocks > need) blocks = need;
   note_launch();
   if (has_lo && uniform_check)
-    encode_hist_kernel<KIND, true, true><<<blocks, threads, 0, s>>>(col, width, n, desc, hi, lo, pl, ghist, seed, subseq);
+    encode_hist_kernel<KIND, true, true><<<blocks, threads, 0, s>>>(col, width, n, desc, hi, lo, pl, ghist, seed, subseq, t_xf, out_of_range);
   else if (has_lo)
-    encode_hist_kernel<KIND, true, false><<<blocks, threads, 0, s>>>(col, width, n, desc, hi, lo, pl, ghist, seed, subseq);
+    encode_hist_kernel<KIND, true, false><<<blocks, threads, 0, s>>>(col, width, n, desc, hi, lo, pl, ghist, seed, subseq, t_xf, out_of_range);
   else if (uniform_check)
-    encode_hist_kernel<KIND, false, true><<<blocks, threads, 0, s>>>(col, width, n, desc, hi, lo, pl, ghist, seed, subseq);
+    encode_hist_kernel<KIND, false, true><<<blocks, threads, 0, s>>>(col, width, n, desc, hi, lo, pl, ghist, seed, subseq, t_xf, out_of_range);
   else
-    encode_hist_kernel<KIND, false, false><<<blocks, threads, 0, s>>>(col, width, n, desc, hi, lo, pl, ghist, seed, subseq);
+    encode_hist_kernel<KIND, false, false><<<blocks, threads, 0, s>>>(col, width, n, desc, hi, lo, pl, ghist, seed, subseq, t_xf, out_of_range);
   return cudaGetLastError();
 }
 
@@ -713,6 +792,7 @@ static ds_status sort_indices_impl(int kind, const void* col, uint32_t width, ui
   const uint32_t n = static_cast<uint32_t>(n64);
   const bool has_lo = kind == KIND_FSB && width > 8;
   const PassList pl = make_passes(kind, width);
+  t_xf = KeyXform{0, 0, 0, 0, 0};  // set again below if this call takes the sub-range hybrid plan
   const int cfg = g_cfg.load(std::memory_order_relaxed);
   const uint32_t tiles = (n + cfg_tile(cfg) - 1) / cfg_tile(cfg);
 
@@ -758,26 +838,36 @@ static ds_status sort_indices_impl(int kind, const void* col, uint32_t width, ui
   bool hybrid = false;
   if (!(options & (DS_SORT_NO_PASS_SKIP | DS_SORT_NO_PREFIX_REPAIR)) && n >= (1u << 16) &&
       pl.count >= 3) {
-    float coll_h[MAX_PASSES];
+    // read back in one copy: coll[MAX_PASSES], too_long, head_count, then the sampled min / max
+    struct SampleReadback {
+      float coll[MAX_PASSES];
+      uint32_t flags[2];
+      unsigned long long inv_min, max;
+    } rb;
+    static_assert(sizeof(SampleReadback) == 4 * (MAX_PASSES + 2) + 16, "layout of ctrl behind coll");
+    float* const coll_h = rb.coll;
+    unsigned long long* const minmax = reinterpret_cast<unsigned long long*>(too_long + 2);
+    const uint32_t stride = n > (1u << 20) ? n >> 20 : 1;
+    const uint32_t ns = (n + stride - 1) / stride;
+    const int sample_blocks = static_cast<int>((ns + 255) / 256 < 1184u ? (ns + 255) / 256 : 1184u);
+    auto sample = [&](const PassList& digits, unsigned long long* mm, const KeyXform& xf) {
+      ds::note_launch();
+      switch (kind) {
+        case KIND_I64: sample_hist_kernel<KIND_I64><<<sample_blocks, 256, 0, s>>>(col, width, n, desc, stride, digits, ghist, mm, xf); break;
+        case KIND_U64: sample_hist_kernel<KIND_U64><<<sample_blocks, 256, 0, s>>>(col, width, n, desc, stride, digits, ghist, mm, xf); break;
+        case KIND_F64: sample_hist_kernel<KIND_F64><<<sample_blocks, 256, 0, s>>>(col, width, n, desc, stride, digits, ghist, mm, xf); break;
+        default: sample_hist_kernel<KIND_FSB><<<sample_blocks, 256, 0, s>>>(col, width, n, desc, stride, digits, ghist, mm, xf); break;
+      }
+      ds::note_launch(); scan_hist_kernel<<<digits.count, RADIX, 0, s>>>(ghist, ns, bin_base, skip, coll);
+    };
     if (kind == KIND_PHILOX) {
       for (int p = 0; p < pl.count; ++p) coll_h[p] = 1.0f / 256.0f;
     } else {
-      const uint32_t stride = n > (1u << 20) ? n >> 20 : 1;
-      const uint32_t ns = (n + stride - 1) / stride;
-      const int blocks = static_cast<int>((ns + 255) / 256 < 1184u ? (ns + 255) / 256 : 1184u);
-      ds::note_launch();
-      switch (kind) {
-        case KIND_I64: sample_hist_kernel<KIND_I64><<<blocks, 256, 0, s>>>(col, width, n, desc, stride, pl, ghist); break;
-        case KIND_U64: sample_hist_kernel<KIND_U64><<<blocks, 256, 0, s>>>(col, width, n, desc, stride, pl, ghist); break;
-        case KIND_F64: sample_hist_kernel<KIND_F64><<<blocks, 256, 0, s>>>(col, width, n, desc, stride, pl, ghist); break;
-        default: sample_hist_kernel<KIND_FSB><<<blocks, 256, 0, s>>>(col, width, n, desc, stride, pl, ghist); break;
-      }
+      sample(pl, minmax, KeyXform{0, 0, 0, 0, 0});
       DS_LAUNCH_CHECK();
-      ds::note_launch(); scan_hist_kernel<<<pl.count, RADIX, 0, s>>>(ghist, ns, bin_base, skip, coll);
-      DS_LAUNCH_CHECK();
-      DS_CUDA(cudaMemcpyAsync(coll_h, coll, sizeof(coll_h), cudaMemcpyDeviceToHost, s));
+      DS_CUDA(cudaMemcpyAsync(&rb, coll, sizeof(rb), cudaMemcpyDeviceToHost, s));
       DS_CUDA(cudaMemsetAsync(ctrl, 0, ctrl_bytes, s));
-      DS_CUDA(cudaStreamSynchronize(s));  // host sync: 40 bytes
+      DS_CUDA(cudaStreamSynchronize(s));  // host sync: 64 bytes
     }
     // hybrid plan (bucket_sort.cuh): 10-byte keys whose two leading bytes spread evenly and
     // whose 65536 buckets would fill a CTA reasonably (400..1650 rows on average)
@@ -789,6 +879,46 @@ static ds_status sort_indices_impl(int kind, const void* col, uint32_t width, ui
         (n >= 400u * LS_BUCKETS || hybrid_mode == 2) && n <= 1650u * LS_BUCKETS) {
       const float lim = 1.25f / 256.0f;
       hybrid = coll_h[pl.count - 1] <= lim && coll_h[pl.count - 2] <= lim;
+      if (!hybrid && kind != KIND_PHILOX && !g_no_subrange.load(std::memory_order_relaxed)) {
+        // The leading bytes do not spread: the keys may still fill a SUB-RANGE of the key space
+        // evenly (see KeyXform).  Take the range from the sampled extremes plus 1/64 on either
+        // side, and look at the digits of G over the same sample before committing to it.
+        const uint64_t mn = ~rb.inv_min, mx = rb.max;
+        KeyXform xf = {0, 0, 0, 0, 0};
+        if (mx > mn) {
+          const uint64_t margin = (mx - mn) / 64 + 1;
+          xf.base = mn > margin ? mn - margin : 0;
+          const uint64_t top = mx < UINT64_MAX - margin ? mx + margin : UINT64_MAX;
+          // fewer distinct leading words than n / 4: runs of equal G beyond the repair limit
+          if (top - xf.base < UINT64_MAX && top - xf.base >= n / 4) {
+            xf.span = top - xf.base + 1;
+            xf.s = static_cast<uint32_t>(__builtin_clzll(xf.span));
+            xf.R = static_cast<uint64_t>(((static_cast<unsigned __int128>(1) << 92) - 1) / (xf.span << xf.s));
+            xf.on = 1;
+          }
+        }
+        if (xf.on) {
+          PassList g;  // bits [4,12), [12,20), [20,28) of G
+          g.count = 3;
+          for (int k = 0; k < 3; ++k) {
+            g.shift[k] = 4 + 8 * k;
+            g.from_lo[k] = 0;
+          }
+          float c[3];
+          sample(g, nullptr, xf);
+          DS_LAUNCH_CHECK();
+          DS_CUDA(cudaMemcpyAsync(c, coll, sizeof(c), cudaMemcpyDeviceToHost, s));
+          DS_CUDA(cudaMemsetAsync(ctrl, 0, ctrl_bytes, s));
+          DS_CUDA(cudaStreamSynchronize(s));  // host sync: 12 bytes (sub-range candidates only)
+          // expected pairs of rows with equal G (28 bits): the same head-room as the
+          // prefix_shift >= 32 rule of the plain hybrid plan below
+          const double pairs28 = 0.5 * static_cast<double>(n) * static_cast<double>(n) * c[0] * c[1] * c[2] / 16.0;
+          if (c[1] <= lim && c[2] <= lim && pairs28 <= 0.32 * static_cast<double>(n)) {
+            hybrid = true;
+            t_xf = xf;
+          }
+        }
+      }
     }
     double pairs = 0.5 * static_cast<double>(n) * static_cast<double>(n);
     for (int m = 1; m <= pl.count - 2; ++m) {
@@ -808,28 +938,29 @@ static ds_status sort_indices_impl(int kind, const void* col, uint32_t width, ui
   }
 
   // the hybrid plan needs the prefix plan's guarantee (few ties on the leading 32 bits)
-  hybrid = hybrid && prefix_shift >= 32;
+  hybrid = hybrid && (t_xf.on || prefix_shift >= 32);
   if (hybrid) {  // only the two leading digits run as global passes
     run.count = 2;
     for (int k = 0; k < 2; ++k) {
-      run.shift[k] = pl.shift[pl.count - 2 + k];
+      run.shift[k] = t_xf.on ? 12 + 8 * k : pl.shift[pl.count - 2 + k];  // sub-range keys: digits of G
       run.from_lo[k] = 0;
     }
   }
-  const bool uchk = prefix_shift < 0;  // prefix mode was chosen because the digits spread
+  g_last_plan.store(hybrid ? (t_xf.on ? 3 : 2) : (prefix_shift >= 0 ? 1 : 0), std::memory_order_relaxed);
+  const bool uchk = prefix_shift < 0 && !t_xf.on;  // prefix mode was chosen because the digits spread
   switch (kind) {
-    case KIND_I64: e = launch_encode<KIND_I64>(has_lo, uchk, col, width, n, desc, hi[0], lo[0], run, ghist, s); break;
-    case KIND_U64: e = launch_encode<KIND_U64>(has_lo, uchk, col, width, n, desc, hi[0], lo[0], run, ghist, s); break;
-    case KIND_F64: e = launch_encode<KIND_F64>(has_lo, uchk, col, width, n, desc, hi[0], lo[0], run, ghist, s); break;
-    case KIND_PHILOX: e = launch_encode<KIND_PHILOX>(false, false, nullptr, 8, n, false, hi[0], lo[0], run, ghist, s, seed, subseq); break;
-    default: e = launch_encode<KIND_FSB>(has_lo, uchk, col, width, n, desc, hi[0], lo[0], run, ghist, s); break;
+    case KIND_I64: e = launch_encode<KIND_I64>(has_lo, uchk, col, width, n, desc, hi[0], lo[0], run, ghist, s, 0, 0, too_long); break;
+    case KIND_U64: e = launch_encode<KIND_U64>(has_lo, uchk, col, width, n, desc, hi[0], lo[0], run, ghist, s, 0, 0, too_long); break;
+    case KIND_F64: e = launch_encode<KIND_F64>(has_lo, uchk, col, width, n, desc, hi[0], lo[0], run, ghist, s, 0, 0, too_long); break;
+    case KIND_PHILOX: e = launch_encode<KIND_PHILOX>(false, false, nullptr, 8, n, false, hi[0], lo[0], run, ghist, s, seed, subseq, too_long); break;
+    default: e = launch_encode<KIND_FSB>(has_lo, uchk, col, width, n, desc, hi[0], lo[0], run, ghist, s, 0, 0, too_long); break;
   }
   DS_CUDA(e);
   ds::note_launch(); scan_hist_kernel<<<run.count, RADIX, 0, s>>>(ghist, n, bin_base, skip, coll);
   DS_LAUNCH_CHECK();
 
   uint32_t skip_h[MAX_PASSES] = {0};
-  if (prefix_shift < 0 && !(options & DS_SORT_NO_PASS_SKIP)) {
+  if (prefix_shift < 0 && !t_xf.on && !(options & DS_SORT_NO_PASS_SKIP)) {
     DS_CUDA(cudaMemcpyAsync(skip_h, skip, sizeof(skip_h), cudaMemcpyDeviceToHost, s));
     DS_CUDA(cudaStreamSynchronize(s));  // host sync: 40 bytes (constant digits are skipped)
   }
@@ -856,7 +987,7 @@ static ds_status sort_indices_impl(int kind, const void* col, uint32_t width, ui
   if (hybrid) {
     uint32_t* starts = bucket_starts;
     ds::note_launch();
-    bucket_bounds_kernel<<<(n + 1023) / 1024, 256, 0, s>>>(hi[cur], n, starts);
+    bucket_bounds_kernel<<<(n + 1023) / 1024, 256, 0, s>>>(hi[cur], n, starts, t_xf);
     DS_LAUNCH_CHECK();
     int out_kind = LS_OUT_NONE;  // float64 keys: the caller's gather below produces the column
     if (sorted_out != nullptr) {
@@ -864,13 +995,20 @@ static ds_status sort_indices_impl(int kind, const void* col, uint32_t width, ui
       if (kind == KIND_I64) out_kind = LS_OUT_I64;
       if (kind == KIND_U64) out_kind = LS_OUT_U64;
     }
-    static DoneMask attr_done[4];
-#define DS_BUCKET_LAUNCH(HL, OUT)                                                                      \
+    static DoneMask attr_done[8];
+#define DS_BUCKET_LAUNCH_X(HL, OUT, XF)                                                                \
   do {                                                                                                 \
-    DS_CUDA(set_smem_attr(bucket_local_sort_kernel<HL, OUT>, LS_SMEM_BYTES, &attr_done[OUT]));         \
+    DS_CUDA(set_smem_attr(bucket_local_sort_kernel<HL, OUT, XF>, LS_SMEM_BYTES, &attr_done[OUT + (XF ? 4 : 0)])); \
     ds::note_launch();                                                                                 \
-    bucket_local_sort_kernel<HL, OUT><<<LS_BUCKETS, LS_THREADS, LS_SMEM_BYTES, s>>>(                   \
-        hi[cur], lo[cur], idx_src, starts, desc, static_cast<uint8_t*>(sorted_out), idx_out, too_long); \
+    bucket_local_sort_kernel<HL, OUT, XF><<<LS_BUCKETS, LS_THREADS, LS_SMEM_BYTES, s>>>(               \
+        hi[cur], lo[cur], idx_src, starts, desc, static_cast<uint8_t*>(sorted_out), idx_out, too_long, t_xf); \
+  } while (0)
+#define DS_BUCKET_LAUNCH(HL, OUT)          \
+  do {                                     \
+    if (t_xf.on)                           \
+      DS_BUCKET_LAUNCH_X(HL, OUT, true);   \
+    else                                   \
+      DS_BUCKET_LAUNCH_X(HL, OUT, false);  \
   } while (0)
     switch (out_kind) {
       case LS_OUT_FSB10: DS_BUCKET_LAUNCH(true, LS_OUT_FSB10); break;
@@ -879,6 +1017,7 @@ static ds_status sort_indices_impl(int kind, const void* col, uint32_t width, ui
       default: DS_BUCKET_LAUNCH(false, LS_OUT_NONE); break;
     }
 #undef DS_BUCKET_LAUNCH
+#undef DS_BUCKET_LAUNCH_X
     DS_LAUNCH_CHECK();
     uint32_t flag = 0;
     DS_CUDA(cudaMemcpyAsync(&flag, too_long, sizeof(flag), cudaMemcpyDeviceToHost, s));
@@ -1009,6 +1148,18 @@ int32_t ds_debug_set_hybrid(int32_t mode) {
   if (mode >= 0 && mode <= 2) ds::g_hybrid_mode.store(mode);
   return old;
 }
+
+// The hybrid plan on keys that fill only a sub-range of the key space (KeyXform): 1 (default)
+// on, 0 off.  Returns the previous setting.
+int32_t ds_debug_set_subrange(int32_t enable) {
+  const int old = ds::g_no_subrange.load() ? 0 : 1;
+  ds::g_no_subrange.store(enable == 0);
+  return old;
+}
+
+// Plan the last sort call of this process ended with (after any fall-back): 0 all passes,
+// 1 prefix passes + run repair, 2 hybrid, 3 hybrid on a sub-range of the key space; -1 none yet.
+int32_t ds_debug_last_sort_plan(void) { return ds::g_last_plan.load(); }
 
 int32_t ds_debug_set_radix_config(int32_t cfg) {
   int old = ds::g_cfg.load();

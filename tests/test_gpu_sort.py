@@ -506,6 +506,115 @@ def test_hybrid_bucket_plan_falls_back(ds):
         assert np.array_equal(sa.reshape(n, 10), col[want]), kind
 
 
+def _subrange_fsb(rng, n, lo16, hi16):
+    """10-byte keys whose leading 16 bits lie in [lo16, hi16): one rank's share of a
+    range-partitioned dataset; the other bytes are random."""
+    col = rng.integers(0, 256, (n, 10), dtype=np.uint8)
+    top = rng.integers(lo16, hi16, n)
+    col[:, 0] = top >> 8
+    col[:, 1] = top & 255
+    return col
+
+
+@pytest.mark.parametrize("desc", [False, True])
+@pytest.mark.parametrize("lo16,hi16", [(0x2000, 0x4000), (0xE000, 0x10000), (0, 0x1555), (0x7123, 0x7124), (0x5555, 0xAAAB)])
+def test_hybrid_plan_on_a_subrange_of_the_key_space(ds, desc, lo16, hi16):
+    """keys that fill only part of the key space (any part, not a power of two wide) still take
+    the hybrid plan: the bucket digits come from the keys' position inside the sampled range
+    (KeyXform in radix_sort.cu).  Same order as Arrow and as the all-global plan, with ties on
+    the leading bytes and exact duplicates in the data."""
+    L = ds._lib
+    n = 300_011
+    rng = np.random.default_rng(lo16 + desc)
+    col = _subrange_fsb(rng, n, lo16, hi16)
+    for s in range(300):
+        rows = rng.choice(n, int(rng.integers(2, 10)), replace=False)
+        col[rows, :7] = col[rows[0], :7]
+        col[rows[-1]] = col[rows[0]]
+    want = _arrow_order(col, "fsb", desc)
+    old = L.lib.ds_debug_set_hybrid(2)
+    try:
+        a, sa = _argsort_c(ds, col, "fsb", desc, width=10)
+        plan = L.lib.ds_debug_last_sort_plan()
+        off = L.lib.ds_debug_set_subrange(0)
+        c, sc = _argsort_c(ds, col, "fsb", desc, width=10)
+        plan_off = L.lib.ds_debug_last_sort_plan()
+        L.lib.ds_debug_set_subrange(off)
+    finally:
+        L.lib.ds_debug_set_hybrid(old)
+    b, sb = _argsort_c(ds, col, "fsb", desc, width=10, options=L.DS_SORT_NO_HYBRID)
+    assert plan == 3 and plan_off in (0, 1), (plan, plan_off)
+    assert np.array_equal(a.astype(np.int64), want) and np.array_equal(a, b) and np.array_equal(a, c)
+    assert np.array_equal(sa, sb) and np.array_equal(sa, sc) and np.array_equal(sa.reshape(n, 10), col[want])
+
+
+@pytest.mark.parametrize("desc", [False, True])
+def test_hybrid_plan_on_a_subrange_64bit_keys(ds, desc):
+    """the same for one-word keys: ids clustered in a window, time stamps, negative ranges that
+    cross zero, doubles in a narrow interval."""
+    L = ds._lib
+    n = 250_003
+    rng = np.random.default_rng(77 + desc)
+    cases = {
+        "i64": [rng.integers(10**15, 10**15 + 3 * 10**12, n, dtype=np.int64),
+                rng.integers(-(10**9), 10**9, n, dtype=np.int64)],
+        "u64": [rng.integers(2**63 - 10**13, 2**63 + 10**13, n, dtype=np.uint64)],
+        "f64": [rng.uniform(1.0e6, 1.0e6 + 1.0, n)],   # ~2^33 distinct values in range
+    }
+    old = L.lib.ds_debug_set_hybrid(2)
+    try:
+        for kind, cols in cases.items():
+            for col in cols:
+                for g in range(200):
+                    rows = rng.choice(n, int(rng.integers(2, 9)), replace=False)
+                    col[rows] = col[rows[0]]
+                a, sa = _argsort_c(ds, col, kind, desc)
+                plan = L.lib.ds_debug_last_sort_plan()
+                b, sb = _argsort_c(ds, col, kind, desc, options=L.DS_SORT_NO_HYBRID)
+                assert plan == 3, (kind, plan)
+                assert np.array_equal(a.astype(np.int64), _arrow_order(col, kind, desc)), kind
+                assert np.array_equal(a, b) and np.array_equal(sa, sb), kind
+                assert np.array_equal(sa.view(col.dtype), col[a.astype(np.int64)]), kind
+    finally:
+        L.lib.ds_debug_set_hybrid(old)
+
+
+def test_hybrid_plan_on_a_subrange_falls_back(ds):
+    """keys outside the sampled range (the sample takes every n/2^20-th row), a sub-range filled
+    unevenly, and a range with too few distinct values: the plan is refused up front or the call
+    falls back after the range check; the order is Arrow's either way."""
+    L = ds._lib
+    rng = np.random.default_rng(9)
+    old = L.lib.ds_debug_set_hybrid(2)
+    try:
+        # 1. outliers the sample cannot see (n > 2^21: stride 2, odd rows are never sampled)
+        n = (1 << 21) + 5
+        col = _subrange_fsb(rng, n, 0x4000, 0x6000)
+        col[1, :2] = (0xFF, 0xFF)
+        col[12345, :2] = (0, 0)
+        a, sa = _argsort_c(ds, col, "fsb", False, width=10)
+        assert L.lib.ds_debug_last_sort_plan() != 3
+        want = _arrow_order(col, "fsb", False)
+        assert np.array_equal(a.astype(np.int64), want) and np.array_equal(sa.reshape(n, 10), col[want])
+        # 2. a range filled unevenly (half of the rows in 1/64 of it): refused by the second sample
+        n = 300_000
+        col = _subrange_fsb(rng, n, 0x4000, 0x8000)
+        col[: n // 2, 0] = 0x40
+        col[: n // 2, 1] = rng.integers(0, 256, n // 2)
+        a, sa = _argsort_c(ds, col, "fsb", True, width=10)
+        assert L.lib.ds_debug_last_sort_plan() != 3
+        want = _arrow_order(col, "fsb", True)
+        assert np.array_equal(a.astype(np.int64), want) and np.array_equal(sa.reshape(n, 10), col[want])
+        # 3. 64-bit keys with 1000 distinct values: G collides, refused
+        k = rng.integers(5000, 6000, n, dtype=np.int64)
+        a, sa = _argsort_c(ds, k, "i64", False)
+        assert L.lib.ds_debug_last_sort_plan() != 3
+        assert np.array_equal(a.astype(np.int64), _arrow_order(k, "i64", False))
+        assert np.array_equal(sa.view(np.int64), np.sort(k))
+    finally:
+        L.lib.ds_debug_set_hybrid(old)
+
+
 @pytest.mark.parametrize("width", [1, 8, 10, 90, 100])
 def test_scatter_rows_to_parts_c_abi(ds, width):
     """the fused map-side slicing kernel against numpy (local destinations; over NVLink it is
