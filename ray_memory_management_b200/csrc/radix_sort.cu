@@ -73,6 +73,23 @@ __device__ __forceinline__ uint32_t g28t(uint64_t hix, const KeyXform& x) {
 }
 static thread_local KeyXform t_xf = {0, 0, 0, 0, 0};  // of the sort call running on this thread
 
+// The transform for n keys whose sample spans [mn, mx] (both in the encoded, unsigned order):
+// the range widened by 1/64 on either side.  on == 0 when there is nothing to gain or the range
+// holds fewer than n / 4 distinct leading words (runs of equal G beyond the repair limit).
+static KeyXform make_key_xform(uint64_t mn, uint64_t mx, uint64_t n) {
+  KeyXform xf = {0, 0, 0, 0, 0};
+  if (mx <= mn) return xf;
+  const uint64_t margin = (mx - mn) / 64 + 1;
+  xf.base = mn > margin ? mn - margin : 0;
+  const uint64_t top = mx < UINT64_MAX - margin ? mx + margin : UINT64_MAX;
+  if (top - xf.base == UINT64_MAX || top - xf.base < n / 4) return xf;
+  xf.span = top - xf.base + 1;
+  xf.s = static_cast<uint32_t>(__builtin_clzll(xf.span));
+  xf.R = static_cast<uint64_t>(((static_cast<unsigned __int128>(1) << 92) - 1) / (xf.span << xf.s));
+  xf.on = 1;
+  return xf;
+}
+
 // ---------------------------------------------------------------- encode + hist
 // UNIFORM_CHECK: test every digit for being constant across the warp first (one atomic instead
 // of 32 colliding ones on skewed keys).  Off when the caller already knows the digits spread
@@ -702,6 +719,15 @@ static int cfg_tile(int cfg) {
   }
 }
 
+constexpr uint32_t min_cfg_tile() {
+  uint32_t m = 0xffffffffu;
+#define X(id, v, t, i, m_) m = (t) * (i) < m ? (t) * (i) : m;
+  DS_PASS_CONFIGS(X)
+#undef X
+  return m;
+}
+constexpr uint32_t MIN_CFG_TILE = min_cfg_tile();
+
 static cudaError_t launch_pass(int cfg, bool has_lo, bool digit_lo, bool gen_idx,
                                const uint64_t* hi_in, const uint16_t* lo_in, const uint32_t* idx_in,
                                uint64_t* hi_out, uint16_t* lo_out, uint32_t* idx_out, uint32_t n,
@@ -805,7 +831,9 @@ static ds_status sort_indices_impl(int kind, const void* col, uint32_t width, ui
   }
   uint32_t* idx_alt = w.take<uint32_t>(n);
   uint32_t* ctrl = w.take<uint32_t>(MAX_PASSES * RADIX * 2 + 4 * MAX_PASSES);
-  uint32_t* lookback = w.take<uint32_t>(static_cast<size_t>(tiles) * RADIX);
+  // sized for the smallest tile of any pass configuration: the size query and the run may see
+  // different ds_debug_set_radix_config settings
+  uint32_t* lookback = w.take<uint32_t>(static_cast<size_t>((n + MIN_CFG_TILE - 1) / MIN_CFG_TILE) * RADIX);
   uint32_t* bucket_starts = w.take<uint32_t>(LS_BUCKETS + 1);  // hybrid plan only (257 KB)
   ds_status st;
   if (ws_resolve(w, ws, ws_bytes, fn, &st)) return st;
@@ -883,20 +911,7 @@ static ds_status sort_indices_impl(int kind, const void* col, uint32_t width, ui
         // The leading bytes do not spread: the keys may still fill a SUB-RANGE of the key space
         // evenly (see KeyXform).  Take the range from the sampled extremes plus 1/64 on either
         // side, and look at the digits of G over the same sample before committing to it.
-        const uint64_t mn = ~rb.inv_min, mx = rb.max;
-        KeyXform xf = {0, 0, 0, 0, 0};
-        if (mx > mn) {
-          const uint64_t margin = (mx - mn) / 64 + 1;
-          xf.base = mn > margin ? mn - margin : 0;
-          const uint64_t top = mx < UINT64_MAX - margin ? mx + margin : UINT64_MAX;
-          // fewer distinct leading words than n / 4: runs of equal G beyond the repair limit
-          if (top - xf.base < UINT64_MAX && top - xf.base >= n / 4) {
-            xf.span = top - xf.base + 1;
-            xf.s = static_cast<uint32_t>(__builtin_clzll(xf.span));
-            xf.R = static_cast<uint64_t>(((static_cast<unsigned __int128>(1) << 92) - 1) / (xf.span << xf.s));
-            xf.on = 1;
-          }
-        }
+        const KeyXform xf = make_key_xform(~rb.inv_min, rb.max, n);
         if (xf.on) {
           PassList g;  // bits [4,12), [12,20), [20,28) of G
           g.count = 3;
@@ -1160,6 +1175,19 @@ int32_t ds_debug_set_subrange(int32_t enable) {
 // Plan the last sort call of this process ended with (after any fall-back): 0 all passes,
 // 1 prefix passes + run repair, 2 hybrid, 3 hybrid on a sub-range of the key space; -1 none yet.
 int32_t ds_debug_last_sort_plan(void) { return ds::g_last_plan.load(); }
+
+// Host arithmetic of the sub-range transform, for tests without a GPU: out = {base, span, R, s};
+// returns 1 when the transform would be used for n keys whose sample spans [min, max].
+int32_t ds_debug_key_xform(uint64_t min, uint64_t max, uint64_t n, uint64_t* out) {
+  const ds::KeyXform xf = ds::make_key_xform(min, max, n);
+  if (out != nullptr) {
+    out[0] = xf.base;
+    out[1] = xf.span;
+    out[2] = xf.R;
+    out[3] = xf.s;
+  }
+  return static_cast<int32_t>(xf.on);
+}
 
 int32_t ds_debug_set_radix_config(int32_t cfg) {
   int old = ds::g_cfg.load();

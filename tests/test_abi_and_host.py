@@ -45,6 +45,53 @@ def test_workspace_size_queries_need_no_gpu():
     assert _lib.lib.ds_sort_indices_i64(None, 1 << 30, 0, None, None, 0, None, ctypes.byref(need), None) == _lib.DS_ERR_TOO_LARGE
 
 
+def test_subrange_key_transform_arithmetic():
+    """host arithmetic of the hybrid sort plan on a sub-range of the key space (KeyXform in
+    csrc/radix_sort.cu): for any sampled [min, max] the 28-bit G = (hi' * R) >> 64 of
+    hi' = (hi - base) << s is monotone in hi, stays below 2^28, reaches the top of that range,
+    and (hi' >> s) + base gives the key back.  Checked with Python integers."""
+    import random
+
+    from ray_memory_management_b200 import _lib
+
+    f = _lib.lib.ds_debug_key_xform
+    f.argtypes = [ctypes.c_uint64, ctypes.c_uint64, ctypes.c_uint64, ctypes.POINTER(ctypes.c_uint64)]
+    f.restype = ctypes.c_int32
+    out = (ctypes.c_uint64 * 4)()
+    M = (1 << 64) - 1
+    rnd = random.Random(5)
+    used = 0
+    for _ in range(3000):
+        bits = rnd.choice([1, 9, 17, 33, 47, 62, 63, 64])
+        mn = rnd.getrandbits(64)
+        mx = min(M, mn + rnd.getrandbits(bits))
+        n = rnd.choice([1, 1000, 100_000_000])
+        on = f(mn, mx, n, out)
+        base, span, R, s = (int(v) for v in out)
+        if not on:
+            # nothing sampled apart, the range is the whole key space, or too few distinct values
+            margin = (mx - mn) // 64 + 1
+            lo = mn - margin if mn > margin else 0
+            hi = mx + margin if mx < M - margin else M
+            assert mx <= mn or hi - lo == M or hi - lo < n // 4
+            continue
+        used += 1
+        assert base <= mn and mx <= base + span - 1 <= M
+        assert (span << s) >> 63 == 1 and (span << s) <= M   # hi' fills 64 bits, no overflow
+        prev = -1
+        for d0 in sorted([0, span - 1, mn - base, mx - base] + [rnd.randrange(span) for _ in range(16)]):
+            hp = d0 << s
+            g = (hp * R) >> 64
+            assert prev <= g < (1 << 28)
+            prev = g
+            assert (hp >> s) + base == base + d0
+        if span >= 1 << 30:
+            assert prev >= (1 << 28) - 2                       # the top of the range maps to the last bucket
+    assert used > 1000
+    assert f(5, 5, 10, out) == 0 and f(0, M, 10, out) == 0
+    assert f(5000, 6000, 300_000, out) == 0                    # 1000 values for 300 k rows
+
+
 def test_nearest_rank_matches_oracle_and_golden(golden):
     from oracle import datasets_oracle as O
     from ray_memory_management_b200 import sort
