@@ -161,6 +161,12 @@ __global__ void __launch_bounds__(LS_THREADS, 4)
   // ---- order the runs of rows that share a bin by (key, position on entry): the thread that
   // holds a run's first row sorts it by insertion.  (Letting every member count its rank and
   // move after a barrier was measured slower: 1.41 against 1.20 ms.)
+  // There is no barrier between finding the heads and sorting: a thread may read a neighbouring
+  // run's ex_hi words (head test, scan for the run's end) while that run's owner moves them.
+  // What it compares is G only, which is equal for all members of a run by definition, an
+  // insertion sort only permutes words inside its run, and aligned 64-bit shared-memory stores
+  // do not tear -- so every value it can see gives the same answer.  Runs never overlap and only
+  // the owner writes.  (A racecheck tool reports these reads; they are intended.)
   {
     uint32_t heads = 0;
 #pragma unroll

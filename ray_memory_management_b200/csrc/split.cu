@@ -65,6 +65,86 @@ __device__ __forceinline__ uint64_t load_key_prefix(const void* col, uint32_t wi
   return static_cast<uint64_t>(v) << 32;
 }
 
+// One full tile of 10-byte keys by one warp; see the call site.  The key of row j of a lane sits at
+// byte 10 j of the lane's 80 bytes: at a word boundary for even j, two bytes into a word for odd j.
+template <int NG>  // groups of four destinations that can occur: nb + 1 <= 4 * NG
+__device__ __forceinline__ void split_plan_tile_fsb10(const void* __restrict__ col, const uint8_t* __restrict__ valid,
+                                                      uint32_t t, const uint64_t* s_bh, const uint32_t* s_bl,
+                                                      uint32_t nb, bool desc, uint8_t* __restrict__ dest_out,
+                                                      uint32_t* __restrict__ tile_counts, uint32_t ntiles,
+                                                      uint32_t lane) {
+  constexpr int ROWS = SP_TILE0 / 32;  // 8
+  static_assert(ROWS == 8, "a lane's rows are 80 bytes and its destinations one 8-byte word");
+  const size_t row0 = static_cast<size_t>(t) * SP_TILE0 + lane * ROWS;
+  const uint4* q = reinterpret_cast<const uint4*>(static_cast<const uint8_t*>(col) + row0 * 10);
+  uint32_t w[20];
+#pragma unroll
+  for (int k = 0; k < 5; ++k) {
+    const uint4 v = __ldg(q + k);
+    w[4 * k] = v.x;
+    w[4 * k + 1] = v.y;
+    w[4 * k + 2] = v.z;
+    w[4 * k + 3] = v.w;
+  }
+  unsigned long long vmask = ~0ull;  // byte j != 0: row j is not null
+  if (valid != nullptr) vmask = *reinterpret_cast<const unsigned long long*>(valid + row0);
+  const uint32_t nparts = nb + 1;
+  unsigned long long dest8 = 0;
+  unsigned long long acc[NG];  // per-lane counts, four 16-bit fields per word
+#pragma unroll
+  for (int g = 0; g < NG; ++g) acc[g] = 0;
+#pragma unroll
+  for (int j = 0; j < ROWS; ++j) {
+    const int k = (10 * j) / 4;
+    uint32_t h1, h0, l;
+    if (j % 2 == 0) {
+      h1 = __byte_perm(w[k], 0, 0x0123);
+      h0 = __byte_perm(w[k + 1], 0, 0x0123);
+      l = __byte_perm(w[k + 2], 0, 0x4401);
+    } else {
+      h1 = __byte_perm(w[k], w[k + 1], 0x2345);
+      h0 = __byte_perm(w[k + 1], w[k + 2], 0x2345);
+      l = __byte_perm(w[k + 2], 0, 0x4423);
+    }
+    uint64_t kh = (static_cast<uint64_t>(h1) << 32) | h0;
+    uint32_t kl = l;
+    if (desc) {  // the encoding of load_key<KIND_FSB>
+      kh = ~kh;
+      kl = ~kl & 0xFFFFu;
+    }
+    // asc: number of splitters <= key; desc: number of splitters strictly before the key (in
+    // the encoded order) -- the rule of the general path below
+    uint32_t a = 0, b = nb;
+    while (a < b) {
+      const uint32_t mid = (a + b) >> 1;
+      const uint64_t sh = s_bh[mid];
+      bool before = sh < kh;
+      if (sh == kh) before = desc ? s_bl[mid] < kl : s_bl[mid] <= kl;
+      if (before) a = mid + 1;
+      else b = mid;
+    }
+    const uint32_t d = ((vmask >> (8 * j)) & 0xFFu) ? a : nb;  // null keys travel to the last partition
+    dest8 |= static_cast<unsigned long long>(d) << (8 * j);
+    const uint32_t grp = d >> 2, sh = 16 * (d & 3);
+#pragma unroll
+    for (int g = 0; g < NG; ++g)  // arithmetic, not `if`: keeps acc[] in registers
+      acc[g] += static_cast<unsigned long long>(grp == (uint32_t)g) << sh;
+  }
+  *reinterpret_cast<unsigned long long*>(dest_out + row0) = dest8;
+  uint32_t mine = 0;
+#pragma unroll
+  for (int g = 0; g < NG; ++g) {
+    // a field holds at most 256 after the reduction: 16 bits are enough
+    const uint32_t lo = __reduce_add_sync(0xffffffffu, static_cast<uint32_t>(acc[g]));
+    const uint32_t hi = __reduce_add_sync(0xffffffffu, static_cast<uint32_t>(acc[g] >> 32));
+    if ((lane >> 2) == (uint32_t)g) {
+      const uint32_t pair = (lane & 2) ? hi : lo;
+      mine = (pair >> (16 * (lane & 1))) & 0xFFFFu;
+    }
+  }
+  if (lane < nparts) tile_counts[static_cast<size_t>(lane) * (ntiles + 1) + t] = mine;
+}
+
 template <int KIND>
 __global__ void __launch_bounds__(SP_THREADS)
     split_plan_kernel(const void* __restrict__ col, uint32_t width, const uint8_t* __restrict__ valid,
@@ -87,7 +167,19 @@ __global__ void __launch_bounds__(SP_THREADS)
   __syncthreads();
   constexpr int PER = SP_TILE0 / 32;
   const uint32_t warps = gridDim.x * (SP_THREADS / 32);
+  // 10-byte keys (the GraySort key), full tiles, 16-byte aligned column: a lane takes 8
+  // CONSECUTIVE rows -- 80 bytes, five 16-byte loads, the whole key in registers -- and writes
+  // their 8 destination bytes with one store (split_plan_tile_fsb10 below).
+  const bool fast10 = KIND == KIND_FSB && width == 10 && (reinterpret_cast<uintptr_t>(col) & 15) == 0 &&
+                      (reinterpret_cast<uintptr_t>(dest_out) & 7) == 0 &&
+                      (valid == nullptr || (reinterpret_cast<uintptr_t>(valid) & 7) == 0);
   for (uint32_t t = blockIdx.x * (SP_THREADS / 32) + warp; t < ntiles; t += warps) {
+    if (fast10 && static_cast<uint64_t>(t + 1) * SP_TILE0 <= n) {
+      if (nb < 8) split_plan_tile_fsb10<2>(col, valid, t, s_bh, s_bl, nb, desc, dest_out, tile_counts, ntiles, lane);
+      else if (nb < 16) split_plan_tile_fsb10<4>(col, valid, t, s_bh, s_bl, nb, desc, dest_out, tile_counts, ntiles, lane);
+      else split_plan_tile_fsb10<8>(col, valid, t, s_bh, s_bl, nb, desc, dest_out, tile_counts, ntiles, lane);
+      continue;
+    }
     const uint32_t base = t * SP_TILE0 + lane;
     uint64_t kp[PER];
     uint32_t d[PER];

@@ -141,6 +141,48 @@ def test_split_rows_unaligned_source_and_fsb_keys(lib):
             assert np.array_equal(outs[d].cpu().numpy().reshape(-1, width), rows[want_dest == d])
 
 
+@pytest.mark.parametrize("desc", [False, True])
+@pytest.mark.parametrize("nb", [1, 7, 8, 15, 31])
+def test_split_plan_fsb10_full_tiles(lib, desc, nb):
+    """10-byte keys on the register path of the plan kernel (full tiles of an aligned column, 8
+    consecutive rows per lane) and on the general path (the ragged last tile, an unaligned
+    column): keys equal to splitters, ties on the leading 8 bytes decided by the last two,
+    nulls, every number of destinations' groups of four."""
+    import bisect
+
+    rng = np.random.default_rng(nb * 2 + desc)
+    n = 256 * 37 + 101
+    keys = rng.integers(0, 256, (n, 10), dtype=np.uint8)
+    keys[rng.choice(n, n // 3, replace=False), :8] = 7       # ties on the leading 8 bytes
+    keys[rng.choice(n, n // 5, replace=False), :9] = 7       # ... and on 9
+    spl = keys[rng.choice(n, nb, replace=False)].copy()      # splitters are keys of the column
+    if nb >= 7:
+        spl[3] = spl[2]                                      # an empty destination
+    order = sorted(range(nb), key=lambda i: bytes(spl[i]), reverse=desc)
+    spl = spl[order]
+    valid = (rng.random(n) > 0.05).astype(np.uint8)
+    sb = [bytes(r) for r in spl]
+    if desc:   # ArrowBlockAccessor.sort_and_partition on a descending sort: boundaries strictly greater
+        asc = sb[::-1]
+        want = np.array([nb - bisect.bisect_right(asc, bytes(k)) for k in keys], dtype=np.int64)
+    else:
+        want = np.array([bisect.bisect_right(sb, bytes(k)) for k in keys], dtype=np.int64)
+    want = np.where(valid != 0, want, nb)
+    dbnd = torch.from_numpy(spl.reshape(-1).copy()).cuda()
+    dval = torch.from_numpy(valid).cuda()
+    whole = torch.from_numpy(np.concatenate([np.zeros(16, np.uint8), keys.reshape(-1)])).cuda()
+    for shift in (16, 14):                                   # aligned -> register path; 14 -> general path
+        col = whole[shift:] if shift == 16 else torch.cat([whole[:14], whole[16:]])[14:]
+        assert (col.data_ptr() % 16 == 0) == (shift == 16)
+        dest, table, counts, _, _ = _plan(lib, lib.DS_KEY_FSB, col, 10, dval, n, dbnd, nb, desc)
+        assert np.array_equal(dest.astype(np.int64), want), shift
+        assert np.array_equal(counts, np.bincount(want, minlength=nb + 1))
+        T = lib.DS_SPLIT_TILE_ROWS
+        for d in range(nb + 1):
+            per_tile = np.add.reduceat((want == d).astype(np.int64), np.arange(0, n, T))
+            assert np.array_equal(table[d], np.concatenate([[0], np.cumsum(per_tile)])), (shift, d)
+
+
 def test_split_rejects_bad_arguments(lib):
     z = torch.zeros(16, dtype=torch.uint8, device="cuda")
     arr = (ctypes.c_void_p * 1)(z.data_ptr())
