@@ -426,12 +426,23 @@ def run_ours(args):
     launches0 = lib.ds_debug_launch_count()
     lib.ds_debug_pass_timing(1)
     step_ev = [torch.cuda.Event(enable_timing=True) for _ in range(args.steps + 1)]
+    # Objects that exist now (modules, the input, cached buffers) leave the collector's sight: a
+    # full collection over them pauses one rank's host thread for tens of ms, and with a host
+    # read-back inside the multi-GPU step every rank waits for it.  The collector stays on.
+    import gc
+
+    gc.collect()
+    gc.freeze()
+    host_t = [time.perf_counter()]
     step_ev[0].record()
     for k in range(args.steps):
         out = one_step()
         del out
         step_ev[k + 1].record()
+        host_t.append(time.perf_counter())
     barrier()
+    gc.unfreeze()
+    host_ms = sorted((b - a) * 1e3 for a, b in zip(host_t, host_t[1:]))
     lib.ds_debug_pass_timing(0)
     launches = int(lib.ds_debug_launch_count() - launches0)
     ms = step_ev[0].elapsed_time(step_ev[-1])
@@ -449,7 +460,8 @@ def run_ours(args):
     ms_per_step = ms / args.steps
     value = world * n * ROW_BYTES / (ms_per_step * 1e-3) / 1e9
     ss = sorted(step_ms)
-    step_stats = {"min": ss[0], "median": ss[len(ss) // 2], "max": ss[-1]}
+    step_stats = {"min": ss[0], "median": ss[len(ss) // 2], "max": ss[-1],
+                  "host_issue_ms_rank0": {"median": host_ms[len(host_ms) // 2], "max": host_ms[-1]}}
 
     peak, peak_src = measured_peak()
     try:
@@ -588,6 +600,7 @@ def run_ours(args):
             "plan": (plan + (f" x{rounds}" if rounds and plan == "push" else "")) if world > 1 else None,
             "l2": f"inputs ({n * ROW_BYTES / 1e9:.1f} GB/GPU) far exceed the 126 MB L2; no flush needed",
             "parallelism": f"range-partitioned x{world}" if world > 1 else "single GPU",
+            "host": "gc.freeze() before the timed steps (collector left on)",
         },
         "clocks": clocks,
         "gpu_launches": launches,
