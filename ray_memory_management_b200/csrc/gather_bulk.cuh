@@ -81,8 +81,9 @@ struct GatherSources {
 };
 constexpr uint64_t GB_GUARDED = 1ull << 63;  // flag in a resolved address: fetch this row byte by byte
 
-// One thread per row of a tile: blockDim.x == R.
-template <int FETCH>
+// One thread per row of a tile: blockDim.x == R.  MULTI = false: one source (srcs.base[0], rows
+// [0, srcs.start[1])) -- its address and bounds stay in registers, no source table in shared memory.
+template <int FETCH, bool MULTI>
 __global__ void __launch_bounds__(GB_THREADS)
     gather_bulk_kernel(const GatherSources srcs, uint32_t W, const uint32_t* __restrict__ idx, uint32_t n,
                        uint8_t* __restrict__ dst, uint32_t R, uint32_t stages, uint32_t slot, uint32_t chunks,
@@ -101,15 +102,25 @@ __global__ void __launch_bounds__(GB_THREADS)
   const uint32_t tid = threadIdx.x;
   const uint32_t lane = tid & 31;
   const uint32_t nsrc = srcs.nsrc;
-  for (uint32_t b = tid; b < nsrc; b += blockDim.x) {
-    s_base[b] = reinterpret_cast<uint64_t>(srcs.base[b]);
-    s_start[b] = srcs.start[b];
+  if (MULTI) {
+    for (uint32_t b = tid; b < nsrc; b += blockDim.x) {
+      s_base[b] = reinterpret_cast<uint64_t>(srcs.base[b]);
+      s_start[b] = srcs.start[b];
+    }
+    if (tid == 0) s_start[nsrc] = srcs.start[nsrc];
+    __syncthreads();
   }
-  if (tid == 0) s_start[nsrc] = srcs.start[nsrc];
-  __syncthreads();
+  const uint64_t base0 = reinterpret_cast<uint64_t>(srcs.base[0]);
+  const uint64_t safe_lo0 = (base0 + 15) & ~uint64_t(15);
+  const uint64_t safe_hi0 = (base0 + static_cast<uint64_t>(srcs.start[1]) * W) & ~uint64_t(15);
   // row number over the concatenated sources -> address of the row; GB_GUARDED is set when the
   // 16-byte-aligned span around the row would leave its source buffer
   auto resolve = [&](uint32_t row) -> uint64_t {
+    if (!MULTI) {
+      const uint64_t a = base0 + static_cast<uint64_t>(row) * W;
+      const bool safe = (a & ~uint64_t(15)) >= safe_lo0 && ((a + W + 15) & ~uint64_t(15)) <= safe_hi0;
+      return safe ? a : (a | GB_GUARDED);
+    }
     uint32_t b = 0;
     if (nsrc > 1) {
       uint32_t lo = 0, hi = nsrc;  // last b with start[b] <= row
@@ -287,14 +298,15 @@ static bool gather_bulk_eligible(const void* src, uint32_t W, uint64_t src_rows,
 }
 
 static cudaError_t launch_gather_bulk(int fetch, const GatherSources& srcs, uint32_t W, const uint32_t* idx,
-                                      uint32_t n, void* dst, cudaStream_t s) {
+                                      uint32_t n, void* dst, cudaStream_t s, bool multi = true) {
   GatherBulkPlan p;
   if (!gather_bulk_plan(W, &p)) return cudaErrorInvalidConfiguration;
   const uint32_t tiles = (n + p.rows - 1) / p.rows;
   uint32_t blocks = static_cast<uint32_t>(sm_count()) * p.ctas_per_sm;
   if (blocks > tiles) blocks = tiles;
   const uint32_t magic_c = static_cast<uint32_t>((0x100000000ull + p.chunks - 1) / p.chunks);
-  auto k = fetch == FETCH_BULK ? gather_bulk_kernel<FETCH_BULK> : gather_bulk_kernel<FETCH_LDGSTS>;
+  auto k = fetch == FETCH_BULK ? (multi ? gather_bulk_kernel<FETCH_BULK, true> : gather_bulk_kernel<FETCH_BULK, false>)
+                               : (multi ? gather_bulk_kernel<FETCH_LDGSTS, true> : gather_bulk_kernel<FETCH_LDGSTS, false>);
   cudaError_t e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(p.smem));
   if (e != cudaSuccess) return e;
   ds::note_launch();
@@ -310,7 +322,7 @@ static cudaError_t launch_gather_bulk(int fetch, const void* src, uint32_t W, ui
   srcs.start[0] = 0;
   srcs.start[1] = static_cast<uint32_t>(src_rows);
   srcs.base[0] = static_cast<const uint8_t*>(src);
-  return launch_gather_bulk(fetch, srcs, W, idx, n, dst, s);
+  return launch_gather_bulk(fetch, srcs, W, idx, n, dst, s, false);
 }
 
 }  // namespace ds
