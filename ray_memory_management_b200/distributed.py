@@ -861,6 +861,17 @@ PUSH_ROUNDS = int(_os.environ.get("DS_PUSH_ROUNDS", "2"))  # rounds of the push-
 PUSH_STAGED = int(_os.environ.get("DS_PUSH_STAGED", "-1"))  # staged rounds (-1: all but the first)
 
 
+def _require_columns(block, fn: str) -> None:
+    """The ranks do not exchange schemas: a block without columns (DeviceArrowBlock.empty()) would
+    send this rank into different collectives than the others and hang the job.  Fail here, on the
+    rank that holds it, with the way out."""
+    if block.num_columns == 0:
+        raise ValueError(
+            f"{fn}: this rank's block has no columns.  Every rank must pass a block with the dataset's "
+            "columns; a rank without rows passes zero-row columns, e.g. "
+            "DeviceArrowBlock.from_arrow(schema.empty_table()).")
+
+
 def sort_block_push(block, key: str, descending: bool = False, group=None, consume: bool = False,
                     rounds: Optional[int] = None, staged: Optional[int] = None):
     """Dataset.sort across the ranks of ``group`` with the push-based plan
@@ -871,6 +882,8 @@ def sort_block_push(block, key: str, descending: bool = False, group=None, consu
     from .block import BlockExecStats, BlockMetadata, DeviceArrowBlock
 
     world = dist.get_world_size(group)
+    if world > 1:
+        _require_columns(block, "sort_block_push")
     var_names = _fixed_width_only(block, "sort_block_push", key, payload_ok=True)
     ph = _Phases()
     ph.mark("start")
@@ -915,9 +928,11 @@ def sort_block(block, key: str, descending: bool = False, group=None, consume: b
     from .block import (DeviceArrowBlock, DeviceArrowBlockAccessor, DeviceColumn,
                         _argsort_nulls_last, _gather)
 
+    world = dist.get_world_size(group)
+    if world > 1:
+        _require_columns(block, "sort_block")
     var_names = _fixed_width_only(block, "sort_block", key, payload_ok=True, key_ok=True)
     key_is_var = key in var_names
-    world = dist.get_world_size(group)
     rank = dist.get_rank(group)
     dev = _dev()
     ph = _Phases()
@@ -1115,8 +1130,10 @@ def random_shuffle_block(block, seed: Optional[int], group=None):
 
     from .block import DeviceArrowBlock, DeviceArrowBlockAccessor, DeviceColumn
 
-    var_names = _fixed_width_only(block, "random_shuffle_block", None, payload_ok=True)
     world = dist.get_world_size(group)
+    if world > 1:
+        _require_columns(block, "random_shuffle_block")
+    var_names = _fixed_width_only(block, "random_shuffle_block", None, payload_ok=True)
     rank = dist.get_rank(group)
     dev = _dev()
     seed_i = seed + rank if seed is not None else None
@@ -1170,8 +1187,10 @@ def groupby_block(block, key: str, aggs, group=None):
     local sort + combine, range-partition the partial rows, exchange, merge + finalize."""
     from .block import DeviceArrowBlock, DeviceArrowBlockAccessor, DeviceColumn, PartialAggBlock, _searchsorted
 
-    _fixed_width_only(block, "groupby_block", key)
     world = dist.get_world_size(group)
+    if world > 1:
+        _require_columns(block, "groupby_block")
+    _fixed_width_only(block, "groupby_block", key)
     rank = dist.get_rank(group)
     dev = _dev()
     width, ktype = _key_width(block, key, group)

@@ -138,3 +138,14 @@ def test_two_rank_variable_length_wire():
             start = sum(counts[:dst])
             want += rows[start:start + counts[dst]]
         assert res[dst][3] == want
+
+
+def test_block_without_columns_is_refused_with_the_way_out():
+    """the ranks do not exchange schemas (distributed.sort_block docstring): a block without
+    columns would desynchronise the collectives, so every multi-rank entry point refuses it on
+    the rank that holds it."""
+    from ray_memory_management_b200 import distributed as D
+    from ray_memory_management_b200.block import DeviceArrowBlock
+
+    with pytest.raises(ValueError, match="no columns.*empty_table"):
+        D._require_columns(DeviceArrowBlock.empty(), "sort_block")
