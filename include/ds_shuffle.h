@@ -86,8 +86,12 @@ const char* ds_last_error(void);
  *                  is long).  Unless DS_SORT_NO_HYBRID is set, keys whose two leading bytes
  *                  spread evenly (and 26 M <= n <= 108 M) run only those two digits as global
  *                  passes and finish with one thread block per 16-bit bucket in shared
- *                  memory (same verification, same fallback).  The result is identical in
- *                  every mode.
+ *                  memory (same verification, same fallback).  Keys that fill only a
+ *                  sub-range of the key space evenly (one rank's share of a range partition,
+ *                  clustered ids) take the same plan with the bucket digits computed from the
+ *                  key's position between the sampled minimum and maximum; every key is
+ *                  checked against that range on the device and an outlier falls back.  The
+ *                  result is identical in every mode.
  * float64 order: -inf < ... < -0.0 == 0.0 ... < +inf < NaN (NaNs last in ascending
  * and in descending order, like Arrow); -0.0 and 0.0 compare equal (stable). */
 ds_status ds_sort_indices_i64(const int64_t* col, uint64_t n, int32_t descending,
