@@ -11,7 +11,6 @@ import collections
 import os
 from typing import Dict
 
-import numpy as np
 import pyarrow as pa
 import torch
 

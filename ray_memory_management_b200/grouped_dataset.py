@@ -9,7 +9,7 @@ from typing import List, Optional, Tuple, Union
 import pyarrow as pa
 
 from . import sort
-from .aggregate import AbsMax, AggregateFn, Count, Max, Mean, Min, Std, Sum
+from .aggregate import AggregateFn, Count, Max, Mean, Min, Std, Sum
 from .block import Block, BlockAccessor, BlockExecStats, BlockList, BlockMetadata
 from .context import DatasetContext
 from .shuffle import DeviceShufflePlan, ShuffleOp

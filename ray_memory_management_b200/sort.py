@@ -19,7 +19,6 @@ from .block import (
     BlockList,
     BlockMetadata,
     DeviceArrowBlock,
-    _key_kind,
 )
 from .context import DatasetContext
 from .shuffle import DeviceShufflePlan, ShuffleOp

@@ -7,7 +7,6 @@ import ctypes
 import numpy as np
 import pandas as pd
 import pyarrow as pa
-import pyarrow.compute as pc
 import pytest
 
 pytestmark = pytest.mark.gpu

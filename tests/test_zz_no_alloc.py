@@ -12,8 +12,6 @@ that anything the first call left in the shared array would show up.
 Kept in a file that pytest collects last: if it fails under ``-x`` every other test has
 already run.
 """
-import ctypes
-
 import numpy as np
 import pytest
 
